@@ -1,0 +1,259 @@
+// isect_tiles (tile-bbox count, key emit, sort) and isect_offset_encode.
+//
+// Replaces (behaviour, not code): gsplat/triton_impl/isect_tiles.py:14-282, isect_offset.py:9-63,
+// gsplat/triton_impl/radix_sort/radix_sort.cu, gsplat/cuda/csrc/IntersectTile.cu:24-344.
+// Integer outputs are bit-exact against oracle/gs_oracle.py::isect_tiles / isect_offset_encode.
+//
+// Key layout (int64): camera << (32 + tile_bits) | tile << 32 | bitcast<int32>(depth).
+#include "common.cuh"
+#include "gsplat_b200.h"
+
+#include <cub/device/device_radix_sort.cuh>
+
+namespace {
+
+constexpr int kThreads = 256;
+
+struct TileBox {
+    int x0, x1, y0, y1;
+};
+
+// floor((p - r)/ts) .. ceil((p + r)/ts), clamped to the tile grid; max is exclusive.
+// Written as p/ts -/+ r/ts like _torch_impl._isect_tiles:351-358 (identical to the Triton form for
+// power-of-two tile sizes, where the division is exact).
+__device__ __forceinline__ TileBox tile_box(float mx, float my, int radius, int tile_size, int tw, int th) {
+    float ts = (float)tile_size;
+    float tr = __fdiv_rn((float)radius, ts);
+    float tx = __fdiv_rn(mx, ts), ty = __fdiv_rn(my, ts);
+    TileBox b;
+    b.x0 = min(max((int)floorf(tx - tr), 0), tw);
+    b.x1 = min(max((int)ceilf(tx + tr), 0), tw);
+    b.y0 = min(max((int)floorf(ty - tr), 0), th);
+    b.y1 = min(max((int)ceilf(ty + tr), 0), th);
+    return b;
+}
+
+__device__ __forceinline__ int block_exclusive_scan(int v, int *s_warp, int &block_total) {
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    int base = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) {
+        int s = s_warp[w];
+        base += (w < warp) ? s : 0;
+        total += s;
+    }
+    block_total = total;
+    return base + inc - v;
+}
+
+__global__ void __launch_bounds__(kThreads)
+isect_count_kernel(int64_t P, const float *__restrict__ means2d, const int32_t *__restrict__ radii, int tile_size,
+                   int tw, int th, int32_t *__restrict__ tiles_per_gauss, int32_t *__restrict__ block_sums) {
+    __shared__ int s_warp[kThreads / 32];
+    int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    int cnt = 0;
+    if (i < P) {
+        int r = radii[i];
+        if (r > 0) {
+            float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * i);
+            TileBox b = tile_box(m.x, m.y, r, tile_size, tw, th);
+            cnt = (b.x1 - b.x0) * (b.y1 - b.y0);
+        }
+        tiles_per_gauss[i] = cnt;
+    }
+    int s = cnt;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; ++w) t += s_warp[w];
+        block_sums[blockIdx.x] = t;
+    }
+}
+
+// single-block exclusive scan int32 -> int64 (n is the number of 256-row blocks: at most a few 100k)
+__global__ void __launch_bounds__(1024)
+scan_block_sums_kernel(int64_t n, const int32_t *__restrict__ in, int64_t *__restrict__ out,
+                       int64_t *__restrict__ total_out) {
+    __shared__ long long s_warp[32];
+    __shared__ long long s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t base = 0; base < n; base += 1024) {
+        int64_t i = base + threadIdx.x;
+        long long v = i < n ? (long long)in[i] : 0;
+        long long inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            long long t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        long long wbase = 0, total = 0;
+        for (int w = 0; w < 32; ++w) {
+            long long s = s_warp[w];
+            wbase += (w < warp) ? s : 0;
+            total += s;
+        }
+        long long carry = s_carry;
+        if (i < n) out[i] = carry + wbase + inc - v;
+        __syncthreads();
+        if (threadIdx.x == 0) s_carry = carry + total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total_out = s_carry;
+}
+
+template <bool PACKED>
+__global__ void __launch_bounds__(kThreads)
+isect_emit_kernel(int64_t P, int N, const float *__restrict__ means2d, const int32_t *__restrict__ radii,
+                  const float *__restrict__ depths, const int64_t *__restrict__ camera_ids, int tile_size, int tw,
+                  int th, int tile_n_bits, const int32_t *__restrict__ tiles_per_gauss,
+                  const int64_t *__restrict__ block_offsets, int64_t *__restrict__ isect_ids,
+                  int32_t *__restrict__ flatten_ids) {
+    __shared__ int s_warp[kThreads / 32];
+    int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    int cnt = i < P ? tiles_per_gauss[i] : 0;
+    int block_total;
+    int local = block_exclusive_scan(cnt, s_warp, block_total);
+    if (cnt == 0) return;
+    int64_t out = block_offsets[blockIdx.x] + local;
+    float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * i);
+    TileBox b = tile_box(m.x, m.y, radii[i], tile_size, tw, th);
+    int64_t cam = PACKED ? camera_ids[i] : (i / N);
+    int64_t hi = cam << (32 + tile_n_bits);
+    int64_t depth_bits = (int64_t)__float_as_int(depths[i]);  // sign-extending like the reference casts
+    for (int y = b.y0; y < b.y1; ++y) {
+        for (int x = b.x0; x < b.x1; ++x) {
+            int64_t tile = (int64_t)(y * tw + x);
+            isect_ids[out] = hi | (tile << 32) | depth_bits;
+            flatten_ids[out] = (int32_t)i;
+            ++out;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads)
+isect_offsets_kernel(int64_t n_isects, const int64_t *__restrict__ isect_ids, int n_tiles, int tile_n_bits,
+                     int64_t total_tiles, int32_t *__restrict__ offsets) {
+    int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (i >= n_isects) return;
+    const int64_t tile_mask = ((int64_t)1 << tile_n_bits) - 1;
+    int64_t id = isect_ids[i] >> 32;
+    int64_t cur = (id >> tile_n_bits) * n_tiles + (id & tile_mask);
+    if (i == 0) {
+        for (int64_t t = 0; t <= cur; ++t) offsets[t] = 0;
+    } else {
+        int64_t pid = isect_ids[i - 1] >> 32;
+        if (pid != id) {
+            int64_t prev = (pid >> tile_n_bits) * n_tiles + (pid & tile_mask);
+            for (int64_t t = prev + 1; t <= cur; ++t) offsets[t] = (int32_t)i;
+        }
+    }
+    if (i == n_isects - 1) {
+        for (int64_t t = cur + 1; t < total_tiles; ++t) offsets[t] = (int32_t)n_isects;
+    }
+}
+
+}  // namespace
+
+extern "C" int64_t gsb_isect_num_blocks(int64_t P) { return (P + kThreads - 1) / kThreads; }
+
+extern "C" int gsb_isect_count(int64_t P, const float *means2d, const int32_t *radii, int tile_size, int tile_width,
+                               int tile_height, int32_t *tiles_per_gauss, int32_t *block_sums,
+                               int64_t *block_offsets, int64_t *n_isects_out, cudaStream_t stream) {
+    GSB_REQUIRE(P >= 0 && tile_size > 0 && tile_width >= 0 && tile_height >= 0, "bad sizes");
+    int64_t nblk = gsb_isect_num_blocks(P);
+    if (P > 0) {
+        isect_count_kernel<<<(unsigned)nblk, kThreads, 0, stream>>>(P, means2d, radii, tile_size, tile_width,
+                                                                   tile_height, tiles_per_gauss, block_sums);
+        if (int e = gsb_check_launch("isect_count")) return e;
+    }
+    scan_block_sums_kernel<<<1, 1024, 0, stream>>>(nblk, block_sums, block_offsets, n_isects_out);
+    return gsb_check_launch("scan_block_sums");
+}
+
+extern "C" int gsb_scan_i32_to_i64(int64_t n, const int32_t *in, int64_t *out, int64_t *total_out,
+                                   cudaStream_t stream) {
+    GSB_REQUIRE(n >= 0, "negative size");
+    scan_block_sums_kernel<<<1, 1024, 0, stream>>>(n, in, out, total_out);
+    return gsb_check_launch("scan_i32_to_i64");
+}
+
+extern "C" int gsb_isect_emit(int64_t P, int N, int packed, const float *means2d, const int32_t *radii,
+                              const float *depths, const int64_t *camera_ids, int tile_size, int tile_width,
+                              int tile_height, int tile_n_bits, const int32_t *tiles_per_gauss,
+                              const int64_t *block_offsets, int64_t *isect_ids, int32_t *flatten_ids,
+                              cudaStream_t stream) {
+    GSB_REQUIRE(P >= 0 && tile_size > 0, "bad sizes");
+    GSB_REQUIRE(!packed || camera_ids != nullptr, "camera_ids required when packed");
+    GSB_REQUIRE(packed || N > 0 || P == 0, "N required when not packed");
+    if (P == 0) return GSB_OK;
+    unsigned nblk = (unsigned)gsb_isect_num_blocks(P);
+    if (packed)
+        isect_emit_kernel<true><<<nblk, kThreads, 0, stream>>>(P, N, means2d, radii, depths, camera_ids, tile_size,
+                                                               tile_width, tile_height, tile_n_bits, tiles_per_gauss,
+                                                               block_offsets, isect_ids, flatten_ids);
+    else
+        isect_emit_kernel<false><<<nblk, kThreads, 0, stream>>>(P, N, means2d, radii, depths, camera_ids, tile_size,
+                                                                tile_width, tile_height, tile_n_bits, tiles_per_gauss,
+                                                                block_offsets, isect_ids, flatten_ids);
+    return gsb_check_launch("isect_emit");
+}
+
+extern "C" int64_t gsb_sort_pairs_temp_bytes(int64_t n) {
+    size_t bytes = 0;
+    cub::DoubleBuffer<int64_t> k(nullptr, nullptr);
+    cub::DoubleBuffer<int32_t> v(nullptr, nullptr);
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, k, v, (int64_t)n, 0, 64, (cudaStream_t)0);
+    return (int64_t)bytes;
+}
+
+// Stable LSD radix sort of (int64 key, int32 value) pairs over key bits [0, end_bit).
+// keys_alt / vals_alt are caller-allocated ping-pong buffers; *result_in_alt tells which one holds the result.
+extern "C" int gsb_sort_pairs(int64_t n, int end_bit, int64_t *keys, int64_t *keys_alt, int32_t *vals,
+                              int32_t *vals_alt, void *temp, int64_t temp_bytes, int *result_in_alt,
+                              cudaStream_t stream) {
+    GSB_REQUIRE(n >= 0 && end_bit >= 0 && end_bit <= 64, "bad sizes");
+    *result_in_alt = 0;
+    if (n == 0) return GSB_OK;
+    cub::DoubleBuffer<int64_t> k(keys, keys_alt);
+    cub::DoubleBuffer<int32_t> v(vals, vals_alt);
+    size_t bytes = (size_t)temp_bytes;
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(temp, bytes, k, v, n, 0, end_bit, stream);
+    if (e != cudaSuccess) {
+        gsb_set_error("radix sort: %s", cudaGetErrorString(e));
+        return GSB_ERR_CUDA;
+    }
+    *result_in_alt = (k.Current() == keys_alt) ? 1 : 0;
+    return GSB_OK;
+}
+
+extern "C" int gsb_isect_offsets(int64_t n_isects, const int64_t *isect_ids, int C, int tile_width, int tile_height,
+                                 int tile_n_bits, int32_t *offsets, cudaStream_t stream) {
+    GSB_REQUIRE(n_isects >= 0 && C >= 0, "bad sizes");
+    int64_t n_tiles = (int64_t)tile_width * tile_height;
+    int64_t total = n_tiles * C;
+    if (total == 0) return GSB_OK;
+    if (n_isects == 0) {
+        cudaError_t e = cudaMemsetAsync(offsets, 0, sizeof(int32_t) * total, stream);
+        if (e != cudaSuccess) { gsb_set_error("memset offsets: %s", cudaGetErrorString(e)); return GSB_ERR_CUDA; }
+        return GSB_OK;
+    }
+    isect_offsets_kernel<<<gsb_cdiv(n_isects, kThreads), kThreads, 0, stream>>>(n_isects, isect_ids, (int)n_tiles,
+                                                                               tile_n_bits, total, offsets);
+    return gsb_check_launch("isect_offsets");
+}

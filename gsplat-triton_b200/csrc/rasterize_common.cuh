@@ -1,0 +1,106 @@
+// Shared pieces of the tile compositor (rasterize_to_pixels forward / backward).
+//
+// Layout: one CTA of 256 threads per 16x16 tile; warp w owns the 8x4 pixel block
+// (bx = w & 1, by = w >> 1), lane l the pixel (l & 7, l >> 3) inside it.
+//
+// Per-Gaussian "splat records" are two float4 arrays built once per call by splat_pack_kernel:
+//   recA[g] = (x, y, hx, hy)     hx/hy: half extents of the bbox of {alpha >= 1/255}
+//   recB[g] = (conic_xx, conic_xy, conic_yy, opacity)
+// so that a tile gathers a Gaussian with two aligned 16-byte loads, and both the tile and each
+// warp can reject Gaussians whose alpha would be < 1/255 on all of their pixels *before* any
+// per-pixel work. The reject test is conservative (see splat_extent), so the composited result
+// is the one the reference produces (RasterizeToPixels3DGSFwd.cu:140-169): rejected Gaussians
+// are exactly ones the reference `continue`s over.
+#pragma once
+#include "common.cuh"
+
+namespace raster {
+
+constexpr int kTile = 16;
+constexpr int kThreads = kTile * kTile;
+constexpr int kWarps = kThreads / 32;
+constexpr float kAlphaMin = 1.0f / 255.0f;
+constexpr float kAlphaMax = 0.999f;
+constexpr float kTmin = 1e-4f;
+
+__device__ __forceinline__ void splat_extent(float a, float b, float c, float opac, float &hx, float &hy) {
+    const float inf = __int_as_float(0x7f800000);
+    hx = inf;
+    hy = inf;
+    if (opac < kAlphaMin) {  // alpha = opac * exp(-sigma) <= opac for every counted (sigma >= 0) pixel
+        hx = -inf;
+        hy = -inf;
+        return;
+    }
+    float det = a * c - b * b;
+    if (!(det > 0.f) || !(a > 0.f) || !(c > 0.f) || !(opac <= 1e30f)) return;  // not an ellipse: never reject
+    // alpha >= 1/255  <=>  sigma <= ln(255 opac) =: tau; inflate tau for float rounding of sigma
+    float tau = __logf(255.0f * opac) * 1.001f + 0.05f;
+    float ex = sqrtf(2.0f * tau * c / det) * 1.001f + 0.05f;
+    float ey = sqrtf(2.0f * tau * a / det) * 1.001f + 0.05f;
+    if (ex == ex) hx = ex;
+    if (ey == ey) hy = ey;
+}
+
+// compacting append of this thread's item into the staged batch; returns the slot or -1.
+// Must be called by all 256 threads. s_wcnt: kWarps ints. total = number kept in the batch.
+__device__ __forceinline__ int stage_slot(bool keep, int *s_wcnt, int &total) {
+    unsigned ballot = __ballot_sync(0xffffffffu, keep);
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) s_wcnt[warp] = __popc(ballot);
+    __syncthreads();
+    int base = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+        int c = s_wcnt[w];
+        base += (w < warp) ? c : 0;
+        tot += c;
+    }
+    total = tot;
+    return keep ? base + __popc(ballot & ((1u << lane) - 1u)) : -1;
+}
+
+// pixel-centre bounds of a rectangle of pixels [x0, x0+w) x [y0, y0+h)
+struct Rect {
+    float xlo, xhi, ylo, yhi;
+};
+__device__ __forceinline__ Rect pixel_rect(int x0, int y0, int w, int h) {
+    Rect r;
+    r.xlo = (float)x0 + 0.5f;
+    r.xhi = (float)(x0 + w) - 0.5f;
+    r.ylo = (float)y0 + 0.5f;
+    r.yhi = (float)(y0 + h) - 0.5f;
+    return r;
+}
+// false when no pixel centre of the rectangle can see alpha >= 1/255 from this splat (A = x, y, hx, hy)
+__device__ __forceinline__ bool splat_touches(const float4 &A, const Rect &r) {
+    return !((A.x + A.z < r.xlo) | (A.x - A.z > r.xhi) | (A.y + A.w < r.ylo) | (A.y - A.w > r.yhi));
+}
+
+struct TileGeom {
+    int cam, tile_x, tile_y;
+    int64_t tile_id;      // flat (camera, tile) index
+    int range_start, range_end;
+    int px, py;           // this thread's pixel
+    bool inside;
+    int64_t pix_id;       // flat (camera, y, x) index
+};
+
+__device__ __forceinline__ TileGeom tile_geometry(int64_t n_isects, int W, int H, int tw, int th, int C,
+                                                  const int32_t *__restrict__ offsets) {
+    TileGeom g;
+    g.cam = blockIdx.z;
+    g.tile_y = blockIdx.y;
+    g.tile_x = blockIdx.x;
+    g.tile_id = ((int64_t)g.cam * th + g.tile_y) * tw + g.tile_x;
+    g.range_start = offsets[g.tile_id];
+    g.range_end = (g.tile_id + 1 < (int64_t)C * th * tw) ? offsets[g.tile_id + 1] : (int)n_isects;
+    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    g.px = g.tile_x * kTile + (warp & 1) * 8 + (lane & 7);
+    g.py = g.tile_y * kTile + (warp >> 1) * 4 + (lane >> 3);
+    g.inside = (g.px < W) & (g.py < H);
+    g.pix_id = ((int64_t)g.cam * H + min(g.py, H - 1)) * W + min(g.px, W - 1);
+    return g;
+}
+
+}  // namespace raster

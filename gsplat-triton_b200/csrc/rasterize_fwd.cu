@@ -1,0 +1,183 @@
+// rasterize_to_pixels forward: front-to-back alpha compositing, one CTA per 16x16 tile.
+//
+// Replaces (behaviour, not code): gsplat/triton_impl/rasterize_to_pixels_fwd.py:21-196 and
+// gsplat/cuda/csrc/RasterizeToPixels3DGSFwd.cu:18-188. Oracle: oracle/gs_oracle.py::rasterize_to_pixels.
+//
+// Per pixel p = (x+.5, y+.5), over the tile's Gaussians in sorted order:
+//   sigma = .5(a dx^2 + c dy^2) + b dx dy ; alpha = min(.999, o e^-sigma)
+//   skip if sigma < 0 or alpha < 1/255 ; stop (exclusive) when T(1-alpha) <= 1e-4
+//   colour += alpha T col ; T *= 1-alpha ; last_id = sorted index of the last contributor
+//
+// B200 design: each batch of 256 sorted intersections is gathered once per tile through the packed
+// 2 x float4 splat records and *compacted* into shared memory, dropping splats whose
+// {alpha >= 1/255} bounding box misses the tile; each warp owns an 8x4 pixel block and skips
+// (warp-uniformly, no divergence) the staged splats whose box misses its block, and stops as
+// soon as its 32 pixels are saturated. FP32-pipe / MUFU bound; the records live in L2.
+#include "rasterize_common.cuh"
+
+namespace raster {
+
+__global__ void __launch_bounds__(256)
+splat_pack_kernel(int64_t P, const float *__restrict__ means2d, const float *__restrict__ conics,
+                  const float *__restrict__ opacities, float4 *__restrict__ recA, float4 *__restrict__ recB) {
+    int64_t g = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (g >= P) return;
+    float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * g);
+    const float *cp = conics + 3 * g;
+    float a = cp[0], b = cp[1], c = cp[2];
+    float o = opacities[g];
+    float hx, hy;
+    splat_extent(a, b, c, o, hx, hy);
+    recA[g] = make_float4(m.x, m.y, hx, hy);
+    recB[g] = make_float4(a, b, c, o);
+}
+
+template <int D>
+__global__ void __launch_bounds__(kThreads)
+rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, const float4 *__restrict__ recB,
+                     const float *__restrict__ colors, const float *__restrict__ backgrounds,
+                     const uint8_t *__restrict__ masks, int W, int H, int tw, int th,
+                     const int32_t *__restrict__ offsets, const int32_t *__restrict__ flatten_ids,
+                     float *__restrict__ out_colors, float *__restrict__ out_alphas,
+                     int32_t *__restrict__ last_ids) {
+    __shared__ float4 s_A[kThreads];
+    __shared__ float4 s_B[kThreads];
+    __shared__ int s_idx[kThreads];
+    __shared__ float s_col[kThreads * D];
+    __shared__ int s_wcnt[kWarps];
+
+    const TileGeom tg = tile_geometry(n_isects, W, H, tw, th, C, offsets);
+    const int tid = threadIdx.x, warp = tid >> 5;
+
+    float pix[D];
+#pragma unroll
+    for (int k = 0; k < D; ++k) pix[k] = 0.f;
+    float T = 1.0f;
+    int cur = 0;
+
+    const bool render = (masks == nullptr) || masks[tg.tile_id];
+    if (render) {
+        const float pxf = (float)tg.px + 0.5f, pyf = (float)tg.py + 0.5f;
+        const Rect tile_rect = pixel_rect(tg.tile_x * kTile, tg.tile_y * kTile, kTile, kTile);
+        const Rect warp_rect = pixel_rect(tg.tile_x * kTile + (warp & 1) * 8, tg.tile_y * kTile + (warp >> 1) * 4, 8, 4);
+        bool done = !tg.inside;
+        bool warp_done = __all_sync(0xffffffffu, done);
+
+        for (int base = tg.range_start; base < tg.range_end; base += kThreads) {
+            // all 256 pixels saturated (or outside the image): nothing left to composite
+            if (__syncthreads_count(done) == kThreads) break;
+            const int idx = base + tid;
+            bool keep = false;
+            int g = 0;
+            float4 A;
+            if (idx < tg.range_end) {
+                g = flatten_ids[idx];
+                A = __ldg(recA + g);
+                keep = splat_touches(A, tile_rect);
+            }
+            int total;
+            const int slot = stage_slot(keep, s_wcnt, total);
+            if (keep) {
+                s_A[slot] = A;
+                s_B[slot] = __ldg(recB + g);
+                s_idx[slot] = idx;
+                const float *cp = colors + (size_t)g * D;
+#pragma unroll
+                for (int k = 0; k < D; ++k) s_col[slot * D + k] = cp[k];
+            }
+            __syncthreads();
+            if (warp_done) continue;
+            for (int j = 0; j < total; ++j) {
+                const float4 a4 = s_A[j];
+                if (!splat_touches(a4, warp_rect)) continue;
+                const float4 b4 = s_B[j];
+                const float dx = a4.x - pxf, dy = a4.y - pyf;
+                const float sigma = 0.5f * (b4.x * dx * dx + b4.z * dy * dy) + b4.y * dx * dy;
+                const float alpha = fminf(kAlphaMax, b4.w * __expf(-sigma));
+                bool hit = !done && !(sigma < 0.f) && !(alpha < kAlphaMin);
+                const float next_T = T * (1.0f - alpha);
+                if (hit && next_T <= kTmin) {
+                    done = true;
+                    hit = false;
+                }
+                if (hit) {
+                    const float w = alpha * T;
+#pragma unroll
+                    for (int k = 0; k < D; ++k) pix[k] = fmaf(s_col[j * D + k], w, pix[k]);
+                    cur = s_idx[j];
+                    T = next_T;
+                }
+                if (__all_sync(0xffffffffu, done)) {
+                    warp_done = true;
+                    break;
+                }
+            }
+        }
+    }
+
+    if (tg.inside) {
+        float *oc = out_colors + tg.pix_id * D;
+        const float *bg = backgrounds != nullptr ? backgrounds + (size_t)tg.cam * D : nullptr;
+#pragma unroll
+        for (int k = 0; k < D; ++k) oc[k] = bg != nullptr ? fmaf(T, bg[k], pix[k]) : pix[k];
+        out_alphas[tg.pix_id] = 1.0f - T;
+        last_ids[tg.pix_id] = cur;
+    }
+}
+
+template <int D>
+int launch_fwd(int C, int64_t n_isects, const float *recA, const float *recB, const float *colors,
+               const float *backgrounds, const uint8_t *masks, int W, int H, int tw, int th,
+               const int32_t *offsets, const int32_t *flatten_ids, float *out_colors, float *out_alphas,
+               int32_t *last_ids, cudaStream_t stream) {
+    dim3 grid(tw, th, C);
+    rasterize_fwd_kernel<D><<<grid, kThreads, 0, stream>>>(
+        C, n_isects, reinterpret_cast<const float4 *>(recA), reinterpret_cast<const float4 *>(recB), colors,
+        backgrounds, masks, W, H, tw, th, offsets, flatten_ids, out_colors, out_alphas, last_ids);
+    return gsb_check_launch("rasterize_fwd");
+}
+
+}  // namespace raster
+
+extern "C" int gsb_rasterize_pack(int64_t P, const float *means2d, const float *conics, const float *opacities,
+                                  float *recA, float *recB, cudaStream_t stream) {
+    GSB_REQUIRE(P >= 0, "negative size");
+    if (P == 0) return GSB_OK;
+    raster::splat_pack_kernel<<<gsb_cdiv(P, 256), 256, 0, stream>>>(
+        P, means2d, conics, opacities, reinterpret_cast<float4 *>(recA), reinterpret_cast<float4 *>(recB));
+    return gsb_check_launch("rasterize_pack");
+}
+
+extern "C" int gsb_rasterize_fwd(int C, int64_t n_isects, int D, const float *recA, const float *recB,
+                                 const float *colors, const float *backgrounds, const uint8_t *masks, int width,
+                                 int height, int tile_size, int tile_width, int tile_height,
+                                 const int32_t *isect_offsets, const int32_t *flatten_ids, float *render_colors,
+                                 float *render_alphas, int32_t *last_ids, cudaStream_t stream) {
+    GSB_REQUIRE(C >= 0 && n_isects >= 0 && width > 0 && height > 0, "bad sizes");
+    GSB_REQUIRE(n_isects < ((int64_t)1 << 31), "more than 2^31-1 intersections");
+    if (tile_size != raster::kTile) {
+        gsb_set_error("rasterize_fwd: tile_size %d unsupported (the b200 compositor is built for 16)", tile_size);
+        return GSB_ERR_UNSUPPORTED;
+    }
+    GSB_REQUIRE(tile_width * tile_size >= width && tile_height * tile_size >= height, "tile grid smaller than image");
+    GSB_REQUIRE(tile_height <= 65535 && C <= 65535, "grid too large");
+    if (C == 0) return GSB_OK;
+#define GSB_FWD_CASE(DD)                                                                                          \
+    case DD:                                                                                                      \
+        return raster::launch_fwd<DD>(C, n_isects, recA, recB, colors, backgrounds, masks, width, height,         \
+                                      tile_width, tile_height, isect_offsets, flatten_ids, render_colors,         \
+                                      render_alphas, last_ids, stream);
+    switch (D) {
+        GSB_FWD_CASE(1)
+        GSB_FWD_CASE(2)
+        GSB_FWD_CASE(3)
+        GSB_FWD_CASE(4)
+        GSB_FWD_CASE(8)
+        GSB_FWD_CASE(16)
+        GSB_FWD_CASE(32)
+        default:
+            gsb_set_error("rasterize_fwd: channel count %d unsupported (1,2,3,4,8,16,32)", D);
+            return GSB_ERR_UNSUPPORTED;
+    }
+#undef GSB_FWD_CASE
+}

@@ -1,0 +1,242 @@
+// Spherical-harmonics colour evaluation, forward and backward (degree 0..4).
+//
+// Replaces (behaviour, not code): gsplat/triton_impl/sh_fwd.py:71-191, sh_bwd.py:38-380,
+// gsplat/cuda/csrc/SphericalHarmonicsCUDA.cu:374/448. Basis polynomials follow Sloan's
+// "Efficient Spherical Harmonic Evaluation" as restated in oracle/gs_oracle.py::sh_bases.
+//
+// B200 design: one thread per coefficient row evaluating all 3 channels; the camera (batch)
+// dimension of a broadcast `coeffs.expand(C, ...)` is a stride-0 loop *inside* the thread, so
+// [C,N,K,3] is never materialised and, in the backward pass, v_coeffs accumulates in registers
+// over cameras and is written once with plain stores (no zero-fill, no atomics).
+#include "common.cuh"
+#include "gsplat_b200.h"
+
+namespace {
+
+constexpr int kThreads = 128;
+
+template <int DEG>
+__device__ __forceinline__ void sh_bases(float x, float y, float z, float *b) {
+    b[0] = 0.2820947917738781f;
+    if (DEG < 1) return;
+    b[1] = -0.48860251190292f * y;
+    b[2] = 0.48860251190292f * z;
+    b[3] = -0.48860251190292f * x;
+    if (DEG < 2) return;
+    float z2 = z * z;
+    float tB = -1.092548430592079f * z;
+    float c1 = x * x - y * y, s1 = 2.f * x * y;
+    b[4] = 0.5462742152960395f * s1;
+    b[5] = tB * y;
+    b[6] = 0.9461746957575601f * z2 - 0.3153915652525201f;
+    b[7] = tB * x;
+    b[8] = 0.5462742152960395f * c1;
+    if (DEG < 3) return;
+    float tC = -2.285228997322329f * z2 + 0.4570457994644658f;
+    float tB3 = 1.445305721320277f * z;
+    float c2 = x * c1 - y * s1, s2 = x * s1 + y * c1;
+    b[9] = -0.5900435899266435f * s2;
+    b[10] = tB3 * s1;
+    b[11] = tC * y;
+    b[12] = z * (1.865881662950577f * z2 - 1.119528997770346f);
+    b[13] = tC * x;
+    b[14] = tB3 * c1;
+    b[15] = -0.5900435899266435f * c2;
+    if (DEG < 4) return;
+    float tD = z * (-4.683325804901025f * z2 + 2.007139630671868f);
+    float tC4 = 3.31161143515146f * z2 - 0.47308734787878f;
+    float tB4 = -1.770130769779931f * z;
+    float c3 = x * c2 - y * s2, s3 = x * s2 + y * c2;
+    b[16] = 0.6258357354491763f * s3;
+    b[17] = tB4 * s2;
+    b[18] = tC4 * s1;
+    b[19] = tD * y;
+    b[20] = 1.984313483298443f * z2 * (1.865881662950577f * z2 - 1.119528997770346f) +
+            -1.006230589874905f * (0.9461746957575601f * z2 - 0.3153915652525201f);
+    b[21] = tD * x;
+    b[22] = tC4 * c1;
+    b[23] = tB4 * c2;
+    b[24] = 0.6258357354491763f * c3;
+}
+
+// gradient of sum_k g[k] * Y_k(x,y,z) w.r.t. (x,y,z), the polynomials differentiated as written
+template <int DEG>
+__device__ __forceinline__ void sh_bases_vjp(float x, float y, float z, const float *g, float &vx, float &vy,
+                                             float &vz) {
+    vx = vy = vz = 0.f;
+    if (DEG < 1) return;
+    vy += -0.48860251190292f * g[1];
+    vz += 0.48860251190292f * g[2];
+    vx += -0.48860251190292f * g[3];
+    if (DEG < 2) return;
+    float z2 = z * z;
+    float tB = -1.092548430592079f * z;
+    float c1 = x * x - y * y, s1 = 2.f * x * y;
+    const float A2 = 0.5462742152960395f;
+    vx += g[4] * A2 * 2.f * y + g[7] * tB + g[8] * A2 * 2.f * x;
+    vy += g[4] * A2 * 2.f * x + g[5] * tB - g[8] * A2 * 2.f * y;
+    vz += g[5] * -1.092548430592079f * y + g[6] * 2.f * 0.9461746957575601f * z + g[7] * -1.092548430592079f * x;
+    if (DEG < 3) return;
+    float tC = -2.285228997322329f * z2 + 0.4570457994644658f;
+    float tB3 = 1.445305721320277f * z;
+    float c2 = x * c1 - y * s1, s2 = x * s1 + y * c1;
+    const float A3 = -0.5900435899266435f;
+    float dtC = -4.570457994644658f * z;
+    vx += g[9] * A3 * 3.f * s1 + g[10] * tB3 * 2.f * y + g[13] * tC + g[14] * tB3 * 2.f * x + g[15] * A3 * 3.f * c1;
+    vy += g[9] * A3 * 3.f * c1 + g[10] * tB3 * 2.f * x + g[11] * tC - g[14] * tB3 * 2.f * y - g[15] * A3 * 3.f * s1;
+    vz += g[10] * 1.445305721320277f * s1 + g[11] * dtC * y +
+          g[12] * (3.f * 1.865881662950577f * z2 - 1.119528997770346f) + g[13] * dtC * x +
+          g[14] * 1.445305721320277f * c1;
+    if (DEG < 4) return;
+    float tD = z * (-4.683325804901025f * z2 + 2.007139630671868f);
+    float dtD = -3.f * 4.683325804901025f * z2 + 2.007139630671868f;
+    float tC4 = 3.31161143515146f * z2 - 0.47308734787878f;
+    float dtC4 = 2.f * 3.31161143515146f * z;
+    float tB4 = -1.770130769779931f * z;
+    const float A4 = 0.6258357354491763f;
+    vx += g[16] * A4 * 4.f * s2 + g[17] * tB4 * 3.f * s1 + g[18] * tC4 * 2.f * y + g[21] * tD +
+          g[22] * tC4 * 2.f * x + g[23] * tB4 * 3.f * c1 + g[24] * A4 * 4.f * c2;
+    vy += g[16] * A4 * 4.f * c2 + g[17] * tB4 * 3.f * c1 + g[18] * tC4 * 2.f * x + g[19] * tD -
+          g[22] * tC4 * 2.f * y - g[23] * tB4 * 3.f * s1 - g[24] * A4 * 4.f * s2;
+    float dY20 = 1.984313483298443f * (4.f * 1.865881662950577f * z2 * z - 2.f * 1.119528997770346f * z) -
+                 1.006230589874905f * 2.f * 0.9461746957575601f * z;
+    vz += g[17] * -1.770130769779931f * s2 + g[18] * dtC4 * s1 + g[19] * dtD * y + g[20] * dY20 +
+          g[21] * dtD * x + g[22] * dtC4 * c1 + g[23] * -1.770130769779931f * c2;
+}
+
+template <int DEG>
+__global__ void __launch_bounds__(kThreads)
+sh_fwd_kernel(int64_t n_rows, int n_batch, int K, const float *__restrict__ dirs, const float *__restrict__ coeffs,
+              const uint8_t *__restrict__ masks, float *__restrict__ colors) {
+    constexpr int NB = (DEG + 1) * (DEG + 1);
+    int64_t r = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (r >= n_rows) return;
+    // gather this row's active coefficients once (shared by all batch entries when broadcast)
+    float cf[NB * 3];
+    const float *cp = coeffs + (size_t)r * K * 3;
+    if (((K * 3) & 3) == 0 && (NB * 3) % 4 == 0) {
+#pragma unroll
+        for (int i = 0; i < NB * 3 / 4; ++i) {
+            float4 v = reinterpret_cast<const float4 *>(cp)[i];
+            cf[4 * i] = v.x; cf[4 * i + 1] = v.y; cf[4 * i + 2] = v.z; cf[4 * i + 3] = v.w;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < NB * 3; ++i) cf[i] = cp[i];
+    }
+    for (int b = 0; b < n_batch; ++b) {
+        size_t e = (size_t)b * n_rows + r;
+        float cr = 0.f, cg = 0.f, cb = 0.f;
+        if (masks == nullptr || masks[e]) {
+            const float *dp = dirs + 3 * e;
+            float x = dp[0], y = dp[1], z = dp[2];
+            float inorm = rsqrtf(x * x + y * y + z * z);
+            float bases[NB];
+            sh_bases<DEG>(x * inorm, y * inorm, z * inorm, bases);
+#pragma unroll
+            for (int k = 0; k < NB; ++k) {
+                cr += bases[k] * cf[3 * k];
+                cg += bases[k] * cf[3 * k + 1];
+                cb += bases[k] * cf[3 * k + 2];
+            }
+        }
+        float *op = colors + 3 * e;
+        op[0] = cr; op[1] = cg; op[2] = cb;
+    }
+}
+
+// per-row coefficient variant (coeffs [B*R, K, 3]): n_batch folded into n_rows by the host
+template <int DEG, bool NEED_DIRS>
+__global__ void __launch_bounds__(kThreads)
+sh_bwd_kernel(int64_t n_rows, int n_batch, int K, const float *__restrict__ dirs, const float *__restrict__ coeffs,
+              const uint8_t *__restrict__ masks, const float *__restrict__ v_colors, float *__restrict__ v_coeffs,
+              float *__restrict__ v_dirs) {
+    constexpr int NB = (DEG + 1) * (DEG + 1);
+    int64_t r = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (r >= n_rows) return;
+    float acc[NB * 3];
+#pragma unroll
+    for (int i = 0; i < NB * 3; ++i) acc[i] = 0.f;
+    const float *cp = coeffs + (size_t)r * K * 3;
+    for (int b = 0; b < n_batch; ++b) {
+        size_t e = (size_t)b * n_rows + r;
+        bool on = (masks == nullptr) || masks[e];
+        float vdx = 0.f, vdy = 0.f, vdz = 0.f;
+        if (on) {
+            const float *dp = dirs + 3 * e;
+            float x = dp[0], y = dp[1], z = dp[2];
+            float inorm = rsqrtf(x * x + y * y + z * z);
+            x *= inorm; y *= inorm; z *= inorm;
+            const float *vp = v_colors + 3 * e;
+            float vr = vp[0], vg = vp[1], vb = vp[2];
+            float bases[NB];
+            sh_bases<DEG>(x, y, z, bases);
+#pragma unroll
+            for (int k = 0; k < NB; ++k) {
+                acc[3 * k] += bases[k] * vr;
+                acc[3 * k + 1] += bases[k] * vg;
+                acc[3 * k + 2] += bases[k] * vb;
+            }
+            if (NEED_DIRS) {
+                float g[NB];
+#pragma unroll
+                for (int k = 0; k < NB; ++k) g[k] = cp[3 * k] * vr + cp[3 * k + 1] * vg + cp[3 * k + 2] * vb;
+                float vx, vy, vz;
+                sh_bases_vjp<DEG>(x, y, z, g, vx, vy, vz);
+                // VJP of the normalisation d / |d|
+                float dot = x * vx + y * vy + z * vz;
+                vdx = (vx - dot * x) * inorm;
+                vdy = (vy - dot * y) * inorm;
+                vdz = (vz - dot * z) * inorm;
+            }
+        }
+        if (NEED_DIRS) {
+            float *op = v_dirs + 3 * e;
+            op[0] = vdx; op[1] = vdy; op[2] = vdz;
+        }
+    }
+    float *op = v_coeffs + (size_t)r * K * 3;
+#pragma unroll
+    for (int i = 0; i < NB * 3; ++i) op[i] = acc[i];
+    for (int i = NB * 3; i < K * 3; ++i) op[i] = 0.f;
+}
+
+}  // namespace
+
+#define DISPATCH_DEG(deg, ...)                                        \
+    switch (deg) {                                                    \
+        case 0: { constexpr int D = 0; __VA_ARGS__; } break;          \
+        case 1: { constexpr int D = 1; __VA_ARGS__; } break;          \
+        case 2: { constexpr int D = 2; __VA_ARGS__; } break;          \
+        case 3: { constexpr int D = 3; __VA_ARGS__; } break;          \
+        default: { constexpr int D = 4; __VA_ARGS__; } break;         \
+    }
+
+extern "C" int gsb_sh_fwd(int degree, int64_t n_rows, int n_batch, int K, const float *dirs, const float *coeffs,
+                          const uint8_t *masks, float *colors, cudaStream_t stream) {
+    GSB_REQUIRE(degree >= 0 && degree <= 4, "degree must be in [0, 4]");
+    GSB_REQUIRE((degree + 1) * (degree + 1) <= K, "K is smaller than (degree+1)^2");
+    GSB_REQUIRE(n_rows >= 0 && n_batch >= 0, "negative size");
+    if (n_rows == 0 || n_batch == 0) return GSB_OK;
+    unsigned nblk = gsb_cdiv(n_rows, kThreads);
+    DISPATCH_DEG(degree, (sh_fwd_kernel<D><<<nblk, kThreads, 0, stream>>>(n_rows, n_batch, K, dirs, coeffs, masks, colors)));
+    return gsb_check_launch("sh_fwd");
+}
+
+extern "C" int gsb_sh_bwd(int degree, int64_t n_rows, int n_batch, int K, const float *dirs, const float *coeffs,
+                          const uint8_t *masks, const float *v_colors, float *v_coeffs, float *v_dirs,
+                          cudaStream_t stream) {
+    GSB_REQUIRE(degree >= 0 && degree <= 4, "degree must be in [0, 4]");
+    GSB_REQUIRE((degree + 1) * (degree + 1) <= K, "K is smaller than (degree+1)^2");
+    GSB_REQUIRE(n_rows >= 0 && n_batch >= 0, "negative size");
+    if (n_rows == 0) return GSB_OK;
+    unsigned nblk = gsb_cdiv(n_rows, kThreads);
+    if (v_dirs != nullptr) {
+        DISPATCH_DEG(degree, (sh_bwd_kernel<D, true><<<nblk, kThreads, 0, stream>>>(n_rows, n_batch, K, dirs, coeffs, masks,
+                                                                                  v_colors, v_coeffs, v_dirs)));
+    } else {
+        DISPATCH_DEG(degree, (sh_bwd_kernel<D, false><<<nblk, kThreads, 0, stream>>>(n_rows, n_batch, K, dirs, coeffs, masks,
+                                                                                   v_colors, v_coeffs, v_dirs)));
+    }
+    return gsb_check_launch("sh_bwd");
+}

@@ -1,0 +1,541 @@
+"""Python side of the `b200` backend: the five functions `gsplat/rendering.py` imports.
+
+Mirrors (same names, arguments, defaults, return values, error behaviour)
+  reference gsplat/triton_impl/_wrapper.py: fully_fused_projection :429, isect_tiles :544,
+  isect_offset_encode :548, spherical_harmonics :596, rasterize_to_pixels :185
+and, for the arguments Triton does not implement (packed, sparse_grad, covars, ortho),
+  reference gsplat/cuda/_wrapper.py :209, :349, :422, :441, :82.
+
+Every function allocates its outputs with torch (so the caching allocator and the current
+stream stay PyTorch's) and passes raw device pointers to libgsplat_b200.so through ctypes.
+No Triton, no torch fallback: a missing library or a CPU tensor raises.
+"""
+import os
+from typing import Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from ._lib import lib, ptr, require_cuda, stream_of
+
+_CAMERA_MODELS = {"pinhole": 0, "ortho": 1}
+_RASTER_CHANNELS = (1, 2, 3, 4, 8, 16, 32)
+
+
+def _camera_model_id(camera_model: str) -> int:
+    if camera_model not in _CAMERA_MODELS:
+        # the Triton reference only has pinhole (triton_impl/_wrapper.py:322-323)
+        raise NotImplementedError(f"camera_model={camera_model!r} is not implemented by the b200 backend")
+    return _CAMERA_MODELS[camera_model]
+
+
+def tile_n_bits(n_tiles: int) -> int:
+    """Bits reserved for the tile id inside an intersection key.
+
+    Triton rule `(n_tiles-1).bit_length()` (triton_impl/isect_tiles.py:105, isect_offset.py:23) by
+    default; GSPLAT_B200_TILE_BITS=cuda selects `n_tiles.bit_length()` (IntersectTile.cu:145,
+    _torch_impl.py:367). They differ only when n_tiles is a power of two.
+    """
+    if os.environ.get("GSPLAT_B200_TILE_BITS", "triton") == "cuda":
+        return int(n_tiles).bit_length()
+    return max(int(n_tiles) - 1, 0).bit_length()
+
+
+# --------------------------------------------------------------------------------------------
+# fully_fused_projection
+# --------------------------------------------------------------------------------------------
+def fully_fused_projection(
+    means: Tensor,  # [N, 3]
+    covars: Optional[Tensor],  # [N, 6] or None
+    quats: Optional[Tensor],  # [N, 4] or None
+    scales: Optional[Tensor],  # [N, 3] or None
+    viewmats: Tensor,  # [C, 4, 4]
+    Ks: Tensor,  # [C, 3, 3]
+    width: int,
+    height: int,
+    eps2d: float = 0.3,
+    near_plane: float = 0.01,
+    far_plane: float = 1e10,
+    radius_clip: float = 0.0,
+    packed: bool = False,
+    sparse_grad: bool = False,
+    calc_compensations: bool = False,
+    camera_model: str = "pinhole",
+):
+    """Projects Gaussians to 2D (quat/scale -> covariance, EWA projection, blur, radius, culling).
+
+    Returns `(radii[C,N] int32, means2d[C,N,2], depths[C,N], conics[C,N,3], compensations|None)`
+    or, with `packed=True`, `(camera_ids, gaussian_ids, radii, means2d, depths, conics,
+    compensations)` with [nnz] rows in (camera, Gaussian) row-major order, ids int64.
+    """
+    C = viewmats.size(0)
+    N = means.size(0)
+    assert means.size() == (N, 3), means.size()
+    assert viewmats.size() == (C, 4, 4), viewmats.size()
+    assert Ks.size() == (C, 3, 3), Ks.size()
+    means = means.contiguous()
+    if covars is not None:
+        assert covars.size() == (N, 6), covars.size()
+        covars = covars.contiguous()
+    else:
+        assert quats is not None, "covars or quats is required"
+        assert scales is not None, "covars or scales is required"
+        assert quats.size() == (N, 4), quats.size()
+        assert scales.size() == (N, 3), scales.size()
+        quats = quats.contiguous()
+        scales = scales.contiguous()
+    if sparse_grad:
+        assert packed, "sparse_grad is only supported when packed is True"
+    _camera_model_id(camera_model)
+    require_cuda(means, covars, quats, scales, viewmats, Ks)
+    viewmats = viewmats.contiguous()
+    Ks = Ks.contiguous()
+    if packed:
+        return _FullyFusedProjectionPacked.apply(
+            means, covars, quats, scales, viewmats, Ks, width, height, eps2d, near_plane, far_plane,
+            radius_clip, sparse_grad, calc_compensations, camera_model,
+        )
+    return _FullyFusedProjection.apply(
+        means, covars, quats, scales, viewmats, Ks, width, height, eps2d, near_plane, far_plane,
+        radius_clip, calc_compensations, camera_model,
+    )
+
+
+def _f32(t: Optional[Tensor]) -> Optional[Tensor]:
+    if t is None:
+        return None
+    return t.contiguous() if t.dtype == torch.float32 else t.float().contiguous()
+
+
+class _FullyFusedProjection(torch.autograd.Function):
+    """Unpacked projection. cf. triton_impl/_wrapper.py:300-427."""
+
+    @staticmethod
+    def forward(ctx, means, covars, quats, scales, viewmats, Ks, width, height, eps2d, near_plane,
+                far_plane, radius_clip, calc_compensations, camera_model):
+        C, N = viewmats.size(0), means.size(0)
+        dev = means.device
+        model = _camera_model_id(camera_model)
+        radii = torch.empty((C, N), dtype=torch.int32, device=dev)
+        means2d = torch.empty((C, N, 2), dtype=torch.float32, device=dev)
+        depths = torch.empty((C, N), dtype=torch.float32, device=dev)
+        conics = torch.empty((C, N, 3), dtype=torch.float32, device=dev)
+        compensations = torch.empty((C, N), dtype=torch.float32, device=dev) if calc_compensations else None
+        lib.gsb_projection_fwd(
+            C, N, ptr(means), ptr(covars), ptr(quats), ptr(scales), ptr(viewmats), ptr(Ks), width, height,
+            eps2d, near_plane, far_plane, radius_clip, model, ptr(radii), ptr(means2d), ptr(depths),
+            ptr(conics), ptr(compensations), stream_of(means),
+        )
+        ctx.save_for_backward(means, covars, quats, scales, viewmats, Ks, radii, conics, compensations)
+        ctx.width, ctx.height, ctx.eps2d, ctx.model = width, height, eps2d, model
+        ctx.mark_non_differentiable(radii)
+        return radii, means2d, depths, conics, compensations
+
+    @staticmethod
+    def backward(ctx, v_radii, v_means2d, v_depths, v_conics, v_compensations):
+        means, covars, quats, scales, viewmats, Ks, radii, conics, compensations = ctx.saved_tensors
+        C, N = viewmats.size(0), means.size(0)
+        need = ctx.needs_input_grad
+        v_means = torch.empty_like(means) if need[0] else None
+        v_covars = torch.empty_like(covars) if (covars is not None and need[1]) else None
+        v_quats = torch.empty_like(quats) if (quats is not None and need[2]) else None
+        v_scales = torch.empty_like(scales) if (scales is not None and need[3]) else None
+        v_viewmats = torch.empty_like(viewmats) if need[4] else None
+        if compensations is None:
+            v_compensations = None
+        lib.gsb_projection_bwd(
+            C, N, ptr(means), ptr(covars), ptr(quats), ptr(scales), ptr(viewmats), ptr(Ks), ctx.width,
+            ctx.height, ctx.eps2d, ctx.model, ptr(radii), ptr(conics), ptr(compensations),
+            ptr(_f32(v_means2d)), ptr(_f32(v_depths)), ptr(_f32(v_conics)), ptr(_f32(v_compensations)),
+            ptr(v_means), ptr(v_covars), ptr(v_quats), ptr(v_scales), ptr(v_viewmats), stream_of(means),
+        )
+        return (v_means, v_covars, v_quats, v_scales, v_viewmats) + (None,) * 9
+
+
+class _FullyFusedProjectionPacked(torch.autograd.Function):
+    """Packed (COO) projection. cf. cuda/_wrapper.py:998-1190."""
+
+    @staticmethod
+    def forward(ctx, means, covars, quats, scales, viewmats, Ks, width, height, eps2d, near_plane,
+                far_plane, radius_clip, sparse_grad, calc_compensations, camera_model):
+        C, N = viewmats.size(0), means.size(0)
+        dev = means.device
+        model = _camera_model_id(camera_model)
+        st = stream_of(means)
+        nblk = (N + 255) // 256
+        block_counts = torch.empty((C * nblk,), dtype=torch.int32, device=dev)
+        block_offsets = torch.empty((C * nblk + 1,), dtype=torch.int64, device=dev)
+        args = (C, N, ptr(means), ptr(covars), ptr(quats), ptr(scales), ptr(viewmats), ptr(Ks), width, height,
+                eps2d, near_plane, far_plane, radius_clip, model)
+        lib.gsb_projection_packed_count(*args, ptr(block_counts), st)
+        lib.gsb_scan_i32_to_i64(C * nblk, ptr(block_counts), ptr(block_offsets),
+                                block_offsets.data_ptr() + 8 * C * nblk, st)
+        nnz = int(block_offsets[-1].item())  # size read-back, as Projection.cpp:332-333
+        camera_ids = torch.empty((nnz,), dtype=torch.int64, device=dev)
+        gaussian_ids = torch.empty((nnz,), dtype=torch.int64, device=dev)
+        radii = torch.empty((nnz,), dtype=torch.int32, device=dev)
+        means2d = torch.empty((nnz, 2), dtype=torch.float32, device=dev)
+        depths = torch.empty((nnz,), dtype=torch.float32, device=dev)
+        conics = torch.empty((nnz, 3), dtype=torch.float32, device=dev)
+        compensations = torch.empty((nnz,), dtype=torch.float32, device=dev) if calc_compensations else None
+        if nnz > 0:
+            lib.gsb_projection_packed_write(
+                *args, ptr(block_offsets), ptr(camera_ids), ptr(gaussian_ids), ptr(radii), ptr(means2d),
+                ptr(depths), ptr(conics), ptr(compensations), st,
+            )
+        ctx.save_for_backward(camera_ids, gaussian_ids, means, covars, quats, scales, viewmats, Ks, conics,
+                              compensations)
+        ctx.width, ctx.height, ctx.eps2d, ctx.model, ctx.sparse_grad = width, height, eps2d, model, sparse_grad
+        ctx.mark_non_differentiable(camera_ids, gaussian_ids, radii)
+        return camera_ids, gaussian_ids, radii, means2d, depths, conics, compensations
+
+    @staticmethod
+    def backward(ctx, v_camera_ids, v_gaussian_ids, v_radii, v_means2d, v_depths, v_conics, v_compensations):
+        (camera_ids, gaussian_ids, means, covars, quats, scales, viewmats, Ks, conics,
+         compensations) = ctx.saved_tensors
+        C, N, nnz = viewmats.size(0), means.size(0), camera_ids.numel()
+        need = ctx.needs_input_grad
+        sparse = ctx.sparse_grad
+        dev = means.device
+        rows = nnz if sparse else N
+
+        def out(t, width, needed):
+            if t is None or not needed:
+                return None
+            return torch.empty((rows, width), dtype=torch.float32, device=dev)
+
+        v_means = out(means, 3, need[0])
+        v_covars = out(covars, 6, need[1])
+        v_quats = out(quats, 4, need[2])
+        v_scales = out(scales, 3, need[3])
+        v_viewmats = torch.empty_like(viewmats) if need[4] else None
+        acc = None if sparse else torch.empty((N, 9), dtype=torch.float32, device=dev)
+        if compensations is None:
+            v_compensations = None
+        lib.gsb_projection_packed_bwd(
+            C, N, nnz, ptr(means), ptr(covars), ptr(quats), ptr(scales), ptr(viewmats), ptr(Ks), ctx.width,
+            ctx.height, ctx.eps2d, ctx.model, ptr(camera_ids), ptr(gaussian_ids), ptr(conics),
+            ptr(compensations), ptr(_f32(v_means2d)), ptr(_f32(v_depths)), ptr(_f32(v_conics)),
+            ptr(_f32(v_compensations)), int(sparse), ptr(acc), ptr(v_means), ptr(v_covars), ptr(v_quats),
+            ptr(v_scales), ptr(v_viewmats), stream_of(means),
+        )
+        if sparse:
+            def coo(values, like):
+                if values is None:
+                    return None
+                return torch.sparse_coo_tensor(indices=gaussian_ids[None], values=values, size=like.size(),
+                                               is_coalesced=(C == 1))
+
+            v_means, v_covars = coo(v_means, means), coo(v_covars, covars) if covars is not None else None
+            v_quats = coo(v_quats, quats) if quats is not None else None
+            v_scales = coo(v_scales, scales) if scales is not None else None
+        return (v_means, v_covars, v_quats, v_scales, v_viewmats) + (None,) * 10
+
+
+# --------------------------------------------------------------------------------------------
+# spherical_harmonics
+# --------------------------------------------------------------------------------------------
+def spherical_harmonics(
+    degrees_to_use: int,
+    dirs: Tensor,  # [..., 3]
+    coeffs: Tensor,  # [..., K, 3]
+    masks: Optional[Tensor] = None,  # [...]
+) -> Tensor:
+    """Colours from SH coefficients (degree <= 4); `dirs` need not be normalised.
+
+    Same contract as triton_impl/_wrapper.py:596-620 / cuda/_wrapper.py:82-118. Additionally,
+    `coeffs` may omit the leading camera dim (`dirs[C,N,3]`, `coeffs[N,K,3]`): the kernel then
+    broadcasts inside the thread and `[C,N,K,3]` is never materialised. A stride-0
+    `coeffs.expand(C, ...)` as built by the reference's rendering.py:402 is detected and
+    handled the same way.
+    """
+    assert (degrees_to_use + 1) ** 2 <= coeffs.shape[-2], coeffs.shape
+    assert dirs.shape[-1] == 3, dirs.shape
+    assert coeffs.shape[-1] == 3, coeffs.shape
+    if coeffs.dim() == dirs.dim() + 1:
+        assert dirs.shape[:-1] == coeffs.shape[:-2], (dirs.shape, coeffs.shape)
+        # undo a stride-0 broadcast over the leading dim (camera axis)
+        if dirs.dim() == 3 and coeffs.stride(0) == 0 and coeffs.shape[0] > 1:
+            coeffs = coeffs[0]
+    else:
+        assert dirs.dim() == 3 and coeffs.dim() == 3 and dirs.shape[1] == coeffs.shape[0], (
+            dirs.shape, coeffs.shape)
+    if masks is not None:
+        assert masks.shape == dirs.shape[:-1], masks.shape
+        masks = masks.contiguous()
+    require_cuda(dirs, coeffs, masks)
+    return _SphericalHarmonics.apply(degrees_to_use, dirs.contiguous(), coeffs.contiguous(), masks)
+
+
+class _SphericalHarmonics(torch.autograd.Function):
+    """cf. triton_impl/_wrapper.py:552-594."""
+
+    @staticmethod
+    def _geometry(dirs, coeffs):
+        K = coeffs.shape[-2]
+        if coeffs.dim() == dirs.dim() + 1:
+            return 1, dirs.numel() // 3, K
+        return dirs.shape[0], dirs.shape[1], K
+
+    @staticmethod
+    def forward(ctx, sh_degree, dirs, coeffs, masks):
+        n_batch, n_rows, K = _SphericalHarmonics._geometry(dirs, coeffs)
+        colors = torch.empty_like(dirs)
+        m8 = masks.to(torch.uint8) if masks is not None else None
+        lib.gsb_sh_fwd(sh_degree, n_rows, n_batch, K, ptr(dirs), ptr(coeffs), ptr(m8), ptr(colors),
+                       stream_of(dirs))
+        ctx.save_for_backward(dirs, coeffs, m8)
+        ctx.sh_degree = sh_degree
+        return colors
+
+    @staticmethod
+    def backward(ctx, v_colors):
+        dirs, coeffs, m8 = ctx.saved_tensors
+        n_batch, n_rows, K = _SphericalHarmonics._geometry(dirs, coeffs)
+        v_coeffs = torch.empty_like(coeffs)
+        v_dirs = torch.empty_like(dirs) if ctx.needs_input_grad[1] else None
+        if n_rows == 0 or n_batch == 0:
+            v_coeffs.zero_()
+        lib.gsb_sh_bwd(ctx.sh_degree, n_rows, n_batch, K, ptr(dirs), ptr(coeffs), ptr(m8),
+                       ptr(_f32(v_colors)), ptr(v_coeffs), ptr(v_dirs), stream_of(dirs))
+        if not ctx.needs_input_grad[2]:
+            v_coeffs = None
+        return None, v_dirs, v_coeffs, None
+
+
+# --------------------------------------------------------------------------------------------
+# isect_tiles / isect_offset_encode
+# --------------------------------------------------------------------------------------------
+@torch.no_grad()
+def isect_tiles(
+    means2d: Tensor,  # [C, N, 2] or [nnz, 2]
+    radii: Tensor,  # [C, N] or [nnz]
+    depths: Tensor,  # [C, N] or [nnz]
+    tile_size: int,
+    tile_width: int,
+    tile_height: int,
+    sort: bool = True,
+    packed: bool = False,
+    n_cameras: Optional[int] = None,
+    camera_ids: Optional[Tensor] = None,
+    gaussian_ids: Optional[Tensor] = None,
+) -> Tuple[Tensor, Tensor, Tensor]:
+    """Maps projected Gaussians to the tiles they overlap.
+
+    Returns `(tiles_per_gauss int32 [C,N]|[nnz], isect_ids int64 [n_isects],
+    flatten_ids int32 [n_isects])`, sorted by key when `sort`. Contract:
+    triton_impl/isect_tiles.py:14-133, cuda/_wrapper.py:349-419.
+    """
+    if packed:
+        nnz = means2d.size(0)
+        assert means2d.shape == (nnz, 2), means2d.size()
+        assert radii.shape == (nnz,), radii.size()
+        assert depths.shape == (nnz,), depths.size()
+        assert camera_ids is not None, "camera_ids is required if packed is True"
+        assert gaussian_ids is not None, "gaussian_ids is required if packed is True"
+        assert n_cameras is not None, "n_cameras is required if packed is True"
+        camera_ids = camera_ids.contiguous()
+        if camera_ids.dtype != torch.int64:
+            camera_ids = camera_ids.long()
+        C, N, P = n_cameras, 0, nnz
+    else:
+        C, N, _ = means2d.shape
+        assert means2d.shape == (C, N, 2), means2d.size()
+        assert radii.shape == (C, N), radii.size()
+        assert depths.shape == (C, N), depths.size()
+        P = C * N
+    require_cuda(means2d, radii, depths, camera_ids)
+    means2d = _f32(means2d)
+    depths = _f32(depths)
+    radii = radii.contiguous()
+    if radii.dtype != torch.int32:
+        radii = radii.int()
+    dev = means2d.device
+    st = stream_of(means2d)
+
+    nblk = int(lib.gsb_isect_num_blocks(P))
+    tiles_per_gauss = torch.empty(radii.shape, dtype=torch.int32, device=dev)
+    block_sums = torch.empty((max(nblk, 1),), dtype=torch.int32, device=dev)
+    block_offsets = torch.empty((nblk + 1,), dtype=torch.int64, device=dev)
+    lib.gsb_isect_count(P, ptr(means2d), ptr(radii), tile_size, tile_width, tile_height, ptr(tiles_per_gauss),
+                        ptr(block_sums), ptr(block_offsets), block_offsets.data_ptr() + 8 * nblk, st)
+    n_isects = int(block_offsets[-1].item())  # size read-back (isect_tiles.py:102, Intersect.cpp:77-78)
+
+    n_tiles = tile_width * tile_height
+    tb = tile_n_bits(n_tiles)
+    cb = max(C - 1, 0).bit_length()
+    assert 32 + tb + cb <= 64, "camera/tile ids do not fit a 64-bit intersection key"
+    isect_ids = torch.empty((n_isects,), dtype=torch.int64, device=dev)
+    flatten_ids = torch.empty((n_isects,), dtype=torch.int32, device=dev)
+    if n_isects == 0:
+        return tiles_per_gauss, isect_ids, flatten_ids
+    lib.gsb_isect_emit(P, N, int(packed), ptr(means2d), ptr(radii), ptr(depths), ptr(camera_ids), tile_size,
+                       tile_width, tile_height, tb, ptr(tiles_per_gauss), ptr(block_offsets), ptr(isect_ids),
+                       ptr(flatten_ids), st)
+    if sort:
+        isect_ids, flatten_ids = _sort_pairs(isect_ids, flatten_ids, 32 + tb + cb)
+    return tiles_per_gauss, isect_ids, flatten_ids
+
+
+def _sort_pairs(keys: Tensor, vals: Tensor, end_bit: int) -> Tuple[Tensor, Tensor]:
+    """Stable LSD radix sort of (int64, int32) pairs over bits [0, end_bit) (radix_sort.cu:10-62)."""
+    import ctypes
+
+    n = keys.numel()
+    keys_alt = torch.empty_like(keys)
+    vals_alt = torch.empty_like(vals)
+    temp_bytes = int(lib.gsb_sort_pairs_temp_bytes(n))
+    temp = torch.empty((max(temp_bytes, 1),), dtype=torch.uint8, device=keys.device)
+    in_alt = ctypes.c_int(0)
+    lib.gsb_sort_pairs(n, end_bit, ptr(keys), ptr(keys_alt), ptr(vals), ptr(vals_alt), ptr(temp), temp_bytes,
+                       ctypes.addressof(in_alt), stream_of(keys))
+    return (keys_alt, vals_alt) if in_alt.value else (keys, vals)
+
+
+@torch.no_grad()
+def isect_offset_encode(isect_ids: Tensor, n_cameras: int, tile_width: int, tile_height: int) -> Tensor:
+    """First sorted-intersection index of every (camera, tile): int32 [C, tile_height, tile_width].
+
+    Contract: triton_impl/isect_offset.py:9-35, cuda/_wrapper.py:422-438.
+    """
+    require_cuda(isect_ids)
+    isect_ids = isect_ids.contiguous()
+    offsets = torch.empty((n_cameras, tile_height, tile_width), dtype=torch.int32, device=isect_ids.device)
+    lib.gsb_isect_offsets(isect_ids.numel(), ptr(isect_ids), n_cameras, tile_width, tile_height,
+                          tile_n_bits(tile_width * tile_height), ptr(offsets), stream_of(isect_ids))
+    return offsets
+
+
+# --------------------------------------------------------------------------------------------
+# rasterize_to_pixels
+# --------------------------------------------------------------------------------------------
+def rasterize_to_pixels(
+    means2d: Tensor,  # [C, N, 2] or [nnz, 2]
+    conics: Tensor,  # [C, N, 3] or [nnz, 3]
+    colors: Tensor,  # [C, N, channels] or [nnz, channels]
+    opacities: Tensor,  # [C, N] or [nnz]
+    image_width: int,
+    image_height: int,
+    tile_size: int,
+    isect_offsets: Tensor,  # [C, tile_height, tile_width]
+    flatten_ids: Tensor,  # [n_isects]
+    backgrounds: Optional[Tensor] = None,  # [C, channels]
+    masks: Optional[Tensor] = None,  # [C, tile_height, tile_width]
+    packed: bool = False,
+    absgrad: bool = False,
+) -> Tuple[Tensor, Tensor]:
+    """Alpha-composites the sorted Gaussians of every tile.
+
+    Returns `(render_colors [C,H,W,channels], render_alphas [C,H,W,1])`. Contract:
+    triton_impl/_wrapper.py:185-296, cuda/_wrapper.py:441-575 (masks: True = render the tile,
+    the upstream/CUDA polarity).
+    """
+    C = isect_offsets.size(0)
+    if packed:
+        nnz = means2d.size(0)
+        assert means2d.shape == (nnz, 2), means2d.shape
+        assert conics.shape == (nnz, 3), conics.shape
+        assert colors.shape[0] == nnz, colors.shape
+        assert opacities.shape == (nnz,), opacities.shape
+    else:
+        N = means2d.size(1)
+        assert means2d.shape == (C, N, 2), means2d.shape
+        assert conics.shape == (C, N, 3), conics.shape
+        assert colors.shape[:2] == (C, N), colors.shape
+        assert opacities.shape == (C, N), opacities.shape
+    channels = colors.shape[-1]
+    if backgrounds is not None:
+        assert backgrounds.shape == (C, channels), backgrounds.shape
+        backgrounds = backgrounds.contiguous()
+    if masks is not None:
+        assert masks.shape == isect_offsets.shape, masks.shape
+        masks = masks.contiguous()
+    if channels > 513 or channels == 0:
+        raise ValueError(f"Unsupported number of color channels: {channels}")
+    tile_height, tile_width = isect_offsets.shape[1:3]
+    assert tile_height * tile_size >= image_height, f"Assert Failed: {tile_height} * {tile_size} >= {image_height}"
+    assert tile_width * tile_size >= image_width, f"Assert Failed: {tile_width} * {tile_size} >= {image_width}"
+    require_cuda(means2d, conics, colors, opacities, isect_offsets, flatten_ids, backgrounds, masks)
+
+    def run(colors_c, backgrounds_c):
+        ch = colors_c.shape[-1]
+        target = next(c for c in _RASTER_CHANNELS if c >= ch)
+        pad = target - ch
+        if pad:
+            colors_c = torch.nn.functional.pad(colors_c, (0, pad))
+            if backgrounds_c is not None:
+                backgrounds_c = torch.nn.functional.pad(backgrounds_c, (0, pad))
+        rc, ra = _RasterizeToPixels.apply(
+            means2d.contiguous(), conics.contiguous(), colors_c.contiguous(), opacities.contiguous(),
+            backgrounds_c, masks, image_width, image_height, tile_size, isect_offsets.contiguous(),
+            flatten_ids.contiguous(), absgrad,
+        )
+        return (rc[..., :ch] if pad else rc), ra
+
+    top = _RASTER_CHANNELS[-1]
+    if channels <= top:
+        return run(colors, backgrounds)
+    outs, alphas = [], None
+    for lo in range(0, channels, top):
+        bg = backgrounds[..., lo:lo + top] if backgrounds is not None else None
+        rc, ra = run(colors[..., lo:lo + top], bg)
+        outs.append(rc)
+        alphas = ra if alphas is None else alphas
+    return torch.cat(outs, dim=-1), alphas
+
+
+class _RasterizeToPixels(torch.autograd.Function):
+    """cf. triton_impl/_wrapper.py:42-183, cuda/_wrapper.py:845-995."""
+
+    @staticmethod
+    def forward(ctx, means2d, conics, colors, opacities, backgrounds, masks, width, height, tile_size,
+                isect_offsets, flatten_ids, absgrad):
+        C, tile_height, tile_width = isect_offsets.shape
+        D = colors.shape[-1]
+        dev = means2d.device
+        st = stream_of(means2d)
+        P = opacities.numel()
+        n_isects = flatten_ids.numel()
+        if flatten_ids.dtype != torch.int32:
+            flatten_ids = flatten_ids.int()
+        m8 = masks.to(torch.uint8) if masks is not None else None
+        rec = torch.empty((2, max(P, 1), 4), dtype=torch.float32, device=dev)
+        lib.gsb_rasterize_pack(P, ptr(means2d), ptr(conics), ptr(opacities), ptr(rec[0]), ptr(rec[1]), st)
+        render_colors = torch.empty((C, height, width, D), dtype=torch.float32, device=dev)
+        render_alphas = torch.empty((C, height, width, 1), dtype=torch.float32, device=dev)
+        last_ids = torch.empty((C, height, width), dtype=torch.int32, device=dev)
+        lib.gsb_rasterize_fwd(C, n_isects, D, ptr(rec[0]), ptr(rec[1]), ptr(colors), ptr(backgrounds), ptr(m8),
+                              width, height, tile_size, tile_width, tile_height, ptr(isect_offsets),
+                              ptr(flatten_ids), ptr(render_colors), ptr(render_alphas), ptr(last_ids), st)
+        ctx.save_for_backward(means2d, rec, colors, backgrounds, m8, isect_offsets, flatten_ids, render_alphas,
+                              last_ids)
+        ctx.width, ctx.height, ctx.tile_size, ctx.absgrad = width, height, tile_size, absgrad
+        ctx.shapes = (conics.shape, opacities.shape)
+        return render_colors, render_alphas
+
+    @staticmethod
+    def backward(ctx, v_render_colors, v_render_alphas):
+        (means2d, rec, colors, backgrounds, m8, isect_offsets, flatten_ids, render_alphas,
+         last_ids) = ctx.saved_tensors
+        C, tile_height, tile_width = isect_offsets.shape
+        D = colors.shape[-1]
+        dev = means2d.device
+        conics_shape, opac_shape = ctx.shapes
+        v_render_colors = _f32(v_render_colors)
+        v_render_alphas = _f32(v_render_alphas)
+        v_means2d = torch.zeros_like(means2d)
+        v_conics = torch.zeros(conics_shape, dtype=torch.float32, device=dev)
+        v_colors = torch.zeros_like(colors)
+        v_opacities = torch.zeros(opac_shape, dtype=torch.float32, device=dev)
+        v_abs = torch.zeros_like(means2d) if ctx.absgrad else None
+        lib.gsb_rasterize_bwd(C, flatten_ids.numel(), D, ptr(rec[0]), ptr(rec[1]), ptr(colors), ptr(backgrounds),
+                              ptr(m8), ctx.width, ctx.height, ctx.tile_size, tile_width, tile_height,
+                              ptr(isect_offsets), ptr(flatten_ids), ptr(render_alphas), ptr(last_ids),
+                              ptr(v_render_colors), ptr(v_render_alphas), ptr(v_abs), ptr(v_means2d),
+                              ptr(v_conics), ptr(v_colors), ptr(v_opacities), stream_of(means2d))
+        if ctx.absgrad:
+            means2d.absgrad = v_abs
+        v_backgrounds = None
+        if ctx.needs_input_grad[4]:
+            v_backgrounds = (v_render_colors * (1.0 - render_alphas).float()).sum(dim=(1, 2))
+        return (v_means2d, v_conics, v_colors, v_opacities, v_backgrounds) + (None,) * 7

@@ -1,0 +1,266 @@
+"""`rasterization()` — the public entry of the hot path, with the `GSPLAT_BACKEND` switch.
+
+Same signature, defaults, outputs and `meta` keys as the reference's gsplat/rendering.py:44-598.
+`GSPLAT_BACKEND=b200` (default here) selects the sm_100a CUDA kernels of `gsplat.b200_impl`;
+`triton` / `cuda` import the reference's own backends when they are importable (parity runs
+with GSPLAT_REFERENCE_PATH set, see gsplat/__init__.py). Unknown names raise ValueError like
+rendering.py:28-29.
+"""
+import math
+import os
+from typing import Dict, Optional, Tuple
+
+import torch
+from torch import Tensor
+from typing_extensions import Literal
+
+BACKEND = os.environ.get("GSPLAT_BACKEND", "b200")
+if BACKEND == "b200":
+    from .b200_impl._wrapper import (
+        fully_fused_projection,
+        isect_offset_encode,
+        isect_tiles,
+        rasterize_to_pixels,
+        spherical_harmonics,
+    )
+elif BACKEND == "cuda":
+    from .cuda._wrapper import (  # type: ignore  # reference backend via GSPLAT_REFERENCE_PATH
+        fully_fused_projection,
+        isect_offset_encode,
+        isect_tiles,
+        rasterize_to_pixels,
+        spherical_harmonics,
+    )
+elif BACKEND == "triton":
+    from .triton_impl._wrapper import (  # type: ignore  # reference backend via GSPLAT_REFERENCE_PATH
+        fully_fused_projection,
+        isect_offset_encode,
+        isect_tiles,
+        rasterize_to_pixels,
+        spherical_harmonics,
+    )
+else:
+    raise ValueError(f"Unknown GSPLAT_BACKEND: {BACKEND}")
+
+from .distributed import (
+    all_gather_int32,
+    all_gather_tensor_list,
+    all_to_all_int32,
+    all_to_all_rows,
+    all_to_all_tensor_list,
+    interleave_camera_major,
+    pack_rows,
+    unpack_rows,
+)
+
+_RENDER_MODES = ("RGB", "D", "ED", "RGB+D", "RGB+ED")
+
+
+def rasterization(
+    means: Tensor,  # [N, 3]
+    quats: Tensor,  # [N, 4]
+    scales: Tensor,  # [N, 3]
+    opacities: Tensor,  # [N]
+    colors: Tensor,  # [(C,) N, D] or [(C,) N, K, 3]
+    viewmats: Tensor,  # [C, 4, 4]
+    Ks: Tensor,  # [C, 3, 3]
+    width: int,
+    height: int,
+    near_plane: float = 0.01,
+    far_plane: float = 1e10,
+    radius_clip: float = 0.0,
+    eps2d: float = 0.3,
+    sh_degree: Optional[int] = None,
+    packed: bool = True,
+    tile_size: int = 16,
+    backgrounds: Optional[Tensor] = None,
+    render_mode: Literal["RGB", "D", "ED", "RGB+D", "RGB+ED"] = "RGB",
+    sparse_grad: bool = False,
+    absgrad: bool = False,
+    rasterize_mode: Literal["classic", "antialiased"] = "classic",
+    channel_chunk: int = 32,
+    distributed: bool = False,
+    camera_model: Literal["pinhole", "ortho", "fisheye"] = "pinhole",
+    covars: Optional[Tensor] = None,
+) -> Tuple[Tensor, Tensor, Dict]:
+    """Rasterizes N 3D Gaussians to C image planes; differentiable w.r.t. the Gaussian parameters.
+
+    Returns `(render_colors [C,H,W,X], render_alphas [C,H,W,1], meta)`; X is D, 1 (depth modes)
+    or D+1 ("RGB+D"/"RGB+ED"). `meta` carries the intermediate tensors the training strategies
+    read (`means2d` is a live autograd intermediate: `.retain_grad()`, `.absgrad`).
+    See the reference docstring (rendering.py:70-239) for the argument semantics; they are kept.
+    """
+    meta: Dict = {}
+    N = means.shape[0]
+    C = viewmats.shape[0]
+    device = means.device
+    assert means.shape == (N, 3), means.shape
+    if covars is None:
+        assert quats.shape == (N, 4), quats.shape
+        assert scales.shape == (N, 3), scales.shape
+    else:
+        assert covars.shape == (N, 3, 3), covars.shape
+        quats, scales = None, None
+        rows, cols = (0, 0, 0, 1, 1, 2), (0, 1, 2, 1, 2, 2)
+        covars = covars[..., rows, cols]  # upper triangle, [N, 6]
+    assert opacities.shape == (N,), opacities.shape
+    assert viewmats.shape == (C, 4, 4), viewmats.shape
+    assert Ks.shape == (C, 3, 3), Ks.shape
+    assert render_mode in _RENDER_MODES, render_mode
+
+    if sh_degree is None:
+        # post-activation colours [N, D] or [C, N, D]
+        assert (colors.dim() == 2 and colors.shape[0] == N) or (
+            colors.dim() == 3 and colors.shape[:2] == (C, N)
+        ), colors.shape
+        if distributed:
+            assert colors.dim() == 2, "Distributed mode only supports per-Gaussian colors."
+    else:
+        # SH coefficients [N, K, 3] or [C, N, K, 3]
+        assert (colors.dim() == 3 and colors.shape[0] == N and colors.shape[2] == 3) or (
+            colors.dim() == 4 and colors.shape[:2] == (C, N) and colors.shape[3] == 3
+        ), colors.shape
+        assert (sh_degree + 1) ** 2 <= colors.shape[-2], colors.shape
+        if distributed:
+            assert colors.dim() == 3, "Distributed mode only supports per-Gaussian colors."
+    if absgrad:
+        assert not distributed, "AbsGrad is not supported in distributed mode."
+
+    # Distributed: Gaussians are sharded over ranks for projection, cameras for compositing.
+    if distributed:
+        world_rank = torch.distributed.get_rank()
+        world_size = torch.distributed.get_world_size()
+        N_world = all_gather_int32(world_size, N, device=device)
+        C_world = [C] * world_size  # every rank must bring the same number of cameras
+        viewmats, Ks = all_gather_tensor_list(world_size, [viewmats, Ks])
+        C = len(viewmats)  # global camera count from here on
+
+    proj_results = fully_fused_projection(
+        means, covars, quats, scales, viewmats, Ks, width, height,
+        eps2d=eps2d, packed=packed, near_plane=near_plane, far_plane=far_plane, radius_clip=radius_clip,
+        sparse_grad=sparse_grad, calc_compensations=(rasterize_mode == "antialiased"),
+        camera_model=camera_model,
+    )
+    if packed:
+        camera_ids, gaussian_ids, radii, means2d, depths, conics, compensations = proj_results
+        opacities = opacities[gaussian_ids]  # [nnz]
+    else:
+        radii, means2d, depths, conics, compensations = proj_results
+        opacities = opacities.repeat(C, 1)  # [C, N]
+        camera_ids, gaussian_ids = None, None
+    if compensations is not None:
+        opacities = opacities * compensations
+
+    meta.update({
+        "camera_ids": camera_ids,  # global camera ids
+        "gaussian_ids": gaussian_ids,  # local Gaussian ids
+        "radii": radii,
+        "means2d": means2d,
+        "depths": depths,
+        "conics": conics,
+        "opacities": opacities,
+    })
+
+    # Colours -> [C, N, D] or [nnz, D]
+    if sh_degree is None:
+        if packed:
+            colors = colors[gaussian_ids] if colors.dim() == 2 else colors[camera_ids, gaussian_ids]
+        elif colors.dim() == 2:
+            colors = colors.expand(C, -1, -1)
+    else:
+        camtoworlds = torch.inverse(viewmats)
+        if packed:
+            dirs = means[gaussian_ids, :] - camtoworlds[camera_ids, :3, 3]  # [nnz, 3]
+            shs = colors[gaussian_ids, :, :] if colors.dim() == 3 else colors[camera_ids, gaussian_ids, :, :]
+            colors = spherical_harmonics(sh_degree, dirs, shs, masks=radii > 0)  # [nnz, 3]
+        else:
+            dirs = means[None, :, :] - camtoworlds[:, None, :3, 3]  # [C, N, 3]
+            if BACKEND == "b200" or colors.dim() == 4:
+                shs = colors  # b200 broadcasts [N,K,3] over cameras inside the kernel
+            else:
+                shs = colors.expand(C, -1, -1, -1)
+            colors = spherical_harmonics(sh_degree, dirs, shs, masks=radii > 0)  # [C, N, 3]
+        colors = torch.clamp_min(colors + 0.5, 0.0)  # as rendering.py:408
+
+    # Distributed: hand every projected Gaussian to the rank that owns its camera.
+    if distributed:
+        D = colors.shape[-1]
+        if packed:
+            cnts = torch.bincount(camera_ids, minlength=C).split(C_world, dim=0)
+            cnts = [int(c.sum().item()) for c in cnts]
+            recv = all_to_all_int32(world_size, cnts, device=device)
+            rows = pack_rows(means2d, depths, conics, opacities, colors, radii)
+            rows = all_to_all_rows(rows, cnts, recv)
+            means2d, depths, conics, opacities, colors, radii = unpack_rows(rows, D)
+            # camera ids global -> local to the destination; Gaussian ids local -> global
+            cnts_t = torch.tensor(cnts, device=device)
+            cam_base = torch.tensor([sum(C_world[:i]) for i in range(world_size)], device=device)
+            gau_base = sum(N_world[:world_rank])
+            ids = torch.stack([camera_ids - cam_base.repeat_interleave(cnts_t), gaussian_ids + gau_base], dim=-1)
+            ids = all_to_all_rows(ids, cnts, recv)
+            camera_ids, gaussian_ids = ids[:, 0].contiguous(), ids[:, 1].contiguous()
+            C = C_world[world_rank]
+        else:
+            C = C_world[world_rank]
+            rows = pack_rows(means2d.flatten(0, 1), depths.flatten(0, 1), conics.flatten(0, 1),
+                             opacities.flatten(0, 1), colors.flatten(0, 1), radii.flatten(0, 1))
+            rows = all_to_all_rows(rows, [C_i * N for C_i in C_world], [C * N_i for N_i in N_world])
+            rows = interleave_camera_major(rows, C, N_world)  # [C, N_total, 8+D]
+            N_total = rows.shape[1]
+            means2d, depths, conics, opacities, colors, radii = unpack_rows(rows.reshape(C * N_total, -1), D)
+            means2d, conics, colors = (t.reshape(C, N_total, -1) for t in (means2d, conics, colors))
+            depths, opacities, radii = (t.reshape(C, N_total) for t in (depths, opacities, radii))
+
+    if render_mode in ("RGB+D", "RGB+ED"):
+        colors = torch.cat((colors, depths[..., None]), dim=-1)
+        if backgrounds is not None:
+            backgrounds = torch.cat([backgrounds, torch.zeros(C, 1, device=backgrounds.device)], dim=-1)
+    elif render_mode in ("D", "ED"):
+        colors = depths[..., None]
+        if backgrounds is not None:
+            backgrounds = torch.zeros(C, 1, device=backgrounds.device)
+
+    # Tile intersection, sort, per-tile ranges
+    tile_width = math.ceil(width / float(tile_size))
+    tile_height = math.ceil(height / float(tile_size))
+    tiles_per_gauss, isect_ids, flatten_ids = isect_tiles(
+        means2d, radii, depths, tile_size, tile_width, tile_height,
+        packed=packed, n_cameras=C, camera_ids=camera_ids, gaussian_ids=gaussian_ids,
+    )
+    isect_offsets = isect_offset_encode(isect_ids, C, tile_width, tile_height)
+    meta.update({
+        "tile_width": tile_width,
+        "tile_height": tile_height,
+        "tiles_per_gauss": tiles_per_gauss,
+        "isect_ids": isect_ids,
+        "flatten_ids": flatten_ids,
+        "isect_offsets": isect_offsets,
+        "width": width,
+        "height": height,
+        "tile_size": tile_size,
+        "n_cameras": C,
+    })
+
+    # Composite
+    def composite(colors_c, backgrounds_c):
+        return rasterize_to_pixels(
+            means2d, conics, colors_c, opacities, width, height, tile_size, isect_offsets, flatten_ids,
+            backgrounds=backgrounds_c, packed=packed, absgrad=absgrad,
+        )
+
+    if colors.shape[-1] > channel_chunk:
+        chunks, render_alphas = [], None
+        for lo in range(0, colors.shape[-1], channel_chunk):
+            bg = backgrounds[..., lo:lo + channel_chunk] if backgrounds is not None else None
+            rc, ra = composite(colors[..., lo:lo + channel_chunk], bg)
+            chunks.append(rc)
+            render_alphas = ra if render_alphas is None else render_alphas
+        render_colors = torch.cat(chunks, dim=-1)
+    else:
+        render_colors, render_alphas = composite(colors, backgrounds)
+
+    if render_mode in ("ED", "RGB+ED"):
+        render_colors = torch.cat(
+            [render_colors[..., :-1], render_colors[..., -1:] / render_alphas.clamp(min=1e-10)], dim=-1
+        )
+    return render_colors, render_alphas, meta

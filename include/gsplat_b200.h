@@ -1,0 +1,158 @@
+/* gsplat_b200.h — C ABI of the B200 (sm_100a) backend for gsplat's rasterization() hot path.
+ *
+ * This is the drop-in boundary: the Python wrappers in gsplat/b200_impl/_wrapper.py bind these
+ * symbols with ctypes exactly where the reference binds its own kernels
+ *   - gsplat/triton_impl/_wrapper.py (Triton launchers) and
+ *   - gsplat/cuda/csrc/ext.cpp:31-56 (pybind `_C` op list of the `cuda` backend).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in `_host`;
+ *   - the caller owns every buffer (outputs, scratch, sort temp): nothing here allocates;
+ *   - all floating tensors are contiguous float32, ids int32/int64 as noted;
+ *   - `stream` is the CUDA stream to launch on (torch.cuda.current_stream().cuda_stream);
+ *   - return value: GSB_OK (0) or a negative error code; gsb_last_error() gives the text.
+ *   - no host synchronisation happens inside any entry point.
+ */
+#ifndef GSPLAT_B200_H
+#define GSPLAT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef __CUDA_RUNTIME_H__
+typedef struct CUstream_st *cudaStream_t;
+#endif
+
+#define GSB_OK 0
+#define GSB_ERR_INVALID (-1)
+#define GSB_ERR_CUDA (-2)
+#define GSB_ERR_UNSUPPORTED (-3)
+
+#define GSB_CAMERA_PINHOLE 0
+#define GSB_CAMERA_ORTHO 1
+
+/* library identity / diagnostics */
+const char *gsb_last_error(void);
+int gsb_abi_version(void);
+/* number of kernels launched by this library since load (or since gsb_reset_launch_count) */
+int64_t gsb_launch_count(void);
+void gsb_reset_launch_count(void);
+
+/* ---- fully_fused_projection ------------------------------------------------------------------
+ * replaces triton_impl/fused_projection_fwd.py:232-300 (launcher) / :18-228 (kernel) and
+ * cuda/csrc/ProjectionEWA3DGSFused.cu:16-260. means[N,3]; covars[N,6] (triu) or NULL;
+ * quats[N,4] wxyz, scales[N,3] (used when covars==NULL); viewmats[C,16]; Ks[C,9].
+ * outputs: radii int32[C,N], means2d[C,N,2], depths[C,N], conics[C,N,3], compensations[C,N] or NULL.
+ * slots with radii==0 get zeros in means2d/conics/compensations (depths always written). */
+int gsb_projection_fwd(int C, int N, const float *means, const float *covars, const float *quats,
+                       const float *scales, const float *viewmats, const float *Ks, int width, int height,
+                       float eps2d, float near_plane, float far_plane, float radius_clip, int camera_model,
+                       int32_t *radii, float *means2d, float *depths, float *conics, float *compensations,
+                       cudaStream_t stream);
+
+/* replaces triton_impl/fused_projection_bwd.py:367-450 / :26-363 and ProjectionEWA3DGSFused.cu:266-500.
+ * Any of v_means/v_covars/v_quats/v_scales/v_viewmats may be NULL (not needed). Outputs are
+ * fully written (no pre-zeroing needed; v_viewmats is zeroed internally). */
+int gsb_projection_bwd(int C, int N, const float *means, const float *covars, const float *quats,
+                       const float *scales, const float *viewmats, const float *Ks, int width, int height,
+                       float eps2d, int camera_model, const int32_t *radii, const float *conics,
+                       const float *compensations, const float *v_means2d, const float *v_depths,
+                       const float *v_conics, const float *v_compensations, float *v_means, float *v_covars,
+                       float *v_quats, float *v_scales, float *v_viewmats, cudaStream_t stream);
+
+/* packed (COO) projection: replaces cuda/csrc/ProjectionEWA3DGSPacked.cu:17-233 and
+ * Projection.cpp:254-395. Two passes around a caller-side scan of block_counts
+ * (gsb_scan_i32_to_i64): block_counts int32[C * ceil(N/256)], camera-major. Row order of
+ * the outputs is row-major (camera, then Gaussian). camera_ids/gaussian_ids are int64. */
+int gsb_projection_packed_count(int C, int N, const float *means, const float *covars, const float *quats,
+                                const float *scales, const float *viewmats, const float *Ks, int width,
+                                int height, float eps2d, float near_plane, float far_plane, float radius_clip,
+                                int camera_model, int32_t *block_counts, cudaStream_t stream);
+int gsb_projection_packed_write(int C, int N, const float *means, const float *covars, const float *quats,
+                                const float *scales, const float *viewmats, const float *Ks, int width,
+                                int height, float eps2d, float near_plane, float far_plane, float radius_clip,
+                                int camera_model, const int64_t *block_offsets, int64_t *camera_ids,
+                                int64_t *gaussian_ids, int32_t *radii, float *means2d, float *depths,
+                                float *conics, float *compensations, cudaStream_t stream);
+/* replaces ProjectionEWA3DGSPacked.cu:349-560. dense: acc is a float[N,9] scratch and the
+ * outputs are [N,*]; sparse_grad: outputs are per-row [nnz,*] (COO values), acc unused. */
+int gsb_projection_packed_bwd(int C, int N, int64_t nnz, const float *means, const float *covars,
+                              const float *quats, const float *scales, const float *viewmats, const float *Ks,
+                              int width, int height, float eps2d, int camera_model, const int64_t *camera_ids,
+                              const int64_t *gaussian_ids, const float *conics, const float *compensations,
+                              const float *v_means2d, const float *v_depths, const float *v_conics,
+                              const float *v_compensations, int sparse_grad, float *acc, float *v_means,
+                              float *v_covars, float *v_quats, float *v_scales, float *v_viewmats,
+                              cudaStream_t stream);
+
+/* ---- spherical_harmonics ----------------------------------------------------------------------
+ * replaces triton_impl/sh_fwd.py:194-230 / sh_bwd.py:383-430 and SphericalHarmonicsCUDA.cu:374/448.
+ * dirs[n_batch, n_rows, 3], masks uint8[n_batch, n_rows] or NULL, colors[n_batch, n_rows, 3];
+ * coeffs[n_rows, K, 3] is shared by all n_batch entries (the stride-0 camera broadcast of
+ * rendering.py:402); per-view coefficients are passed as n_batch=1, n_rows=C*N.
+ * Masked-out entries produce 0. */
+int gsb_sh_fwd(int degree, int64_t n_rows, int n_batch, int K, const float *dirs, const float *coeffs,
+               const uint8_t *masks, float *colors, cudaStream_t stream);
+/* v_coeffs[n_rows,K,3] fully written (sum over the batch); v_dirs[n_batch,n_rows,3] or NULL. */
+int gsb_sh_bwd(int degree, int64_t n_rows, int n_batch, int K, const float *dirs, const float *coeffs,
+               const uint8_t *masks, const float *v_colors, float *v_coeffs, float *v_dirs,
+               cudaStream_t stream);
+
+/* ---- isect_tiles / isect_offset_encode --------------------------------------------------------
+ * replaces triton_impl/isect_tiles.py:14-133, radix_sort/radix_sort.cu:10-62, isect_offset.py:9-63
+ * and cuda/csrc/IntersectTile.cu:24-344. P = C*N (unpacked) or nnz (packed). */
+int64_t gsb_isect_num_blocks(int64_t P); /* rows of block_sums / block_offsets */
+int gsb_isect_count(int64_t P, const float *means2d, const int32_t *radii, int tile_size, int tile_width,
+                    int tile_height, int32_t *tiles_per_gauss, int32_t *block_sums, int64_t *block_offsets,
+                    int64_t *n_isects_out, cudaStream_t stream);
+int gsb_scan_i32_to_i64(int64_t n, const int32_t *in, int64_t *out, int64_t *total_out, cudaStream_t stream);
+int gsb_isect_emit(int64_t P, int N, int packed, const float *means2d, const int32_t *radii,
+                   const float *depths, const int64_t *camera_ids, int tile_size, int tile_width,
+                   int tile_height, int tile_n_bits, const int32_t *tiles_per_gauss,
+                   const int64_t *block_offsets, int64_t *isect_ids, int32_t *flatten_ids, cudaStream_t stream);
+int64_t gsb_sort_pairs_temp_bytes(int64_t n);
+int gsb_sort_pairs(int64_t n, int end_bit, int64_t *keys, int64_t *keys_alt, int32_t *vals, int32_t *vals_alt,
+                   void *temp, int64_t temp_bytes, int *result_in_alt_host, cudaStream_t stream);
+int gsb_isect_offsets(int64_t n_isects, const int64_t *isect_ids, int C, int tile_width, int tile_height,
+                      int tile_n_bits, int32_t *offsets, cudaStream_t stream);
+
+/* ---- rasterize_to_pixels ----------------------------------------------------------------------
+ * replaces triton_impl/rasterize_to_pixels_fwd.py:200-275 / :21-196, rasterize_to_pixels_bwd.py:341-430
+ * / :21-337 and cuda/csrc/RasterizeToPixels3DGSFwd.cu:18-188, RasterizeToPixels3DGSBwd.cu:16-278.
+ * P rows of projected Gaussians (C*N or nnz); D colour channels, D in {1,2,3,4,8,16,32}
+ * (the Python wrapper zero-pads other widths like the reference does); tile_size must be 16.
+ * gsb_rasterize_pack builds the 2 x float4 splat records the compositor gathers. */
+int gsb_rasterize_pack(int64_t P, const float *means2d, const float *conics, const float *opacities,
+                       float *recA, float *recB, cudaStream_t stream);
+/* backgrounds[C,D] or NULL; masks uint8[C,th,tw] or NULL (true = render, false = background only);
+ * outputs render_colors[C,H,W,D], render_alphas[C,H,W], last_ids int32[C,H,W]. */
+int gsb_rasterize_fwd(int C, int64_t n_isects, int D, const float *recA, const float *recB, const float *colors,
+                      const float *backgrounds, const uint8_t *masks, int width, int height, int tile_size,
+                      int tile_width, int tile_height, const int32_t *isect_offsets, const int32_t *flatten_ids,
+                      float *render_colors, float *render_alphas, int32_t *last_ids, cudaStream_t stream);
+/* v_means2d[P,2], v_conics[P,3], v_colors[P,D], v_opacities[P] must be ZERO-filled by the caller
+ * (the kernel accumulates with atomics); v_means2d_abs[P,2] (zero-filled) or NULL. */
+int gsb_rasterize_bwd(int C, int64_t n_isects, int D, const float *recA, const float *recB, const float *colors,
+                      const float *backgrounds, const uint8_t *masks, int width, int height, int tile_size,
+                      int tile_width, int tile_height, const int32_t *isect_offsets, const int32_t *flatten_ids,
+                      const float *render_alphas, const int32_t *last_ids, const float *v_render_colors,
+                      const float *v_render_alphas, float *v_means2d_abs, float *v_means2d, float *v_conics,
+                      float *v_colors, float *v_opacities, cudaStream_t stream);
+
+/* ---- distributed exchange rows (rendering.py:413-494, distributed.py:170-257) -----------------
+ * One fused row per projected Gaussian: means2d(2) depths(1) conics(3) opacities(1) colors(D)
+ * radii(1, int32 bit pattern) = (8+D) 4-byte words, so a single all-to-all per direction
+ * replaces the reference's cat/split + separate int32 exchange. */
+int gsb_a2a_pack(int64_t rows, int D, const float *means2d, const float *depths, const float *conics,
+                 const float *opacities, const float *colors, const int32_t *radii, float *packed,
+                 cudaStream_t stream);
+int gsb_a2a_unpack(int64_t rows, int D, const float *packed, float *means2d, float *depths, float *conics,
+                   float *opacities, float *colors, int32_t *radii, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSPLAT_B200_H */
