@@ -1,0 +1,266 @@
+"""Pins oracle/gs_oracle.py against the reference's OWN CPU code and freezes golden vectors.
+
+TEST INFRASTRUCTURE. Run in the build container only (needs /root/reference, read-only):
+
+    python oracle/make_golden.py            # writes tests/golden/*.npz, asserts oracle == reference
+
+What runs here is the reference's `gsplat/cuda/_torch_impl.py` itself (imported from
+/root/reference): `_quat_scale_to_covar_preci`, `_fully_fused_projection`, `_spherical_harmonics`,
+`_isect_tiles`, `_isect_offset_encode` and `_rasterize_to_pixels` + `accumulate`. The last two
+need (i) the third-party package `nerfacc` (absent, un-vendored) and (ii) the CUDA-only op
+`rasterize_to_indices_in_range`. Both are replaced by the small restatements below
+(`_nerfacc_stub`, `_indices_in_range_cpu`, following RasterizeToIndices3DGS.cu:14-170), so the
+reference's compositor math (`accumulate`, `_rasterize_to_pixels`) executes unmodified on top
+of them. The outputs are stored as the golden vectors the `-m "not gpu"` tests check the oracle
+against and the `-m gpu` tests check the CUDA kernels against.
+"""
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+REF = os.environ.get("GSPLAT_REFERENCE_PATH", "/root/reference")
+GOLD = os.path.join(ROOT, "tests", "golden")
+sys.path.insert(0, HERE)
+sys.path.insert(0, REF)
+
+import gs_oracle as O  # noqa: E402
+
+
+# ---------------------------------------------------------------------------------------------
+# restated third-party / CUDA-only pieces the reference's torch compositor sits on
+# ---------------------------------------------------------------------------------------------
+def _segment_layout(ray_indices, n_rays):
+    """ray_indices must be grouped (ascending); returns (start[n_rays], pos[M], maxlen)."""
+    counts = torch.bincount(ray_indices, minlength=n_rays)
+    start = torch.cumsum(counts, 0) - counts
+    pos = torch.arange(ray_indices.numel()) - start[ray_indices]
+    return counts, pos, int(counts.max().item()) if counts.numel() else 0
+
+
+def _render_weight_from_alpha(alphas, ray_indices=None, n_rays=None, **_):
+    """nerfacc.render_weight_from_alpha: w_i = alpha_i * prod_{j<i, same ray}(1 - alpha_j)."""
+    _, pos, maxlen = _segment_layout(ray_indices, n_rays)
+    dense = torch.ones((n_rays, maxlen + 1), dtype=alphas.dtype)
+    dense = dense.index_put((ray_indices, pos + 1), 1.0 - alphas)
+    trans = torch.cumprod(dense, dim=1)[ray_indices, pos]  # exclusive product
+    return alphas * trans, trans
+
+
+def _accumulate_along_rays(weights, values=None, ray_indices=None, n_rays=None):
+    """nerfacc.accumulate_along_rays: segmented sum of weights (* values)."""
+    src = weights[:, None] if values is None else weights[:, None] * values
+    out = torch.zeros((n_rays, src.shape[-1]), dtype=src.dtype)
+    return out.index_add(0, ray_indices, src)
+
+
+def _install_nerfacc_stub():
+    m = types.ModuleType("nerfacc")
+    m.render_weight_from_alpha = _render_weight_from_alpha
+    m.accumulate_along_rays = _accumulate_along_rays
+    sys.modules["nerfacc"] = m
+
+
+@torch.no_grad()
+def _indices_in_range_cpu(range_start, range_end, transmittances, means2d, conics, opacities, image_width,
+                          image_height, tile_size, isect_offsets, flatten_ids):
+    """RasterizeToIndices3DGS.cu:14-170 on the CPU, one pixel at a time (grouped by camera, pixel)."""
+    C, N, _ = means2d.shape
+    th, tw = isect_offsets.shape[1:]
+    n_isects = flatten_ids.numel()
+    offs = torch.cat([isect_offsets.flatten().long(), torch.tensor([n_isects])]).numpy()
+    fid = flatten_ids.long().numpy()
+    m = means2d.reshape(-1, 2).numpy()
+    cn = conics.reshape(-1, 3).numpy()
+    op = opacities.reshape(-1).numpy()
+    block = tile_size * tile_size
+    gs, px, cam = [], [], []
+    for c in range(C):
+        for i in range(image_height):
+            for j in range(image_width):
+                t = (c * th + i // tile_size) * tw + j // tile_size
+                lo, hi = int(offs[t]), int(offs[t + 1])
+                lo2 = lo + block * range_start
+                hi2 = min(hi, lo + block * range_end)
+                if lo2 >= hi2:
+                    continue
+                g = fid[lo2:hi2]
+                dx = m[g, 0] - np.float32(j + 0.5)
+                dy = m[g, 1] - np.float32(i + 0.5)
+                sigma = np.float32(0.5) * (cn[g, 0] * dx * dx + cn[g, 2] * dy * dy) + cn[g, 1] * dx * dy
+                alpha = np.minimum(np.float32(0.999), op[g] * np.exp(-sigma))
+                T = np.float32(transmittances[c, i, j].item())
+                for k in range(g.shape[0]):
+                    if sigma[k] < 0 or alpha[k] < np.float32(1.0 / 255.0):
+                        continue
+                    nT = T * (np.float32(1.0) - alpha[k])
+                    if nT <= np.float32(1e-4):
+                        break
+                    gs.append(int(g[k]) % N)
+                    px.append(i * image_width + j)
+                    cam.append(c)
+                    T = nT
+    return (torch.tensor(gs, dtype=torch.long), torch.tensor(px, dtype=torch.long),
+            torch.tensor(cam, dtype=torch.long))
+
+
+def _close(a, b, rtol=1e-4, atol=1e-4, what=""):
+    torch.testing.assert_close(a, b, rtol=rtol, atol=atol, msg=lambda m: f"{what}: {m}")
+
+
+def _np(**kw):
+    return {k: (v.detach().numpy() if torch.is_tensor(v) else np.asarray(v)) for k, v in kw.items() if v is not None}
+
+
+# ---------------------------------------------------------------------------------------------
+# cases
+# ---------------------------------------------------------------------------------------------
+def case_projection(T):
+    """Garden fixture (every 40th point), 3 cameras: reference _fully_fused_projection fwd + autograd grads."""
+    from gsplat._helper import load_test_data
+
+    torch.manual_seed(42)
+    means, quats, scales, opacities, colors, viewmats, Ks, W, H = load_test_data(device="cpu")
+    sel = slice(0, None, 40)
+    means, quats, scales, opacities, colors = means[sel], quats[sel], scales[sel], opacities[sel], colors[sel]
+    scales = scales * 3.0 + 0.002  # a wider radius spread than the fixture's U[0, 0.02)
+    out = {}
+    for name, eps2d, comp, model in (("pinhole", 0.3, True, "pinhole"), ("ortho", 0.3, True, "ortho")):
+        p = [t.clone().requires_grad_(True) for t in (means, quats, scales, viewmats)]
+        covars, _ = T._quat_scale_to_covar_preci(p[1], p[2], True, False, triu=False)
+        radii, means2d, depths, conics, comps = T._fully_fused_projection(
+            p[0], covars, p[3], Ks, W, H, eps2d=eps2d, calc_compensations=comp, camera_model=model)
+        o_radii, o_means2d, o_depths, o_conics, o_comps = O.fully_fused_projection(
+            means, O.quat_scale_to_covar(quats, scales), viewmats, Ks, W, H, eps2d=eps2d, calc_compensations=comp,
+            camera_model=model)
+        assert torch.equal(radii, o_radii), f"{name}: oracle radii differ from reference"
+        sel_v = radii > 0
+        _close(o_means2d[sel_v], means2d[sel_v], what=name + " means2d")
+        _close(o_depths[sel_v], depths[sel_v], what=name + " depths")
+        _close(o_conics[sel_v], conics[sel_v], what=name + " conics")
+        _close(o_comps[sel_v], comps[sel_v], what=name + " comps")
+        g = torch.Generator().manual_seed(7)
+        w2, wd, wc, wp = (torch.randn(t.shape, generator=g) for t in (means2d, depths, conics, comps))
+        mask = sel_v.float()
+        loss = ((means2d * w2 * 1e-2).sum(-1) * mask + depths * wd * mask + (conics * wc).sum(-1) * mask
+                + comps * wp * mask).sum()
+        grads = torch.autograd.grad(loss, p)
+        out.update(_np(**{
+            f"{name}_radii": radii, f"{name}_means2d": means2d, f"{name}_depths": depths, f"{name}_conics": conics,
+            f"{name}_comps": comps, f"{name}_w_means2d": w2 * 1e-2, f"{name}_w_depths": wd, f"{name}_w_conics": wc,
+            f"{name}_w_comps": wp, f"{name}_v_means": grads[0], f"{name}_v_quats": grads[1],
+            f"{name}_v_scales": grads[2], f"{name}_v_viewmats": grads[3]}))
+    out.update(_np(means=means, quats=quats, scales=scales, opacities=opacities, colors=colors, viewmats=viewmats,
+                   Ks=Ks, width=W, height=H))
+    np.savez_compressed(os.path.join(GOLD, "projection.npz"), **out)
+    print("projection: N=%d visible=%d" % (means.shape[0], int((out["pinhole_radii"] > 0).sum())))
+    return out
+
+
+def case_sh(T):
+    """triton_tests/test_sh.py protocol (seed 43), degrees 0-4: reference _spherical_harmonics fwd + grads."""
+    torch.manual_seed(43)
+    n = 257
+    dirs = torch.randn(n, 3)
+    coeffs = torch.randn(n, 25, 3)
+    w = torch.randn(n, 3)
+    out = _np(dirs=dirs, coeffs=coeffs, w=w)
+    for deg in range(5):
+        d = dirs.clone().requires_grad_(True)
+        c = coeffs.clone().requires_grad_(True)
+        col = T._spherical_harmonics(deg, d, c)
+        _close(O.spherical_harmonics(deg, dirs, coeffs), col, what=f"sh deg {deg}")
+        vd, vc = torch.autograd.grad((col * w).sum(), (d, c), allow_unused=True)
+        out.update(_np(**{f"colors_{deg}": col, f"v_dirs_{deg}": vd if vd is not None else torch.zeros_like(dirs),
+                          f"v_coeffs_{deg}": vc}))
+    np.savez_compressed(os.path.join(GOLD, "sh.npz"), **out)
+    print("sh: ok")
+
+
+def case_isect(T, proj):
+    """Reference _isect_tiles / _isect_offset_encode on the projection golden (cuda/torch tile-bit rule)."""
+    means2d = torch.from_numpy(proj["pinhole_means2d"])
+    radii = torch.from_numpy(proj["pinhole_radii"])
+    depths = torch.from_numpy(proj["pinhole_depths"])
+    W, H = int(proj["width"]), int(proj["height"])
+    ts = 16
+    tw, th = -(-W // ts), -(-H // ts)
+    tpg, ids, flat = T._isect_tiles(means2d, radii, depths, ts, tw, th, sort=True)
+    offs = T._isect_offset_encode(ids, means2d.shape[0], tw, th)
+    # torch.sort is not stable: canonicalise ties (equal keys) by ascending flatten id, which is
+    # what a stable sort of the emission order gives (CUB radix sort, IntersectTile.cu:288-344)
+    order = np.lexsort((flat.numpy(), ids.numpy()))
+    ids, flat = ids[order], flat[order]
+    o_tpg, o_ids, o_flat = O.isect_tiles(means2d, radii, depths, ts, tw, th, bits_rule="cuda")
+    o_offs = O.isect_offset_encode(o_ids, means2d.shape[0], tw, th, bits_rule="cuda")
+    assert torch.equal(tpg, o_tpg) and torch.equal(ids, o_ids) and torch.equal(flat, o_flat), "isect_tiles"
+    assert torch.equal(offs, o_offs), "isect_offset_encode"
+    # the literal known-answer vector of the reference docstring (isect_offset.py:17-20)
+    doc = O.isect_offset_encode(torch.tensor([1, 1, 1, 3, 3, 5, 5], dtype=torch.int64) << 32, 1, 7, 1)
+    assert doc.flatten().tolist() == [0, 0, 3, 3, 5, 5, 7], doc
+    np.savez_compressed(os.path.join(GOLD, "isect.npz"), **_np(
+        tiles_per_gauss=tpg, isect_ids=ids, flatten_ids=flat, offsets=offs, tile_size=ts, tile_width=tw,
+        tile_height=th))
+    print("isect: n_isects=%d" % ids.numel())
+
+
+def case_raster(T):
+    """Reference _rasterize_to_pixels (+accumulate) on a small synthetic scene, fwd + autograd grads."""
+    import gsplat.cuda._wrapper as W_
+
+    _install_nerfacc_stub()
+    W_.rasterize_to_indices_in_range = _indices_in_range_cpu
+    g = torch.Generator().manual_seed(50)
+    C, N, Wd, Ht, ts, D = 2, 400, 56, 40, 16, 3
+    means2d = torch.rand(C, N, 2, generator=g) * torch.tensor([Wd + 8.0, Ht + 8.0]) - 4.0
+    s = torch.exp(torch.rand(C, N, 2, generator=g) * 2.0 - 0.2)  # std-dev 0.8 .. 6 px
+    rho = torch.rand(C, N, generator=g) * 1.6 - 0.8
+    cxx, cyy, cxy = s[..., 0] ** 2, s[..., 1] ** 2, rho * s[..., 0] * s[..., 1]
+    det = cxx * cyy - cxy * cxy
+    conics = torch.stack([cyy / det, -cxy / det, cxx / det], dim=-1)
+    radii = torch.ceil(3.0 * torch.sqrt(torch.maximum(cxx, cyy))).int()
+    depths = torch.rand(C, N, generator=g) * 9.0 + 1.0
+    opacities = torch.rand(C, N, generator=g) * 0.98 + 0.01
+    opacities[:, ::7] = 1.0  # exercise the 0.999 alpha clamp
+    colors = torch.rand(C, N, D, generator=g)
+    backgrounds = torch.rand(C, D, generator=g)
+    tw, th = -(-Wd // ts), -(-Ht // ts)
+    _, ids, flat = O.isect_tiles(means2d, radii, depths, ts, tw, th)
+    offs = O.isect_offset_encode(ids, C, tw, th)
+    p = [t.clone().requires_grad_(True) for t in (means2d, conics, colors, opacities, backgrounds)]
+    rc, ra = T._rasterize_to_pixels(p[0], p[1], p[2], p[3], Wd, Ht, ts, offs, flat, backgrounds=p[4])
+    w_c = torch.randn(rc.shape, generator=g)
+    w_a = torch.randn(ra.shape, generator=g)
+    grads = torch.autograd.grad((rc * w_c).sum() + (ra * w_a).sum(), p)
+    q = [t.clone().requires_grad_(True) for t in (means2d, conics, colors, opacities, backgrounds)]
+    o_rc, o_ra = O.rasterize_to_pixels(q[0], q[1], q[2], q[3], Wd, Ht, ts, offs, flat, backgrounds=q[4])
+    o_grads = torch.autograd.grad((o_rc * w_c).sum() + (o_ra * w_a).sum(), q)
+    _close(o_rc, rc, what="render_colors")
+    _close(o_ra, ra, what="render_alphas")
+    for name, a, b in zip(("v_means2d", "v_conics", "v_colors", "v_opacities", "v_backgrounds"), o_grads, grads):
+        _close(a, b, rtol=1e-4, atol=1e-5, what=name)
+    np.savez_compressed(os.path.join(GOLD, "raster.npz"), **_np(
+        means2d=means2d, conics=conics, colors=colors, opacities=opacities, backgrounds=backgrounds, radii=radii,
+        depths=depths, offsets=offs, flatten_ids=flat, isect_ids=ids, width=Wd, height=Ht, tile_size=ts,
+        render_colors=rc, render_alphas=ra, w_colors=w_c, w_alphas=w_a, v_means2d=grads[0], v_conics=grads[1],
+        v_colors=grads[2], v_opacities=grads[3], v_backgrounds=grads[4]))
+    print("raster: n_isects=%d mean alpha=%.3f" % (flat.numel(), float(ra.mean())))
+
+
+def main():
+    import gsplat.cuda._torch_impl as T
+
+    os.makedirs(GOLD, exist_ok=True)
+    proj = case_projection(T)
+    case_sh(T)
+    case_isect(T, proj)
+    case_raster(T)
+    print("golden vectors written to", GOLD)
+
+
+if __name__ == "__main__":
+    main()

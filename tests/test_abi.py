@@ -1,0 +1,85 @@
+"""CPU: the C-ABI library loads and exports every symbol include/gsplat_b200.h declares; the
+product path refuses CPU tensors / a missing library instead of falling back."""
+import ctypes
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from conftest import PKG, ROOT
+
+from gsplat.b200_impl import _lib
+
+
+def test_header_parses_and_library_exports_every_symbol():
+    protos = _lib.parse_header()
+    expected = {
+        "gsb_last_error", "gsb_abi_version", "gsb_launch_count", "gsb_reset_launch_count", "gsb_projection_fwd",
+        "gsb_projection_bwd", "gsb_projection_packed_count", "gsb_projection_packed_write",
+        "gsb_projection_packed_bwd", "gsb_sh_fwd", "gsb_sh_bwd", "gsb_isect_num_blocks", "gsb_isect_count",
+        "gsb_scan_i32_to_i64", "gsb_isect_emit", "gsb_sort_pairs_temp_bytes", "gsb_sort_pairs", "gsb_isect_offsets",
+        "gsb_rasterize_pack", "gsb_rasterize_fwd", "gsb_rasterize_bwd", "gsb_a2a_pack", "gsb_a2a_unpack",
+    }
+    assert expected <= set(protos), expected - set(protos)
+    assert os.path.exists(_lib.LIB_PATH), "run `python gsplat-triton_b200/build.py` (or __graft_entry__.build())"
+    dll = ctypes.CDLL(_lib.LIB_PATH)
+    for name in protos:
+        assert hasattr(dll, name), f"{name} declared in the header but not exported"
+    dll.gsb_abi_version.restype = ctypes.c_int
+    assert dll.gsb_abi_version() >= 1
+
+
+def test_pure_queries_work_without_a_gpu():
+    assert int(_lib.lib.gsb_isect_num_blocks(1000)) == 4
+    assert int(_lib.lib.gsb_isect_num_blocks(0)) == 0
+    _lib.lib.gsb_reset_launch_count()
+    assert int(_lib.lib.gsb_launch_count()) == 0
+
+
+def test_library_is_sm100a_only():
+    out = subprocess.run(["cuobjdump", "--list-elf", _lib.LIB_PATH], capture_output=True, text=True)
+    if out.returncode != 0:
+        pytest.skip("cuobjdump unavailable")
+    archs = {line.split(".")[-2] for line in out.stdout.splitlines() if ".cubin" in line}
+    assert archs == {"sm_100a"}, archs
+
+
+def test_cpu_tensors_are_refused_not_emulated():
+    from gsplat.b200_impl import fully_fused_projection, isect_tiles, spherical_harmonics
+
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        fully_fused_projection(torch.zeros(4, 3), None, torch.ones(4, 4), torch.ones(4, 3), torch.eye(4)[None],
+                               torch.eye(3)[None], 32, 32)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        spherical_harmonics(1, torch.zeros(4, 3), torch.zeros(4, 4, 3))
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        isect_tiles(torch.zeros(1, 4, 2), torch.ones(1, 4, dtype=torch.int32), torch.ones(1, 4), 16, 2, 2)
+
+
+def test_missing_library_fails_loudly():
+    code = (
+        "import sys; sys.path.insert(0, %r)\n"
+        "from gsplat.b200_impl import _lib\n"
+        "try:\n    _lib.lib.gsb_abi_version()\nexcept RuntimeError as e:\n    print('RAISED', 'no CPU fallback' in str(e))\n"
+    ) % PKG
+    env = dict(os.environ, GSPLAT_B200_LIB="/nonexistent/libgsplat_b200.so")
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env)
+    assert "RAISED True" in out.stdout, out.stdout + out.stderr
+
+
+def test_unknown_backend_raises_like_the_reference():
+    code = "import sys; sys.path.insert(0, %r)\nimport gsplat.rendering\n" % PKG
+    env = dict(os.environ, GSPLAT_BACKEND="nope")
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env)
+    assert out.returncode != 0 and "Unknown GSPLAT_BACKEND" in out.stderr
+
+
+def test_product_never_imports_the_oracle():
+    for dirpath, _, files in os.walk(PKG):
+        for f in files:
+            if f.endswith(".py"):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "gs_oracle" not in text and "import oracle" not in text, os.path.join(dirpath, f)
+    assert os.path.isdir(os.path.join(ROOT, "oracle"))

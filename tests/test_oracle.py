@@ -1,0 +1,132 @@
+"""CPU: the oracle (oracle/gs_oracle.py) against the golden vectors frozen from the reference's
+own `_torch_impl` by oracle/make_golden.py, plus the literal known-answer vectors of the reference."""
+import torch
+
+import gs_oracle as O
+
+
+def _close(a, b, rtol=1e-4, atol=1e-4):
+    torch.testing.assert_close(a, b, rtol=rtol, atol=atol)
+
+
+def test_projection_matches_reference(golden):
+    g = golden("projection")
+    covars = O.quat_scale_to_covar(g["quats"], g["scales"])
+    for model in ("pinhole", "ortho"):
+        radii, means2d, depths, conics, comps = O.fully_fused_projection(
+            g["means"], covars, g["viewmats"], g["Ks"], g["width"], g["height"], eps2d=0.3,
+            calc_compensations=True, camera_model=model)
+        assert torch.equal(radii, g[f"{model}_radii"])  # bit-exact integer output
+        v = radii > 0
+        assert v.sum() > 100
+        _close(means2d[v], g[f"{model}_means2d"][v])
+        _close(depths[v], g[f"{model}_depths"][v])
+        _close(conics[v], g[f"{model}_conics"][v])
+        _close(comps[v], g[f"{model}_comps"][v])
+
+
+def test_projection_gradients_match_reference(golden):
+    g = golden("projection")
+    p = [g[k].clone().requires_grad_(True) for k in ("means", "quats", "scales", "viewmats")]
+    radii, means2d, depths, conics, comps = O.fully_fused_projection(
+        p[0], O.quat_scale_to_covar(p[1], p[2]), p[3], g["Ks"], g["width"], g["height"], calc_compensations=True)
+    m = (radii > 0).float()
+    loss = ((means2d * g["pinhole_w_means2d"]).sum(-1) * m + depths * g["pinhole_w_depths"] * m
+            + (conics * g["pinhole_w_conics"]).sum(-1) * m + comps * g["pinhole_w_comps"] * m).sum()
+    grads = torch.autograd.grad(loss, p)
+    for got, name in zip(grads, ("v_means", "v_quats", "v_scales", "v_viewmats")):
+        ref = g["pinhole_" + name]
+        _close(got, ref, rtol=1e-3, atol=1e-3 * float(ref.abs().max()))
+
+
+def test_sh_matches_reference(golden):
+    g = golden("sh")
+    for deg in range(5):
+        d = g["dirs"].clone().requires_grad_(True)
+        c = g["coeffs"].clone().requires_grad_(True)
+        col = O.spherical_harmonics(deg, d, c)
+        _close(col, g[f"colors_{deg}"], atol=1e-5)
+        vd, vc = torch.autograd.grad((col * g["w"]).sum(), (d, c), allow_unused=True)
+        _close(vc, g[f"v_coeffs_{deg}"], atol=1e-5)
+        if deg > 0:
+            _close(vd, g[f"v_dirs_{deg}"], atol=1e-4)
+
+
+def test_sh_masks_zero_the_output():
+    torch.manual_seed(0)
+    dirs, coeffs = torch.randn(2, 33, 3), torch.randn(2, 33, 16, 3)
+    masks = torch.rand(2, 33) > 0.5
+    col = O.spherical_harmonics(3, dirs, coeffs, masks)
+    assert (col[~masks] == 0).all() and (col[masks] != 0).any()
+
+
+def test_isect_matches_reference(golden):
+    p, g = golden("projection"), golden("isect")
+    tpg, ids, flat = O.isect_tiles(p["pinhole_means2d"], p["pinhole_radii"], p["pinhole_depths"], g["tile_size"],
+                                   g["tile_width"], g["tile_height"], bits_rule="cuda")
+    assert torch.equal(tpg, g["tiles_per_gauss"])
+    assert torch.equal(ids, g["isect_ids"])
+    assert torch.equal(flat, g["flatten_ids"])
+    offs = O.isect_offset_encode(ids, 3, g["tile_width"], g["tile_height"], bits_rule="cuda")
+    assert torch.equal(offs, g["offsets"])
+    assert bool((ids[1:] >= ids[:-1]).all())  # sortedness
+
+
+def test_offsets_docstring_vector():
+    # reference triton_impl/isect_offset.py:17-20 / IntersectTile.cu:211-214
+    ids = torch.tensor([1, 1, 1, 3, 3, 5, 5], dtype=torch.int64) << 32
+    assert O.isect_offset_encode(ids, 1, 7, 1).flatten().tolist() == [0, 0, 3, 3, 5, 5, 7]
+
+
+def test_tile_bits_rules():
+    # the two reference rules differ only at powers of two (SURVEY 8a hazard 3)
+    assert O.tile_n_bits(1107, "triton") == O.tile_n_bits(1107, "cuda") == 11
+    assert O.tile_n_bits(256, "triton") == 8 and O.tile_n_bits(256, "cuda") == 9
+
+
+def test_isect_empty_and_packed():
+    means2d = torch.tensor([[8.0, 8.0], [100.0, 40.0], [30.0, 30.0]])
+    radii = torch.tensor([0, 0, 0], dtype=torch.int32)
+    depths = torch.tensor([1.0, 2.0, 3.0])
+    tpg, ids, flat = O.isect_tiles(means2d[None], radii[None], depths[None], 16, 8, 4)
+    assert ids.numel() == 0 and flat.numel() == 0 and tpg.sum() == 0
+    assert O.isect_offset_encode(ids, 1, 8, 4).sum() == 0
+    radii = torch.tensor([4, 20, 1], dtype=torch.int32)
+    cam = torch.tensor([0, 1, 1])
+    tpg_p, ids_p, flat_p = O.isect_tiles(means2d, radii, depths, 16, 8, 4, camera_ids=cam, n_cameras=2)
+    assert tpg_p.tolist() == [1, 9, 1]
+    tb = O.tile_n_bits(32)
+    assert ((ids_p >> (32 + tb)).tolist()) == [0] + [1] * 10
+
+
+def test_raster_matches_reference(golden):
+    g = golden("raster")
+    p = [g[k].clone().requires_grad_(True) for k in ("means2d", "conics", "colors", "opacities", "backgrounds")]
+    rc, ra, last = O.rasterize_to_pixels(p[0], p[1], p[2], p[3], g["width"], g["height"], g["tile_size"],
+                                         g["offsets"], g["flatten_ids"], backgrounds=p[4], return_last_ids=True)
+    _close(rc, g["render_colors"], atol=1e-5)
+    _close(ra, g["render_alphas"], atol=1e-5)
+    grads = torch.autograd.grad((rc * g["w_colors"]).sum() + (ra * g["w_alphas"]).sum(), p)
+    for got, name in zip(grads, ("v_means2d", "v_conics", "v_colors", "v_opacities", "v_backgrounds")):
+        _close(got, g[name], rtol=1e-3, atol=1e-5)
+    assert last.shape == (2, g["height"], g["width"]) and int(last.max()) < g["flatten_ids"].numel()
+
+
+def test_raster_masks_and_empty():
+    # a masked-out tile shows only the background; an empty scene renders background with alpha 0
+    offs = torch.zeros((1, 2, 2), dtype=torch.int32)
+    flat = torch.zeros((0,), dtype=torch.int32)
+    z = torch.zeros
+    bg = torch.tensor([[0.25, 0.5, 0.75]])
+    rc, ra = O.rasterize_to_pixels(z(1, 1, 2), z(1, 1, 3), z(1, 1, 3), z(1, 1), 20, 18, 16, offs, flat, backgrounds=bg)
+    assert rc.shape == (1, 18, 20, 3) and torch.equal(rc[0, 3, 4], bg[0]) and float(ra.abs().max()) == 0.0
+
+
+def test_whole_path_runs_on_garden_subset():
+    from conftest import garden_scene
+
+    means, quats, scales, opac, colors, viewmats, Ks, W, H = garden_scene(step=400)
+    rc, ra, meta = O.rasterization(means, quats, scales * 4, opac, colors, viewmats[:1], Ks[:1], W, H)
+    assert rc.shape == (1, H, W, 3) and ra.shape == (1, H, W, 1)
+    assert float(ra.max()) <= 1.0 and float(ra.max()) > 0.0
+    assert int(meta["isect_offsets"][-1, -1, -1]) <= meta["flatten_ids"].numel()
