@@ -50,6 +50,27 @@ def parse_header(path: str = HEADER_PATH):
     return protos
 
 
+class _Timing:
+    """Optional per-entry-point CUDA-event timing (bench.py's per-stage roofline): when enabled, every
+    status-returning launcher is bracketed by events recorded on the stream it launches on."""
+
+    def __init__(self):
+        self.enabled = False
+        self.records = {}
+
+    def reset(self, enabled: bool):
+        self.enabled = enabled
+        self.records = {}
+
+    def summary(self):
+        """{entry point: (calls, total ms)}; synchronises."""
+        torch.cuda.synchronize()
+        return {k: (len(v), sum(a.elapsed_time(b) for a, b in v)) for k, v in self.records.items()}
+
+
+timing = _Timing()
+
+
 class _Lib:
     def __init__(self):
         self._dll = None
@@ -80,7 +101,14 @@ class _Lib:
             return fn  # plain query, not a status-returning launcher
 
         def checked(*args):
-            rc = fn(*args)
+            if timing.enabled:
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                rc = fn(*args)
+                b.record()
+                timing.records.setdefault(name, []).append((a, b))
+            else:
+                rc = fn(*args)
             if rc != 0:
                 raise RuntimeError(f"{name} failed ({rc}): {dll.gsb_last_error().decode()}")
             return rc

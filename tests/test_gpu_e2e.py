@@ -1,0 +1,142 @@
+"""GPU: `gsplat.rendering.rasterization()` end to end under GSPLAT_BACKEND=b200 against the oracle
+restatement of the reference's rendering.py, plus size-independent properties at BASELINE cfg2 size.
+Protocol of the reference's tests/test_rasterization.py:22-89 (rtol = atol = 1e-4 on images/alphas).
+"""
+import math
+
+import pytest
+import torch
+
+import gs_oracle as O
+from conftest import garden_scene
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _close_frac(a, b, rtol, atol, max_bad=2e-3):
+    a, b = a.cpu().double(), b.cpu().double()
+    bad = ((a - b).abs() > atol + rtol * b.abs()).double().mean().item()
+    assert bad <= max_bad, f"{bad:.2e} of the elements differ beyond rtol={rtol} atol={atol}"
+
+
+def _scene(step=25, cams=2):
+    means, quats, scales, opac, colors, viewmats, Ks, W, H = garden_scene(step=step)
+    return means, quats, scales * 3 + 0.002, opac, colors, viewmats[:cams], Ks[:cams], W, H
+
+
+@pytest.mark.parametrize("sh_degree", [None, 3])
+@pytest.mark.parametrize("render_mode", ["RGB", "RGB+D", "D", "RGB+ED"])
+@pytest.mark.parametrize("packed", [False, True])
+def test_rasterization_matches_oracle(sh_degree, render_mode, packed):
+    from gsplat.rendering import rasterization
+
+    means, quats, scales, opac, colors, viewmats, Ks, W, H = _scene()
+    if sh_degree is not None:
+        g = torch.Generator().manual_seed(42)
+        colors = torch.cat([colors[:, None, :], torch.randn(len(means), 15, 3, generator=g) * 0.2], dim=1)
+    bg = torch.rand(len(viewmats), 3, generator=torch.Generator().manual_seed(1))
+    cpu = (means, quats, scales, opac, colors, viewmats, Ks)
+    rc, ra, meta = rasterization(*[t.to(DEV) for t in cpu], W, H, sh_degree=sh_degree, packed=packed,
+                                 render_mode=render_mode, backgrounds=bg.to(DEV))
+    o_rc, o_ra, o_meta = O.rasterization(*cpu, W, H, sh_degree=sh_degree, render_mode=render_mode, backgrounds=bg)
+    assert rc.shape == o_rc.shape and ra.shape == (len(viewmats), H, W, 1)
+    _close_frac(rc, o_rc, rtol=1e-4, atol=1e-4)
+    _close_frac(ra, o_ra, rtol=1e-4, atol=1e-4)
+    for key in ("camera_ids", "gaussian_ids", "radii", "means2d", "depths", "conics", "opacities", "tile_width",
+                "tile_height", "tiles_per_gauss", "isect_ids", "flatten_ids", "isect_offsets", "width", "height",
+                "tile_size", "n_cameras"):
+        assert key in meta, key
+    if not packed:
+        assert meta["radii"].shape == o_meta["radii"].shape
+        assert float((meta["radii"].cpu() != o_meta["radii"]).float().mean()) < 2e-3
+
+
+@pytest.mark.parametrize("antialiased", [False, True])
+def test_rasterization_gradients_match_oracle(antialiased):
+    from gsplat.rendering import rasterization
+
+    means, quats, scales, opac, colors, viewmats, Ks, W, H = _scene(step=60, cams=2)
+    g = torch.Generator().manual_seed(42)
+    shs = torch.cat([colors[:, None, :], torch.randn(len(means), 8, 3, generator=g) * 0.2], dim=1)
+    w_c = torch.randn(2, H, W, 3, generator=g)
+    w_a = torch.randn(2, H, W, 1, generator=g)
+    mode = "antialiased" if antialiased else "classic"
+
+    def run(fn, dev, **kw):
+        p = [t.clone().to(dev).requires_grad_(True) for t in (means, quats, scales, opac, shs)]
+        rc, ra, meta = fn(p[0], p[1], p[2], p[3], p[4], viewmats.to(dev), Ks.to(dev), W, H, sh_degree=2,
+                          rasterize_mode=mode, **kw)
+        if dev == DEV:
+            meta["means2d"].retain_grad()  # the densification strategy's contract (strategy/default.py:150)
+        loss = (rc * w_c.to(dev)).sum() + (ra * w_a.to(dev)).sum()
+        loss.backward()
+        return [t.grad for t in p], meta
+
+    grads, meta = run(rasterization, DEV, packed=False, absgrad=True)
+    o_grads, _ = run(O.rasterization, "cpu")
+    assert meta["means2d"].grad is not None and meta["means2d"].absgrad.shape == meta["means2d"].shape
+    tol = {"means": 1e-3, "quats": 5e-3, "scales": 5e-2, "opacities": 1e-3, "colors": 1e-3}
+    for name, a, b in zip(tol, grads, o_grads):
+        _close_frac(a, b, rtol=tol[name], atol=tol[name] * 1e-2 * float(b.abs().max()) + 1e-7, max_bad=1e-2)
+    p_grads, _ = run(rasterization, DEV, packed=True)
+    for name, a, b in zip(tol, p_grads, grads):
+        _close_frac(a, b, rtol=tol[name], atol=tol[name] * 1e-2 * float(b.abs().max()) + 1e-7, max_bad=1e-2)
+
+
+def test_rasterization_covars_channels_and_ortho():
+    from gsplat.rendering import rasterization
+
+    means, quats, scales, opac, colors, viewmats, Ks, W, H = _scene(step=50, cams=1)
+    feats = torch.rand(len(means), 40, generator=torch.Generator().manual_seed(5))  # > channel_chunk
+    covars = O.quat_scale_to_covar(quats, scales)
+    cpu = (means, quats, scales, opac, feats, viewmats, Ks)
+    rc, ra, _ = rasterization(*[t.to(DEV) for t in cpu], W, H, packed=False, covars=covars.to(DEV))
+    o_rc, o_ra, _ = O.rasterization(*cpu, W, H, covars=covars)
+    assert rc.shape == (1, H, W, 40)
+    _close_frac(rc, o_rc, rtol=1e-4, atol=1e-4)
+    Ko = Ks.clone()
+    Ko[:, 0, 0] = Ko[:, 1, 1] = 150.0
+    cpu = (means, quats, scales, opac, colors, viewmats, Ko)
+    rc, ra, _ = rasterization(*[t.to(DEV) for t in cpu], W, H, packed=False, camera_model="ortho")
+    o_rc, o_ra, _ = O.rasterization(*cpu, W, H, camera_model="ortho")
+    _close_frac(rc, o_rc, rtol=1e-4, atol=1e-4)
+    with pytest.raises(NotImplementedError):
+        rasterization(*[t.to(DEV) for t in cpu], W, H, camera_model="fisheye")
+
+
+def test_full_size_properties_cfg2():
+    """BASELINE cfg2 (1M Gaussians, SH deg 3, 1920x1080): size-independent properties."""
+    import sys, os
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from bench import make_cfg2
+    from gsplat.rendering import rasterization
+
+    s = make_cfg2(DEV)
+    p = [s[k].requires_grad_(True) for k in ("means", "quats", "scales", "opacities", "shs")]
+    rc, ra, meta = rasterization(*p, s["viewmats"], s["Ks"], s["width"], s["height"], sh_degree=3, packed=False)
+    ids, flat, offs = meta["isect_ids"], meta["flatten_ids"], meta["isect_offsets"]
+    n_isects = ids.numel()
+    assert n_isects == int(meta["tiles_per_gauss"].sum())  # count == emitted
+    assert bool((ids[1:] >= ids[:-1]).all())  # sorted
+    tb = (meta["tile_width"] * meta["tile_height"] - 1).bit_length()
+    tiles = (ids >> 32) & ((1 << tb) - 1)
+    counts = torch.bincount(tiles, minlength=offs.numel())
+    assert torch.equal((torch.cumsum(counts, 0) - counts).int(), offs.flatten())  # offsets == histogram scan
+    assert torch.equal(torch.sort(flat.long()).values,
+                       torch.repeat_interleave(torch.arange(flat.max() + 1, device=DEV),
+                                               meta["tiles_per_gauss"].flatten()[: flat.max() + 1]))
+    depth_bits = (ids & 0xFFFFFFFF).int().view(torch.float32)
+    assert torch.equal(depth_bits, meta["depths"].flatten()[flat.long()])  # key carries the depth bit pattern
+    assert float(ra.min()) >= 0.0 and float(ra.max()) <= 1.0 and bool(torch.isfinite(rc).all())
+    (rc.sum() + ra.sum()).backward()
+    for t in p:
+        assert t.grad is not None and bool(torch.isfinite(t.grad).all())
+    # linearity of the compositor in the colours: render(2c) == 2 render(c)
+    with torch.no_grad():
+        rc2, _, _ = rasterization(p[0], p[1], p[2], p[3], torch.rand(len(p[0]), 3, device=DEV) * 0 + 0.5,
+                                  s["viewmats"], s["Ks"], s["width"], s["height"], packed=False)
+        rc4, ra4, _ = rasterization(p[0], p[1], p[2], p[3], torch.ones(len(p[0]), 3, device=DEV), s["viewmats"],
+                                    s["Ks"], s["width"], s["height"], packed=False)
+    torch.testing.assert_close(rc2 * 2, rc4, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(rc4[..., :1], ra4, rtol=1e-4, atol=1e-5)  # unit colours render the alpha

@@ -1,0 +1,227 @@
+"""GPU parity tests: SH, tile intersection (bit-exact), compositor fwd/bwd, against golden + oracle."""
+import pytest
+import torch
+
+import gs_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _close(a, b, rtol=1e-4, atol=1e-4):
+    torch.testing.assert_close(a.cpu(), b.cpu(), rtol=rtol, atol=atol)
+
+
+def _close_frac(a, b, rtol, atol, max_bad=1e-3):
+    a, b = a.cpu().double(), b.cpu().double()
+    bad = ((a - b).abs() > atol + rtol * b.abs()).double().mean().item()
+    assert bad <= max_bad, f"{bad:.2e} of the elements differ beyond rtol={rtol} atol={atol}"
+
+
+# ---------------------------------------------------------------------------------------------
+# spherical harmonics
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("deg", [0, 1, 2, 3, 4])
+def test_sh_forward_backward(golden, deg):
+    from gsplat.b200_impl import spherical_harmonics
+
+    g = golden("sh")
+    d = g["dirs"].to(DEV).requires_grad_(True)
+    c = g["coeffs"].to(DEV).requires_grad_(True)
+    col = spherical_harmonics(deg, d, c)
+    _close(col, g[f"colors_{deg}"], rtol=1e-4, atol=1e-5)
+    vd, vc = torch.autograd.grad((col * g["w"].to(DEV)).sum(), (d, c))
+    _close(vc, g[f"v_coeffs_{deg}"], rtol=1e-4, atol=1e-5)
+    _close(vd, g[f"v_dirs_{deg}"], rtol=1e-3, atol=1e-4)
+
+
+def test_sh_broadcast_masks_and_shapes():
+    from gsplat.b200_impl import spherical_harmonics
+
+    torch.manual_seed(43)
+    C, N, K = 3, 1031, 16
+    dirs = torch.randn(C, N, 3, device=DEV, requires_grad=True)
+    coeffs = torch.randn(N, K, 3, device=DEV, requires_grad=True)
+    masks = torch.rand(C, N, device=DEV) > 0.3
+    w = torch.randn(C, N, 3, device=DEV)
+    outs = []
+    for form in ("broadcast", "expand", "materialised"):
+        cf = {"broadcast": coeffs, "expand": coeffs.expand(C, -1, -1, -1),
+              "materialised": coeffs.expand(C, -1, -1, -1).contiguous()}[form]
+        col = spherical_harmonics(3, dirs, cf, masks=masks)
+        vd, vc = torch.autograd.grad((col * w).sum(), (dirs, coeffs))
+        outs.append((col, vd, vc))
+    ref_d = dirs.detach().cpu().requires_grad_(True)
+    ref_c = coeffs.detach().cpu().requires_grad_(True)
+    ref = O.spherical_harmonics(3, ref_d, ref_c.expand(C, -1, -1, -1), masks.cpu())
+    rvd, rvc = torch.autograd.grad((ref * w.cpu()).sum(), (ref_d, ref_c))
+    for col, vd, vc in outs:
+        _close(col, ref, atol=1e-5)
+        _close(vd, rvd, rtol=1e-3, atol=1e-4)
+        _close(vc, rvc, rtol=1e-4, atol=1e-4)
+        assert float(col[~masks].abs().max()) == 0.0 and float(vd[~masks].abs().max()) == 0.0
+    # flat [..., 3] / [..., K, 3] inputs of any rank (triton_tests/test_sh.py shape (129, 31, ...))
+    d2 = torch.randn(129, 31, 3, device=DEV)
+    c2 = torch.randn(129, 31, 25, 3, device=DEV)
+    _close(spherical_harmonics(4, d2, c2), O.spherical_harmonics(4, d2.cpu(), c2.cpu()), atol=1e-5)
+
+
+# ---------------------------------------------------------------------------------------------
+# isect_tiles / isect_offset_encode: bit-exact given the reference's projection outputs
+# ---------------------------------------------------------------------------------------------
+def test_isect_bit_exact_against_reference(golden, monkeypatch):
+    from gsplat.b200_impl import isect_offset_encode, isect_tiles
+
+    monkeypatch.setenv("GSPLAT_B200_TILE_BITS", "cuda")  # the golden was made with _torch_impl's rule
+    p, g = golden("projection"), golden("isect")
+    means2d, radii, depths = (p[k].to(DEV) for k in ("pinhole_means2d", "pinhole_radii", "pinhole_depths"))
+    tpg, ids, flat = isect_tiles(means2d, radii, depths, g["tile_size"], g["tile_width"], g["tile_height"])
+    assert tpg.dtype == torch.int32 and ids.dtype == torch.int64 and flat.dtype == torch.int32
+    assert torch.equal(tpg.cpu(), g["tiles_per_gauss"])
+    assert torch.equal(ids.cpu(), g["isect_ids"])
+    assert torch.equal(flat.cpu(), g["flatten_ids"])
+    offs = isect_offset_encode(ids, 3, g["tile_width"], g["tile_height"])
+    assert offs.dtype == torch.int32 and torch.equal(offs.cpu(), g["offsets"])
+
+
+@pytest.mark.parametrize("C,N,W,H", [(3, 1000, 40, 60), (1, 5000, 256, 256), (2, 1, 33, 17), (4, 3000, 640, 360)])
+def test_isect_random_against_oracle(C, N, W, H):
+    # tests/test_basic.py:410 protocol (random data); 256x256 -> 256 tiles is the power-of-two bit-rule case
+    from gsplat.b200_impl import isect_offset_encode, isect_tiles
+
+    torch.manual_seed(50)
+    ts = 16
+    tw, th = -(-W // ts), -(-H // ts)
+    means2d = torch.rand(C, N, 2) * torch.tensor([W + 40.0, H + 40.0]) - 20.0
+    radii = torch.randint(0, 40, (C, N), dtype=torch.int32)
+    depths = torch.rand(C, N) * 10 + 0.01
+    depths[:, ::5] = 1.0  # equal depths: ties must keep emission order (stable sort)
+    tpg, ids, flat = isect_tiles(means2d.to(DEV), radii.to(DEV), depths.to(DEV), ts, tw, th)
+    o_tpg, o_ids, o_flat = O.isect_tiles(means2d, radii, depths, ts, tw, th)
+    assert torch.equal(tpg.cpu(), o_tpg) and torch.equal(ids.cpu(), o_ids) and torch.equal(flat.cpu(), o_flat)
+    offs = isect_offset_encode(ids, C, tw, th)
+    assert torch.equal(offs.cpu(), O.isect_offset_encode(o_ids, C, tw, th))
+    # unsorted emission order
+    _, ids_u, flat_u = isect_tiles(means2d.to(DEV), radii.to(DEV), depths.to(DEV), ts, tw, th, sort=False)
+    _, o_ids_u, o_flat_u = O.isect_tiles(means2d, radii, depths, ts, tw, th, sort=False)
+    assert torch.equal(ids_u.cpu(), o_ids_u) and torch.equal(flat_u.cpu(), o_flat_u)
+
+
+def test_isect_packed_empty_and_docstring():
+    from gsplat.b200_impl import isect_offset_encode, isect_tiles
+
+    torch.manual_seed(1)
+    nnz, C, ts, tw, th = 777, 3, 16, 9, 7
+    cam = torch.sort(torch.randint(0, C, (nnz,))).values
+    gid = torch.arange(nnz)
+    means2d = torch.rand(nnz, 2) * 140
+    radii = torch.randint(1, 30, (nnz,), dtype=torch.int32)
+    depths = torch.rand(nnz) + 0.5
+    tpg, ids, flat = isect_tiles(means2d.to(DEV), radii.to(DEV), depths.to(DEV), ts, tw, th, packed=True,
+                                 n_cameras=C, camera_ids=cam.to(DEV), gaussian_ids=gid.to(DEV))
+    o = O.isect_tiles(means2d, radii, depths, ts, tw, th, camera_ids=cam, n_cameras=C)
+    assert torch.equal(tpg.cpu(), o[0]) and torch.equal(ids.cpu(), o[1]) and torch.equal(flat.cpu(), o[2])
+    # empty scene
+    z = torch.zeros(1, 8, dtype=torch.int32, device=DEV)
+    tpg, ids, flat = isect_tiles(torch.zeros(1, 8, 2, device=DEV), z, torch.ones(1, 8, device=DEV), ts, tw, th)
+    assert ids.numel() == 0 and flat.numel() == 0 and int(tpg.sum()) == 0
+    assert int(isect_offset_encode(ids, 1, tw, th).abs().sum()) == 0
+    # reference docstring vector (isect_offset.py:17-20)
+    doc = (torch.tensor([1, 1, 1, 3, 3, 5, 5], dtype=torch.int64) << 32).to(DEV)
+    assert isect_offset_encode(doc, 1, 7, 1).flatten().tolist() == [0, 0, 3, 3, 5, 5, 7]
+    # a single intersection: trailing tiles must still be filled (Triton reference defect)
+    one = (torch.tensor([2], dtype=torch.int64) << 32).to(DEV)
+    assert isect_offset_encode(one, 1, 5, 1).flatten().tolist() == [0, 0, 0, 1, 1]
+
+
+# ---------------------------------------------------------------------------------------------
+# compositor
+# ---------------------------------------------------------------------------------------------
+def test_raster_against_reference_golden(golden):
+    from gsplat.b200_impl import rasterize_to_pixels
+
+    g = golden("raster")
+    p = [g[k].to(DEV).requires_grad_(True) for k in ("means2d", "conics", "colors", "opacities", "backgrounds")]
+    offs, flat = g["offsets"].to(DEV), g["flatten_ids"].to(DEV)
+    rc, ra = rasterize_to_pixels(p[0], p[1], p[2], p[3], g["width"], g["height"], g["tile_size"], offs, flat,
+                                 backgrounds=p[4])
+    assert rc.shape == g["render_colors"].shape and ra.shape == g["render_alphas"].shape
+    _close_frac(rc, g["render_colors"], rtol=1e-4, atol=1e-5, max_bad=2e-3)
+    _close_frac(ra, g["render_alphas"], rtol=1e-4, atol=1e-5, max_bad=2e-3)
+    grads = torch.autograd.grad((rc * g["w_colors"].to(DEV)).sum() + (ra * g["w_alphas"].to(DEV)).sum(), p)
+    for got, name in zip(grads, ("v_means2d", "v_conics", "v_colors", "v_opacities", "v_backgrounds")):
+        ref = g[name]
+        _close_frac(got, ref, rtol=1e-3, atol=1e-3 * float(ref.abs().max()) * 1e-2 + 1e-6, max_bad=5e-3)
+
+
+def _random_splats(C, N, W, H, D, seed):
+    g = torch.Generator().manual_seed(seed)
+    means2d = torch.rand(C, N, 2, generator=g) * torch.tensor([W + 8.0, H + 8.0]) - 4.0
+    s = torch.exp(torch.rand(C, N, 2, generator=g) * 2.0 - 0.2)
+    rho = torch.rand(C, N, generator=g) * 1.6 - 0.8
+    cxx, cyy, cxy = s[..., 0] ** 2, s[..., 1] ** 2, rho * s[..., 0] * s[..., 1]
+    det = cxx * cyy - cxy * cxy
+    conics = torch.stack([cyy / det, -cxy / det, cxx / det], dim=-1)
+    radii = torch.ceil(3.0 * torch.sqrt(torch.maximum(cxx, cyy))).int()
+    depths = torch.rand(C, N, generator=g) * 9.0 + 1.0
+    opacities = torch.rand(C, N, generator=g) * 0.98 + 0.01
+    opacities[:, ::7] = 1.0
+    colors = torch.rand(C, N, D, generator=g)
+    return means2d, conics, colors, opacities, radii, depths
+
+
+@pytest.mark.parametrize("D,bg,absgrad", [(1, False, False), (3, True, True), (4, False, False), (5, True, False),
+                                          (8, False, True), (17, True, False), (32, False, False), (40, True, False)])
+def test_raster_channels_against_oracle(D, bg, absgrad):
+    from gsplat.b200_impl import rasterize_to_pixels
+
+    C, N, W, H, ts = 2, 600, 70, 50, 16
+    means2d, conics, colors, opac, radii, depths = _random_splats(C, N, W, H, D, seed=D)
+    tw, th = -(-W // ts), -(-H // ts)
+    _, ids, flat = O.isect_tiles(means2d, radii, depths, ts, tw, th)
+    offs = O.isect_offset_encode(ids, C, tw, th)
+    backgrounds = torch.rand(C, D) if bg else None
+    gw = torch.Generator().manual_seed(99)
+    w_c, w_a = torch.randn(C, H, W, D, generator=gw), torch.randn(C, H, W, 1, generator=gw)
+
+    def run(fn, dev):
+        p = [t.clone().to(dev).requires_grad_(True) for t in (means2d, conics, colors, opac)]
+        b = backgrounds.clone().to(dev).requires_grad_(True) if bg else None
+        kw = {"absgrad": absgrad} if dev == DEV else {}
+        rc, ra = fn(p[0], p[1], p[2], p[3], W, H, ts, offs.to(dev), flat.to(dev), backgrounds=b, **kw)
+        grads = torch.autograd.grad((rc * w_c.to(dev)).sum() + (ra * w_a.to(dev)).sum(), p + ([b] if bg else []))
+        return rc, ra, grads, p
+
+    rc, ra, grads, p = run(rasterize_to_pixels, DEV)
+    o_rc, o_ra, o_grads, _ = run(O.rasterize_to_pixels, "cpu")
+    _close_frac(rc, o_rc, rtol=1e-4, atol=1e-5, max_bad=2e-3)
+    _close_frac(ra, o_ra, rtol=1e-4, atol=1e-5, max_bad=2e-3)
+    for a, b in zip(grads, o_grads):
+        _close_frac(a, b, rtol=1e-3, atol=1e-5 * float(b.abs().max()) + 1e-6, max_bad=5e-3)
+    if absgrad:
+        ab = p[0].absgrad
+        assert ab.shape == p[0].shape and bool((ab + 1e-6 >= grads[0].abs()).all())
+
+
+def test_raster_masks_empty_and_last_tile():
+    from gsplat.b200_impl import rasterize_to_pixels
+
+    C, N, W, H, ts, D = 1, 300, 48, 48, 16, 3
+    means2d, conics, colors, opac, radii, depths = _random_splats(C, N, W, H, D, seed=3)
+    tw = th = 3
+    _, ids, flat = O.isect_tiles(means2d, radii, depths, ts, tw, th)
+    offs = O.isect_offset_encode(ids, C, tw, th)
+    masks = torch.ones(C, th, tw, dtype=torch.bool)
+    masks[0, 1, 1] = False
+    bg = torch.rand(C, D)
+    args = (means2d, conics, colors, opac, W, H, ts, offs, flat)
+    rc, ra = rasterize_to_pixels(*[a.to(DEV) if torch.is_tensor(a) else a for a in args], backgrounds=bg.to(DEV),
+                                 masks=masks.to(DEV))
+    o_rc, o_ra = O.rasterize_to_pixels(*args, backgrounds=bg, masks=masks)
+    _close_frac(rc, o_rc, rtol=1e-4, atol=1e-5, max_bad=2e-3)
+    assert torch.equal(rc[0, 20, 20].cpu(), bg[0]) and float(ra[0, 16:32, 16:32].abs().max()) == 0.0
+    # no intersections at all
+    e = torch.zeros((0,), dtype=torch.int32, device=DEV)
+    rc, ra = rasterize_to_pixels(means2d.to(DEV), conics.to(DEV), colors.to(DEV), opac.to(DEV), W, H, ts,
+                                 torch.zeros_like(offs).to(DEV), e, backgrounds=bg.to(DEV))
+    assert float(ra.abs().max()) == 0.0 and torch.equal(rc[0, 0, 0].cpu(), bg[0])
