@@ -467,7 +467,8 @@ def rasterize_to_pixels(
                 backgrounds_c = torch.nn.functional.pad(backgrounds_c, (0, pad))
         rc, ra = _RasterizeToPixels.apply(
             means2d.contiguous(), conics.contiguous(), colors_c.contiguous(), opacities.contiguous(),
-            backgrounds_c, masks, image_width, image_height, tile_size, isect_offsets.contiguous(),
+            backgrounds_c.contiguous() if backgrounds_c is not None else None, masks, image_width, image_height,
+            tile_size, isect_offsets.contiguous(),
             flatten_ids.contiguous(), absgrad,
         )
         return (rc[..., :ch] if pad else rc), ra
