@@ -13,13 +13,13 @@
 //                           v_xy = v_sigma (a dx + b dy, b dx + c dy) ; v_o = e^-sigma v_alpha
 //
 // B200 design (what differs from the reference's "warpSum of every value, lane-0 atomics"):
-//   * same compacted staging and warp-uniform 8x4 block culling as the forward kernel;
+//   * same compacted staging, per-warp block masks and ballot-compacted splat lists as the forward kernel;
 //   * the 6+D(+2) per-pixel gradient values are reduced over the warp with a *transposing*
 //     butterfly: every xor step halves the number of live values per lane, so 9 values cost
 //     12 shuffles instead of 45; the sums end up one per lane;
-//   * those lanes store (not atomically add) into a per-warp partial table in shared memory;
-//     after the batch one thread per staged splat sums the <= 8 partials and issues a single
-//     set of global reductions per (tile, splat) instead of one per (warp, splat).
+//   * those lanes add into one row of sums per staged splat in shared memory (9 KB at D=3, so 4
+//     CTAs stay resident per SM); after the batch one thread per staged splat issues a single set
+//     of global reductions per (tile, splat) instead of one per (warp, splat).
 #include "rasterize_common.cuh"
 
 namespace raster {
@@ -94,9 +94,17 @@ __device__ __forceinline__ float *grad_address(const GradTargets &t, int value, 
     return t.v_abs + 2 * g + (value - 6 - D);
 }
 
-// SMEM_ACC: partial sums per (warp, staged splat) in shared memory, one flush per (tile, splat).
-template <int D, bool ABS, bool SMEM_ACC>
-__global__ void __launch_bounds__(kThreads)
+// Shared-memory layout (dynamic): the staged batch + one row of NV gradient sums per staged splat.
+template <int D, bool ABS>
+struct BwdSmem {
+    static constexpr int NV = GradLayout<D, ABS>::kN;
+    static constexpr size_t bytes = sizeof(float4) * kThreads + sizeof(float2) * kThreads +
+                                    sizeof(int) * (3 * kThreads + 2 * kWarps) +
+                                    sizeof(float) * kThreads * (D + NV);
+};
+
+template <int D, bool ABS>
+__global__ void __launch_bounds__(kThreads, (D <= 4 ? 4 : (D <= 16 ? 3 : 2)))
 rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, const float4 *__restrict__ recB,
                      const float *__restrict__ colors, const float *__restrict__ backgrounds,
                      const uint8_t *__restrict__ masks, int W, int H, int tw, int th,
@@ -107,23 +115,20 @@ rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
     using L = GradLayout<D, ABS>;
     constexpr int NV = L::kN;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float4 *s_A = reinterpret_cast<float4 *>(smem_raw);
-    float4 *s_B = s_A + kThreads;
-    int *s_idx = reinterpret_cast<int *>(s_B + kThreads);
+    float4 *s_B = reinterpret_cast<float4 *>(smem_raw);
+    float2 *s_xy = reinterpret_cast<float2 *>(s_B + kThreads);
+    int *s_idx = reinterpret_cast<int *>(s_xy + kThreads);
     int *s_gid = s_idx + kThreads;
-    int *s_wcnt = s_gid + kThreads;                       // kWarps
-    int *s_red = s_wcnt + kWarps;                         // kWarps
-    unsigned *s_visit = reinterpret_cast<unsigned *>(s_red + kWarps);  // kWarps * 8
-    float *s_col = reinterpret_cast<float *>(s_visit + kWarps * 8);    // kThreads * D
-    float *s_part = s_col + kThreads * D;                 // SMEM_ACC: kWarps * kThreads * NV
+    unsigned *s_mask = reinterpret_cast<unsigned *>(s_gid + kThreads);
+    int *s_wcnt = reinterpret_cast<int *>(s_mask + kThreads);  // kWarps
+    int *s_red = s_wcnt + kWarps;                              // kWarps
+    float *s_col = reinterpret_cast<float *>(s_red + kWarps);  // kThreads * D
+    float *s_acc = s_col + kThreads * D;                       // kThreads * NV, zero between batches
 
     const TileGeom tg = tile_geometry(n_isects, W, H, tw, th, C, offsets);
     if (masks != nullptr && !masks[tg.tile_id]) return;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-
     const float pxf = (float)tg.px + 0.5f, pyf = (float)tg.py + 0.5f;
-    const Rect tile_rect = pixel_rect(tg.tile_x * kTile, tg.tile_y * kTile, kTile, kTile);
-    const Rect warp_rect = pixel_rect(tg.tile_x * kTile + (warp & 1) * 8, tg.tile_y * kTile + (warp >> 1) * 4, 8, 4);
 
     // per-pixel state
     const float T_final = tg.inside ? 1.0f - render_alphas[tg.pix_id] : 1.0f;
@@ -146,6 +151,7 @@ rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
 
     const int warp_last = warp_max_i(bin_final);
     if (lane == 0) s_red[warp] = warp_last;
+    for (int i = tid; i < kThreads * NV; i += kThreads) s_acc[i] = 0.f;
     __syncthreads();
     int tile_last = s_red[0];
 #pragma unroll
@@ -158,45 +164,45 @@ rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
 
     const int hi_start = min(tg.range_end - 1, tile_last);
     for (int hi = hi_start; hi >= tg.range_start; hi -= kThreads) {
-        __syncthreads();  // previous batch fully consumed
         const int idx = hi - tid;
-        bool keep = false;
+        unsigned mask = 0u;
         int g = 0;
         float4 A;
         if (idx >= tg.range_start) {
             g = flatten_ids[idx];
             A = __ldg(recA + g);
-            keep = splat_touches(A, tile_rect);
+            mask = splat_block_mask(A, tg.tile_x * kTile, tg.tile_y * kTile);
         }
         int total;
-        const int slot = stage_slot(keep, s_wcnt, total);
-        if (keep) {
-            s_A[slot] = A;
+        const int slot = stage_slot(mask != 0u, s_wcnt, total);  // syncs: previous batch fully flushed
+        if (mask != 0u) {
+            s_xy[slot] = make_float2(A.x, A.y);
             s_B[slot] = __ldg(recB + g);
             s_idx[slot] = idx;
             s_gid[slot] = g;
+            s_mask[slot] = mask;
             const float *cp = colors + (size_t)g * D;
 #pragma unroll
             for (int k = 0; k < D; ++k) s_col[slot * D + k] = cp[k];
         }
         __syncthreads();
 
-        for (int j0 = 0; j0 < total; j0 += 32) {
-            unsigned visited = 0u;
-            const int jn = min(32, total - j0);
-            for (int jj = 0; jj < jn; ++jj) {
-                const int j = j0 + jj;
-                const int sidx = s_idx[j];
-                if (sidx > warp_last) continue;  // behind every pixel's last contributor in this warp
-                const float4 a4 = s_A[j];
-                if (!splat_touches(a4, warp_rect)) continue;
+        for (int c0 = 0; c0 < total; c0 += 32) {
+            const int jl = c0 + lane;
+            // this warp's splats of the chunk: box reaches its 8x4 block and not behind every pixel's last id
+            unsigned todo = __ballot_sync(0xffffffffu, jl < total && ((s_mask[jl] >> warp) & 1u) &&
+                                                           s_idx[jl] <= warp_last);
+            while (todo) {
+                const int j = c0 + __ffs(todo) - 1;
+                todo &= todo - 1u;
+                const float2 xy = s_xy[j];
                 const float4 b4 = s_B[j];
-                const float dx = a4.x - pxf, dy = a4.y - pyf;
+                const float dx = xy.x - pxf, dy = xy.y - pyf;
                 const float sigma = 0.5f * (b4.x * dx * dx + b4.z * dy * dy) + b4.y * dx * dy;
                 const float vis = __expf(-sigma);
                 const float ov = b4.w * vis;
                 const float alpha = fminf(kAlphaMax, ov);
-                const bool hit = (sidx <= bin_final) && !(sigma < 0.f) && !(alpha < kAlphaMin);
+                const bool hit = (s_idx[j] <= bin_final) && !(sigma < 0.f) && !(alpha < kAlphaMin);
                 if (!__any_sync(0xffffffffu, hit)) continue;
 
                 float v[NV];
@@ -230,60 +236,39 @@ rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
                     }
                 }
                 warp_transpose_sum<NV>(v, lane);
-                if (SMEM_ACC) {
-                    float *dst = s_part + ((size_t)warp * kThreads + j) * NV;
+                float *dst = s_acc + j * NV;
 #pragma unroll
-                    for (int i = 0; i < L::kPerLane; ++i)
-                        if (own[i] >= 0) dst[own[i]] = v[i];
-                    visited |= 1u << jj;
-                } else {
-                    const int64_t gid = s_gid[j];
-#pragma unroll
-                    for (int i = 0; i < L::kPerLane; ++i)
-                        if (own[i] >= 0 && v[i] != 0.f) atomicAdd(grad_address<D, ABS>(out, own[i], gid), v[i]);
-                }
+                for (int i = 0; i < L::kPerLane; ++i)
+                    if (own[i] >= 0) atomicAdd(dst + own[i], v[i]);
             }
-            if (SMEM_ACC && lane == 0) s_visit[warp * 8 + (j0 >> 5)] = visited;
         }
 
-        if (SMEM_ACC) {
-            __syncthreads();
-            if (tid < total) {
-                float acc[NV];
+        __syncthreads();
+        // one flush per (tile, splat): the row owner adds the tile's sums to global memory and re-zeroes the row
+        if (tid < total) {
+            const int64_t gid = s_gid[tid];
+            float *row = s_acc + tid * NV;
 #pragma unroll
-                for (int i = 0; i < NV; ++i) acc[i] = 0.f;
-                bool any = false;
-#pragma unroll
-                for (int w = 0; w < kWarps; ++w) {
-                    if ((s_visit[w * 8 + (tid >> 5)] >> (tid & 31)) & 1u) {
-                        any = true;
-                        const float *src = s_part + ((size_t)w * kThreads + tid) * NV;
-#pragma unroll
-                        for (int i = 0; i < NV; ++i) acc[i] += src[i];
-                    }
-                }
-                if (any) {
-                    const int64_t gid = s_gid[tid];
-#pragma unroll
-                    for (int i = 0; i < NV; ++i)
-                        if (acc[i] != 0.f) atomicAdd(grad_address<D, ABS>(out, i, gid), acc[i]);
+            for (int i = 0; i < NV; ++i) {
+                const float a = row[i];
+                if (a != 0.f) {
+                    atomicAdd(grad_address<D, ABS>(out, i, gid), a);
+                    row[i] = 0.f;
                 }
             }
         }
     }
 }
 
-template <int D, bool ABS, bool SMEM_ACC>
+template <int D, bool ABS>
 int launch_bwd(int C, int64_t n_isects, const float *recA, const float *recB, const float *colors,
                const float *backgrounds, const uint8_t *masks, int W, int H, int tw, int th,
                const int32_t *offsets, const int32_t *flatten_ids, const float *render_alphas,
                const int32_t *last_ids, const float *v_render_colors, const float *v_render_alphas,
                GradTargets out, cudaStream_t stream) {
-    constexpr int NV = GradLayout<D, ABS>::kN;
-    size_t smem = sizeof(float4) * 2 * kThreads + sizeof(int) * (2 * kThreads + 2 * kWarps + 8 * kWarps) +
-                  sizeof(float) * kThreads * D + (SMEM_ACC ? sizeof(float) * kWarps * kThreads * NV : 0);
-    auto kernel = rasterize_bwd_kernel<D, ABS, SMEM_ACC>;
-    static bool configured = false;  // one instantiation per (D, ABS, SMEM_ACC)
+    constexpr size_t smem = BwdSmem<D, ABS>::bytes;
+    auto kernel = rasterize_bwd_kernel<D, ABS>;
+    static bool configured = false;  // one instantiation per (D, ABS)
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) {
@@ -300,19 +285,18 @@ int launch_bwd(int C, int64_t n_isects, const float *recA, const float *recB, co
     return gsb_check_launch("rasterize_bwd");
 }
 
-template <int D, bool SMEM_ACC>
+template <int D>
 int dispatch_abs(bool abs, int C, int64_t n_isects, const float *recA, const float *recB, const float *colors,
                  const float *backgrounds, const uint8_t *masks, int W, int H, int tw, int th,
                  const int32_t *offsets, const int32_t *flatten_ids, const float *render_alphas,
                  const int32_t *last_ids, const float *v_render_colors, const float *v_render_alphas,
                  GradTargets out, cudaStream_t stream) {
     if (abs)
-        return launch_bwd<D, true, SMEM_ACC>(C, n_isects, recA, recB, colors, backgrounds, masks, W, H, tw, th,
-                                             offsets, flatten_ids, render_alphas, last_ids, v_render_colors,
-                                             v_render_alphas, out, stream);
-    return launch_bwd<D, false, SMEM_ACC>(C, n_isects, recA, recB, colors, backgrounds, masks, W, H, tw, th, offsets,
-                                          flatten_ids, render_alphas, last_ids, v_render_colors, v_render_alphas,
-                                          out, stream);
+        return launch_bwd<D, true>(C, n_isects, recA, recB, colors, backgrounds, masks, W, H, tw, th, offsets,
+                                   flatten_ids, render_alphas, last_ids, v_render_colors, v_render_alphas, out,
+                                   stream);
+    return launch_bwd<D, false>(C, n_isects, recA, recB, colors, backgrounds, masks, W, H, tw, th, offsets,
+                                flatten_ids, render_alphas, last_ids, v_render_colors, v_render_alphas, out, stream);
 }
 
 }  // namespace raster
@@ -334,20 +318,20 @@ extern "C" int gsb_rasterize_bwd(int C, int64_t n_isects, int D, const float *re
     if (C == 0 || n_isects == 0) return GSB_OK;
     raster::GradTargets out = {v_means2d, v_conics, v_opacities, v_colors, v_means2d_abs};
     const bool abs = v_means2d_abs != nullptr;
-#define GSB_BWD_CASE(DD, ACC)                                                                                     \
+#define GSB_BWD_CASE(DD)                                                                                          \
     case DD:                                                                                                      \
-        return raster::dispatch_abs<DD, ACC>(abs, C, n_isects, recA, recB, colors, backgrounds, masks, width,     \
+        return raster::dispatch_abs<DD>(abs, C, n_isects, recA, recB, colors, backgrounds, masks, width,     \
                                              height, tile_width, tile_height, isect_offsets, flatten_ids,         \
                                              render_alphas, last_ids, v_render_colors, v_render_alphas, out,      \
                                              stream);
     switch (D) {
-        GSB_BWD_CASE(1, true)
-        GSB_BWD_CASE(2, true)
-        GSB_BWD_CASE(3, true)
-        GSB_BWD_CASE(4, true)
-        GSB_BWD_CASE(8, false)
-        GSB_BWD_CASE(16, false)
-        GSB_BWD_CASE(32, false)
+        GSB_BWD_CASE(1)
+        GSB_BWD_CASE(2)
+        GSB_BWD_CASE(3)
+        GSB_BWD_CASE(4)
+        GSB_BWD_CASE(8)
+        GSB_BWD_CASE(16)
+        GSB_BWD_CASE(32)
         default:
             gsb_set_error("rasterize_bwd: channel count %d unsupported (1,2,3,4,8,16,32)", D);
             return GSB_ERR_UNSUPPORTED;

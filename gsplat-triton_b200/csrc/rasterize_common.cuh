@@ -6,9 +6,10 @@
 // Per-Gaussian "splat records" are two float4 arrays built once per call by splat_pack_kernel:
 //   recA[g] = (x, y, hx, hy)     hx/hy: half extents of the bbox of {alpha >= 1/255}
 //   recB[g] = (conic_xx, conic_xy, conic_yy, opacity)
-// so that a tile gathers a Gaussian with two aligned 16-byte loads, and both the tile and each
-// warp can reject Gaussians whose alpha would be < 1/255 on all of their pixels *before* any
-// per-pixel work. The reject test is conservative (see splat_extent), so the composited result
+// so that a tile gathers a Gaussian with two aligned 16-byte loads. While staging a batch, the
+// loading thread turns the box into an 8-bit mask of the warps (8x4 pixel blocks) it can touch;
+// every warp then walks only its own splats through ballot-compacted bit lists, so Gaussians whose
+// alpha would be < 1/255 on all pixels of a block cost that warp nothing. The reject test is conservative (see splat_extent), so the composited result
 // is the one the reference produces (RasterizeToPixels3DGSFwd.cu:140-169): rejected Gaussians
 // are exactly ones the reference `continue`s over.
 #pragma once
@@ -75,6 +76,24 @@ __device__ __forceinline__ Rect pixel_rect(int x0, int y0, int w, int h) {
 // false when no pixel centre of the rectangle can see alpha >= 1/255 from this splat (A = x, y, hx, hy)
 __device__ __forceinline__ bool splat_touches(const float4 &A, const Rect &r) {
     return !((A.x + A.z < r.xlo) | (A.x - A.z > r.xhi) | (A.y + A.w < r.ylo) | (A.y - A.w > r.yhi));
+}
+
+// bit w set <=> the splat's {alpha >= 1/255} box reaches the 8x4 pixel block of warp w
+// (bx = w & 1, by = w >> 1) of the tile whose first pixel is (x0, y0). 0 = misses the whole tile.
+__device__ __forceinline__ unsigned splat_block_mask(const float4 &A, int x0, int y0) {
+    const float xlo = A.x - A.z, xhi = A.x + A.z, ylo = A.y - A.w, yhi = A.y + A.w;
+    const float fx = (float)x0, fy = (float)y0;
+    unsigned xb = 0u, yb = 0u;
+#pragma unroll
+    for (int bx = 0; bx < 2; ++bx)  // pixel centres fx + 8 bx + .5 .. fx + 8 bx + 7.5
+        xb |= (!((xhi < fx + 8.f * bx + 0.5f) | (xlo > fx + 8.f * bx + 7.5f))) ? (1u << bx) : 0u;
+#pragma unroll
+    for (int by = 0; by < 4; ++by)
+        yb |= (!((yhi < fy + 4.f * by + 0.5f) | (ylo > fy + 4.f * by + 3.5f))) ? (1u << by) : 0u;
+    unsigned m = 0u;
+#pragma unroll
+    for (int by = 0; by < 4; ++by) m |= ((yb >> by) & 1u) ? (xb << (2 * by)) : 0u;
+    return m;
 }
 
 struct TileGeom {

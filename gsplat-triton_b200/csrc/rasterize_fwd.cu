@@ -10,9 +10,10 @@
 //
 // B200 design: each batch of 256 sorted intersections is gathered once per tile through the packed
 // 2 x float4 splat records and *compacted* into shared memory, dropping splats whose
-// {alpha >= 1/255} bounding box misses the tile; each warp owns an 8x4 pixel block and skips
-// (warp-uniformly, no divergence) the staged splats whose box misses its block, and stops as
-// soon as its 32 pixels are saturated. FP32-pipe / MUFU bound; the records live in L2.
+// {alpha >= 1/255} bounding box misses the tile; the staging thread also records which of the 8
+// warps (8x4 pixel blocks) the box reaches. Each warp turns those bits into a 32-wide ballot and
+// walks only its own splats (find-first-set), so skipped splats cost no issue slots, and stops as
+// soon as its 32 pixels are saturated. Issue / FP32-pipe bound; the records live in L2.
 #include "rasterize_common.cuh"
 
 namespace raster {
@@ -40,14 +41,15 @@ rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
                      const int32_t *__restrict__ offsets, const int32_t *__restrict__ flatten_ids,
                      float *__restrict__ out_colors, float *__restrict__ out_alphas,
                      int32_t *__restrict__ last_ids) {
-    __shared__ float4 s_A[kThreads];
+    __shared__ float2 s_xy[kThreads];
     __shared__ float4 s_B[kThreads];
     __shared__ int s_idx[kThreads];
+    __shared__ unsigned s_mask[kThreads];
     __shared__ float s_col[kThreads * D];
     __shared__ int s_wcnt[kWarps];
 
     const TileGeom tg = tile_geometry(n_isects, W, H, tw, th, C, offsets);
-    const int tid = threadIdx.x, warp = tid >> 5;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
     float pix[D];
 #pragma unroll
@@ -58,8 +60,6 @@ rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
     const bool render = (masks == nullptr) || masks[tg.tile_id];
     if (render) {
         const float pxf = (float)tg.px + 0.5f, pyf = (float)tg.py + 0.5f;
-        const Rect tile_rect = pixel_rect(tg.tile_x * kTile, tg.tile_y * kTile, kTile, kTile);
-        const Rect warp_rect = pixel_rect(tg.tile_x * kTile + (warp & 1) * 8, tg.tile_y * kTile + (warp >> 1) * 4, 8, 4);
         bool done = !tg.inside;
         bool warp_done = __all_sync(0xffffffffu, done);
 
@@ -67,50 +67,57 @@ rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
             // all 256 pixels saturated (or outside the image): nothing left to composite
             if (__syncthreads_count(done) == kThreads) break;
             const int idx = base + tid;
-            bool keep = false;
+            unsigned mask = 0u;
             int g = 0;
             float4 A;
             if (idx < tg.range_end) {
                 g = flatten_ids[idx];
                 A = __ldg(recA + g);
-                keep = splat_touches(A, tile_rect);
+                mask = splat_block_mask(A, tg.tile_x * kTile, tg.tile_y * kTile);
             }
             int total;
-            const int slot = stage_slot(keep, s_wcnt, total);
-            if (keep) {
-                s_A[slot] = A;
+            const int slot = stage_slot(mask != 0u, s_wcnt, total);
+            if (mask != 0u) {
+                s_xy[slot] = make_float2(A.x, A.y);
                 s_B[slot] = __ldg(recB + g);
                 s_idx[slot] = idx;
+                s_mask[slot] = mask;
                 const float *cp = colors + (size_t)g * D;
 #pragma unroll
                 for (int k = 0; k < D; ++k) s_col[slot * D + k] = cp[k];
             }
             __syncthreads();
             if (warp_done) continue;
-            for (int j = 0; j < total; ++j) {
-                const float4 a4 = s_A[j];
-                if (!splat_touches(a4, warp_rect)) continue;
-                const float4 b4 = s_B[j];
-                const float dx = a4.x - pxf, dy = a4.y - pyf;
-                const float sigma = 0.5f * (b4.x * dx * dx + b4.z * dy * dy) + b4.y * dx * dy;
-                const float alpha = fminf(kAlphaMax, b4.w * __expf(-sigma));
-                bool hit = !done && !(sigma < 0.f) && !(alpha < kAlphaMin);
-                const float next_T = T * (1.0f - alpha);
-                if (hit && next_T <= kTmin) {
-                    done = true;
-                    hit = false;
-                }
-                if (hit) {
-                    const float w = alpha * T;
+            for (int c0 = 0; c0 < total; c0 += 32) {
+                const int jl = c0 + lane;
+                unsigned todo = __ballot_sync(0xffffffffu, jl < total && ((s_mask[jl] >> warp) & 1u));
+                while (todo) {
+                    const int j = c0 + __ffs(todo) - 1;
+                    todo &= todo - 1u;
+                    const float2 xy = s_xy[j];
+                    const float4 b4 = s_B[j];
+                    const float dx = xy.x - pxf, dy = xy.y - pyf;
+                    const float sigma = 0.5f * (b4.x * dx * dx + b4.z * dy * dy) + b4.y * dx * dy;
+                    const float alpha = fminf(kAlphaMax, b4.w * __expf(-sigma));
+                    bool hit = !done && !(sigma < 0.f) && !(alpha < kAlphaMin);
+                    const float next_T = T * (1.0f - alpha);
+                    if (hit && next_T <= kTmin) {
+                        done = true;
+                        hit = false;
+                    }
+                    if (hit) {
+                        const float w = alpha * T;
 #pragma unroll
-                    for (int k = 0; k < D; ++k) pix[k] = fmaf(s_col[j * D + k], w, pix[k]);
-                    cur = s_idx[j];
-                    T = next_T;
+                        for (int k = 0; k < D; ++k) pix[k] = fmaf(s_col[j * D + k], w, pix[k]);
+                        cur = s_idx[j];
+                        T = next_T;
+                    }
+                    if (__all_sync(0xffffffffu, done)) {
+                        warp_done = true;
+                        break;
+                    }
                 }
-                if (__all_sync(0xffffffffu, done)) {
-                    warp_done = true;
-                    break;
-                }
+                if (warp_done) break;
             }
         }
     }
