@@ -4,7 +4,8 @@
 // gsplat/cuda/csrc/SphericalHarmonicsCUDA.cu:374/448. Basis polynomials follow Sloan's
 // "Efficient Spherical Harmonic Evaluation" as restated in oracle/gs_oracle.py::sh_bases.
 //
-// B200 design: one thread per coefficient row evaluating all 3 channels; the camera (batch)
+// B200 design: one thread per coefficient row evaluating all 3 channels, the rows of a block
+// staged through shared memory so that every global access is coalesced; the camera (batch)
 // dimension of a broadcast `coeffs.expand(C, ...)` is a stride-0 loop *inside* the thread, so
 // [C,N,K,3] is never materialised and, in the backward pass, v_coeffs accumulates in registers
 // over cameras and is written once with plain stores (no zero-fill, no atomics).
@@ -104,26 +105,68 @@ __device__ __forceinline__ void sh_bases_vjp(float x, float y, float z, const fl
           g[21] * dtD * x + g[22] * dtC4 * c1 + g[23] * -1.770130769779931f * c2;
 }
 
+// ---- coalesced staging of coefficient rows -------------------------------------------------------
+// A block owns kThreads consecutive rows. Their first NB3 = 3 (DEG+1)^2 floats are moved between
+// global memory (row stride K3 floats) and shared memory (row stride NB3|1, conflict-free for the
+// one-thread-per-row access of the math) with fully coalesced, 16-byte where possible, accesses.
+template <int NB3>
+__device__ __forceinline__ void rows_to_smem(float *s, const float *__restrict__ src, int64_t r0, int rows, int K3) {
+    constexpr int S = NB3 | 1;
+    if constexpr (NB3 % 4 == 0) {
+        if (K3 == NB3) {
+            constexpr int Q = NB3 / 4;
+            const float4 *p = reinterpret_cast<const float4 *>(src + (size_t)r0 * NB3);
+            for (int q = threadIdx.x; q < rows * Q; q += kThreads) {
+                const float4 v = p[q];
+                const int row = q / Q, i = (q - row * Q) * 4;
+                float *d = s + row * S + i;
+                d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+            }
+            return;
+        }
+    }
+    for (int e = threadIdx.x; e < rows * NB3; e += kThreads) {
+        const int row = e / NB3, i = e - row * NB3;
+        s[row * S + i] = src[(size_t)(r0 + row) * K3 + i];
+    }
+}
+
+// smem rows -> dst rows; floats [NB3, K3) of every row are zero-filled
+template <int NB3>
+__device__ __forceinline__ void smem_to_rows(const float *s, float *__restrict__ dst, int64_t r0, int rows, int K3) {
+    constexpr int S = NB3 | 1;
+    if constexpr (NB3 % 4 == 0) {
+        if (K3 == NB3) {
+            constexpr int Q = NB3 / 4;
+            float4 *p = reinterpret_cast<float4 *>(dst + (size_t)r0 * NB3);
+            for (int q = threadIdx.x; q < rows * Q; q += kThreads) {
+                const int row = q / Q, i = (q - row * Q) * 4;
+                const float *d = s + row * S + i;
+                p[q] = make_float4(d[0], d[1], d[2], d[3]);
+            }
+            return;
+        }
+    }
+    for (int e = threadIdx.x; e < rows * K3; e += kThreads) {
+        const int row = e / K3, i = e - row * K3;
+        dst[(size_t)(r0 + row) * K3 + i] = i < NB3 ? s[row * S + i] : 0.f;
+    }
+}
+
 template <int DEG>
 __global__ void __launch_bounds__(kThreads)
 sh_fwd_kernel(int64_t n_rows, int n_batch, int K, const float *__restrict__ dirs, const float *__restrict__ coeffs,
               const uint8_t *__restrict__ masks, float *__restrict__ colors) {
     constexpr int NB = (DEG + 1) * (DEG + 1);
-    int64_t r = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    constexpr int S = (NB * 3) | 1;
+    __shared__ float s_cf[kThreads * S];
+    const int64_t r0 = (int64_t)blockIdx.x * kThreads;
+    const int rows = (int)min((int64_t)kThreads, n_rows - r0);
+    rows_to_smem<NB * 3>(s_cf, coeffs, r0, rows, K * 3);
+    __syncthreads();
+    const int64_t r = r0 + threadIdx.x;
     if (r >= n_rows) return;
-    // gather this row's active coefficients once (shared by all batch entries when broadcast)
-    float cf[NB * 3];
-    const float *cp = coeffs + (size_t)r * K * 3;
-    if (((K * 3) & 3) == 0 && (NB * 3) % 4 == 0) {
-#pragma unroll
-        for (int i = 0; i < NB * 3 / 4; ++i) {
-            float4 v = reinterpret_cast<const float4 *>(cp)[i];
-            cf[4 * i] = v.x; cf[4 * i + 1] = v.y; cf[4 * i + 2] = v.z; cf[4 * i + 3] = v.w;
-        }
-    } else {
-#pragma unroll
-        for (int i = 0; i < NB * 3; ++i) cf[i] = cp[i];
-    }
+    const float *cf = s_cf + threadIdx.x * S;  // shared by all batch entries when broadcast
     for (int b = 0; b < n_batch; ++b) {
         size_t e = (size_t)b * n_rows + r;
         float cr = 0.f, cg = 0.f, cb = 0.f;
@@ -145,60 +188,69 @@ sh_fwd_kernel(int64_t n_rows, int n_batch, int K, const float *__restrict__ dirs
     }
 }
 
-// per-row coefficient variant (coeffs [B*R, K, 3]): n_batch folded into n_rows by the host
 template <int DEG, bool NEED_DIRS>
 __global__ void __launch_bounds__(kThreads)
 sh_bwd_kernel(int64_t n_rows, int n_batch, int K, const float *__restrict__ dirs, const float *__restrict__ coeffs,
               const uint8_t *__restrict__ masks, const float *__restrict__ v_colors, float *__restrict__ v_coeffs,
               float *__restrict__ v_dirs) {
     constexpr int NB = (DEG + 1) * (DEG + 1);
-    int64_t r = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    if (r >= n_rows) return;
-    float acc[NB * 3];
+    constexpr int S = (NB * 3) | 1;
+    __shared__ float s_cf[kThreads * S];  // coefficients in, then (same rows) their gradients out
+    const int64_t r0 = (int64_t)blockIdx.x * kThreads;
+    const int rows = (int)min((int64_t)kThreads, n_rows - r0);
+    if (NEED_DIRS) {
+        rows_to_smem<NB * 3>(s_cf, coeffs, r0, rows, K * 3);
+        __syncthreads();
+    }
+    const int64_t r = r0 + threadIdx.x;
+    float *cp = s_cf + threadIdx.x * S;
+    if (r < n_rows) {
+        float acc[NB * 3];
 #pragma unroll
-    for (int i = 0; i < NB * 3; ++i) acc[i] = 0.f;
-    const float *cp = coeffs + (size_t)r * K * 3;
-    for (int b = 0; b < n_batch; ++b) {
-        size_t e = (size_t)b * n_rows + r;
-        bool on = (masks == nullptr) || masks[e];
-        float vdx = 0.f, vdy = 0.f, vdz = 0.f;
-        if (on) {
-            const float *dp = dirs + 3 * e;
-            float x = dp[0], y = dp[1], z = dp[2];
-            float inorm = rsqrtf(x * x + y * y + z * z);
-            x *= inorm; y *= inorm; z *= inorm;
-            const float *vp = v_colors + 3 * e;
-            float vr = vp[0], vg = vp[1], vb = vp[2];
-            float bases[NB];
-            sh_bases<DEG>(x, y, z, bases);
+        for (int i = 0; i < NB * 3; ++i) acc[i] = 0.f;
+        for (int b = 0; b < n_batch; ++b) {
+            size_t e = (size_t)b * n_rows + r;
+            bool on = (masks == nullptr) || masks[e];
+            float vdx = 0.f, vdy = 0.f, vdz = 0.f;
+            if (on) {
+                const float *dp = dirs + 3 * e;
+                float x = dp[0], y = dp[1], z = dp[2];
+                float inorm = rsqrtf(x * x + y * y + z * z);
+                x *= inorm; y *= inorm; z *= inorm;
+                const float *vp = v_colors + 3 * e;
+                float vr = vp[0], vg = vp[1], vb = vp[2];
+                float bases[NB];
+                sh_bases<DEG>(x, y, z, bases);
 #pragma unroll
-            for (int k = 0; k < NB; ++k) {
-                acc[3 * k] += bases[k] * vr;
-                acc[3 * k + 1] += bases[k] * vg;
-                acc[3 * k + 2] += bases[k] * vb;
+                for (int k = 0; k < NB; ++k) {
+                    acc[3 * k] += bases[k] * vr;
+                    acc[3 * k + 1] += bases[k] * vg;
+                    acc[3 * k + 2] += bases[k] * vb;
+                }
+                if (NEED_DIRS) {
+                    float g[NB];
+#pragma unroll
+                    for (int k = 0; k < NB; ++k) g[k] = cp[3 * k] * vr + cp[3 * k + 1] * vg + cp[3 * k + 2] * vb;
+                    float vx, vy, vz;
+                    sh_bases_vjp<DEG>(x, y, z, g, vx, vy, vz);
+                    // VJP of the normalisation d / |d|
+                    float dot = x * vx + y * vy + z * vz;
+                    vdx = (vx - dot * x) * inorm;
+                    vdy = (vy - dot * y) * inorm;
+                    vdz = (vz - dot * z) * inorm;
+                }
             }
             if (NEED_DIRS) {
-                float g[NB];
-#pragma unroll
-                for (int k = 0; k < NB; ++k) g[k] = cp[3 * k] * vr + cp[3 * k + 1] * vg + cp[3 * k + 2] * vb;
-                float vx, vy, vz;
-                sh_bases_vjp<DEG>(x, y, z, g, vx, vy, vz);
-                // VJP of the normalisation d / |d|
-                float dot = x * vx + y * vy + z * vz;
-                vdx = (vx - dot * x) * inorm;
-                vdy = (vy - dot * y) * inorm;
-                vdz = (vz - dot * z) * inorm;
+                float *op = v_dirs + 3 * e;
+                op[0] = vdx; op[1] = vdy; op[2] = vdz;
             }
         }
-        if (NEED_DIRS) {
-            float *op = v_dirs + 3 * e;
-            op[0] = vdx; op[1] = vdy; op[2] = vdz;
-        }
-    }
-    float *op = v_coeffs + (size_t)r * K * 3;
+        // only this thread ever touches its shared row: overwrite the coefficients with their gradients
 #pragma unroll
-    for (int i = 0; i < NB * 3; ++i) op[i] = acc[i];
-    for (int i = NB * 3; i < K * 3; ++i) op[i] = 0.f;
+        for (int i = 0; i < NB * 3; ++i) cp[i] = acc[i];
+    }
+    __syncthreads();
+    smem_to_rows<NB * 3>(s_cf, v_coeffs, r0, rows, K * 3);
 }
 
 }  // namespace
