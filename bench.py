@@ -247,17 +247,45 @@ def run_b200(args):
     h2d = sum(t.numel() * t.element_size() for t in host_params)
     d2h = out_c.numel() * 4 + out_a.numel() * 4 + 4
 
-    def e2e_step():
-        ps = [t.to(dev, non_blocking=True).requires_grad_(True) for t in host_params]
-        rc, ra, loss, _ = iteration(ps)
-        out_c.copy_(rc.detach(), non_blocking=True)
-        out_a.copy_(ra.detach(), non_blocking=True)
-        loss.item()
+    # double-buffered: step i+1's host->device copy (copy stream) overlaps step i's kernels; every step
+    # still copies all of its inputs from pinned host memory and reads its image + loss back to the host
+    main_stream = torch.cuda.current_stream()
+    copy_stream = torch.cuda.Stream()
+    bufs = [[torch.empty(t.shape, dtype=t.dtype, device=dev) for t in host_params] for _ in range(2)]
+    ready = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
 
-    for _ in range(3):
-        e2e_step()
+    def prefetch(i):
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[i % 2])
+            for b, h in zip(bufs[i % 2], host_params):
+                b.copy_(h, non_blocking=True)
+            ready[i % 2].record(copy_stream)
+
+    def e2e_loop(steps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        copy_stream.wait_event(a)
+        for e in consumed:
+            e.record()
+        prefetch(0)
+        for i in range(steps):
+            if i + 1 < steps:
+                prefetch(i + 1)
+            main_stream.wait_event(ready[i % 2])
+            ps = [t.detach().requires_grad_(True) for t in bufs[i % 2]]
+            rc, ra, loss, _ = iteration(ps)
+            consumed[i % 2].record()
+            out_c.copy_(rc.detach(), non_blocking=True)
+            out_a.copy_(ra.detach(), non_blocking=True)
+            loss.item()  # the host reads every step's result before the next step is issued
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b)
+
+    e2e_loop(3)
     barrier()
-    e2e_ms = timed_loop(e2e_step, args.steps)
+    e2e_ms = e2e_loop(args.steps)
     barrier()
 
     ms = torch.tensor([total_ms / args.steps, e2e_ms / args.steps], device=dev, dtype=torch.float64)
@@ -292,7 +320,9 @@ def run_b200(args):
                        "l2": "inputs 236 MB/step > 126 MB L2 and a 256 MB flush write between steps (untimed)",
                        "timing": "sum of per-step CUDA-event times on the launch stream, max over ranks"},
             "e2e": {"value": round(world * 1e3 / ms_e2e, 3), "unit": "iters/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "ms_per_step": round(ms_e2e, 4)},
+                    "d2h_bytes_per_step": d2h, "ms_per_step": round(ms_e2e, 4),
+                    "pipeline": "double-buffered H2D on a copy stream (step i+1's copy overlaps step i's kernels); "
+                                "one CUDA-event bracket around all K steps; inputs (236 MB/step by DMA) exceed L2"},
             "gpu_launches": launches, "wall_s_timed_region": round(wall_s, 3), "clocks": clk,
             "roofline": roof, "stages": stages,
         }

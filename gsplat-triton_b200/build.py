@@ -19,7 +19,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "--use_fast_math", "-Xcompiler", "-fPIC", "-I", os.path.join(ROOT, "include"), "-I", CSRC,
-]
+] + os.environ.get("GSB_NVCC_FLAGS", "").split()  # tuning experiments: e.g. GSB_NVCC_FLAGS=-DGSB_BWD_MIN_BLOCKS=3
 
 
 def _stale(target, deps):
@@ -35,6 +35,11 @@ def build(force=False, verbose=False):
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
     headers.append(os.path.join(ROOT, "include", "gsplat_b200.h"))
     headers.append(os.path.abspath(__file__))
+    stamp = os.path.join(OBJ_DIR, "flags.txt")
+    flags_now = " ".join(FLAGS)
+    if not os.path.exists(stamp) or open(stamp).read() != flags_now:
+        force = True  # different compile flags than the objects on disk were built with
+        open(stamp, "w").write(flags_now)
     jobs = []
     objs = []
     for src in SOURCES:

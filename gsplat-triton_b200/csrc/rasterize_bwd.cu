@@ -13,98 +13,136 @@
 //                           v_xy = v_sigma (a dx + b dy, b dx + c dy) ; v_o = e^-sigma v_alpha
 //
 // B200 design (what differs from the reference's "warpSum of every value, lane-0 atomics"):
-//   * same compacted staging, per-warp block masks and ballot-compacted splat lists as the forward kernel;
-//   * the 6+D(+2) per-pixel gradient values are reduced over the warp with a *transposing*
-//     butterfly: every xor step halves the number of live values per lane, so 9 values cost
-//     12 shuffles instead of 45; the sums end up one per lane;
-//   * those lanes add into one row of sums per staged splat in shared memory (9 KB at D=3, so 4
-//     CTAs stay resident per SM); after the batch one thread per staged splat issues a single set
-//     of global reductions per (tile, splat) instead of one per (warp, splat).
+//   * same compacted staging, exact per-warp block culling and ballot-compacted splat lists as the
+//     forward kernel;
+//   * two-phase reduction without a cross-lane reduction tree. Phase 1 (lane = pixel, sequential over
+//     the warp's splats because of the transmittance recurrence) only produces two scalars per
+//     (pixel, splat): w1 = d loss / d sigma and w2 = alpha T, parked in a per-warp shared table.
+//     Phase 2 (every 16 splats; lane = splat x half block) walks the 32 pixels of the block and
+//     accumulates in registers the moments of w1 about the block centre (sum w1 {1, x, y, x^2, xy, y^2})
+//     and sum w2 v_out; the conic / mean / opacity gradients are closed forms of those moments.
+//     ~11 issue slots per (warp, splat) instead of ~70 for a shuffle tree over 9 values;
+//   * one set of global reductions per (warp, splat), issued by the lane that owns the splat.
 #include "rasterize_common.cuh"
 
 namespace raster {
-
-// ---- transposing warp reduction ---------------------------------------------------------------
-// After the call, v[i] for i < ceil(N/32) holds the warp-wide sum of the original value
-// reduce_origin<N>(lane, i) (or garbage when that returns -1).
-template <int N>
-__device__ __forceinline__ void warp_transpose_sum(float (&v)[N], int lane) {
-    int n = N;
-#pragma unroll
-    for (int m = 16; m >= 1; m >>= 1) {
-        if (n > 1) {
-            const int h = (n + 1) >> 1;
-            const bool up = (lane & m) != 0;
-#pragma unroll
-            for (int i = 0; i < (N + 1) / 2; ++i) {
-                if (i < h) {
-                    const float lo = v[i];
-                    const float hi = (i + h < n) ? v[i + h] : 0.f;
-                    const float send = up ? lo : hi;
-                    const float keep = up ? hi : lo;
-                    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, m);
-                }
-            }
-            n = h;
-        } else {
-            v[0] += __shfl_xor_sync(0xffffffffu, v[0], m);
-        }
-    }
-}
-
-// which original value ends up in v[i] of this lane; -1 = none (padding or a duplicate copy)
-template <int N>
-__device__ __forceinline__ int reduce_origin(int lane, int i) {
-    int cnt[6];
-    cnt[0] = N;
-#pragma unroll
-    for (int k = 0; k < 5; ++k) cnt[k + 1] = cnt[k] > 1 ? (cnt[k] + 1) >> 1 : 1;
-    int p = i;
-    bool ok = i < cnt[5];
-#pragma unroll
-    for (int k = 4; k >= 0; --k) {
-        const bool up = (lane & (16 >> k)) != 0;
-        if (cnt[k] > 1) {
-            p += up ? cnt[k + 1] : 0;
-            ok = ok && (p < cnt[k]);
-        } else {
-            ok = ok && !up;  // plain butterfly step: every lane holds a copy, the low lane owns it
-        }
-    }
-    return ok ? p : -1;
-}
-
-// Layout of the reduced values: [0,1] v_xy, [2..4] v_conic, [5] v_opacity, [6..6+D) v_color, then [abs_x, abs_y]
-template <int D, bool ABS>
-struct GradLayout {
-    static constexpr int kN = 6 + D + (ABS ? 2 : 0);
-    static constexpr int kPerLane = (kN + 31) / 32;
-};
 
 struct GradTargets {
     float *v_means2d, *v_conics, *v_opacities, *v_colors, *v_abs;
 };
 
-template <int D, bool ABS>
-__device__ __forceinline__ float *grad_address(const GradTargets &t, int value, int64_t g) {
-    if (value < 2) return t.v_means2d + 2 * g + value;
-    if (value < 5) return t.v_conics + 3 * g + (value - 2);
-    if (value == 5) return t.v_opacities + g;
-    if (value < 6 + D) return t.v_colors + (int64_t)D * g + (value - 6);
-    return t.v_abs + 2 * g + (value - 6 - D);
-}
+#ifndef GSB_BWD_MIN_BLOCKS
+#define GSB_BWD_MIN_BLOCKS 4  // resident CTAs per SM the D <= 4 instantiations are register-limited to
+#endif
+constexpr int kChunk = 16;       // splats per splat-parallel reduction pass
+constexpr int kChunkStride = 33; // float2 row stride of the per-warp weight table (bank-conflict free)
 
-// Shared-memory layout (dynamic): the staged batch + one row of NV gradient sums per staged splat.
-template <int D, bool ABS>
+template <int D>
 struct BwdSmem {
-    static constexpr int NV = GradLayout<D, ABS>::kN;
-    static constexpr size_t bytes = sizeof(float4) * kThreads + sizeof(float2) * kThreads +
-                                    sizeof(int) * (3 * kThreads + 2 * kWarps) +
-                                    sizeof(float) * kThreads * (D + NV);
+    static constexpr int DP = (D + 3) & ~3;  // per-pixel cotangent row, padded for 16-byte loads
+    static constexpr int CS = D <= 4 ? 4 : D;  // colour row of a staged splat (one float4 when D <= 4)
+    static constexpr size_t bytes = sizeof(float4) * 2 * kThreads                       // s_P, s_B
+                                    + sizeof(float) * kThreads * CS                     // s_col
+                                    + sizeof(float2) * kWarps * kChunk * kChunkStride   // s_w
+                                    + sizeof(float) * kWarps * (32 * DP + 4)            // s_vout
+                                    + sizeof(int) * (kWarps * kChunk + 2 * kWarps);     // s_cj, counters
 };
 
+// Second half of the backward pass for up to kChunk splats of ONE warp (8x4 pixel block):
+// lane (s = lane & 15, h = lane >> 4) owns splat s and sums over the 16 pixels of block rows 2h, 2h+1.
+// Inputs per (splat, pixel): w1 = d loss / d sigma, w2 = alpha * T (weight of the colour cotangent).
+// Geometry gradients come from the moments of w1 over the block, taken about the block centre:
+//   sum w1 dx = ux M0 - Mx, sum w1 dx^2 = ux^2 M0 - 2 ux Mx + Mxx, ...   (dx = ux - cx, ux = mu_x - centre_x)
 template <int D, bool ABS>
-__global__ void __launch_bounds__(kThreads, (D <= 4 ? 4 : (D <= 16 ? 3 : 2)))
+__device__ __forceinline__ void reduce_chunk(int count, int lane, const float2 *s_w, const float *s_vout,
+                                             const int *s_cj, const float4 *s_P, const float4 *s_B,
+                                             const int32_t *__restrict__ flatten_ids,
+                                             float bcx, float bcy, const GradTargets &out) {
+    constexpr int DP = BwdSmem<D>::DP;
+    __syncwarp();
+    const int s = lane & (kChunk - 1), h = lane >> 4;
+    const float2 *wrow = s_w + s * kChunkStride + h * 16;
+    const float *vrow = s_vout + h * (16 * DP + 4);
+    float R0[2] = {0.f, 0.f}, Rx[2] = {0.f, 0.f}, Rxx[2] = {0.f, 0.f};
+    float col[D];
+#pragma unroll
+    for (int k = 0; k < D; ++k) col[k] = 0.f;
+    float abs_x = 0.f, abs_y = 0.f;
+    const int j = s_cj[s < count ? s : 0];
+    const float4 mu = s_P[j];  // (x, y, sorted index, -)
+    const float4 b4 = s_B[j];
+    const float ux = mu.x - bcx, uy = mu.y - bcy;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const float2 w = wrow[i];
+        const float cx = (float)(i & 7) - 3.5f;
+        const int r = i >> 3;
+        R0[r] += w.x;
+        Rx[r] = fmaf(w.x, cx, Rx[r]);
+        Rxx[r] = fmaf(w.x, cx * cx, Rxx[r]);
+#pragma unroll
+        for (int k4 = 0; k4 < DP / 4; ++k4) {
+            const float4 v = *reinterpret_cast<const float4 *>(vrow + i * DP + 4 * k4);
+            if (4 * k4 + 0 < D) col[4 * k4 + 0] = fmaf(w.y, v.x, col[4 * k4 + 0]);
+            if (4 * k4 + 1 < D) col[4 * k4 + 1] = fmaf(w.y, v.y, col[4 * k4 + 1]);
+            if (4 * k4 + 2 < D) col[4 * k4 + 2] = fmaf(w.y, v.z, col[4 * k4 + 2]);
+            if (4 * k4 + 3 < D) col[4 * k4 + 3] = fmaf(w.y, v.w, col[4 * k4 + 3]);
+        }
+        if (ABS) {
+            const float dx = ux - cx, dy = uy - ((float)(2 * h + r) - 1.5f);
+            abs_x += fabsf(w.x * (b4.x * dx + b4.y * dy));
+            abs_y += fabsf(w.x * (b4.y * dx + b4.z * dy));
+        }
+    }
+    // rows 2h, 2h+1 have centred y = 2h - 1.5, 2h - 0.5
+    const float y0 = (float)(2 * h) - 1.5f, y1 = y0 + 1.0f;
+    float M0 = R0[0] + R0[1], Mx = Rx[0] + Rx[1], Mxx = Rxx[0] + Rxx[1];
+    float My = y0 * R0[0] + y1 * R0[1], Mxy = y0 * Rx[0] + y1 * Rx[1], Myy = y0 * y0 * R0[0] + y1 * y1 * R0[1];
+    // other half of the block
+    M0 += __shfl_xor_sync(0xffffffffu, M0, 16);
+    Mx += __shfl_xor_sync(0xffffffffu, Mx, 16);
+    My += __shfl_xor_sync(0xffffffffu, My, 16);
+    Mxx += __shfl_xor_sync(0xffffffffu, Mxx, 16);
+    Mxy += __shfl_xor_sync(0xffffffffu, Mxy, 16);
+    Myy += __shfl_xor_sync(0xffffffffu, Myy, 16);
+#pragma unroll
+    for (int k = 0; k < D; ++k) col[k] += __shfl_xor_sync(0xffffffffu, col[k], 16);
+    if (ABS) {
+        abs_x += __shfl_xor_sync(0xffffffffu, abs_x, 16);
+        abs_y += __shfl_xor_sync(0xffffffffu, abs_y, 16);
+    }
+    if (h == 0 && s < count) {
+        const int64_t g = flatten_ids[__float_as_int(mu.z)];
+        const float Sx = ux * M0 - Mx, Sy = uy * M0 - My;
+        const float Sxx = fmaf(ux, fmaf(ux, M0, -2.f * Mx), Mxx);
+        const float Syy = fmaf(uy, fmaf(uy, M0, -2.f * My), Myy);
+        const float Sxy = fmaf(ux, fmaf(uy, M0, -My), fmaf(-uy, Mx, Mxy));
+        float v[6];
+        v[0] = b4.x * Sx + b4.y * Sy;
+        v[1] = b4.y * Sx + b4.z * Sy;
+        v[2] = 0.5f * Sxx;
+        v[3] = Sxy;
+        v[4] = 0.5f * Syy;
+        v[5] = -__fdividef(M0, b4.w);  // v_opacity = sum e^-sigma v_alpha = -sum w1 / opacity
+        if (v[0] != 0.f) atomicAdd(out.v_means2d + 2 * g, v[0]);
+        if (v[1] != 0.f) atomicAdd(out.v_means2d + 2 * g + 1, v[1]);
+        if (v[2] != 0.f) atomicAdd(out.v_conics + 3 * g, v[2]);
+        if (v[3] != 0.f) atomicAdd(out.v_conics + 3 * g + 1, v[3]);
+        if (v[4] != 0.f) atomicAdd(out.v_conics + 3 * g + 2, v[4]);
+        if (v[5] != 0.f) atomicAdd(out.v_opacities + g, v[5]);
+#pragma unroll
+        for (int k = 0; k < D; ++k)
+            if (col[k] != 0.f) atomicAdd(out.v_colors + (int64_t)D * g + k, col[k]);
+        if (ABS) {
+            if (abs_x != 0.f) atomicAdd(out.v_abs + 2 * g, abs_x);
+            if (abs_y != 0.f) atomicAdd(out.v_abs + 2 * g + 1, abs_y);
+        }
+    }
+    __syncwarp();
+}
+
+template <int D, bool ABS>
+__global__ void __launch_bounds__(kThreads, (D <= 4 ? GSB_BWD_MIN_BLOCKS : (D <= 16 ? 2 : 1)))
 rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, const float4 *__restrict__ recB,
                      const float *__restrict__ colors, const float *__restrict__ backgrounds,
                      const uint8_t *__restrict__ masks, int W, int H, int tw, int th,
@@ -112,23 +150,29 @@ rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
                      const float *__restrict__ render_alphas, const int32_t *__restrict__ last_ids,
                      const float *__restrict__ v_render_colors, const float *__restrict__ v_render_alphas,
                      GradTargets out) {
-    using L = GradLayout<D, ABS>;
-    constexpr int NV = L::kN;
+    constexpr int DP = BwdSmem<D>::DP;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float4 *s_B = reinterpret_cast<float4 *>(smem_raw);
-    float2 *s_xy = reinterpret_cast<float2 *>(s_B + kThreads);
-    int *s_idx = reinterpret_cast<int *>(s_xy + kThreads);
-    int *s_gid = s_idx + kThreads;
-    unsigned *s_mask = reinterpret_cast<unsigned *>(s_gid + kThreads);
-    int *s_wcnt = reinterpret_cast<int *>(s_mask + kThreads);  // kWarps
-    int *s_red = s_wcnt + kWarps;                              // kWarps
-    float *s_col = reinterpret_cast<float *>(s_red + kWarps);  // kThreads * D
-    float *s_acc = s_col + kThreads * D;                       // kThreads * NV, zero between batches
+    constexpr int CS = BwdSmem<D>::CS;
+    // staged batch: P = (x, y, sorted index, warp mask), B = (conic xx, xy, yy, opacity), colours; same stride
+    float4 *s_P = reinterpret_cast<float4 *>(smem_raw);
+    float4 *s_B = s_P + kThreads;
+    float *s_col = reinterpret_cast<float *>(s_B + kThreads);
+    float2 *s_w_all = reinterpret_cast<float2 *>(s_col + kThreads * CS);
+    float *s_vout_all = reinterpret_cast<float *>(s_w_all + kWarps * kChunk * kChunkStride);
+    int *s_cj_all = reinterpret_cast<int *>(s_vout_all + kWarps * (32 * DP + 4));
+    int *s_wcnt = s_cj_all + kWarps * kChunk;
+    int *s_red = s_wcnt + kWarps;
 
     const TileGeom tg = tile_geometry(n_isects, W, H, tw, th, C, offsets);
     if (masks != nullptr && !masks[tg.tile_id]) return;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const float pxf = (float)tg.px + 0.5f, pyf = (float)tg.py + 0.5f;
+    float2 *s_w = s_w_all + warp * kChunk * kChunkStride;
+    float *s_vout = s_vout_all + warp * (32 * DP + 4);
+    int *s_cj = s_cj_all + warp * kChunk;
+    // centre of this warp's 8x4 block, in pixel-centre coordinates
+    const float bcx = (float)(tg.tile_x * kTile + (warp & 1) * 8) + 4.0f;
+    const float bcy = (float)(tg.tile_y * kTile + (warp >> 1) * 4) + 2.0f;
 
     // per-pixel state
     const float T_final = tg.inside ? 1.0f - render_alphas[tg.pix_id] : 1.0f;
@@ -148,115 +192,90 @@ rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
     }
     // d(out)/d(alpha_i) carries T_final/(1-alpha_i) * (v_alpha_out - bg . v_out)
     const float tail = T_final * (v_out_a - bg_dot);
+    {   // colour cotangents of the block's pixels, for the splat-parallel pass
+        float *dst = s_vout + lane * DP + (lane >> 4) * 4;
+#pragma unroll
+        for (int k = 0; k < DP; ++k) dst[k] = k < D ? v_out[k] : 0.f;
+    }
 
     const int warp_last = warp_max_i(bin_final);
     if (lane == 0) s_red[warp] = warp_last;
-    for (int i = tid; i < kThreads * NV; i += kThreads) s_acc[i] = 0.f;
     __syncthreads();
     int tile_last = s_red[0];
 #pragma unroll
     for (int w = 1; w < kWarps; ++w) tile_last = max(tile_last, s_red[w]);
-
-    // lane-constant ownership of the reduced values
-    int own[L::kPerLane];
-#pragma unroll
-    for (int i = 0; i < L::kPerLane; ++i) own[i] = reduce_origin<NV>(lane, i);
 
     const int hi_start = min(tg.range_end - 1, tile_last);
     for (int hi = hi_start; hi >= tg.range_start; hi -= kThreads) {
         const int idx = hi - tid;
         unsigned mask = 0u;
         int g = 0;
-        float4 A;
+        float4 A, B;
         if (idx >= tg.range_start) {
             g = flatten_ids[idx];
             A = __ldg(recA + g);
-            mask = splat_block_mask(A, tg.tile_x * kTile, tg.tile_y * kTile);
+            B = __ldg(recB + g);
+            mask = splat_block_mask(A, B, tg.tile_x * kTile, tg.tile_y * kTile);
         }
         int total;
-        const int slot = stage_slot(mask != 0u, s_wcnt, total);  // syncs: previous batch fully flushed
+        const int slot = stage_slot(mask != 0u, s_wcnt, total);  // syncs: previous batch fully consumed
         if (mask != 0u) {
-            s_xy[slot] = make_float2(A.x, A.y);
-            s_B[slot] = __ldg(recB + g);
-            s_idx[slot] = idx;
-            s_gid[slot] = g;
-            s_mask[slot] = mask;
+            s_P[slot] = make_float4(A.x, A.y, __int_as_float(idx), __uint_as_float(mask));
+            s_B[slot] = B;
             const float *cp = colors + (size_t)g * D;
 #pragma unroll
-            for (int k = 0; k < D; ++k) s_col[slot * D + k] = cp[k];
+            for (int k = 0; k < CS; ++k) s_col[slot * CS + k] = k < D ? cp[k] : 0.f;
         }
         __syncthreads();
 
+        int n_chunk = 0;
         for (int c0 = 0; c0 < total; c0 += 32) {
             const int jl = c0 + lane;
-            // this warp's splats of the chunk: box reaches its 8x4 block and not behind every pixel's last id
-            unsigned todo = __ballot_sync(0xffffffffu, jl < total && ((s_mask[jl] >> warp) & 1u) &&
-                                                           s_idx[jl] <= warp_last);
+            // this warp's splats of the chunk: may touch its 8x4 block and not behind every pixel's last id
+            bool mine = false;
+            if (jl < total) {
+                const float4 p4 = s_P[jl];
+                mine = ((__float_as_uint(p4.w) >> warp) & 1u) && __float_as_int(p4.z) <= warp_last;
+            }
+            unsigned todo = __ballot_sync(0xffffffffu, mine);
             while (todo) {
                 const int j = c0 + __ffs(todo) - 1;
                 todo &= todo - 1u;
-                const float2 xy = s_xy[j];
+                const float4 p4 = s_P[j];
                 const float4 b4 = s_B[j];
-                const float dx = xy.x - pxf, dy = xy.y - pyf;
+                const float dx = p4.x - pxf, dy = p4.y - pyf;
                 const float sigma = 0.5f * (b4.x * dx * dx + b4.z * dy * dy) + b4.y * dx * dy;
                 const float vis = __expf(-sigma);
                 const float ov = b4.w * vis;
                 const float alpha = fminf(kAlphaMax, ov);
-                const bool hit = (s_idx[j] <= bin_final) && !(sigma < 0.f) && !(alpha < kAlphaMin);
+                const bool hit = (__float_as_int(p4.z) <= bin_final) && !(sigma < 0.f) && !(alpha < kAlphaMin);
                 if (!__any_sync(0xffffffffu, hit)) continue;
 
-                float v[NV];
-#pragma unroll
-                for (int i = 0; i < NV; ++i) v[i] = 0.f;
+                float w1 = 0.f, w2 = 0.f;
                 if (hit) {
                     const float ra = __fdividef(1.0f, 1.0f - alpha);
                     T *= ra;
-                    const float fac = alpha * T;
+                    w2 = alpha * T;
                     float v_alpha = 0.f;
 #pragma unroll
                     for (int k = 0; k < D; ++k) {
-                        const float c = s_col[j * D + k];
-                        v[6 + k] = fac * v_out[k];
+                        const float c = s_col[j * CS + k];
                         v_alpha = fmaf(c * T - S[k] * ra, v_out[k], v_alpha);
-                        S[k] = fmaf(c, fac, S[k]);
+                        S[k] = fmaf(c, w2, S[k]);
                     }
                     v_alpha = fmaf(tail, ra, v_alpha);
-                    if (ov <= kAlphaMax) {
-                        const float v_sigma = -ov * v_alpha;
-                        v[0] = v_sigma * (b4.x * dx + b4.y * dy);
-                        v[1] = v_sigma * (b4.y * dx + b4.z * dy);
-                        v[2] = 0.5f * v_sigma * dx * dx;
-                        v[3] = v_sigma * dx * dy;
-                        v[4] = 0.5f * v_sigma * dy * dy;
-                        v[5] = vis * v_alpha;
-                        if (ABS) {
-                            v[6 + D] = fabsf(v[0]);
-                            v[7 + D] = fabsf(v[1]);
-                        }
-                    }
+                    if (ov <= kAlphaMax) w1 = -ov * v_alpha;  // no gradient through the alpha clamp
                 }
-                warp_transpose_sum<NV>(v, lane);
-                float *dst = s_acc + j * NV;
-#pragma unroll
-                for (int i = 0; i < L::kPerLane; ++i)
-                    if (own[i] >= 0) atomicAdd(dst + own[i], v[i]);
-            }
-        }
-
-        __syncthreads();
-        // one flush per (tile, splat): the row owner adds the tile's sums to global memory and re-zeroes the row
-        if (tid < total) {
-            const int64_t gid = s_gid[tid];
-            float *row = s_acc + tid * NV;
-#pragma unroll
-            for (int i = 0; i < NV; ++i) {
-                const float a = row[i];
-                if (a != 0.f) {
-                    atomicAdd(grad_address<D, ABS>(out, i, gid), a);
-                    row[i] = 0.f;
+                s_w[n_chunk * kChunkStride + lane] = make_float2(w1, w2);
+                if (lane == 0) s_cj[n_chunk] = j;
+                if (++n_chunk == kChunk) {
+                    reduce_chunk<D, ABS>(n_chunk, lane, s_w, s_vout, s_cj, s_P, s_B, flatten_ids, bcx, bcy, out);
+                    n_chunk = 0;
                 }
             }
         }
+        if (n_chunk > 0)
+            reduce_chunk<D, ABS>(n_chunk, lane, s_w, s_vout, s_cj, s_P, s_B, flatten_ids, bcx, bcy, out);
     }
 }
 
@@ -266,7 +285,7 @@ int launch_bwd(int C, int64_t n_isects, const float *recA, const float *recB, co
                const int32_t *offsets, const int32_t *flatten_ids, const float *render_alphas,
                const int32_t *last_ids, const float *v_render_colors, const float *v_render_alphas,
                GradTargets out, cudaStream_t stream) {
-    constexpr size_t smem = BwdSmem<D, ABS>::bytes;
+    constexpr size_t smem = BwdSmem<D>::bytes;
     auto kernel = rasterize_bwd_kernel<D, ABS>;
     static bool configured = false;  // one instantiation per (D, ABS)
     if (!configured) {

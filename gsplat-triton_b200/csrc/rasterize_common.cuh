@@ -78,9 +78,32 @@ __device__ __forceinline__ bool splat_touches(const float4 &A, const Rect &r) {
     return !((A.x + A.z < r.xlo) | (A.x - A.z > r.xhi) | (A.y + A.w < r.ylo) | (A.y - A.w > r.yhi));
 }
 
-// bit w set <=> the splat's {alpha >= 1/255} box reaches the 8x4 pixel block of warp w
-// (bx = w & 1, by = w >> 1) of the tile whose first pixel is (x0, y0). 0 = misses the whole tile.
-__device__ __forceinline__ unsigned splat_block_mask(const float4 &A, int x0, int y0) {
+// Smallest sigma(p) = .5 (a ex^2 + c ey^2) + b ex ey, e = p - mu, over the rectangle of pixel centres
+// [X0, X1] x [Y0, Y1], minus a bound on the float error of evaluating it. sigma is convex, so unless
+// mu lies inside the rectangle the minimum sits on one of the (at most two) edges facing mu.
+__device__ __forceinline__ float min_sigma_over_rect(float mx, float my, float a, float b, float c, float b_over_a,
+                                                     float b_over_c, float X0, float X1, float Y0, float Y1) {
+    const float px = fminf(fmaxf(mx, X0), X1), py = fminf(fmaxf(my, Y0), Y1);
+    const float ex = px - mx, ey = py - my;
+    if (ex == 0.f && ey == 0.f) return 0.f;
+    // edge x = px: free coordinate y, unconstrained optimum at my - (b/c) ex
+    const float ey1 = fminf(fmaxf(my - b_over_c * ex, Y0), Y1) - my;
+    const float s1 = 0.5f * (a * ex * ex + c * ey1 * ey1), t1 = b * ex * ey1;
+    // edge y = py
+    const float ex2 = fminf(fmaxf(mx - b_over_a * ey, X0), X1) - mx;
+    const float s2 = 0.5f * (a * ex2 * ex2 + c * ey * ey), t2 = b * ex2 * ey;
+    const float q1 = (s1 + t1) - 1e-5f * (s1 + fabsf(t1));
+    const float q2 = (s2 + t2) - 1e-5f * (s2 + fabsf(t2));
+    // an edge that does not face mu (ex == 0 resp. ey == 0) degenerates to a line through the
+    // rectangle that contains the other candidate's optimum or a larger value: min() stays valid
+    return fminf(ex != 0.f ? q1 : q2, ey != 0.f ? q2 : q1);
+}
+
+// bit w set <=> warp w's 8x4 pixel block (bx = w & 1, by = w >> 1) of the tile whose first pixel is
+// (x0, y0) may contain a pixel with alpha >= 1/255 for this splat. 0 = the whole tile can skip it.
+// Two levels: the cheap bounding box of the {alpha >= 1/255} ellipse, then for the blocks that
+// survive the exact minimum of sigma over the block against tau = ln(255 opacity) (+ margins).
+__device__ __forceinline__ unsigned splat_block_mask(const float4 &A, const float4 &B, int x0, int y0) {
     const float xlo = A.x - A.z, xhi = A.x + A.z, ylo = A.y - A.w, yhi = A.y + A.w;
     const float fx = (float)x0, fy = (float)y0;
     unsigned xb = 0u, yb = 0u;
@@ -93,7 +116,20 @@ __device__ __forceinline__ unsigned splat_block_mask(const float4 &A, int x0, in
     unsigned m = 0u;
 #pragma unroll
     for (int by = 0; by < 4; ++by) m |= ((yb >> by) & 1u) ? (xb << (2 * by)) : 0u;
-    return m;
+    if (m == 0u || !(A.z < 3.0e38f)) return m;  // box misses the tile / not an ellipse (never culled)
+    const float tau = __logf(255.0f * B.w) * 1.0001f + 2e-3f;
+    const float b_over_a = __fdividef(B.y, B.x), b_over_c = __fdividef(B.y, B.z);
+    unsigned keep = 0u;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+        if ((m >> w) & 1u) {
+            const float X0 = fx + 8.f * (w & 1) + 0.5f, Y0 = fy + 4.f * (w >> 1) + 0.5f;
+            const float q = min_sigma_over_rect(A.x, A.y, B.x, B.y, B.z, b_over_a, b_over_c, X0, X0 + 7.f, Y0,
+                                                Y0 + 3.f);
+            keep |= (q <= tau) ? (1u << w) : 0u;
+        }
+    }
+    return keep;
 }
 
 struct TileGeom {

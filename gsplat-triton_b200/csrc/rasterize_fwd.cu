@@ -33,20 +33,30 @@ splat_pack_kernel(int64_t P, const float *__restrict__ means2d, const float *__r
     recB[g] = make_float4(a, b, c, o);
 }
 
+#ifndef GSB_FWD_MIN_BLOCKS
+#define GSB_FWD_MIN_BLOCKS 5
+#endif
+
 template <int D>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, (D <= 4 ? GSB_FWD_MIN_BLOCKS : 1))
 rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, const float4 *__restrict__ recB,
                      const float *__restrict__ colors, const float *__restrict__ backgrounds,
                      const uint8_t *__restrict__ masks, int W, int H, int tw, int th,
                      const int32_t *__restrict__ offsets, const int32_t *__restrict__ flatten_ids,
                      float *__restrict__ out_colors, float *__restrict__ out_alphas,
                      int32_t *__restrict__ last_ids) {
-    __shared__ float2 s_xy[kThreads];
-    __shared__ float4 s_B[kThreads];
-    __shared__ int s_idx[kThreads];
-    __shared__ unsigned s_mask[kThreads];
-    __shared__ float s_col[kThreads * D];
-    __shared__ int s_wcnt[kWarps];
+    // staged batch: three float4 arrays with the same 16-byte stride, so one address computation serves all
+    //   P = (x, y, sorted index, warp mask)   B = (conic xx, xy, yy, opacity)   Cq = colours when D <= 4
+    constexpr bool kPacked = (D <= 4);
+    struct __align__(16) Stage {
+        float4 P[kThreads];
+        float4 B[kThreads];
+        float4 Cq[kPacked ? kThreads : 1];
+        float col[kPacked ? 1 : kThreads * D];
+        int wcnt[kWarps];
+    };
+    __shared__ Stage st;
+    int *s_wcnt = st.wcnt;
 
     const TileGeom tg = tile_geometry(n_isects, W, H, tw, th, C, offsets);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -54,65 +64,81 @@ rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
     float pix[D];
 #pragma unroll
     for (int k = 0; k < D; ++k) pix[k] = 0.f;
-    float T = 1.0f;
+    // |T| is the transmittance; T < 0 marks a finished pixel (saturated, or outside the image)
+    float T = tg.inside ? 1.0f : -1.0f;
     int cur = 0;
 
     const bool render = (masks == nullptr) || masks[tg.tile_id];
     if (render) {
         const float pxf = (float)tg.px + 0.5f, pyf = (float)tg.py + 0.5f;
-        bool done = !tg.inside;
-        bool warp_done = __all_sync(0xffffffffu, done);
+        bool warp_done = __all_sync(0xffffffffu, T < 0.f);
 
         for (int base = tg.range_start; base < tg.range_end; base += kThreads) {
             // all 256 pixels saturated (or outside the image): nothing left to composite
-            if (__syncthreads_count(done) == kThreads) break;
+            if (__syncthreads_count(T < 0.f) == kThreads) break;
             const int idx = base + tid;
             unsigned mask = 0u;
             int g = 0;
-            float4 A;
+            float4 A, B;
             if (idx < tg.range_end) {
                 g = flatten_ids[idx];
                 A = __ldg(recA + g);
-                mask = splat_block_mask(A, tg.tile_x * kTile, tg.tile_y * kTile);
+                B = __ldg(recB + g);
+                mask = splat_block_mask(A, B, tg.tile_x * kTile, tg.tile_y * kTile);
             }
             int total;
             const int slot = stage_slot(mask != 0u, s_wcnt, total);
             if (mask != 0u) {
-                s_xy[slot] = make_float2(A.x, A.y);
-                s_B[slot] = __ldg(recB + g);
-                s_idx[slot] = idx;
-                s_mask[slot] = mask;
+                st.P[slot] = make_float4(A.x, A.y, __int_as_float(idx), __uint_as_float(mask));
+                st.B[slot] = B;
                 const float *cp = colors + (size_t)g * D;
+                if (kPacked) {
+                    float4 c4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    c4.x = cp[0];
+                    if (D > 1) c4.y = cp[1];
+                    if (D > 2) c4.z = cp[2];
+                    if (D > 3) c4.w = cp[3];
+                    st.Cq[slot] = c4;
+                } else {
 #pragma unroll
-                for (int k = 0; k < D; ++k) s_col[slot * D + k] = cp[k];
+                    for (int k = 0; k < D; ++k) st.col[slot * D + k] = cp[k];
+                }
             }
             __syncthreads();
             if (warp_done) continue;
             for (int c0 = 0; c0 < total; c0 += 32) {
                 const int jl = c0 + lane;
-                unsigned todo = __ballot_sync(0xffffffffu, jl < total && ((s_mask[jl] >> warp) & 1u));
+                unsigned todo =
+                    __ballot_sync(0xffffffffu, jl < total && ((__float_as_uint(st.P[jl].w) >> warp) & 1u));
                 while (todo) {
                     const int j = c0 + __ffs(todo) - 1;
                     todo &= todo - 1u;
-                    const float2 xy = s_xy[j];
-                    const float4 b4 = s_B[j];
-                    const float dx = xy.x - pxf, dy = xy.y - pyf;
+                    const float4 p4 = st.P[j];
+                    const float4 b4 = st.B[j];
+                    const float dx = p4.x - pxf, dy = p4.y - pyf;
                     const float sigma = 0.5f * (b4.x * dx * dx + b4.z * dy * dy) + b4.y * dx * dy;
                     const float alpha = fminf(kAlphaMax, b4.w * __expf(-sigma));
-                    bool hit = !done && !(sigma < 0.f) && !(alpha < kAlphaMin);
-                    const float next_T = T * (1.0f - alpha);
-                    if (hit && next_T <= kTmin) {
-                        done = true;
-                        hit = false;
-                    }
-                    if (hit) {
-                        const float w = alpha * T;
+                    const float next_T = T * (1.0f - alpha);  // < 0 on finished pixels
+                    if (!(sigma < 0.f) && !(alpha < kAlphaMin)) {
+                        if (next_T <= kTmin) {
+                            T = -fabsf(T);  // stop *before* this splat; no-op when already finished
+                        } else {
+                            const float w = alpha * T;
+                            if (kPacked) {
+                                const float4 c4 = st.Cq[j];
+                                pix[0] = fmaf(c4.x, w, pix[0]);
+                                if (D > 1) pix[1] = fmaf(c4.y, w, pix[1]);
+                                if (D > 2) pix[2] = fmaf(c4.z, w, pix[2]);
+                                if (D > 3) pix[3] = fmaf(c4.w, w, pix[3]);
+                            } else {
 #pragma unroll
-                        for (int k = 0; k < D; ++k) pix[k] = fmaf(s_col[j * D + k], w, pix[k]);
-                        cur = s_idx[j];
-                        T = next_T;
+                                for (int k = 0; k < D; ++k) pix[k] = fmaf(st.col[j * D + k], w, pix[k]);
+                            }
+                            cur = __float_as_int(p4.z);
+                            T = next_T;
+                        }
                     }
-                    if (__all_sync(0xffffffffu, done)) {
+                    if (__all_sync(0xffffffffu, T < 0.f)) {
                         warp_done = true;
                         break;
                     }
@@ -121,6 +147,7 @@ rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
             }
         }
     }
+    T = fabsf(T);
 
     if (tg.inside) {
         float *oc = out_colors + tg.pix_id * D;
