@@ -150,8 +150,13 @@ def _stage_table(summary, steps, meta, n_local, C, D, K, evals, peaks, sm_mhz):
         "gsb_sh_fwd": (12 * K + 12) * n_local + 12 * P + P,
         "gsb_sh_bwd": 24 * P + P + 12 * K * n_local,
         "gsb_isect_count": 12 * P + 4 * P,
+        "gsb_isect_row_keys": 4 * P + 12 * P,
+        "gsb_isect_count_perm": 4 * P + 12 * P + 4 * P,
+        "gsb_isect_emit_perm": 20 * P + 8 * I,
+        "gsb_sort_pairs_u32": math.ceil((bits - 32) / 8) * 16 * I + 4 * I,
+        "gsb_isect_finalize": 8 * I + 4 * I + 8 * I + 4 * C * n_tiles,
         "gsb_isect_emit": 20 * P + 12 * I,
-        "gsb_sort_pairs": math.ceil(bits / 8) * 24 * I + 8 * I,
+        "gsb_sort_pairs": 4 * 24 * P + 8 * P,  # row sort of the presorted path: 32 depth bits over P rows
         "gsb_isect_offsets": 8 * I + 4 * C * n_tiles,
         "gsb_rasterize_pack": 24 * P + 32 * P,
     }

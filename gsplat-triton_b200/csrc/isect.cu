@@ -168,6 +168,109 @@ isect_offsets_kernel(int64_t n_isects, const int64_t *__restrict__ isect_ids, in
     }
 }
 
+// ---- depth-presorted path -----------------------------------------------------------------------------------
+// A stable sort of the (camera | tile | depth) keys in emission order equals: order the ROWS by (camera, depth
+// bits) with a stable sort (ties keep ascending row index), emit every row's tiles in that order, then stably
+// sort the intersections by their (camera | tile) bits alone. The wide pass runs over the P rows (1 M at cfg2)
+// instead of the I intersections (6.3 M), and the intersection sort shrinks from ceil((32+tb+cb)/8) = 6 radix
+// passes over 12-byte pairs to ceil((tb+cb)/8) = 2 passes over 8-byte pairs.
+template <bool PACKED>
+__global__ void __launch_bounds__(kThreads)
+row_keys_kernel(int64_t P, int N, const float *__restrict__ depths, const int64_t *__restrict__ camera_ids,
+                int64_t *__restrict__ keys, int32_t *__restrict__ rows) {
+    int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (i >= P) return;
+    if (keys != nullptr) {
+        int64_t cam = PACKED ? camera_ids[i] : (i / N);
+        keys[i] = (cam << 32) | (int64_t)(unsigned)__float_as_int(depths[i]);
+    }
+    rows[i] = (int32_t)i;
+}
+
+// k-th thread handles row perm[k]: tile count (also stored in natural order) + block sums in permuted order
+__global__ void __launch_bounds__(kThreads)
+count_perm_kernel(int64_t P, const int32_t *__restrict__ perm, const float *__restrict__ means2d,
+                  const int32_t *__restrict__ radii, int tile_size, int tw, int th,
+                  int32_t *__restrict__ tiles_per_gauss, int32_t *__restrict__ block_sums) {
+    __shared__ int s_warp[kThreads / 32];
+    int64_t k = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    int cnt = 0;
+    if (k < P) {
+        int64_t i = perm[k];
+        int r = radii[i];
+        if (r > 0) {
+            float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * i);
+            TileBox b = tile_box(m.x, m.y, r, tile_size, tw, th);
+            cnt = (b.x1 - b.x0) * (b.y1 - b.y0);
+        }
+        tiles_per_gauss[i] = cnt;
+    }
+    int sum = cnt;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; ++w) t += s_warp[w];
+        block_sums[blockIdx.x] = t;
+    }
+}
+
+template <bool PACKED>
+__global__ void __launch_bounds__(kThreads)
+emit_perm_kernel(int64_t P, int N, const int32_t *__restrict__ perm, const float *__restrict__ means2d,
+                 const int32_t *__restrict__ radii, const int64_t *__restrict__ camera_ids, int tile_size, int tw,
+                 int th, int tile_n_bits, const int32_t *__restrict__ tiles_per_gauss,
+                 const int64_t *__restrict__ block_offsets, uint32_t *__restrict__ tile_keys,
+                 int32_t *__restrict__ flatten_ids) {
+    __shared__ int s_warp[kThreads / 32];
+    int64_t k = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    int64_t i = k < P ? perm[k] : 0;
+    int cnt = k < P ? tiles_per_gauss[i] : 0;
+    int block_total;
+    int local = block_exclusive_scan(cnt, s_warp, block_total);
+    if (cnt == 0) return;
+    int64_t out = block_offsets[blockIdx.x] + local;
+    float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * i);
+    TileBox b = tile_box(m.x, m.y, radii[i], tile_size, tw, th);
+    uint32_t cam = (uint32_t)(PACKED ? camera_ids[i] : (i / N));
+    uint32_t hi = cam << tile_n_bits;
+    for (int y = b.y0; y < b.y1; ++y) {
+        for (int x = b.x0; x < b.x1; ++x) {
+            tile_keys[out] = hi | (uint32_t)(y * tw + x);
+            flatten_ids[out] = (int32_t)i;
+            ++out;
+        }
+    }
+}
+
+// sorted (camera | tile) words + row ids -> the reference's 64-bit keys and the per-tile offsets
+__global__ void __launch_bounds__(kThreads)
+finalize_kernel(int64_t n_isects, const uint32_t *__restrict__ tile_keys, const int32_t *__restrict__ flatten_ids,
+                const float *__restrict__ depths, int n_tiles, int tile_n_bits, int64_t total_tiles,
+                int64_t *__restrict__ isect_ids, int32_t *__restrict__ offsets) {
+    int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (i >= n_isects) return;
+    const uint32_t key = tile_keys[i];
+    const uint32_t tile_mask = (1u << tile_n_bits) - 1u;
+    isect_ids[i] = ((int64_t)key << 32) | (int64_t)(unsigned)__float_as_int(depths[flatten_ids[i]]);
+    const int64_t cur = (int64_t)(key >> tile_n_bits) * n_tiles + (key & tile_mask);
+    if (i == 0) {
+        for (int64_t t = 0; t <= cur; ++t) offsets[t] = 0;
+    } else {
+        const uint32_t pkey = tile_keys[i - 1];
+        if (pkey != key) {
+            const int64_t prev = (int64_t)(pkey >> tile_n_bits) * n_tiles + (pkey & tile_mask);
+            for (int64_t t = prev + 1; t <= cur; ++t) offsets[t] = (int32_t)i;
+        }
+    }
+    if (i == n_isects - 1) {
+        for (int64_t t = cur + 1; t < total_tiles; ++t) offsets[t] = (int32_t)n_isects;
+    }
+}
+
 }  // namespace
 
 extern "C" int64_t gsb_isect_num_blocks(int64_t P) { return (P + kThreads - 1) / kThreads; }
@@ -256,4 +359,100 @@ extern "C" int gsb_isect_offsets(int64_t n_isects, const int64_t *isect_ids, int
     isect_offsets_kernel<<<gsb_cdiv(n_isects, kThreads), kThreads, 0, stream>>>(n_isects, isect_ids, (int)n_tiles,
                                                                                tile_n_bits, total, offsets);
     return gsb_check_launch("isect_offsets");
+}
+
+// ---- depth-presorted isect_tiles (see the kernels above) ------------------------------------------------------
+extern "C" int gsb_isect_row_keys(int64_t P, int N, int packed, const float *depths, const int64_t *camera_ids,
+                                  int64_t *keys, int32_t *rows, cudaStream_t stream) {
+    GSB_REQUIRE(P >= 0, "negative size");
+    GSB_REQUIRE(!packed || camera_ids != nullptr || P == 0 || keys == nullptr, "camera_ids required when packed");
+    GSB_REQUIRE(packed || N > 0 || P == 0, "N required when not packed");
+    GSB_REQUIRE(P < ((int64_t)1 << 31), "more than 2^31-1 rows");
+    if (P == 0) return GSB_OK;
+    unsigned nblk = (unsigned)gsb_isect_num_blocks(P);
+    if (packed)
+        row_keys_kernel<true><<<nblk, kThreads, 0, stream>>>(P, N, depths, camera_ids, keys, rows);
+    else
+        row_keys_kernel<false><<<nblk, kThreads, 0, stream>>>(P, N, depths, camera_ids, keys, rows);
+    return gsb_check_launch("isect_row_keys");
+}
+
+extern "C" int gsb_isect_count_perm(int64_t P, const int32_t *perm, const float *means2d, const int32_t *radii,
+                                    int tile_size, int tile_width, int tile_height, int32_t *tiles_per_gauss,
+                                    int32_t *block_sums, int64_t *block_offsets, int64_t *n_isects_out,
+                                    cudaStream_t stream) {
+    GSB_REQUIRE(P >= 0 && tile_size > 0 && tile_width >= 0 && tile_height >= 0, "bad sizes");
+    int64_t nblk = gsb_isect_num_blocks(P);
+    if (P > 0) {
+        count_perm_kernel<<<(unsigned)nblk, kThreads, 0, stream>>>(P, perm, means2d, radii, tile_size, tile_width,
+                                                                  tile_height, tiles_per_gauss, block_sums);
+        if (int e = gsb_check_launch("isect_count_perm")) return e;
+    }
+    scan_block_sums_kernel<<<1, 1024, 0, stream>>>(nblk, block_sums, block_offsets, n_isects_out);
+    return gsb_check_launch("scan_block_sums");
+}
+
+extern "C" int gsb_isect_emit_perm(int64_t P, int N, int packed, const int32_t *perm, const float *means2d,
+                                   const int32_t *radii, const int64_t *camera_ids, int tile_size, int tile_width,
+                                   int tile_height, int tile_n_bits, const int32_t *tiles_per_gauss,
+                                   const int64_t *block_offsets, int32_t *tile_keys, int32_t *flatten_ids,
+                                   cudaStream_t stream) {
+    GSB_REQUIRE(P >= 0 && tile_size > 0, "bad sizes");
+    GSB_REQUIRE(!packed || camera_ids != nullptr, "camera_ids required when packed");
+    if (P == 0) return GSB_OK;
+    unsigned nblk = (unsigned)gsb_isect_num_blocks(P);
+    auto tk = reinterpret_cast<uint32_t *>(tile_keys);
+    if (packed)
+        emit_perm_kernel<true><<<nblk, kThreads, 0, stream>>>(P, N, perm, means2d, radii, camera_ids, tile_size,
+                                                              tile_width, tile_height, tile_n_bits, tiles_per_gauss,
+                                                              block_offsets, tk, flatten_ids);
+    else
+        emit_perm_kernel<false><<<nblk, kThreads, 0, stream>>>(P, N, perm, means2d, radii, camera_ids, tile_size,
+                                                               tile_width, tile_height, tile_n_bits, tiles_per_gauss,
+                                                               block_offsets, tk, flatten_ids);
+    return gsb_check_launch("isect_emit_perm");
+}
+
+extern "C" int64_t gsb_sort_pairs_u32_temp_bytes(int64_t n) {
+    size_t bytes = 0;
+    cub::DoubleBuffer<uint32_t> k(nullptr, nullptr);
+    cub::DoubleBuffer<int32_t> v(nullptr, nullptr);
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, k, v, (int64_t)n, 0, 32, (cudaStream_t)0);
+    return (int64_t)bytes;
+}
+
+extern "C" int gsb_sort_pairs_u32(int64_t n, int end_bit, int32_t *keys, int32_t *keys_alt, int32_t *vals,
+                                  int32_t *vals_alt, void *temp, int64_t temp_bytes, int *result_in_alt,
+                                  cudaStream_t stream) {
+    GSB_REQUIRE(n >= 0 && end_bit >= 0 && end_bit <= 32, "bad sizes");
+    *result_in_alt = 0;
+    if (n == 0 || end_bit == 0) return GSB_OK;
+    cub::DoubleBuffer<uint32_t> k(reinterpret_cast<uint32_t *>(keys), reinterpret_cast<uint32_t *>(keys_alt));
+    cub::DoubleBuffer<int32_t> v(vals, vals_alt);
+    size_t bytes = (size_t)temp_bytes;
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(temp, bytes, k, v, n, 0, end_bit, stream);
+    if (e != cudaSuccess) {
+        gsb_set_error("radix sort (u32): %s", cudaGetErrorString(e));
+        return GSB_ERR_CUDA;
+    }
+    *result_in_alt = (reinterpret_cast<int32_t *>(k.Current()) == keys_alt) ? 1 : 0;
+    return GSB_OK;
+}
+
+extern "C" int gsb_isect_finalize(int64_t n_isects, const int32_t *tile_keys, const int32_t *flatten_ids,
+                                  const float *depths, int C, int tile_width, int tile_height, int tile_n_bits,
+                                  int64_t *isect_ids, int32_t *offsets, cudaStream_t stream) {
+    GSB_REQUIRE(n_isects >= 0 && C >= 0, "bad sizes");
+    int64_t n_tiles = (int64_t)tile_width * tile_height;
+    int64_t total = n_tiles * C;
+    if (total == 0) return GSB_OK;
+    if (n_isects == 0) {
+        cudaError_t e = cudaMemsetAsync(offsets, 0, sizeof(int32_t) * total, stream);
+        if (e != cudaSuccess) { gsb_set_error("memset offsets: %s", cudaGetErrorString(e)); return GSB_ERR_CUDA; }
+        return GSB_OK;
+    }
+    finalize_kernel<<<gsb_cdiv(n_isects, kThreads), kThreads, 0, stream>>>(
+        n_isects, reinterpret_cast<const uint32_t *>(tile_keys), flatten_ids, depths, (int)n_tiles, tile_n_bits, total,
+        isect_ids, offsets);
+    return gsb_check_launch("isect_finalize");
 }

@@ -353,18 +353,52 @@ def isect_tiles(
     dev = means2d.device
     st = stream_of(means2d)
 
-    nblk = int(lib.gsb_isect_num_blocks(P))
+    n_tiles = tile_width * tile_height
+    tb = tile_n_bits(n_tiles)
+    cb = max(C - 1, 0).bit_length()
+    assert 32 + tb + cb <= 64, "camera/tile ids do not fit a 64-bit intersection key"
     tiles_per_gauss = torch.empty(radii.shape, dtype=torch.int32, device=dev)
+
+    if sort and tb + cb <= 32 and os.environ.get("GSPLAT_B200_SORT", "presort") != "global":
+        # depth-presorted path (include/gsplat_b200.h): sort the P rows by (camera, depth), emit in that order,
+        # then sort the intersections by their (camera | tile) bits only; offsets fall out of the last pass.
+        nblk = int(lib.gsb_isect_num_blocks(P))
+        rows = torch.empty((P,), dtype=torch.int32, device=dev)
+        if C == 1:
+            # one camera: the row key is the depth bit pattern itself (positive floats order like their bits)
+            lib.gsb_isect_row_keys(P, N, int(packed), ptr(depths), ptr(camera_ids), None, ptr(rows), st)
+            _, perm = _sort_pairs_u32(depths.reshape(-1).view(torch.int32).clone(), rows, 32)
+        else:
+            row_keys = torch.empty((P,), dtype=torch.int64, device=dev)
+            lib.gsb_isect_row_keys(P, N, int(packed), ptr(depths), ptr(camera_ids), ptr(row_keys), ptr(rows), st)
+            _, perm = _sort_pairs(row_keys, rows, 32 + cb)
+        block_sums = torch.empty((max(nblk, 1),), dtype=torch.int32, device=dev)
+        block_offsets = torch.empty((nblk + 1,), dtype=torch.int64, device=dev)
+        lib.gsb_isect_count_perm(P, ptr(perm), ptr(means2d), ptr(radii), tile_size, tile_width, tile_height,
+                                 ptr(tiles_per_gauss), ptr(block_sums), ptr(block_offsets),
+                                 block_offsets.data_ptr() + 8 * nblk, st)
+        n_isects = int(block_offsets[-1].item())  # the one size read-back (isect_tiles.py:102, Intersect.cpp:77-78)
+        isect_ids = torch.empty((n_isects,), dtype=torch.int64, device=dev)
+        offsets = torch.empty((C, tile_height, tile_width), dtype=torch.int32, device=dev)
+        tile_keys = torch.empty((n_isects,), dtype=torch.int32, device=dev)
+        flatten_ids = torch.empty((n_isects,), dtype=torch.int32, device=dev)
+        if n_isects > 0:
+            lib.gsb_isect_emit_perm(P, N, int(packed), ptr(perm), ptr(means2d), ptr(radii), ptr(camera_ids),
+                                    tile_size, tile_width, tile_height, tb, ptr(tiles_per_gauss), ptr(block_offsets),
+                                    ptr(tile_keys), ptr(flatten_ids), st)
+            tile_keys, flatten_ids = _sort_pairs_u32(tile_keys, flatten_ids, tb + cb)
+        lib.gsb_isect_finalize(n_isects, ptr(tile_keys), ptr(flatten_ids), ptr(depths), C, tile_width, tile_height,
+                               tb, ptr(isect_ids), ptr(offsets), st)
+        # the finalize pass already produced isect_offset_encode's answer for these ids: hand it over with them
+        isect_ids._b200_offsets = (C, tile_width, tile_height, tb, offsets)
+        return tiles_per_gauss, isect_ids, flatten_ids
+
+    nblk = int(lib.gsb_isect_num_blocks(P))
     block_sums = torch.empty((max(nblk, 1),), dtype=torch.int32, device=dev)
     block_offsets = torch.empty((nblk + 1,), dtype=torch.int64, device=dev)
     lib.gsb_isect_count(P, ptr(means2d), ptr(radii), tile_size, tile_width, tile_height, ptr(tiles_per_gauss),
                         ptr(block_sums), ptr(block_offsets), block_offsets.data_ptr() + 8 * nblk, st)
     n_isects = int(block_offsets[-1].item())  # size read-back (isect_tiles.py:102, Intersect.cpp:77-78)
-
-    n_tiles = tile_width * tile_height
-    tb = tile_n_bits(n_tiles)
-    cb = max(C - 1, 0).bit_length()
-    assert 32 + tb + cb <= 64, "camera/tile ids do not fit a 64-bit intersection key"
     isect_ids = torch.empty((n_isects,), dtype=torch.int64, device=dev)
     flatten_ids = torch.empty((n_isects,), dtype=torch.int32, device=dev)
     if n_isects == 0:
@@ -392,6 +426,21 @@ def _sort_pairs(keys: Tensor, vals: Tensor, end_bit: int) -> Tuple[Tensor, Tenso
     return (keys_alt, vals_alt) if in_alt.value else (keys, vals)
 
 
+def _sort_pairs_u32(keys: Tensor, vals: Tensor, end_bit: int) -> Tuple[Tensor, Tensor]:
+    """Stable LSD radix sort of (uint32 bit pattern, int32) pairs over bits [0, end_bit)."""
+    import ctypes
+
+    n = keys.numel()
+    keys_alt = torch.empty_like(keys)
+    vals_alt = torch.empty_like(vals)
+    temp_bytes = int(lib.gsb_sort_pairs_u32_temp_bytes(n))
+    temp = torch.empty((max(temp_bytes, 1),), dtype=torch.uint8, device=keys.device)
+    in_alt = ctypes.c_int(0)
+    lib.gsb_sort_pairs_u32(n, end_bit, ptr(keys), ptr(keys_alt), ptr(vals), ptr(vals_alt), ptr(temp), temp_bytes,
+                           ctypes.addressof(in_alt), stream_of(keys))
+    return (keys_alt, vals_alt) if in_alt.value else (keys, vals)
+
+
 @torch.no_grad()
 def isect_offset_encode(isect_ids: Tensor, n_cameras: int, tile_width: int, tile_height: int) -> Tensor:
     """First sorted-intersection index of every (camera, tile): int32 [C, tile_height, tile_width].
@@ -399,6 +448,10 @@ def isect_offset_encode(isect_ids: Tensor, n_cameras: int, tile_width: int, tile
     Contract: triton_impl/isect_offset.py:9-35, cuda/_wrapper.py:422-438.
     """
     require_cuda(isect_ids)
+    cached = getattr(isect_ids, "_b200_offsets", None)
+    if cached is not None and cached[:4] == (n_cameras, tile_width, tile_height,
+                                             tile_n_bits(tile_width * tile_height)):
+        return cached[4]  # produced by isect_tiles' bucket scan for exactly these ids
     isect_ids = isect_ids.contiguous()
     offsets = torch.empty((n_cameras, tile_height, tile_width), dtype=torch.int32, device=isect_ids.device)
     lib.gsb_isect_offsets(isect_ids.numel(), ptr(isect_ids), n_cameras, tile_width, tile_height,

@@ -119,6 +119,33 @@ int gsb_sort_pairs(int64_t n, int end_bit, int64_t *keys, int64_t *keys_alt, int
 int gsb_isect_offsets(int64_t n_isects, const int64_t *isect_ids, int C, int tile_width, int tile_height,
                       int tile_n_bits, int32_t *offsets, cudaStream_t stream);
 
+/* Depth-presorted isect_tiles (sort=True), bit-identical to a stable radix sort of the emitted 64-bit keys:
+ *   1. gsb_isect_row_keys: key = camera << 32 | depth bits per ROW, rows = 0..P-1; the caller sorts them with
+ *      gsb_sort_pairs over 32 + camera_bits bits (P rows, not n_isects intersections). keys may be NULL (only
+ *      rows is written): with one camera the depth bit patterns themselves are the keys (gsb_sort_pairs_u32);
+ *   2. gsb_isect_count_perm / gsb_isect_emit_perm: tile counts and (camera | tile) 32-bit words + row ids emitted
+ *      in that row order (perm = the sorted rows);
+ *   3. gsb_sort_pairs_u32 over tile_bits + camera_bits bits only (2 radix passes at 1080p instead of 6);
+ *   4. gsb_isect_finalize: rebuilds the 64-bit isect_ids (word << 32 | depth bits of the row) and writes
+ *      isect_offsets (the output of isect_offset_encode) in the same pass.
+ * Depths must be positive (as projection produces; a negative depth sign-extends into the tile bits in the
+ * reference's own key). tile_bits + camera_bits must be <= 32. */
+int gsb_isect_row_keys(int64_t P, int N, int packed, const float *depths, const int64_t *camera_ids, int64_t *keys,
+                       int32_t *rows, cudaStream_t stream);
+int gsb_isect_count_perm(int64_t P, const int32_t *perm, const float *means2d, const int32_t *radii, int tile_size,
+                         int tile_width, int tile_height, int32_t *tiles_per_gauss, int32_t *block_sums,
+                         int64_t *block_offsets, int64_t *n_isects_out, cudaStream_t stream);
+int gsb_isect_emit_perm(int64_t P, int N, int packed, const int32_t *perm, const float *means2d,
+                        const int32_t *radii, const int64_t *camera_ids, int tile_size, int tile_width,
+                        int tile_height, int tile_n_bits, const int32_t *tiles_per_gauss,
+                        const int64_t *block_offsets, int32_t *tile_keys, int32_t *flatten_ids, cudaStream_t stream);
+int64_t gsb_sort_pairs_u32_temp_bytes(int64_t n);
+int gsb_sort_pairs_u32(int64_t n, int end_bit, int32_t *keys, int32_t *keys_alt, int32_t *vals, int32_t *vals_alt,
+                       void *temp, int64_t temp_bytes, int *result_in_alt_host, cudaStream_t stream);
+int gsb_isect_finalize(int64_t n_isects, const int32_t *tile_keys, const int32_t *flatten_ids, const float *depths,
+                       int C, int tile_width, int tile_height, int tile_n_bits, int64_t *isect_ids, int32_t *offsets,
+                       cudaStream_t stream);
+
 /* ---- rasterize_to_pixels ----------------------------------------------------------------------
  * replaces triton_impl/rasterize_to_pixels_fwd.py:200-275 / :21-196, rasterize_to_pixels_bwd.py:341-430
  * / :21-337 and cuda/csrc/RasterizeToPixels3DGSFwd.cu:18-188, RasterizeToPixels3DGSBwd.cu:16-278.

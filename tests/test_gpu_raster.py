@@ -107,6 +107,34 @@ def test_isect_random_against_oracle(C, N, W, H):
     assert torch.equal(ids_u.cpu(), o_ids_u) and torch.equal(flat_u.cpu(), o_flat_u)
 
 
+@pytest.mark.parametrize("N,packed", [(3000, False), (30000, True), (400000, False)])
+def test_isect_presorted_path_equals_global_radix_sort(N, packed, monkeypatch):
+    """The depth-presorted path (default: row sort + 2-pass tile sort) against the global stable radix sort of
+    the 64-bit keys: equal depths (ties), empty tiles, very full tiles, packed rows."""
+    from gsplat.b200_impl import isect_offset_encode, isect_tiles
+
+    torch.manual_seed(N)
+    C, W, H, ts = 3, 96, 80, 16
+    tw, th = 6, 5
+    shape = (C * N,) if packed else (C, N)
+    means2d = (torch.rand(*shape, 2) * torch.tensor([W * 0.6, H * 1.0])).to(DEV)  # right-hand tiles stay empty-ish
+    radii = torch.randint(0, 12, shape, dtype=torch.int32).to(DEV)
+    depths = (torch.rand(*shape) * 5 + 0.1).to(DEV)
+    depths[..., ::3] = 2.5
+    kw = {}
+    if packed:
+        cam = torch.sort(torch.randint(0, C, shape)).values.to(DEV)
+        kw = dict(packed=True, n_cameras=C, camera_ids=cam, gaussian_ids=torch.arange(C * N, device=DEV))
+    out = {}
+    for mode in ("presort", "global"):
+        monkeypatch.setenv("GSPLAT_B200_SORT", mode)
+        tpg, ids, flat = isect_tiles(means2d, radii, depths, ts, tw, th, **kw)
+        out[mode] = (tpg, ids, flat, isect_offset_encode(ids, C, tw, th))
+    for a, b in zip(out["presort"], out["global"]):
+        assert torch.equal(a, b)
+    assert out["presort"][1].numel() > N
+
+
 def test_isect_packed_empty_and_docstring():
     from gsplat.b200_impl import isect_offset_encode, isect_tiles
 
