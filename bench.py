@@ -148,6 +148,8 @@ def _stage_table(summary, steps, meta, n_local, C, D, K, evals, peaks, sm_mhz):
         "gsb_projection_fwd": 40 * n_local + 28 * P,
         "gsb_projection_bwd": 80 * n_local + 40 * P,
         "gsb_sh_fwd": (12 * K + 12) * n_local + 12 * P + P,
+        "gsb_sh_colors_fwd": (12 * K + 12) * n_local + 12 * P + 4 * P,
+        "gsb_sh_colors_bwd": (12 * K + 12) * n_local + 12 * P + 4 * P + (12 * K + 12) * n_local,
         "gsb_sh_bwd": 24 * P + P + 12 * K * n_local,
         "gsb_isect_count": 12 * P + 4 * P,
         "gsb_isect_row_keys": 4 * P + 12 * P,

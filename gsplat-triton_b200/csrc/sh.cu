@@ -253,6 +253,115 @@ sh_bwd_kernel(int64_t n_rows, int n_batch, int K, const float *__restrict__ dirs
     smem_to_rows<NB * 3>(s_cf, v_coeffs, r0, rows, K * 3);
 }
 
+// ---- fused view-dependent colour: what gsplat/rendering.py:384-408 does around spherical_harmonics ------------
+//   dirs = means[n] - campos[c]; colour = max(SH(dirs, coeffs[n]) + 0.5, 0) where radii[c, n] > 0, else max(0.5, 0)
+// (masked rows evaluate to SH = 0, exactly as `spherical_harmonics(..., masks=radii > 0)` followed by the clamp).
+// Backward: v_coeffs[n] and v_means[n] summed over cameras in registers (dirs is linear in means), the clamp's
+// pass-through mask recomputed from the forward value.
+template <int DEG>
+__global__ void __launch_bounds__(kThreads)
+sh_colors_fwd_kernel(int64_t N, int C, int K, const float *__restrict__ means, const float *__restrict__ campos,
+                     const float *__restrict__ coeffs, const int32_t *__restrict__ radii,
+                     float *__restrict__ colors) {
+    constexpr int NB = (DEG + 1) * (DEG + 1);
+    constexpr int S = (NB * 3) | 1;
+    __shared__ float s_cf[kThreads * S];
+    const int64_t r0 = (int64_t)blockIdx.x * kThreads;
+    const int rows = (int)min((int64_t)kThreads, N - r0);
+    rows_to_smem<NB * 3>(s_cf, coeffs, r0, rows, K * 3);
+    __syncthreads();
+    const int64_t r = r0 + threadIdx.x;
+    if (r >= N) return;
+    const float *cf = s_cf + threadIdx.x * S;
+    const float mx = means[3 * r], my = means[3 * r + 1], mz = means[3 * r + 2];
+    for (int c = 0; c < C; ++c) {
+        const size_t e = (size_t)c * N + r;
+        float cr = 0.f, cg = 0.f, cb = 0.f;
+        if (radii[e] > 0) {
+            float x = mx - campos[3 * c], y = my - campos[3 * c + 1], z = mz - campos[3 * c + 2];
+            float inorm = rsqrtf(x * x + y * y + z * z);
+            float bases[NB];
+            sh_bases<DEG>(x * inorm, y * inorm, z * inorm, bases);
+#pragma unroll
+            for (int k = 0; k < NB; ++k) {
+                cr += bases[k] * cf[3 * k];
+                cg += bases[k] * cf[3 * k + 1];
+                cb += bases[k] * cf[3 * k + 2];
+            }
+        }
+        float *op = colors + 3 * e;
+        op[0] = fmaxf(cr + 0.5f, 0.f);
+        op[1] = fmaxf(cg + 0.5f, 0.f);
+        op[2] = fmaxf(cb + 0.5f, 0.f);
+    }
+}
+
+template <int DEG, bool NEED_MEANS>
+__global__ void __launch_bounds__(kThreads)
+sh_colors_bwd_kernel(int64_t N, int C, int K, const float *__restrict__ means, const float *__restrict__ campos,
+                     const float *__restrict__ coeffs, const int32_t *__restrict__ radii,
+                     const float *__restrict__ v_colors, float *__restrict__ v_coeffs, float *__restrict__ v_means) {
+    constexpr int NB = (DEG + 1) * (DEG + 1);
+    constexpr int S = (NB * 3) | 1;
+    __shared__ float s_cf[kThreads * S];  // coefficients in, then (same rows) their gradients out
+    const int64_t r0 = (int64_t)blockIdx.x * kThreads;
+    const int rows = (int)min((int64_t)kThreads, N - r0);
+    rows_to_smem<NB * 3>(s_cf, coeffs, r0, rows, K * 3);
+    __syncthreads();
+    const int64_t r = r0 + threadIdx.x;
+    float *cp = s_cf + threadIdx.x * S;
+    if (r < N) {
+        float acc[NB * 3];
+#pragma unroll
+        for (int i = 0; i < NB * 3; ++i) acc[i] = 0.f;
+        float vmx = 0.f, vmy = 0.f, vmz = 0.f;
+        const float mx = means[3 * r], my = means[3 * r + 1], mz = means[3 * r + 2];
+        for (int c = 0; c < C; ++c) {
+            const size_t e = (size_t)c * N + r;
+            if (radii[e] <= 0) continue;
+            float x = mx - campos[3 * c], y = my - campos[3 * c + 1], z = mz - campos[3 * c + 2];
+            float inorm = rsqrtf(x * x + y * y + z * z);
+            x *= inorm; y *= inorm; z *= inorm;
+            float bases[NB];
+            sh_bases<DEG>(x, y, z, bases);
+            float cr = 0.5f, cg = 0.5f, cb = 0.5f;
+#pragma unroll
+            for (int k = 0; k < NB; ++k) {
+                cr += bases[k] * cp[3 * k];
+                cg += bases[k] * cp[3 * k + 1];
+                cb += bases[k] * cp[3 * k + 2];
+            }
+            const float *vp = v_colors + 3 * e;
+            // clamp_min(x, 0) passes the gradient where x >= 0 (torch semantics)
+            const float vr = cr >= 0.f ? vp[0] : 0.f, vg = cg >= 0.f ? vp[1] : 0.f, vb = cb >= 0.f ? vp[2] : 0.f;
+            if (NEED_MEANS) {
+                float g[NB];
+#pragma unroll
+                for (int k = 0; k < NB; ++k) g[k] = cp[3 * k] * vr + cp[3 * k + 1] * vg + cp[3 * k + 2] * vb;
+                float vx, vy, vz;
+                sh_bases_vjp<DEG>(x, y, z, g, vx, vy, vz);
+                float dot = x * vx + y * vy + z * vz;
+                vmx += (vx - dot * x) * inorm;
+                vmy += (vy - dot * y) * inorm;
+                vmz += (vz - dot * z) * inorm;
+            }
+#pragma unroll
+            for (int k = 0; k < NB; ++k) {
+                acc[3 * k] += bases[k] * vr;
+                acc[3 * k + 1] += bases[k] * vg;
+                acc[3 * k + 2] += bases[k] * vb;
+            }
+        }
+        if (NEED_MEANS) {
+            v_means[3 * r] = vmx; v_means[3 * r + 1] = vmy; v_means[3 * r + 2] = vmz;
+        }
+#pragma unroll
+        for (int i = 0; i < NB * 3; ++i) cp[i] = acc[i];
+    }
+    __syncthreads();
+    smem_to_rows<NB * 3>(s_cf, v_coeffs, r0, rows, K * 3);
+}
+
 }  // namespace
 
 #define DISPATCH_DEG(deg, ...)                                        \
@@ -291,4 +400,61 @@ extern "C" int gsb_sh_bwd(int degree, int64_t n_rows, int n_batch, int K, const 
                                                                                    v_colors, v_coeffs, v_dirs)));
     }
     return gsb_check_launch("sh_bwd");
+}
+
+extern "C" int gsb_sh_colors_fwd(int degree, int64_t N, int C, int K, const float *means, const float *campos,
+                                 const float *coeffs, const int32_t *radii, float *colors, cudaStream_t stream) {
+    GSB_REQUIRE(degree >= 0 && degree <= 4, "degree must be in [0, 4]");
+    GSB_REQUIRE((degree + 1) * (degree + 1) <= K, "K is smaller than (degree+1)^2");
+    GSB_REQUIRE(N >= 0 && C >= 0, "negative size");
+    if (N == 0 || C == 0) return GSB_OK;
+    unsigned nblk = gsb_cdiv(N, kThreads);
+    DISPATCH_DEG(degree, (sh_colors_fwd_kernel<D><<<nblk, kThreads, 0, stream>>>(N, C, K, means, campos, coeffs, radii, colors)));
+    return gsb_check_launch("sh_colors_fwd");
+}
+
+extern "C" int gsb_sh_colors_bwd(int degree, int64_t N, int C, int K, const float *means, const float *campos,
+                                 const float *coeffs, const int32_t *radii, const float *v_colors, float *v_coeffs,
+                                 float *v_means, cudaStream_t stream) {
+    GSB_REQUIRE(degree >= 0 && degree <= 4, "degree must be in [0, 4]");
+    GSB_REQUIRE((degree + 1) * (degree + 1) <= K, "K is smaller than (degree+1)^2");
+    GSB_REQUIRE(N >= 0 && C >= 0, "negative size");
+    if (N == 0) return GSB_OK;
+    unsigned nblk = gsb_cdiv(N, kThreads);
+    if (v_means != nullptr) {
+        DISPATCH_DEG(degree, (sh_colors_bwd_kernel<D, true><<<nblk, kThreads, 0, stream>>>(N, C, K, means, campos, coeffs, radii,
+                                                                                         v_colors, v_coeffs, v_means)));
+    } else {
+        DISPATCH_DEG(degree, (sh_colors_bwd_kernel<D, false><<<nblk, kThreads, 0, stream>>>(N, C, K, means, campos, coeffs, radii,
+                                                                                          v_colors, v_coeffs, v_means)));
+    }
+    return gsb_check_launch("sh_colors_bwd");
+}
+
+// camera centres of [C, 4, 4] row-major world-to-camera matrices: -A^-1 t (A = upper-left 3x3, t = last column),
+// i.e. torch.inverse(viewmats)[:, :3, 3] for affine matrices with last row (0, 0, 0, 1) (rendering.py:386)
+namespace {
+__global__ void camera_centers_kernel(int C, const float *__restrict__ viewmats, float *__restrict__ campos) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float *m = viewmats + 16 * c;
+    float a00 = m[0], a01 = m[1], a02 = m[2], t0 = m[3];
+    float a10 = m[4], a11 = m[5], a12 = m[6], t1 = m[7];
+    float a20 = m[8], a21 = m[9], a22 = m[10], t2 = m[11];
+    float c00 = a11 * a22 - a12 * a21, c01 = a02 * a21 - a01 * a22, c02 = a01 * a12 - a02 * a11;
+    float c10 = a12 * a20 - a10 * a22, c11 = a00 * a22 - a02 * a20, c12 = a02 * a10 - a00 * a12;
+    float c20 = a10 * a21 - a11 * a20, c21 = a01 * a20 - a00 * a21, c22 = a00 * a11 - a01 * a10;
+    float det = a00 * c00 + a01 * c10 + a02 * c20;
+    float id = 1.0f / det;
+    campos[3 * c + 0] = -(c00 * t0 + c01 * t1 + c02 * t2) * id;
+    campos[3 * c + 1] = -(c10 * t0 + c11 * t1 + c12 * t2) * id;
+    campos[3 * c + 2] = -(c20 * t0 + c21 * t1 + c22 * t2) * id;
+}
+}  // namespace
+
+extern "C" int gsb_camera_centers(int C, const float *viewmats, float *campos, cudaStream_t stream) {
+    GSB_REQUIRE(C >= 0, "negative size");
+    if (C == 0) return GSB_OK;
+    camera_centers_kernel<<<gsb_cdiv(C, 64), 64, 0, stream>>>(C, viewmats, campos);
+    return gsb_check_launch("camera_centers");
 }

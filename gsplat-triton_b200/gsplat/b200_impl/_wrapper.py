@@ -303,6 +303,48 @@ class _SphericalHarmonics(torch.autograd.Function):
         return None, v_dirs, v_coeffs, None
 
 
+def view_dependent_colors(sh_degree: int, means: Tensor, viewmats: Tensor, coeffs: Tensor, radii: Tensor) -> Tensor:
+    """`clamp_min(spherical_harmonics(deg, means - campos, coeffs, masks=radii > 0) + 0.5, 0)` in one kernel.
+
+    The fused form of the reference's rendering.py:384-408 for unpacked rows and per-Gaussian coefficients
+    (`means [N,3]`, `viewmats [C,4,4]` without gradient, `coeffs [N,K,3]`, `radii [C,N]`) -> `[C,N,3]`.
+    b200-only helper used by this package's `rasterization()`; the five reference-facing functions are unchanged.
+    """
+    C, N = radii.shape
+    assert means.shape == (N, 3) and viewmats.shape == (C, 4, 4), (means.shape, viewmats.shape)
+    assert coeffs.dim() == 3 and coeffs.shape[0] == N and coeffs.shape[2] == 3, coeffs.shape
+    assert (sh_degree + 1) ** 2 <= coeffs.shape[1], coeffs.shape
+    assert not viewmats.requires_grad, "use spherical_harmonics() when camera poses need gradients"
+    require_cuda(means, viewmats, coeffs, radii)
+    return _ViewColors.apply(sh_degree, means.contiguous(), viewmats.contiguous(), coeffs.contiguous(),
+                             radii.contiguous())
+
+
+class _ViewColors(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, sh_degree, means, viewmats, coeffs, radii):
+        C, N = radii.shape
+        K = coeffs.shape[1]
+        st = stream_of(means)
+        campos = torch.empty((C, 3), dtype=torch.float32, device=means.device)
+        lib.gsb_camera_centers(C, ptr(viewmats), ptr(campos), st)
+        colors = torch.empty((C, N, 3), dtype=torch.float32, device=means.device)
+        lib.gsb_sh_colors_fwd(sh_degree, N, C, K, ptr(means), ptr(campos), ptr(coeffs), ptr(radii), ptr(colors), st)
+        ctx.save_for_backward(means, campos, coeffs, radii)
+        ctx.sh_degree = sh_degree
+        return colors
+
+    @staticmethod
+    def backward(ctx, v_colors):
+        means, campos, coeffs, radii = ctx.saved_tensors
+        C, N = radii.shape
+        v_coeffs = torch.empty_like(coeffs)
+        v_means = torch.empty_like(means) if ctx.needs_input_grad[1] else None
+        lib.gsb_sh_colors_bwd(ctx.sh_degree, N, C, coeffs.shape[1], ptr(means), ptr(campos), ptr(coeffs), ptr(radii),
+                              ptr(_f32(v_colors)), ptr(v_coeffs), ptr(v_means), stream_of(means))
+        return None, v_means, None, (v_coeffs if ctx.needs_input_grad[3] else None), None
+
+
 # --------------------------------------------------------------------------------------------
 # isect_tiles / isect_offset_encode
 # --------------------------------------------------------------------------------------------
@@ -577,11 +619,16 @@ class _RasterizeToPixels(torch.autograd.Function):
         conics_shape, opac_shape = ctx.shapes
         v_render_colors = _f32(v_render_colors)
         v_render_alphas = _f32(v_render_alphas)
-        v_means2d = torch.zeros_like(means2d)
-        v_conics = torch.zeros(conics_shape, dtype=torch.float32, device=dev)
-        v_colors = torch.zeros_like(colors)
-        v_opacities = torch.zeros(opac_shape, dtype=torch.float32, device=dev)
-        v_abs = torch.zeros_like(means2d) if ctx.absgrad else None
+        # one zero-filled buffer, five views: the kernel accumulates into them with reductions
+        P = means2d.numel() // 2
+        widths = (2, 3, D, 1) + ((2,) if ctx.absgrad else ())
+        flat = torch.zeros((P * sum(widths),), dtype=torch.float32, device=dev)
+        parts = flat.split([P * w for w in widths])
+        v_means2d = parts[0].view(means2d.shape)
+        v_conics = parts[1].view(conics_shape)
+        v_colors = parts[2].view(colors.shape)
+        v_opacities = parts[3].view(opac_shape)
+        v_abs = parts[4].view(means2d.shape) if ctx.absgrad else None
         lib.gsb_rasterize_bwd(C, flatten_ids.numel(), D, ptr(rec[0]), ptr(rec[1]), ptr(colors), ptr(backgrounds),
                               ptr(m8), ctx.width, ctx.height, ctx.tile_size, tile_width, tile_height,
                               ptr(isect_offsets), ptr(flatten_ids), ptr(render_alphas), ptr(last_ids),

@@ -168,19 +168,25 @@ def rasterization(
         elif colors.dim() == 2:
             colors = colors.expand(C, -1, -1)
     else:
-        camtoworlds = torch.inverse(viewmats)
-        if packed:
-            dirs = means[gaussian_ids, :] - camtoworlds[camera_ids, :3, 3]  # [nnz, 3]
-            shs = colors[gaussian_ids, :, :] if colors.dim() == 3 else colors[camera_ids, gaussian_ids, :, :]
-            colors = spherical_harmonics(sh_degree, dirs, shs, masks=radii > 0)  # [nnz, 3]
+        if BACKEND == "b200" and not packed and colors.dim() == 3 and not viewmats.requires_grad:
+            # dirs, the radii > 0 mask, + 0.5 and the clamp folded into the SH kernels (one pass over [C, N])
+            from .b200_impl._wrapper import view_dependent_colors
+
+            colors = view_dependent_colors(sh_degree, means, viewmats, colors, radii)  # [C, N, 3]
         else:
-            dirs = means[None, :, :] - camtoworlds[:, None, :3, 3]  # [C, N, 3]
-            if BACKEND == "b200" or colors.dim() == 4:
-                shs = colors  # b200 broadcasts [N,K,3] over cameras inside the kernel
+            camtoworlds = torch.inverse(viewmats)
+            if packed:
+                dirs = means[gaussian_ids, :] - camtoworlds[camera_ids, :3, 3]  # [nnz, 3]
+                shs = colors[gaussian_ids, :, :] if colors.dim() == 3 else colors[camera_ids, gaussian_ids, :, :]
+                colors = spherical_harmonics(sh_degree, dirs, shs, masks=radii > 0)  # [nnz, 3]
             else:
-                shs = colors.expand(C, -1, -1, -1)
-            colors = spherical_harmonics(sh_degree, dirs, shs, masks=radii > 0)  # [C, N, 3]
-        colors = torch.clamp_min(colors + 0.5, 0.0)  # as rendering.py:408
+                dirs = means[None, :, :] - camtoworlds[:, None, :3, 3]  # [C, N, 3]
+                if BACKEND == "b200" or colors.dim() == 4:
+                    shs = colors  # b200 broadcasts [N,K,3] over cameras inside the kernel
+                else:
+                    shs = colors.expand(C, -1, -1, -1)
+                colors = spherical_harmonics(sh_degree, dirs, shs, masks=radii > 0)  # [C, N, 3]
+            colors = torch.clamp_min(colors + 0.5, 0.0)  # as rendering.py:408
 
     # Distributed: hand every projected Gaussian to the rank that owns its camera.
     if distributed:

@@ -101,6 +101,18 @@ int gsb_sh_bwd(int degree, int64_t n_rows, int n_batch, int K, const float *dirs
                const uint8_t *masks, const float *v_colors, float *v_coeffs, float *v_dirs,
                cudaStream_t stream);
 
+/* Fused view-dependent colour = the torch glue of rendering.py:384-408 folded into the SH kernels (unpacked rows,
+ * per-Gaussian coefficients): dirs = means[n] - campos[c]; colors[c,n] = max(SH(dirs, coeffs[n]) + 0.5, 0), with
+ * SH := 0 where radii[c,n] <= 0 (masks = radii > 0). campos[C,3] = torch.inverse(viewmats)[:, :3, 3]
+ * (gsb_camera_centers for affine matrices). Backward: v_coeffs[N,K,3] and v_means[N,3] (or NULL), summed over
+ * cameras, fully written; the clamp passes gradient where SH + 0.5 >= 0. */
+int gsb_camera_centers(int C, const float *viewmats, float *campos, cudaStream_t stream);
+int gsb_sh_colors_fwd(int degree, int64_t N, int C, int K, const float *means, const float *campos,
+                      const float *coeffs, const int32_t *radii, float *colors, cudaStream_t stream);
+int gsb_sh_colors_bwd(int degree, int64_t N, int C, int K, const float *means, const float *campos,
+                      const float *coeffs, const int32_t *radii, const float *v_colors, float *v_coeffs,
+                      float *v_means, cudaStream_t stream);
+
 /* ---- isect_tiles / isect_offset_encode --------------------------------------------------------
  * replaces triton_impl/isect_tiles.py:14-133, radix_sort/radix_sort.cu:10-62, isect_offset.py:9-63
  * and cuda/csrc/IntersectTile.cu:24-344. P = C*N (unpacked) or nnz (packed). */

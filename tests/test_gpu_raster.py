@@ -66,6 +66,34 @@ def test_sh_broadcast_masks_and_shapes():
     _close(spherical_harmonics(4, d2, c2), O.spherical_harmonics(4, d2.cpu(), c2.cpu()), atol=1e-5)
 
 
+def test_fused_view_dependent_colors_equals_the_unfused_glue():
+    """b200_impl.view_dependent_colors == clamp_min(spherical_harmonics(means - campos, masks=radii>0) + .5, 0)."""
+    from gsplat.b200_impl import spherical_harmonics
+    from gsplat.b200_impl._wrapper import view_dependent_colors
+
+    torch.manual_seed(7)
+    C, N = 3, 2049
+    means = torch.randn(N, 3, device=DEV, requires_grad=True)
+    coeffs = (torch.randn(N, 16, 3, device=DEV) * 0.4).requires_grad_(True)
+    radii = torch.randint(0, 3, (C, N), dtype=torch.int32, device=DEV)
+    A = torch.linalg.qr(torch.randn(C, 3, 3))[0] * (1 + 0.1 * torch.rand(C, 1, 1))  # rotation x scale: affine
+    viewmats = torch.eye(4).repeat(C, 1, 1)
+    viewmats[:, :3, :3] = A
+    viewmats[:, :3, 3] = torch.randn(C, 3) * 3
+    viewmats = viewmats.to(DEV)
+    w = torch.randn(C, N, 3, device=DEV)
+    for deg in (0, 2, 3):
+        fused = view_dependent_colors(deg, means, viewmats, coeffs, radii)
+        g_f = torch.autograd.grad((fused * w).sum(), (means, coeffs))
+        dirs = means[None] - torch.inverse(viewmats)[:, None, :3, 3]
+        ref = torch.clamp_min(spherical_harmonics(deg, dirs, coeffs, masks=radii > 0) + 0.5, 0.0)
+        g_r = torch.autograd.grad((ref * w).sum(), (means, coeffs))
+        _close(fused, ref, rtol=1e-5, atol=1e-5)
+        _close(g_f[0], g_r[0], rtol=1e-3, atol=1e-4)
+        _close(g_f[1], g_r[1], rtol=1e-4, atol=1e-5)
+        assert bool((fused[radii == 0] == 0.5).all())
+
+
 # ---------------------------------------------------------------------------------------------
 # isect_tiles / isect_offset_encode: bit-exact given the reference's projection outputs
 # ---------------------------------------------------------------------------------------------
