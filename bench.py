@@ -28,7 +28,7 @@ os.environ.setdefault("GSPLAT_BACKEND", "b200")
 
 WIDTH, HEIGHT, N_GAUSS, SH_DEGREE = 1920, 1080, 1_000_000, 3
 SM_COUNT, FP32_LANES = 148, 128
-# FP32 issue slots per pixel-Gaussian evaluation, counted from the kernels' inner loops
+# FP32 issue slots per composited pixel-Gaussian pair (14 fwd incl. the D=3 blend, 40 bwd); DESIGN.md 4
 SLOTS_FWD, SLOTS_BWD = 14, 40
 
 
@@ -110,8 +110,9 @@ def measured_peaks():
 # ------------------------------------------------------------------------------------------------
 # the b200 arm
 # ------------------------------------------------------------------------------------------------
-def _raster_eval_count(meta, device):
-    """Algorithmic pixel-Gaussian evaluations: 256 * sum_tiles (last contributing index - tile start + 1)."""
+def _raster_work_counts(meta, device):
+    """(E, Hits): E = reference-algorithm evaluations 256 * sum_tiles(last contributing index - tile start + 1)
+    (SURVEY 8d); Hits = pixel-Gaussian pairs actually composited (alpha >= 1/255, before termination)."""
     from gsplat.b200_impl._lib import lib, ptr, stream_of
 
     means2d, conics, opac = meta["means2d"].detach(), meta["conics"].detach(), meta["opacities"].detach()
@@ -119,25 +120,25 @@ def _raster_eval_count(meta, device):
     C, th, tw = offs.shape
     P, W, H = opac.numel(), meta["width"], meta["height"]
     rec = torch.empty((2, P, 4), device=device)
-    col = torch.zeros((P, 1), device=device)
-    rc, ra = torch.empty((C, H, W, 1), device=device), torch.empty((C, H, W), device=device)
+    ones = torch.ones((P,), device=device)
+    cnt, ra = torch.empty((C, H, W), device=device), torch.empty((C, H, W), device=device)
     last = torch.empty((C, H, W), dtype=torch.int32, device=device)
     st = stream_of(rec)
     lib.gsb_rasterize_pack(P, ptr(means2d.contiguous()), ptr(conics.contiguous()), ptr(opac.contiguous()),
                            ptr(rec[0]), ptr(rec[1]), st)
-    lib.gsb_rasterize_fwd(C, flat.numel(), 1, ptr(rec[0]), ptr(rec[1]), ptr(col), None, None, W, H, 16, tw, th,
-                          ptr(offs), ptr(flat), ptr(rc), ptr(ra), ptr(last), st)
-    hit = ra > 0
-    last = torch.where(hit, last, torch.full_like(last, -1))
+    lib.gsb_rasterize_count(C, flat.numel(), ptr(rec[0]), ptr(rec[1]), ptr(ones), W, H, 16, tw, th, ptr(offs),
+                            ptr(flat), ptr(cnt), ptr(ra), ptr(last), st)
+    hits = int(cnt.double().sum().item())
+    last = torch.where(cnt > 0, last, torch.full_like(last, -1))
     pad_h, pad_w = th * 16 - H, tw * 16 - W
     last = torch.nn.functional.pad(last, (0, pad_w, 0, pad_h), value=-1)
     tile_last = last.reshape(C, th, 16, tw, 16).amax(dim=(2, 4))
     work = (tile_last - offs + 1).clamp(min=0)
     work = torch.where(tile_last >= 0, work, torch.zeros_like(work))
-    return 256 * int(work.sum().item())
+    return 256 * int(work.sum().item()), hits
 
 
-def _stage_table(summary, steps, meta, n_local, C, D, K, evals, peaks, sm_mhz):
+def _stage_table(summary, steps, meta, n_local, C, D, K, work, peaks, sm_mhz):
     """Per-entry-point ms/step, algorithmic bytes (SURVEY 8d formulas) or FP32 slots, achieved vs peak."""
     P = C * n_local
     I = meta["flatten_ids"].numel()
@@ -163,7 +164,8 @@ def _stage_table(summary, steps, meta, n_local, C, D, K, evals, peaks, sm_mhz):
         "gsb_rasterize_pack": 24 * P + 32 * P,
     }
     fp32_peak = SM_COUNT * FP32_LANES * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12  # TFLOP/s at max clock, FMA = 2
-    flops = {"gsb_rasterize_fwd": 2 * SLOTS_FWD * evals, "gsb_rasterize_bwd": 2 * SLOTS_BWD * evals}
+    evals, hits = work if work is not None else (None, None)
+    flops = {} if hits is None else {"gsb_rasterize_fwd": 2 * SLOTS_FWD * hits, "gsb_rasterize_bwd": 2 * SLOTS_BWD * hits}
     out = {}
     for name, (calls, ms) in summary.items():
         per_step = ms / steps
@@ -175,7 +177,8 @@ def _stage_table(summary, steps, meta, n_local, C, D, K, evals, peaks, sm_mhz):
         elif name in flops and per_step > 0:
             a = flops[name] / (per_step * 1e-3) / 1e12
             row.update(bound="fp32", achieved=round(a, 2), peak=round(fp32_peak, 2), unit="TFLOP/s",
-                       frac=round(a / fp32_peak, 4), evals=evals)
+                       frac=round(a / fp32_peak, 4), composited_pairs=hits, reference_evaluations=evals,
+                       frac_vs_reference_evaluations=round(a / fp32_peak * evals / max(hits, 1), 4))
         out[name] = row
     return out
 
@@ -300,19 +303,24 @@ def run_b200(args):
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_step, ms_e2e = ms.tolist()
 
+    # one more (untimed) iteration on EVERY rank (it contains collectives) to read the stage geometry from `meta`
+    for p in params:
+        p.grad = None
+    _, _, _, meta = iteration(params)
+    barrier()
     if rank == 0:
-        for p in params:
-            p.grad = None
-        _, _, _, meta = iteration(params)
-        evals = _raster_eval_count(meta, dev)
+        # exchange rows are re-laid out after `meta` is filled when distributed: count on a single GPU only
+        work = _raster_work_counts(meta, dev) if world == 1 else None
         peaks = measured_peaks()
         clk = clocks.summary()
         C_local, D, K = 1, 3, (SH_DEGREE + 1) ** 2
         n_rows = meta["means2d"].shape[1]
-        stages = _stage_table(stage_summary, args.steps, meta, n_rows, C_local, D, K, evals, peaks, clk["sm_mhz"])
+        stages = _stage_table(stage_summary, args.steps, meta, n_rows, C_local, D, K, work, peaks, clk["sm_mhz"])
         top = max((k for k in stages if "bound" in stages[k]), key=lambda k: stages[k]["ms_per_step"])
         roof = {k: stages[top][k] for k in ("bound", "achieved", "peak", "unit", "frac")}
-        roof.update(kernel=top, traffic=None, peak_source=(
+        traffic_file = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+        traffic = json.load(open(traffic_file)).get(top) if os.path.exists(traffic_file) else None
+        roof.update(kernel=top, traffic=traffic, peak_source=(
             "148 SMs*128 lanes*2*sm_max_mhz (no measured FP32 peak in MEASURED_PEAKS.json)"
             if roof["bound"] == "fp32" else peaks["source"] + " MEASURED_PEAKS.json hbm_gbs"),
             share_of_step=round(stages[top]["ms_per_step"] / ms_step, 4))

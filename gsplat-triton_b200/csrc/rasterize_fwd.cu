@@ -37,7 +37,9 @@ splat_pack_kernel(int64_t P, const float *__restrict__ means2d, const float *__r
 #define GSB_FWD_MIN_BLOCKS 5
 #endif
 
-template <int D>
+// COUNT (diagnostics, D = 1): every contribution weighs 1 instead of alpha T, so with unit colours the
+// "image" is the number of Gaussians composited into each pixel (bench.py's useful-work count).
+template <int D, bool COUNT = false>
 __global__ void __launch_bounds__(kThreads, (D <= 4 ? GSB_FWD_MIN_BLOCKS : 1))
 rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, const float4 *__restrict__ recB,
                      const float *__restrict__ colors, const float *__restrict__ backgrounds,
@@ -123,7 +125,7 @@ rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
                         if (next_T <= kTmin) {
                             T = -fabsf(T);  // stop *before* this splat; no-op when already finished
                         } else {
-                            const float w = alpha * T;
+                            const float w = COUNT ? 1.0f : alpha * T;
                             if (kPacked) {
                                 const float4 c4 = st.Cq[j];
                                 pix[0] = fmaf(c4.x, w, pix[0]);
@@ -214,4 +216,19 @@ extern "C" int gsb_rasterize_fwd(int C, int64_t n_isects, int D, const float *re
             return GSB_ERR_UNSUPPORTED;
     }
 #undef GSB_FWD_CASE
+}
+
+extern "C" int gsb_rasterize_count(int C, int64_t n_isects, const float *recA, const float *recB, const float *ones,
+                                   int width, int height, int tile_size, int tile_width, int tile_height,
+                                   const int32_t *isect_offsets, const int32_t *flatten_ids, float *counts,
+                                   float *render_alphas, int32_t *last_ids, cudaStream_t stream) {
+    GSB_REQUIRE(C >= 0 && n_isects >= 0 && width > 0 && height > 0, "bad sizes");
+    GSB_REQUIRE(tile_size == raster::kTile, "tile_size must be 16");
+    GSB_REQUIRE(tile_width * tile_size >= width && tile_height * tile_size >= height, "tile grid smaller than image");
+    if (C == 0) return GSB_OK;
+    dim3 grid(tile_width, tile_height, C);
+    raster::rasterize_fwd_kernel<1, true><<<grid, raster::kThreads, 0, stream>>>(
+        C, n_isects, reinterpret_cast<const float4 *>(recA), reinterpret_cast<const float4 *>(recB), ones, nullptr,
+        nullptr, width, height, tile_width, tile_height, isect_offsets, flatten_ids, counts, render_alphas, last_ids);
+    return gsb_check_launch("rasterize_count");
 }

@@ -172,6 +172,12 @@ int gsb_rasterize_fwd(int C, int64_t n_isects, int D, const float *recA, const f
                       const float *backgrounds, const uint8_t *masks, int width, int height, int tile_size,
                       int tile_width, int tile_height, const int32_t *isect_offsets, const int32_t *flatten_ids,
                       float *render_colors, float *render_alphas, int32_t *last_ids, cudaStream_t stream);
+/* diagnostics: counts[C,H,W] = number of Gaussians composited into each pixel (ones: float[P] of 1.0f);
+ * same traversal as gsb_rasterize_fwd with D = 1. Used by bench.py for the useful-work roofline. */
+int gsb_rasterize_count(int C, int64_t n_isects, const float *recA, const float *recB, const float *ones, int width,
+                        int height, int tile_size, int tile_width, int tile_height, const int32_t *isect_offsets,
+                        const int32_t *flatten_ids, float *counts, float *render_alphas, int32_t *last_ids,
+                        cudaStream_t stream);
 /* v_means2d[P,2], v_conics[P,3], v_colors[P,D], v_opacities[P] must be ZERO-filled by the caller
  * (the kernel accumulates with atomics); v_means2d_abs[P,2] (zero-filled) or NULL. */
 int gsb_rasterize_bwd(int C, int64_t n_isects, int D, const float *recA, const float *recB, const float *colors,
