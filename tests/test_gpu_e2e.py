@@ -140,3 +140,95 @@ def test_full_size_properties_cfg2():
                                     s["Ks"], s["width"], s["height"], packed=False)
     torch.testing.assert_close(rc2 * 2, rc4, rtol=1e-5, atol=1e-6)
     torch.testing.assert_close(rc4[..., :1], ra4, rtol=1e-4, atol=1e-5)  # unit colours render the alpha
+
+
+def _ring_scene(N, C, W, H, seed=0):
+    """BASELINE cfg3/cfg4 protocol: cameras on a ring of radius 6 looking at the origin."""
+    g = torch.Generator().manual_seed(seed)
+    means = torch.rand(N, 3, generator=g) * 6 - 3
+    quats = torch.randn(N, 4, generator=g)
+    scales = torch.exp(torch.rand(N, 3, generator=g) * (math.log(0.02) - math.log(0.002)) + math.log(0.002)) * 4
+    opac = torch.rand(N, generator=g)
+    shs = torch.randn(N, 16, 3, generator=g) * 0.3
+    shs[:, 0] += 0.5
+    fx = W / (2 * math.tan(math.radians(30)))
+    Ks = torch.tensor([[fx, 0, W / 2], [0, fx, H / 2], [0, 0, 1.0]]).repeat(C, 1, 1)
+    viewmats = []
+    for i in range(C):
+        a = 2 * math.pi * i / C
+        eye = torch.tensor([6 * math.cos(a), 0.5, 6 * math.sin(a)])
+        fwd = -eye / eye.norm()
+        right = torch.linalg.cross(torch.tensor([0.0, 1.0, 0.0]), fwd)
+        right = right / right.norm()
+        up = torch.linalg.cross(fwd, right)
+        R = torch.stack([right, up, fwd])  # world -> camera rows
+        m = torch.eye(4)
+        m[:3, :3] = R
+        m[:3, 3] = -R @ eye
+        viewmats.append(m)
+    return means, quats, scales, opac, shs, torch.stack(viewmats), Ks
+
+
+def test_cfg3_like_packed_antialiased_matches_oracle():
+    """cfg3 shape (C=8 ring cameras, packed + antialiased, SH deg 3) at a size the CPU oracle finishes in seconds."""
+    from gsplat.rendering import rasterization
+
+    W, H, C = 324, 210, 8
+    cpu = _ring_scene(6000, C, W, H)
+    rc, ra, meta = rasterization(*[t.to(DEV) for t in cpu], W, H, sh_degree=3, packed=True,
+                                 rasterize_mode="antialiased")
+    o_rc, o_ra, _ = O.rasterization(*cpu, W, H, sh_degree=3, rasterize_mode="antialiased")
+    _close_frac(rc, o_rc, rtol=1e-4, atol=1e-4)
+    _close_frac(ra, o_ra, rtol=1e-4, atol=1e-4)
+    assert meta["camera_ids"].dtype == torch.int64 and int(meta["camera_ids"].max()) == C - 1
+    assert meta["isect_offsets"].shape == (C, 14, 21)
+
+
+def test_cfg3_full_size_packed_equals_unpacked_and_properties():
+    """cfg3 at full camera count / resolution (C=8, 1297x840): packed == unpacked images and gradients at 300k
+    Gaussians; intersection keys sorted with the camera in the top bits."""
+    from gsplat.rendering import rasterization
+
+    W, H, C = 1297, 840, 8
+    cpu = _ring_scene(300_000, C, W, H, seed=1)
+    outs = []
+    for packed in (True, False):
+        p = [t.to(DEV).requires_grad_(True) for t in cpu[:5]]
+        rc, ra, meta = rasterization(*p, cpu[5].to(DEV), cpu[6].to(DEV), W, H, sh_degree=3, packed=packed,
+                                     rasterize_mode="antialiased")
+        (rc.square().sum() + ra.sum()).backward()
+        outs.append((rc.detach(), ra.detach(), [t.grad for t in p], meta))
+    torch.testing.assert_close(outs[0][0], outs[1][0], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(outs[0][1], outs[1][1], rtol=1e-5, atol=1e-6)
+    for a, b in zip(outs[0][2], outs[1][2]):
+        _close_frac(a, b, rtol=1e-3, atol=1e-5 * float(b.abs().max()) + 1e-8, max_bad=1e-3)
+    ids = outs[0][3]["isect_ids"]
+    assert bool((ids[1:] >= ids[:-1]).all())
+    tb = (82 * 53 - 1).bit_length()
+    assert int((ids >> (32 + tb)).max()) == C - 1
+    assert outs[0][3]["flatten_ids"].numel() == outs[1][3]["flatten_ids"].numel()
+
+
+def test_cfg5_4k_tile_grid_properties():
+    """cfg5's largest grid (3840x2160 -> 240x135 = 32400 tiles): offsets == histogram scan, alpha in [0,1]."""
+    from gsplat.rendering import rasterization
+
+    W, H = 3840, 2160
+    g = torch.Generator().manual_seed(2)
+    N = 400_000
+    fx = 0.5 * W / math.tan(math.radians(30))
+    z = torch.rand(N, generator=g) * 8 + 2
+    means = torch.stack([(torch.rand(N, generator=g) * 2.1 - 1.05) * z * W / (2 * fx),
+                         (torch.rand(N, generator=g) * 2.1 - 1.05) * z * H / (2 * fx), z], dim=-1)
+    quats = torch.randn(N, 4, generator=g)
+    scales = torch.exp(torch.rand(N, 3, generator=g) * 2.3 + math.log(0.002))
+    opac, colors = torch.rand(N, generator=g), torch.rand(N, 3, generator=g)
+    Ks = torch.tensor([[[fx, 0, W / 2], [0, fx, H / 2], [0, 0, 1.0]]])
+    rc, ra, meta = rasterization(*[t.to(DEV) for t in (means, quats, scales, opac, colors)],
+                                 torch.eye(4)[None].to(DEV), Ks.to(DEV), W, H, packed=False)
+    offs, ids = meta["isect_offsets"], meta["isect_ids"]
+    assert offs.shape == (1, 135, 240)
+    tiles = (ids >> 32) & ((1 << 15) - 1)
+    counts = torch.bincount(tiles, minlength=offs.numel())
+    assert torch.equal((torch.cumsum(counts, 0) - counts).int(), offs.flatten())
+    assert float(ra.min()) >= 0 and float(ra.max()) <= 1 and bool(torch.isfinite(rc).all())
