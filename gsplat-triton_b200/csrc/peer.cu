@@ -1,0 +1,315 @@
+// Fused pack + peer-store exchange of projected Gaussians over NVLink (one process per GPU).
+//
+// Replaces (behaviour, not code) the per-camera all-to-all of the reference's distributed path,
+// gsplat/rendering.py:453-494 + gsplat/distributed.py:170-257: cat -> split -> NCCL all_to_all ->
+// cat -> reshape_view, twice per direction (floats, then the int32 radii).
+//
+// Here every rank owns a "mailbox" allocation that its peers map through CUDA IPC. The put kernel
+// reads the projected SoA tensors once and stores each (8+D)-word row straight into the mailbox of
+// the rank that owns the row's camera, already in that rank's final camera-major order
+// [C_local, N_total]; the last CTA to finish publishes an epoch number into every peer's flag slot
+// (release, system scope). The receiving side runs ONE kernel that waits for the W flags (acquire)
+// and unpacks its mailbox into the SoA tensors the compositor reads. No NCCL call, no staging copy,
+// no host synchronisation; the transfer overlaps the packing store by store.
+//
+// Mailbox layout (identical on every rank):
+//   [0, 128)     uint64 flags_fwd[16]   slot s = epoch of the last forward put completed by rank s
+//   [128, 256)   uint64 flags_bwd[16]
+//   [256, 264)   uint32 done[2]         CTA completion counters of the local put kernels
+//   [1024, ...)  4 regions of `cap` bytes: (direction, epoch parity) -> 1024 + (2*dir + parity) * cap
+// Two regions per direction: a peer may start step t+1's put while this rank still unpacks step t,
+// but cannot reach step t+2's put before this rank has published step t+1 (stream order), see DESIGN.md 6.
+#include "common.cuh"
+
+#include <cstring>
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kMaxPeers = GSB_MAX_PEERS;
+constexpr int64_t kHeaderBytes = 1024;
+constexpr unsigned long long kWaitTimeoutNs = 20ull * 1000ull * 1000ull * 1000ull;
+
+struct PeerTable {
+    char *base[kMaxPeers];
+};
+struct RankBases {
+    int64_t base[kMaxPeers + 1];
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// called by every thread of the CTA after its peer stores: the last CTA of the grid publishes `epoch`
+__device__ __forceinline__ void publish_when_grid_done(const PeerTable &peers, int world, int rank, int dir,
+                                                       unsigned long long epoch) {
+    __shared__ bool s_last;
+    __threadfence_system();  // this thread's peer stores are ordered before what follows
+    __syncthreads();
+    unsigned *done = reinterpret_cast<unsigned *>(peers.base[rank] + 256) + dir;
+    if (threadIdx.x == 0) {
+        unsigned prev = atomicAdd(done, 1u);
+        s_last = (prev == gridDim.x - 1);
+        if (s_last) *done = 0u;  // ready for the next put in this direction (stream ordered)
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x < world) {
+        __threadfence_system();
+        unsigned long long *flag =
+            reinterpret_cast<unsigned long long *>(peers.base[threadIdx.x] + 128 * dir) + rank;
+        st_release_sys(flag, epoch);
+    }
+}
+
+// ---- mailbox region layout: structure of arrays ---------------------------------------------------
+// A region holding `rows` rows stores field after field (means2d 2, depths 1, conics 3, opacities 1,
+// colours D, [radii 1]), each field starting on a 16-byte boundary: the receiving rank's six output tensors
+// are views of ONE buffer with the same layout, so unpacking is a straight vectorised copy, and every
+// (camera, field) run a sender owns is contiguous on both sides.
+constexpr int kFields = 6;
+struct Fields {
+    const float *src[kFields];
+    int width[kFields];
+    int count;
+};
+__host__ __device__ __forceinline__ int64_t round_up4(int64_t v) { return (v + 3) & ~(int64_t)3; }
+__host__ __device__ __forceinline__ int64_t field_offset(const int *width, int field, int64_t rows) {
+    int64_t off = 0;
+    for (int g = 0; g < field; ++g) off += round_up4(rows * width[g]);
+    return off;
+}
+
+// copies `len` floats src -> dst with this CTA column (blockIdx.x of gridDim.x); src == NULL stores zeros
+__device__ __forceinline__ void copy_run(const float *__restrict__ src, float *__restrict__ dst, int64_t len) {
+    const int64_t tid = (int64_t)blockIdx.x * kThreads + threadIdx.x, step = (int64_t)gridDim.x * kThreads;
+    const bool vec = (((uintptr_t)dst & 15) == 0) && (src == nullptr || ((uintptr_t)src & 15) == 0);
+    if (vec) {
+        const int64_t n4 = len >> 2;
+        const float4 *s4 = reinterpret_cast<const float4 *>(src);
+        float4 *d4 = reinterpret_cast<float4 *>(dst);
+        for (int64_t i = tid; i < n4; i += step) d4[i] = src ? __ldg(s4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int64_t i = (n4 << 2) + tid; i < len; i += step) dst[i] = src ? src[i] : 0.f;
+    } else {
+        for (int64_t i = tid; i < len; i += step) dst[i] = src ? src[i] : 0.f;
+    }
+}
+
+// forward: segment (camera c of all world*C_local cameras, field f): N_local rows -> the rank owning camera c,
+// at rows [c_local, n_base .. n_base + N_local) of its [C_local, N_total] table
+__global__ void __launch_bounds__(kThreads)
+put_fwd_kernel(PeerTable peers, Fields fields, int world, int rank, int C_local, int64_t N_local, int64_t N_total,
+               int64_t n_base, int64_t region_offset, unsigned long long epoch) {
+    const int f = blockIdx.y % fields.count;
+    const int c = blockIdx.y / fields.count;
+    const int dest = c / C_local, c_local = c - dest * C_local;
+    const int w = fields.width[f];
+    const float *src = fields.src[f] + (int64_t)c * N_local * w;
+    float *dst = reinterpret_cast<float *>(peers.base[dest] + region_offset) +
+                 field_offset(fields.width, f, (int64_t)C_local * N_total) + ((int64_t)c_local * N_total + n_base) * w;
+    copy_run(src, dst, N_local * w);
+    publish_when_grid_done(peers, world, rank, 0, epoch);
+}
+
+// backward: segment (local camera c_local, destination rank r, field f): the N_r gradient rows of rank r's
+// Gaussians -> rank r, at rows [rank*C_local + c_local, 0 .. N_r) of its [world*C_local, N_r] table
+__global__ void __launch_bounds__(kThreads)
+put_bwd_kernel(PeerTable peers, Fields fields, RankBases bases, int world, int rank, int C_local, int64_t N_total,
+               int64_t region_offset, unsigned long long epoch) {
+    const int f = blockIdx.y % fields.count;
+    const int q = blockIdx.y / fields.count;
+    const int dest = q % world, c_local = q / world;
+    const int w = fields.width[f];
+    const int64_t b0 = bases.base[dest], N_dest = bases.base[dest + 1] - b0;
+    const float *src = fields.src[f] ? fields.src[f] + ((int64_t)c_local * N_total + b0) * w : nullptr;
+    float *dst = reinterpret_cast<float *>(peers.base[dest] + region_offset) +
+                 field_offset(fields.width, f, (int64_t)world * C_local * N_dest) +
+                 ((int64_t)rank * C_local + c_local) * N_dest * w;
+    copy_run(src, dst, N_dest * w);
+    publish_when_grid_done(peers, world, rank, 1, epoch);
+}
+
+// wait until every rank has published `epoch` in direction `dir`, then copy the local region out
+__global__ void __launch_bounds__(kThreads)
+wait_copy_kernel(const char *__restrict__ local_base, int world, int dir, unsigned long long epoch,
+                 int64_t region_offset, int64_t n_floats, float *__restrict__ out, int *timeout_flag) {
+    if (threadIdx.x < world) {
+        const unsigned long long *flag =
+            reinterpret_cast<const unsigned long long *>(local_base + 128 * dir) + threadIdx.x;
+        const unsigned long long t0 = global_timer_ns();
+        unsigned spins = 0;
+        while (ld_acquire_sys(flag) < epoch) {
+            if (++spins > 64u) {
+                __nanosleep(100);
+                if (global_timer_ns() - t0 > kWaitTimeoutNs) {  // a peer never arrived: report, do not hang the GPU
+                    if (timeout_flag) *reinterpret_cast<volatile int *>(timeout_flag) = 1 + (int)threadIdx.x;
+                    break;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    // region and `out` are 16-byte aligned (region offsets are multiples of 1 KB); peers wrote through L2,
+    // so read with .cg: never served from a stale L1 line
+    const float4 *box = reinterpret_cast<const float4 *>(local_base + region_offset);
+    float4 *o4 = reinterpret_cast<float4 *>(out);
+    const int64_t n4 = n_floats >> 2;
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n4; i += (int64_t)gridDim.x * kThreads)
+        o4[i] = __ldcg(box + i);
+}
+
+int fill_peers(PeerTable &t, const void *const *peer_bases_host, int world) {
+    for (int i = 0; i < kMaxPeers; ++i) t.base[i] = nullptr;
+    for (int i = 0; i < world; ++i) {
+        if (peer_bases_host[i] == nullptr) return -1;
+        t.base[i] = reinterpret_cast<char *>(const_cast<void *>(peer_bases_host[i]));
+    }
+    return 0;
+}
+
+#define GSB_CUDA_CALL(expr)                                               \
+    do {                                                                  \
+        cudaError_t e_ = (expr);                                          \
+        if (e_ != cudaSuccess) {                                          \
+            gsb_set_error("%s: %s", #expr, cudaGetErrorString(e_));       \
+            (void)cudaGetLastError();                                     \
+            return GSB_ERR_CUDA;                                          \
+        }                                                                 \
+    } while (0)
+
+}  // namespace
+
+extern "C" int64_t gsb_peer_header_bytes(void) { return kHeaderBytes; }
+extern "C" int gsb_peer_handle_bytes(void) { return (int)sizeof(cudaIpcMemHandle_t); }
+
+extern "C" int gsb_peer_alloc(int64_t bytes, void **dptr_out_host) {
+    GSB_REQUIRE(bytes >= kHeaderBytes && dptr_out_host != nullptr, "bad arguments");
+    void *p = nullptr;
+    GSB_CUDA_CALL(cudaMalloc(&p, (size_t)bytes));
+    GSB_CUDA_CALL(cudaMemset(p, 0, (size_t)kHeaderBytes));
+    GSB_CUDA_CALL(cudaDeviceSynchronize());
+    *dptr_out_host = p;
+    return GSB_OK;
+}
+
+extern "C" int gsb_peer_free(void *dptr) {
+    if (dptr != nullptr) GSB_CUDA_CALL(cudaFree(dptr));
+    return GSB_OK;
+}
+
+extern "C" int gsb_peer_get_handle(void *dptr, void *handle_out_host) {
+    GSB_REQUIRE(dptr != nullptr && handle_out_host != nullptr, "bad arguments");
+    GSB_CUDA_CALL(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t *>(handle_out_host), dptr));
+    return GSB_OK;
+}
+
+extern "C" int gsb_peer_open_handle(const void *handle_host, void **dptr_out_host) {
+    GSB_REQUIRE(handle_host != nullptr && dptr_out_host != nullptr, "bad arguments");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle_host, sizeof(h));
+    void *p = nullptr;
+    GSB_CUDA_CALL(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    *dptr_out_host = p;
+    return GSB_OK;
+}
+
+extern "C" int gsb_peer_close_handle(void *dptr) {
+    if (dptr != nullptr) GSB_CUDA_CALL(cudaIpcCloseMemHandle(dptr));
+    return GSB_OK;
+}
+
+extern "C" int gsb_peer_flag_alloc(void **flag_out_host) {
+    GSB_REQUIRE(flag_out_host != nullptr, "bad arguments");
+    int *p = nullptr;
+    GSB_CUDA_CALL(cudaHostAlloc(reinterpret_cast<void **>(&p), sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable));
+    *p = 0;
+    *flag_out_host = p;
+    return GSB_OK;
+}
+
+extern "C" int gsb_peer_flag_free(void *flag_host) {
+    if (flag_host != nullptr) GSB_CUDA_CALL(cudaFreeHost(flag_host));
+    return GSB_OK;
+}
+
+extern "C" int64_t gsb_a2a_field_offset(int64_t rows, int D, int field) {
+    const int width[kFields] = {2, 1, 3, 1, D, 1};
+    if (field < 0 || field > kFields) return -1;
+    return field_offset(width, field, rows);
+}
+
+namespace {
+unsigned blocks_per_run(int64_t len) {
+    int64_t b = (len / 4 + kThreads - 1) / kThreads;  // one float4 per thread
+    return (unsigned)(b < 1 ? 1 : (b > 64 ? 64 : b));
+}
+}  // namespace
+
+extern "C" int gsb_a2a_put_fwd(int world, int rank, int C_local, int64_t N_local, int64_t N_total, int64_t n_base,
+                               int D, const float *means2d, const float *depths, const float *conics,
+                               const float *opacities, const float *colors, const int32_t *radii,
+                               const void *const *peer_bases_host, int64_t region_offset, int64_t epoch,
+                               cudaStream_t stream) {
+    GSB_REQUIRE(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, "bad world/rank");
+    GSB_REQUIRE(C_local >= 1 && N_local >= 0 && N_total >= N_local && n_base >= 0 && D >= 1, "bad sizes");
+    GSB_REQUIRE((int64_t)world * C_local * kFields <= 65535, "too many cameras for one launch");
+    GSB_REQUIRE(region_offset >= kHeaderBytes && epoch > 0, "bad region/epoch");
+    PeerTable peers;
+    GSB_REQUIRE(fill_peers(peers, peer_bases_host, world) == 0, "null peer mailbox");
+    Fields fields = {{means2d, depths, conics, opacities, colors, reinterpret_cast<const float *>(radii)},
+                     {2, 1, 3, 1, D, 1}, kFields};
+    dim3 grid(blocks_per_run(N_local * (D > 3 ? D : 3)), (unsigned)(world * C_local * kFields));
+    put_fwd_kernel<<<grid, kThreads, 0, stream>>>(peers, fields, world, rank, C_local, N_local, N_total, n_base,
+                                                 region_offset, (unsigned long long)epoch);
+    return gsb_check_launch("a2a_put_fwd");
+}
+
+extern "C" int gsb_a2a_put_bwd(int world, int rank, int C_local, int64_t N_total, const int64_t *n_bases_host, int D,
+                               const float *v_means2d, const float *v_depths, const float *v_conics,
+                               const float *v_opacities, const float *v_colors,
+                               const void *const *peer_bases_host, int64_t region_offset, int64_t epoch,
+                               cudaStream_t stream) {
+    GSB_REQUIRE(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, "bad world/rank");
+    GSB_REQUIRE(C_local >= 1 && N_total >= 0 && D >= 1 && n_bases_host != nullptr, "bad sizes");
+    GSB_REQUIRE((int64_t)world * C_local * kFields <= 65535, "too many cameras for one launch");
+    GSB_REQUIRE(region_offset >= kHeaderBytes && epoch > 0, "bad region/epoch");
+    PeerTable peers;
+    GSB_REQUIRE(fill_peers(peers, peer_bases_host, world) == 0, "null peer mailbox");
+    RankBases bases;
+    int64_t widest = 0;
+    for (int i = 0; i <= kMaxPeers; ++i) bases.base[i] = (i <= world) ? n_bases_host[i] : n_bases_host[world];
+    for (int i = 0; i < world; ++i) {
+        GSB_REQUIRE(bases.base[i + 1] >= bases.base[i], "n_bases must be non-decreasing");
+        if (bases.base[i + 1] - bases.base[i] > widest) widest = bases.base[i + 1] - bases.base[i];
+    }
+    GSB_REQUIRE(bases.base[0] == 0 && bases.base[world] == N_total, "n_bases must run from 0 to N_total");
+    Fields fields = {{v_means2d, v_depths, v_conics, v_opacities, v_colors, nullptr}, {2, 1, 3, 1, D, 1}, kFields - 1};
+    dim3 grid(blocks_per_run(widest * (D > 3 ? D : 3)), (unsigned)(world * C_local * (kFields - 1)));
+    put_bwd_kernel<<<grid, kThreads, 0, stream>>>(peers, fields, bases, world, rank, C_local, N_total, region_offset,
+                                                 (unsigned long long)epoch);
+    return gsb_check_launch("a2a_put_bwd");
+}
+
+extern "C" int gsb_a2a_wait_copy(int world, int dir, int64_t epoch, const void *local_base, int64_t region_offset,
+                                 int64_t n_floats, float *out, int *timeout_flag, cudaStream_t stream) {
+    GSB_REQUIRE(world >= 1 && world <= kMaxPeers && (dir == 0 || dir == 1), "bad world/dir");
+    GSB_REQUIRE(n_floats >= 0 && (n_floats & 3) == 0 && local_base != nullptr, "bad sizes");
+    GSB_REQUIRE(region_offset >= kHeaderBytes && (region_offset & 15) == 0 && epoch > 0, "bad region/epoch");
+    GSB_REQUIRE(((uintptr_t)out & 15) == 0, "output buffer must be 16-byte aligned");
+    int64_t b = (n_floats / 4 + kThreads - 1) / kThreads;
+    unsigned grid = (unsigned)(b < 1 ? 1 : (b > 148 * 8 ? 148 * 8 : b));
+    wait_copy_kernel<<<grid, kThreads, 0, stream>>>(reinterpret_cast<const char *>(local_base), world, dir,
+                                                   (unsigned long long)epoch, region_offset, n_floats, out,
+                                                   timeout_flag);
+    return gsb_check_launch("a2a_wait_copy");
+}

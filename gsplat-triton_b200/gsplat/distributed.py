@@ -39,6 +39,31 @@ def all_gather_int32(world_size: int, value: Union[int, Tensor], device: Optiona
     return out.tolist() if scalar else list(out.unbind())
 
 
+_HOST_GROUP = None
+
+
+def all_gather_int_host(world_size: int, value: int) -> List[int]:
+    """Gathers one host integer from every rank WITHOUT touching the GPU stream.
+
+    `all_gather_int32` on a CUDA tensor costs a device-to-host read-back, i.e. the CPU waits for all queued
+    kernels of the previous step and the next forward's launches are exposed. The count of Gaussians is host
+    data already, so it travels over a host-side (gloo) group created on first use: the CPU keeps running ahead
+    of the GPU. Collective: every rank must call it."""
+    global _HOST_GROUP
+    if world_size == 1:
+        return [int(value)]
+    if dist.get_backend() == "gloo":
+        group = None
+    else:
+        if _HOST_GROUP is None:
+            _HOST_GROUP = dist.new_group(backend="gloo")
+        group = _HOST_GROUP
+    mine = torch.tensor([int(value)], dtype=torch.int64)
+    out = [torch.empty(1, dtype=torch.int64) for _ in range(world_size)]
+    dist.all_gather(out, mine, group=group)
+    return [int(t.item()) for t in out]
+
+
 def all_to_all_int32(world_size: int, values: List[Union[int, Tensor]], device: Optional[torch.device] = None):
     """Rank r sends values[i] to rank i and receives one integer from each (not differentiable)."""
     if world_size == 1:
@@ -220,6 +245,231 @@ def interleave_camera_major(rows: Tensor, C_local: int, N_world: Sequence[int]) 
         return rows.reshape(1, rows.shape[0], *rows.shape[1:])
     per_peer = rows.split([C_local * n for n in N_world], dim=0)
     return torch.cat([p.reshape(C_local, n, *rows.shape[1:]) for p, n in zip(per_peer, N_world)], dim=1)
+
+
+# ---------------------------------------------------------------------------------------------
+# peer-memory exchange (NVLink): fused pack + put kernels of csrc/peer.cu instead of NCCL all-to-all
+# ---------------------------------------------------------------------------------------------
+class PeerMailbox:
+    """Per-process mailbox that the other ranks of the node write into over NVLink (CUDA IPC).
+
+    One instance per process group. `ensure(bytes)` (collective: every rank must call it with the
+    same argument) grows the four regions; handles are exchanged with one all_gather. The device
+    protocol (epochs, flags, double-buffered regions) is described in csrc/peer.cu.
+    """
+
+    def __init__(self, group=None):
+        import ctypes
+
+        from .b200_impl._lib import lib
+
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        assert self.world <= 16, "peer exchange supports up to 16 ranks (GSB_MAX_PEERS)"
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        self.header = int(lib.gsb_peer_header_bytes())
+        self.capacity = 0  # bytes per region
+        self.local = None  # own mailbox (device pointer, int)
+        self.peers = [None] * self.world  # mapped peer mailboxes (own pointer at [rank])
+        self.peer_array = (ctypes.c_void_p * self.world)()
+        self.epoch = [0, 0]  # forward, backward
+        flag = ctypes.c_void_p()
+        _check(lib.gsb_peer_flag_alloc(ctypes.byref(flag)), "gsb_peer_flag_alloc")
+        self.timeout_flag = flag.value
+        self._flag_view = ctypes.cast(flag.value, ctypes.POINTER(ctypes.c_int))
+
+    def ensure(self, region_bytes: int) -> None:
+        if region_bytes <= self.capacity:
+            return
+        import ctypes
+
+        from .b200_impl._lib import lib
+
+        cap = max(int(region_bytes * 1.25), 1 << 20)
+        cap = (cap + 1023) // 1024 * 1024
+        # everything in flight (our puts into peers, their puts into us) must have landed before remapping
+        torch.cuda.synchronize(self.device)
+        dist.barrier(self.group)
+        self._release()
+        local = ctypes.c_void_p()
+        _check(lib.gsb_peer_alloc(self.header + 4 * cap, ctypes.byref(local)), "gsb_peer_alloc")
+        self.local = local.value
+        hb = int(lib.gsb_peer_handle_bytes())
+        handle = (ctypes.c_ubyte * hb)()
+        _check(lib.gsb_peer_get_handle(self.local, handle), "gsb_peer_get_handle")
+        mine = torch.tensor(list(handle), dtype=torch.uint8, device=self.device)
+        everyone = torch.empty((self.world, hb), dtype=torch.uint8, device=self.device)
+        dist.all_gather_into_tensor(everyone, mine, group=self.group)
+        everyone = everyone.cpu()
+        for r in range(self.world):
+            if r == self.rank:
+                self.peers[r] = self.local
+            else:
+                raw = (ctypes.c_ubyte * hb)(*everyone[r].tolist())
+                mapped = ctypes.c_void_p()
+                _check(lib.gsb_peer_open_handle(raw, ctypes.byref(mapped)), "gsb_peer_open_handle")
+                self.peers[r] = mapped.value
+            self.peer_array[r] = self.peers[r]
+        self.capacity = cap
+        self.epoch = [0, 0]  # fresh, zeroed flags on every rank
+        dist.barrier(self.group)  # nobody writes before every rank has mapped every mailbox
+
+    def region(self, direction: int, epoch: int) -> int:
+        return self.header + (2 * direction + (epoch & 1)) * self.capacity
+
+    def next_epoch(self, direction: int) -> int:
+        self.check()
+        self.epoch[direction] += 1
+        return self.epoch[direction]
+
+    def check(self) -> None:
+        """Raises if an earlier wait kernel gave up on a peer (it writes 1 + rank into host-mapped memory)."""
+        v = self._flag_view[0]
+        if v != 0:
+            raise RuntimeError(f"gsplat b200 peer exchange: rank {v - 1} never published its rows (timeout)")
+
+    def _release(self):
+        from .b200_impl._lib import lib
+
+        for r, p in enumerate(self.peers):
+            if p is not None and r != self.rank:
+                lib.gsb_peer_close_handle(p)
+            self.peers[r] = None
+        if self.local is not None:
+            lib.gsb_peer_free(self.local)
+            self.local = None
+        self.capacity = 0
+
+    def close(self):
+        from .b200_impl._lib import lib
+
+        torch.cuda.synchronize(self.device)
+        self._release()
+        if self.timeout_flag is not None:
+            lib.gsb_peer_flag_free(self.timeout_flag)
+            self.timeout_flag = None
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        from .b200_impl._lib import lib
+
+        raise RuntimeError(f"{what} failed ({rc}): {lib.gsb_last_error().decode()}")
+
+
+_MAILBOXES = {}
+
+
+def peer_exchange_available() -> bool:
+    """True when the row exchange can go through peer memory: NCCL process group, every rank on this
+    node with its own visible GPU, and GSPLAT_B200_EXCHANGE != "nccl"."""
+    if os.environ.get("GSPLAT_B200_EXCHANGE", "peer") == "nccl":
+        return False
+    if not (dist.is_available() and dist.is_initialized() and torch.cuda.is_available()):
+        return False
+    if dist.get_backend() != "nccl":
+        return False
+    world = dist.get_world_size()
+    return 1 < world <= 16 and world <= torch.cuda.device_count()
+
+
+def get_mailbox(group=None) -> PeerMailbox:
+    key = id(group) if group is not None else None
+    box = _MAILBOXES.get(key)
+    if box is None:
+        box = _MAILBOXES[key] = PeerMailbox(group)
+    return box
+
+
+def close_mailboxes() -> None:
+    for box in _MAILBOXES.values():
+        box.close()
+    _MAILBOXES.clear()
+
+
+def _region_views(rows: int, D: int, with_radii: bool, device):
+    """One flat float32 buffer laid out like a mailbox region (csrc/peer.cu) + its per-field views."""
+    from .b200_impl._lib import lib
+
+    n_fields = 6 if with_radii else 5
+    offs = [int(lib.gsb_a2a_field_offset(rows, D, f)) for f in range(n_fields + 1)]
+    widths = (2, 1, 3, 1, D, 1)
+    out = torch.empty((offs[-1],), dtype=torch.float32, device=device)
+    return out, [out[offs[f]:offs[f] + rows * widths[f]] for f in range(n_fields)]
+
+
+class _PeerExchangeRows(torch.autograd.Function):
+    """Projected rows [C, N_local, .] of all C = world*C_local cameras -> [C_local, N_total, .] of the local
+    cameras, through the peers' mailboxes; backward sends the gradients back the same way."""
+
+    @staticmethod
+    def forward(ctx, means2d, depths, conics, opacities, colors, radii, C_local, N_world):
+        from .b200_impl._lib import lib, ptr, stream_of
+
+        box = get_mailbox()
+        world, rank = box.world, box.rank
+        C, N_local = depths.shape
+        D = colors.shape[-1]
+        assert C == world * C_local and N_world[rank] == N_local
+        N_total = sum(N_world)
+        bases = [0]
+        for n in N_world:
+            bases.append(bases[-1] + n)
+        box.ensure(4 * max(int(lib.gsb_a2a_field_offset(C_local * N_total, D, 6)),
+                           int(lib.gsb_a2a_field_offset(C * max(N_world), D, 5))))
+        dev = means2d.device
+        st = stream_of(means2d)
+        epoch = box.next_epoch(0)
+        region = box.region(0, epoch)
+        lib.gsb_a2a_put_fwd(world, rank, C_local, N_local, N_total, bases[rank], D, ptr(means2d.contiguous()),
+                            ptr(depths.contiguous()), ptr(conics.contiguous()), ptr(opacities.contiguous()),
+                            ptr(colors.contiguous()), ptr(radii.contiguous()), box.peer_array, region, epoch, st)
+        rows = C_local * N_total
+        out, views = _region_views(rows, D, True, dev)
+        lib.gsb_a2a_wait_copy(world, 0, epoch, box.local, region, out.numel(), ptr(out), box.timeout_flag, st)
+        o_means2d, o_depths, o_conics, o_opac, o_colors, o_radii = (
+            views[0].view(C_local, N_total, 2), views[1].view(C_local, N_total), views[2].view(C_local, N_total, 3),
+            views[3].view(C_local, N_total), views[4].view(C_local, N_total, D),
+            views[5].view(torch.int32).view(C_local, N_total))
+        ctx.geom = (C_local, N_local, N_total, D, bases)
+        ctx.mark_non_differentiable(o_radii)
+        return o_means2d, o_depths, o_conics, o_opac, o_colors, o_radii
+
+    @staticmethod
+    def backward(ctx, v_means2d, v_depths, v_conics, v_opac, v_colors, v_radii):
+        import ctypes
+
+        from .b200_impl._lib import lib, ptr, stream_of
+
+        C_local, N_local, N_total, D, bases = ctx.geom
+        box = get_mailbox()
+        world, rank = box.world, box.rank
+        C = world * C_local
+        dev = box.device
+        st = torch.cuda.current_stream(dev).cuda_stream
+
+        def f32(t):
+            return None if t is None else t.float().contiguous()
+
+        epoch = box.next_epoch(1)
+        region = box.region(1, epoch)
+        grads = [f32(t) for t in (v_means2d, v_depths, v_conics, v_opac, v_colors)]
+        bases_arr = (ctypes.c_int64 * (world + 1))(*bases)
+        lib.gsb_a2a_put_bwd(world, rank, C_local, N_total, bases_arr, D, *(ptr(g) for g in grads), box.peer_array,
+                            region, epoch, st)
+        out, views = _region_views(C * N_local, D, False, dev)
+        lib.gsb_a2a_wait_copy(world, 1, epoch, box.local, region, out.numel(), ptr(out), box.timeout_flag, st)
+        g_means2d, g_depths, g_conics, g_opac, g_colors = (
+            views[0].view(C, N_local, 2), views[1].view(C, N_local), views[2].view(C, N_local, 3),
+            views[3].view(C, N_local), views[4].view(C, N_local, D))
+        return g_means2d, g_depths, g_conics, g_opac, g_colors, None, None, None
+
+
+def peer_exchange_rows(means2d, depths, conics, opacities, colors, radii, C_local: int, N_world: Sequence[int]):
+    """Fused exchange of the projected rows (unpacked mode): see `_PeerExchangeRows`."""
+    return _PeerExchangeRows.apply(means2d, depths, conics, opacities, colors, radii, int(C_local),
+                                   tuple(int(n) for n in N_world))
 
 
 # ---------------------------------------------------------------------------------------------

@@ -44,12 +44,15 @@ else:
 
 from .distributed import (
     all_gather_int32,
+    all_gather_int_host,
     all_gather_tensor_list,
     all_to_all_int32,
     all_to_all_rows,
     all_to_all_tensor_list,
     interleave_camera_major,
     pack_rows,
+    peer_exchange_available,
+    peer_exchange_rows,
     unpack_rows,
 )
 
@@ -130,7 +133,10 @@ def rasterization(
     if distributed:
         world_rank = torch.distributed.get_rank()
         world_size = torch.distributed.get_world_size()
-        N_world = all_gather_int32(world_size, N, device=device)
+        if BACKEND == "b200" and os.environ.get("GSPLAT_B200_HOST_COUNTS", "1") == "1":
+            N_world = all_gather_int_host(world_size, N)  # host-side channel: no GPU read-back per step
+        else:
+            N_world = all_gather_int32(world_size, N, device=device)
         C_world = [C] * world_size  # every rank must bring the same number of cameras
         viewmats, Ks = all_gather_tensor_list(world_size, [viewmats, Ks])
         C = len(viewmats)  # global camera count from here on
@@ -206,6 +212,11 @@ def rasterization(
             ids = all_to_all_rows(ids, cnts, recv)
             camera_ids, gaussian_ids = ids[:, 0].contiguous(), ids[:, 1].contiguous()
             C = C_world[world_rank]
+        elif BACKEND == "b200" and peer_exchange_available():
+            # fused pack + NVLink peer stores straight into the camera owner's [C_local, N_total] table
+            C = C_world[world_rank]
+            means2d, depths, conics, opacities, colors, radii = peer_exchange_rows(
+                means2d, depths, conics, opacities, colors, radii, C, N_world)
         else:
             C = C_world[world_rank]
             rows = pack_rows(means2d.flatten(0, 1), depths.flatten(0, 1), conics.flatten(0, 1),

@@ -197,6 +197,50 @@ int gsb_a2a_pack(int64_t rows, int D, const float *means2d, const float *depths,
 int gsb_a2a_unpack(int64_t rows, int D, const float *packed, float *means2d, float *depths, float *conics,
                    float *opacities, float *colors, int32_t *radii, cudaStream_t stream);
 
+/* ---- fused pack + peer-store exchange over NVLink (one process per GPU) -----------------------
+ * replaces the NCCL all_to_all + cat/split/reshape_view sequence of rendering.py:453-494 /
+ * distributed.py:170-257 for ranks of one NVLink domain. Each rank owns a "mailbox" allocation
+ * (gsb_peer_alloc: the one place this library allocates, because CUDA IPC needs its own cudaMalloc
+ * block) whose IPC handle (gsb_peer_handle_bytes bytes) the caller distributes to the peers
+ * (torch.distributed all_gather); peers map it with gsb_peer_open_handle. Layout of a mailbox:
+ * gsb_peer_header_bytes() of flags, then 4 regions of equal capacity, region_offset =
+ * header + (2 * dir + (epoch & 1)) * capacity, dir 0 = forward, 1 = backward.
+ * A region holding `rows` rows is a structure of arrays: means2d(2) depths(1) conics(3) opacities(1)
+ * colours(D) [radii(1), forward only], field f starting at float index gsb_a2a_field_offset(rows, D, f)
+ * (each field 16-byte aligned; f = 6 or 5 gives the region's total floats with / without radii).
+ *   gsb_a2a_put_fwd: every (camera, field) run of the local [world*C_local, N_local] projection is stored
+ *     directly into the mailbox of the rank owning the camera, at rows [c_local, n_base + n] of its
+ *     [C_local, N_total] table; the last CTA publishes `epoch` (> 0, increasing) to every peer.
+ *   gsb_a2a_put_bwd: gradient runs of the local [C_local, N_total] table go to the rank owning each Gaussian
+ *     (n_bases_host[world+1]: first global Gaussian of every rank), at rows [rank*C_local + c_local, n - base]
+ *     of its [world*C_local, N_r] table. NULL gradient pointers send zeros.
+ *   gsb_a2a_wait_copy: waits (device side, bounded: *timeout_flag, a host-mapped int from
+ *     gsb_peer_flag_alloc, becomes 1 + the rank that never arrived) for all `world` flags of direction
+ *     `dir` to reach `epoch`, then copies the local region (n_floats, multiple of 4) into `out`, whose
+ *     field views are the SoA tensors.
+ * `peer_bases_host`: host array of `world` device pointers (own mailbox at [rank]). */
+#define GSB_MAX_PEERS 16
+int64_t gsb_peer_header_bytes(void);
+int gsb_peer_handle_bytes(void);
+int gsb_peer_alloc(int64_t bytes, void **dptr_out_host);
+int gsb_peer_free(void *dptr);
+int gsb_peer_get_handle(void *dptr, void *handle_out_host);
+int gsb_peer_open_handle(const void *handle_host, void **dptr_out_host);
+int gsb_peer_close_handle(void *dptr);
+int gsb_peer_flag_alloc(void **flag_out_host);
+int gsb_peer_flag_free(void *flag_host);
+int gsb_a2a_put_fwd(int world, int rank, int C_local, int64_t N_local, int64_t N_total, int64_t n_base, int D,
+                    const float *means2d, const float *depths, const float *conics, const float *opacities,
+                    const float *colors, const int32_t *radii, const void *const *peer_bases_host,
+                    int64_t region_offset, int64_t epoch, cudaStream_t stream);
+int gsb_a2a_put_bwd(int world, int rank, int C_local, int64_t N_total, const int64_t *n_bases_host, int D,
+                    const float *v_means2d, const float *v_depths, const float *v_conics, const float *v_opacities,
+                    const float *v_colors, const void *const *peer_bases_host, int64_t region_offset,
+                    int64_t epoch, cudaStream_t stream);
+int gsb_a2a_wait_copy(int world, int dir, int64_t epoch, const void *local_base, int64_t region_offset,
+                      int64_t n_floats, float *out, int *timeout_flag, cudaStream_t stream);
+int64_t gsb_a2a_field_offset(int64_t rows, int D, int field);
+
 #ifdef __cplusplus
 }
 #endif

@@ -232,3 +232,21 @@ def test_cfg5_4k_tile_grid_properties():
     counts = torch.bincount(tiles, minlength=offs.numel())
     assert torch.equal((torch.cumsum(counts, 0) - counts).int(), offs.flatten())
     assert float(ra.min()) >= 0 and float(ra.max()) <= 1 and bool(torch.isfinite(rc).all())
+
+
+@pytest.mark.gpu
+def test_distributed_peer_exchange_two_gpus():
+    """rasterization(distributed=True) on 2 GPUs, fused peer-store exchange and NCCL all-to-all, vs a
+    single-GPU render of the whole scene (tools/dist_check.py). Needs two visible GPUs."""
+    import subprocess
+    import sys
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run(
+        [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+         "127.0.0.1", "--master-port", "29533", os.path.join(root, "tools", "dist_check.py")],
+        capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "MISMATCH" not in r.stdout
