@@ -3,6 +3,7 @@ restatement of the reference's rendering.py, plus size-independent properties at
 Protocol of the reference's tests/test_rasterization.py:22-89 (rtol = atol = 1e-4 on images/alphas).
 """
 import math
+import os
 
 import pytest
 import torch
