@@ -68,14 +68,16 @@ class ClockSampler:
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
     NAMES = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
 
-    def __init__(self, index):
-        self.rows, self.proc, self.index = [], None, index
+    def __init__(self, index, enabled=True):
+        self.rows, self.proc, self.index, self.enabled = [], None, index, enabled
 
     def __enter__(self):
+        if not self.enabled:
+            return self
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
         except OSError:
@@ -209,11 +211,16 @@ def run_b200(args):
     G, gA = loss_weights(dev)
     n_local = host_params[0].shape[0]
 
+    from gsplat.distributed import host_trace
+
     def iteration(params):
+        host_trace.mark()
         rc, ra, meta = rasterization(*params, viewmats, Ks, WIDTH, HEIGHT, sh_degree=SH_DEGREE, packed=False,
                                      distributed=(world > 1))
+        host_trace.mark()
         loss = (rc * G).sum() + (ra * gA).sum()
         loss.backward()
+        host_trace.mark("us_loss_backward")
         return rc, ra, loss, meta
 
     params = [t.to(dev).requires_grad_(True) for t in host_params]
@@ -245,14 +252,22 @@ def run_b200(args):
         resident_step()
     barrier()
     lib.gsb_reset_launch_count()
-    timing.reset(True)
-    clocks = ClockSampler(local_rank)
+    timing.reset(False)  # the timed steps carry no per-launch instrumentation; the stage table is measured after
+    # one sampler per NODE (local rank 0, its own GPU): N nvidia-smi pollers contend for the driver's locks
+    clocks = ClockSampler(local_rank, enabled=(local_rank == 0))
     clocks.__enter__()  # sampled through both timed regions (resident steps, then end-to-end steps)
+    host_trace.acc.clear()
     t0 = time.perf_counter()
     total_ms = timed_loop(resident_step, args.steps)
+    host_resident = host_trace.summary()
     barrier()
     wall_s = time.perf_counter() - t0
     launches = int(lib.gsb_launch_count())
+    # per-entry-point CUDA-event timing (the `stages` table / roofline): a second, instrumented pass
+    stage_steps = min(args.steps, 20)
+    timing.reset(True)
+    timed_loop(resident_step, stage_steps)
+    barrier()
     stage_summary = timing.summary()
     timing.reset(False)
 
@@ -321,7 +336,7 @@ def run_b200(args):
         clk = clocks.summary()
         C_local, D, K = 1, 3, (SH_DEGREE + 1) ** 2
         n_rows = meta["means2d"].shape[1]
-        stages = _stage_table(stage_summary, args.steps, meta, n_rows, C_local, D, K, work, peaks, clk["sm_mhz"])
+        stages = _stage_table(stage_summary, stage_steps, meta, n_rows, C_local, D, K, work, peaks, clk["sm_mhz"])
         top = max((k for k in stages if "bound" in stages[k]), key=lambda k: stages[k]["ms_per_step"])
         roof = {k: stages[top][k] for k in ("bound", "achieved", "peak", "unit", "frac")}
         traffic_file = os.path.join(ROOT, "profiles", "ncu_traffic.json")
@@ -347,6 +362,8 @@ def run_b200(args):
             "gpu_launches": launches, "wall_s_timed_region": round(wall_s, 3), "clocks": clk,
             "roofline": roof, "stages": stages,
         }
+        if host_trace.enabled:
+            line["host_trace_us"] = host_resident
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(rows=2, gauss_stride=8)
         print(json.dumps(line), flush=True)

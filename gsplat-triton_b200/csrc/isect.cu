@@ -10,6 +10,8 @@
 
 #include <cub/device/device_radix_sort.cuh>
 
+#include <cstdint>
+
 namespace {
 
 constexpr int kThreads = 256;
@@ -224,7 +226,7 @@ emit_perm_kernel(int64_t P, int N, const int32_t *__restrict__ perm, const float
                  const int32_t *__restrict__ radii, const int64_t *__restrict__ camera_ids, int tile_size, int tw,
                  int th, int tile_n_bits, const int32_t *__restrict__ tiles_per_gauss,
                  const int64_t *__restrict__ block_offsets, uint32_t *__restrict__ tile_keys,
-                 int32_t *__restrict__ flatten_ids) {
+                 int32_t *__restrict__ flatten_ids, int64_t capacity) {
     __shared__ int s_warp[kThreads / 32];
     int64_t k = (int64_t)blockIdx.x * kThreads + threadIdx.x;
     int64_t i = k < P ? perm[k] : 0;
@@ -239,19 +241,40 @@ emit_perm_kernel(int64_t P, int N, const int32_t *__restrict__ perm, const float
     uint32_t hi = cam << tile_n_bits;
     for (int y = b.y0; y < b.y1; ++y) {
         for (int x = b.x0; x < b.x1; ++x) {
-            tile_keys[out] = hi | (uint32_t)(y * tw + x);
-            flatten_ids[out] = (int32_t)i;
+            if (out < capacity) {  // speculative capacity (gsb_isect_emit_perm_cap): never write past the buffers
+                tile_keys[out] = hi | (uint32_t)(y * tw + x);
+                flatten_ids[out] = (int32_t)i;
+            }
             ++out;
         }
     }
 }
 
+// slots [n_isects, capacity) of a speculatively sized buffer: keys that sort behind every real (camera | tile) word
+__global__ void __launch_bounds__(kThreads)
+pad_tail_kernel(const int64_t *__restrict__ n_isects_dev, int64_t capacity, uint32_t *__restrict__ tile_keys,
+                int32_t *__restrict__ flatten_ids) {
+    const int64_t n = *n_isects_dev;
+    for (int64_t i = n + (int64_t)blockIdx.x * kThreads + threadIdx.x; i < capacity; i += (int64_t)gridDim.x * kThreads) {
+        tile_keys[i] = 0xffffffffu;
+        flatten_ids[i] = 0;
+    }
+}
+
 // sorted (camera | tile) words + row ids -> the reference's 64-bit keys and the per-tile offsets
 __global__ void __launch_bounds__(kThreads)
-finalize_kernel(int64_t n_isects, const uint32_t *__restrict__ tile_keys, const int32_t *__restrict__ flatten_ids,
-                const float *__restrict__ depths, int n_tiles, int tile_n_bits, int64_t total_tiles,
-                int64_t *__restrict__ isect_ids, int32_t *__restrict__ offsets) {
+finalize_kernel(int64_t n_isects, const int64_t *__restrict__ n_isects_dev, const uint32_t *__restrict__ tile_keys,
+                const int32_t *__restrict__ flatten_ids, const float *__restrict__ depths, int n_tiles,
+                int tile_n_bits, int64_t total_tiles, int64_t *__restrict__ isect_ids, int32_t *__restrict__ offsets) {
     int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (n_isects_dev != nullptr) {  // n_isects is the buffer capacity, the real count lives on the device
+        const int64_t n = *n_isects_dev;
+        n_isects = n < n_isects ? n : n_isects;
+        if (n_isects == 0) {
+            for (int64_t t = i; t < total_tiles; t += (int64_t)gridDim.x * kThreads) offsets[t] = 0;
+            return;
+        }
+    }
     if (i >= n_isects) return;
     const uint32_t key = tile_keys[i];
     const uint32_t tile_mask = (1u << tile_n_bits) - 1u;
@@ -397,20 +420,38 @@ extern "C" int gsb_isect_emit_perm(int64_t P, int N, int packed, const int32_t *
                                    int tile_height, int tile_n_bits, const int32_t *tiles_per_gauss,
                                    const int64_t *block_offsets, int32_t *tile_keys, int32_t *flatten_ids,
                                    cudaStream_t stream) {
-    GSB_REQUIRE(P >= 0 && tile_size > 0, "bad sizes");
-    GSB_REQUIRE(!packed || camera_ids != nullptr, "camera_ids required when packed");
-    if (P == 0) return GSB_OK;
-    unsigned nblk = (unsigned)gsb_isect_num_blocks(P);
+    return gsb_isect_emit_perm_cap(P, N, packed, perm, means2d, radii, camera_ids, tile_size, tile_width, tile_height,
+                                   tile_n_bits, tiles_per_gauss, block_offsets, tile_keys, flatten_ids,
+                                   INT64_MAX, nullptr, stream);
+}
+
+extern "C" int gsb_isect_emit_perm_cap(int64_t P, int N, int packed, const int32_t *perm, const float *means2d,
+                                       const int32_t *radii, const int64_t *camera_ids, int tile_size, int tile_width,
+                                       int tile_height, int tile_n_bits, const int32_t *tiles_per_gauss,
+                                       const int64_t *block_offsets, int32_t *tile_keys, int32_t *flatten_ids,
+                                       int64_t capacity, const int64_t *n_isects_dev, cudaStream_t stream) {
+    GSB_REQUIRE(P >= 0 && tile_size > 0 && capacity >= 0, "bad sizes");
+    GSB_REQUIRE(!packed || camera_ids != nullptr || P == 0, "camera_ids required when packed");
     auto tk = reinterpret_cast<uint32_t *>(tile_keys);
-    if (packed)
-        emit_perm_kernel<true><<<nblk, kThreads, 0, stream>>>(P, N, perm, means2d, radii, camera_ids, tile_size,
-                                                              tile_width, tile_height, tile_n_bits, tiles_per_gauss,
-                                                              block_offsets, tk, flatten_ids);
-    else
-        emit_perm_kernel<false><<<nblk, kThreads, 0, stream>>>(P, N, perm, means2d, radii, camera_ids, tile_size,
-                                                               tile_width, tile_height, tile_n_bits, tiles_per_gauss,
-                                                               block_offsets, tk, flatten_ids);
-    return gsb_check_launch("isect_emit_perm");
+    if (P > 0) {
+        unsigned nblk = (unsigned)gsb_isect_num_blocks(P);
+        if (packed)
+            emit_perm_kernel<true><<<nblk, kThreads, 0, stream>>>(P, N, perm, means2d, radii, camera_ids, tile_size,
+                                                                  tile_width, tile_height, tile_n_bits,
+                                                                  tiles_per_gauss, block_offsets, tk, flatten_ids,
+                                                                  capacity);
+        else
+            emit_perm_kernel<false><<<nblk, kThreads, 0, stream>>>(P, N, perm, means2d, radii, camera_ids, tile_size,
+                                                                   tile_width, tile_height, tile_n_bits,
+                                                                   tiles_per_gauss, block_offsets, tk, flatten_ids,
+                                                                   capacity);
+        if (int e = gsb_check_launch("isect_emit_perm")) return e;
+    }
+    if (n_isects_dev != nullptr && capacity > 0) {
+        pad_tail_kernel<<<148, kThreads, 0, stream>>>(n_isects_dev, capacity, tk, flatten_ids);
+        return gsb_check_launch("isect_pad_tail");
+    }
+    return GSB_OK;
 }
 
 extern "C" int64_t gsb_sort_pairs_u32_temp_bytes(int64_t n) {
@@ -442,7 +483,16 @@ extern "C" int gsb_sort_pairs_u32(int64_t n, int end_bit, int32_t *keys, int32_t
 extern "C" int gsb_isect_finalize(int64_t n_isects, const int32_t *tile_keys, const int32_t *flatten_ids,
                                   const float *depths, int C, int tile_width, int tile_height, int tile_n_bits,
                                   int64_t *isect_ids, int32_t *offsets, cudaStream_t stream) {
+    return gsb_isect_finalize_cap(n_isects, nullptr, tile_keys, flatten_ids, depths, C, tile_width, tile_height,
+                                  tile_n_bits, isect_ids, offsets, stream);
+}
+
+extern "C" int gsb_isect_finalize_cap(int64_t n_isects, const int64_t *n_isects_dev, const int32_t *tile_keys,
+                                      const int32_t *flatten_ids, const float *depths, int C, int tile_width,
+                                      int tile_height, int tile_n_bits, int64_t *isect_ids, int32_t *offsets,
+                                      cudaStream_t stream) {
     GSB_REQUIRE(n_isects >= 0 && C >= 0, "bad sizes");
+    GSB_REQUIRE(n_isects_dev == nullptr || n_isects > 0, "a speculative capacity must be positive");
     int64_t n_tiles = (int64_t)tile_width * tile_height;
     int64_t total = n_tiles * C;
     if (total == 0) return GSB_OK;
@@ -452,7 +502,7 @@ extern "C" int gsb_isect_finalize(int64_t n_isects, const int32_t *tile_keys, co
         return GSB_OK;
     }
     finalize_kernel<<<gsb_cdiv(n_isects, kThreads), kThreads, 0, stream>>>(
-        n_isects, reinterpret_cast<const uint32_t *>(tile_keys), flatten_ids, depths, (int)n_tiles, tile_n_bits, total,
-        isect_ids, offsets);
+        n_isects, n_isects_dev, reinterpret_cast<const uint32_t *>(tile_keys), flatten_ids, depths, (int)n_tiles,
+        tile_n_bits, total, isect_ids, offsets);
     return gsb_check_launch("isect_finalize");
 }

@@ -55,10 +55,10 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
 __device__ __forceinline__ void publish_when_grid_done(const PeerTable &peers, int world, int rank, int dir,
                                                        unsigned long long epoch) {
     __shared__ bool s_last;
-    __threadfence_system();  // this thread's peer stores are ordered before what follows
-    __syncthreads();
+    __syncthreads();  // every thread's peer stores happen-before thread 0's fence (cumulative)
     unsigned *done = reinterpret_cast<unsigned *>(peers.base[rank] + 256) + dir;
     if (threadIdx.x == 0) {
+        __threadfence_system();
         unsigned prev = atomicAdd(done, 1u);
         s_last = (prev == gridDim.x - 1);
         if (s_last) *done = 0u;  // ready for the next put in this direction (stream ordered)

@@ -361,6 +361,7 @@ def isect_tiles(
     n_cameras: Optional[int] = None,
     camera_ids: Optional[Tensor] = None,
     gaussian_ids: Optional[Tensor] = None,
+    _speculate: bool = False,
 ) -> Tuple[Tensor, Tensor, Tensor]:
     """Maps projected Gaussians to the tiles they overlap.
 
@@ -399,42 +400,16 @@ def isect_tiles(
     tb = tile_n_bits(n_tiles)
     cb = max(C - 1, 0).bit_length()
     assert 32 + tb + cb <= 64, "camera/tile ids do not fit a 64-bit intersection key"
-    tiles_per_gauss = torch.empty(radii.shape, dtype=torch.int32, device=dev)
 
     if sort and tb + cb <= 32 and os.environ.get("GSPLAT_B200_SORT", "presort") != "global":
-        # depth-presorted path (include/gsplat_b200.h): sort the P rows by (camera, depth), emit in that order,
-        # then sort the intersections by their (camera | tile) bits only; offsets fall out of the last pass.
-        nblk = int(lib.gsb_isect_num_blocks(P))
-        rows = torch.empty((P,), dtype=torch.int32, device=dev)
-        if C == 1:
-            # one camera: the row key is the depth bit pattern itself (positive floats order like their bits)
-            lib.gsb_isect_row_keys(P, N, int(packed), ptr(depths), ptr(camera_ids), None, ptr(rows), st)
-            _, perm = _sort_pairs_u32(depths.reshape(-1).view(torch.int32).clone(), rows, 32)
-        else:
-            row_keys = torch.empty((P,), dtype=torch.int64, device=dev)
-            lib.gsb_isect_row_keys(P, N, int(packed), ptr(depths), ptr(camera_ids), ptr(row_keys), ptr(rows), st)
-            _, perm = _sort_pairs(row_keys, rows, 32 + cb)
-        block_sums = torch.empty((max(nblk, 1),), dtype=torch.int32, device=dev)
-        block_offsets = torch.empty((nblk + 1,), dtype=torch.int64, device=dev)
-        lib.gsb_isect_count_perm(P, ptr(perm), ptr(means2d), ptr(radii), tile_size, tile_width, tile_height,
-                                 ptr(tiles_per_gauss), ptr(block_sums), ptr(block_offsets),
-                                 block_offsets.data_ptr() + 8 * nblk, st)
-        n_isects = int(block_offsets[-1].item())  # the one size read-back (isect_tiles.py:102, Intersect.cpp:77-78)
-        isect_ids = torch.empty((n_isects,), dtype=torch.int64, device=dev)
-        offsets = torch.empty((C, tile_height, tile_width), dtype=torch.int32, device=dev)
-        tile_keys = torch.empty((n_isects,), dtype=torch.int32, device=dev)
-        flatten_ids = torch.empty((n_isects,), dtype=torch.int32, device=dev)
-        if n_isects > 0:
-            lib.gsb_isect_emit_perm(P, N, int(packed), ptr(perm), ptr(means2d), ptr(radii), ptr(camera_ids),
-                                    tile_size, tile_width, tile_height, tb, ptr(tiles_per_gauss), ptr(block_offsets),
-                                    ptr(tile_keys), ptr(flatten_ids), st)
-            tile_keys, flatten_ids = _sort_pairs_u32(tile_keys, flatten_ids, tb + cb)
-        lib.gsb_isect_finalize(n_isects, ptr(tile_keys), ptr(flatten_ids), ptr(depths), C, tile_width, tile_height,
-                               tb, ptr(isect_ids), ptr(offsets), st)
-        # the finalize pass already produced isect_offset_encode's answer for these ids: hand it over with them
-        isect_ids._b200_offsets = (C, tile_width, tile_height, tb, offsets)
+        tiles_per_gauss, isect_ids, flatten_ids, offsets, pending = _isect_presorted(
+            means2d, radii, depths, camera_ids, C, N, P, packed, tile_size, tile_width, tile_height, tb, cb,
+            _speculate)
+        if _speculate:
+            return tiles_per_gauss, isect_ids, flatten_ids, offsets, pending
         return tiles_per_gauss, isect_ids, flatten_ids
 
+    tiles_per_gauss = torch.empty(radii.shape, dtype=torch.int32, device=dev)
     nblk = int(lib.gsb_isect_num_blocks(P))
     block_sums = torch.empty((max(nblk, 1),), dtype=torch.int32, device=dev)
     block_offsets = torch.empty((nblk + 1,), dtype=torch.int64, device=dev)
@@ -444,13 +419,95 @@ def isect_tiles(
     isect_ids = torch.empty((n_isects,), dtype=torch.int64, device=dev)
     flatten_ids = torch.empty((n_isects,), dtype=torch.int32, device=dev)
     if n_isects == 0:
-        return tiles_per_gauss, isect_ids, flatten_ids
+        return (tiles_per_gauss, isect_ids, flatten_ids) + ((None, None) if _speculate else ())
     lib.gsb_isect_emit(P, N, int(packed), ptr(means2d), ptr(radii), ptr(depths), ptr(camera_ids), tile_size,
                        tile_width, tile_height, tb, ptr(tiles_per_gauss), ptr(block_offsets), ptr(isect_ids),
                        ptr(flatten_ids), st)
     if sort:
         isect_ids, flatten_ids = _sort_pairs(isect_ids, flatten_ids, 32 + tb + cb)
+    if _speculate:
+        return tiles_per_gauss, isect_ids, flatten_ids, None, None
     return tiles_per_gauss, isect_ids, flatten_ids
+
+
+# last n_isects seen per (device, cameras, tile grid, packed): sizes the next call's buffers without a read-back
+_ISECT_ESTIMATE = {}
+
+
+class _PendingCount:
+    """n_isects of a speculatively sized isect_tiles call: its device-to-host copy is queued right after the
+    count kernel and awaited only after the compositor has been launched, so the GPU never idles on it."""
+
+    def __init__(self, n_dev: Tensor, capacity: int, key):
+        self.n_dev, self.capacity, self.key = n_dev, capacity, key
+        self.host = torch.empty((1,), dtype=torch.int64, pin_memory=True)
+        self.host.copy_(n_dev, non_blocking=True)
+        self.event = torch.cuda.Event()
+        self.event.record()
+        self.n = None
+
+    def wait(self) -> int:
+        if self.n is None:
+            self.event.synchronize()
+            self.n = int(self.host[0])
+            _ISECT_ESTIMATE[self.key] = self.n
+        return self.n
+
+
+def _isect_presorted(means2d, radii, depths, camera_ids, C, N, P, packed, tile_size, tile_width, tile_height, tb, cb,
+                     speculate):
+    """Depth-presorted isect_tiles (include/gsplat_b200.h): sort the P rows by (camera, depth), emit in that
+    order, then sort the intersections by their (camera | tile) bits only; offsets fall out of the last pass.
+
+    `speculate`: size the intersection buffers from the previous call's count (+12.5 %) and keep the real count
+    on the device; returns a `_PendingCount` the caller must `wait()` on (and redo the call exactly if the count
+    exceeded the capacity). Without an estimate, or when not speculating, the count is read back here."""
+    dev = means2d.device
+    st = stream_of(means2d)
+    tiles_per_gauss = torch.empty(radii.shape, dtype=torch.int32, device=dev)
+    nblk = int(lib.gsb_isect_num_blocks(P))
+    rows = torch.empty((P,), dtype=torch.int32, device=dev)
+    if C == 1:
+        # one camera: the row key is the depth bit pattern itself (positive floats order like their bits)
+        lib.gsb_isect_row_keys(P, N, int(packed), ptr(depths), ptr(camera_ids), None, ptr(rows), st)
+        _, perm = _sort_pairs_u32(depths.reshape(-1).view(torch.int32).clone(), rows, 32)
+    else:
+        row_keys = torch.empty((P,), dtype=torch.int64, device=dev)
+        lib.gsb_isect_row_keys(P, N, int(packed), ptr(depths), ptr(camera_ids), ptr(row_keys), ptr(rows), st)
+        _, perm = _sort_pairs(row_keys, rows, 32 + cb)
+    block_sums = torch.empty((max(nblk, 1),), dtype=torch.int32, device=dev)
+    block_offsets = torch.empty((nblk + 1,), dtype=torch.int64, device=dev)
+    lib.gsb_isect_count_perm(P, ptr(perm), ptr(means2d), ptr(radii), tile_size, tile_width, tile_height,
+                             ptr(tiles_per_gauss), ptr(block_sums), ptr(block_offsets),
+                             block_offsets.data_ptr() + 8 * nblk, st)
+    key = (dev.index, C, tile_width, tile_height, tile_size, bool(packed))
+    estimate = _ISECT_ESTIMATE.get(key) if speculate else None
+    pending = None
+    if estimate is None:
+        n_isects = int(block_offsets[-1].item())  # the one size read-back (isect_tiles.py:102, Intersect.cpp:77-78)
+        _ISECT_ESTIMATE[key] = n_isects
+        n_dev = None
+    else:
+        n_isects = min(estimate + estimate // 8 + 4096, (1 << 31) - 1)  # capacity, not the count
+        pending = _PendingCount(block_offsets[nblk:], n_isects, key)
+        n_dev = block_offsets.data_ptr() + 8 * nblk
+    isect_ids = torch.empty((n_isects,), dtype=torch.int64, device=dev)
+    offsets = torch.empty((C, tile_height, tile_width), dtype=torch.int32, device=dev)
+    tile_keys = torch.empty((n_isects,), dtype=torch.int32, device=dev)
+    flatten_ids = torch.empty((n_isects,), dtype=torch.int32, device=dev)
+    if n_isects > 0:
+        lib.gsb_isect_emit_perm_cap(P, N, int(packed), ptr(perm), ptr(means2d), ptr(radii), ptr(camera_ids),
+                                    tile_size, tile_width, tile_height, tb, ptr(tiles_per_gauss), ptr(block_offsets),
+                                    ptr(tile_keys), ptr(flatten_ids), n_isects, n_dev, st)
+        tile_keys, flatten_ids = _sort_pairs_u32(tile_keys, flatten_ids, tb + cb)
+    lib.gsb_isect_finalize_cap(n_isects, n_dev if n_isects > 0 else None, ptr(tile_keys), ptr(flatten_ids),
+                               ptr(depths), C, tile_width, tile_height, tb, ptr(isect_ids), ptr(offsets), st)
+    if pending is None:
+        # the finalize pass already produced isect_offset_encode's answer for these ids: hand it over with them
+        isect_ids._b200_offsets = (C, tile_width, tile_height, tb, offsets)
+    else:
+        flatten_ids._b200_pending = pending
+    return tiles_per_gauss, isect_ids, flatten_ids, offsets, pending
 
 
 def _sort_pairs(keys: Tensor, vals: Tensor, end_bit: int) -> Tuple[Tensor, Tensor]:
@@ -552,6 +609,8 @@ def rasterize_to_pixels(
     assert tile_width * tile_size >= image_width, f"Assert Failed: {tile_width} * {tile_size} >= {image_width}"
     require_cuda(means2d, conics, colors, opacities, isect_offsets, flatten_ids, backgrounds, masks)
 
+    pending = getattr(flatten_ids, "_b200_pending", None)  # speculatively sized ids (see _isect_presorted)
+
     def run(colors_c, backgrounds_c):
         ch = colors_c.shape[-1]
         target = next(c for c in _RASTER_CHANNELS if c >= ch)
@@ -564,7 +623,7 @@ def rasterize_to_pixels(
             means2d.contiguous(), conics.contiguous(), colors_c.contiguous(), opacities.contiguous(),
             backgrounds_c.contiguous() if backgrounds_c is not None else None, masks, image_width, image_height,
             tile_size, isect_offsets.contiguous(),
-            flatten_ids.contiguous(), absgrad,
+            flatten_ids.contiguous(), absgrad, pending,
         )
         return (rc[..., :ch] if pad else rc), ra
 
@@ -585,7 +644,7 @@ class _RasterizeToPixels(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, means2d, conics, colors, opacities, backgrounds, masks, width, height, tile_size,
-                isect_offsets, flatten_ids, absgrad):
+                isect_offsets, flatten_ids, absgrad, pending=None):
         C, tile_height, tile_width = isect_offsets.shape
         D = colors.shape[-1]
         dev = means2d.device
@@ -600,9 +659,13 @@ class _RasterizeToPixels(torch.autograd.Function):
         render_colors = torch.empty((C, height, width, D), dtype=torch.float32, device=dev)
         render_alphas = torch.empty((C, height, width, 1), dtype=torch.float32, device=dev)
         last_ids = torch.empty((C, height, width), dtype=torch.int32, device=dev)
-        lib.gsb_rasterize_fwd(C, n_isects, D, ptr(rec[0]), ptr(rec[1]), ptr(colors), ptr(backgrounds), ptr(m8),
-                              width, height, tile_size, tile_width, tile_height, ptr(isect_offsets),
-                              ptr(flatten_ids), ptr(render_colors), ptr(render_alphas), ptr(last_ids), st)
+        n_dev = ptr(pending.n_dev) if (pending is not None and pending.n is None) else None
+        if pending is not None and pending.n is not None:
+            n_isects = min(n_isects, pending.n)
+        lib.gsb_rasterize_fwd_cap(C, n_isects, n_dev, D, ptr(rec[0]), ptr(rec[1]), ptr(colors), ptr(backgrounds),
+                                  ptr(m8), width, height, tile_size, tile_width, tile_height, ptr(isect_offsets),
+                                  ptr(flatten_ids), ptr(render_colors), ptr(render_alphas), ptr(last_ids), st)
+        ctx.pending = pending
         ctx.save_for_backward(means2d, rec, colors, backgrounds, m8, isect_offsets, flatten_ids, render_alphas,
                               last_ids)
         ctx.width, ctx.height, ctx.tile_size, ctx.absgrad = width, height, tile_size, absgrad
@@ -629,7 +692,8 @@ class _RasterizeToPixels(torch.autograd.Function):
         v_colors = parts[2].view(colors.shape)
         v_opacities = parts[3].view(opac_shape)
         v_abs = parts[4].view(means2d.shape) if ctx.absgrad else None
-        lib.gsb_rasterize_bwd(C, flatten_ids.numel(), D, ptr(rec[0]), ptr(rec[1]), ptr(colors), ptr(backgrounds),
+        n_isects = flatten_ids.numel() if ctx.pending is None else min(flatten_ids.numel(), ctx.pending.wait())
+        lib.gsb_rasterize_bwd(C, n_isects, D, ptr(rec[0]), ptr(rec[1]), ptr(colors), ptr(backgrounds),
                               ptr(m8), ctx.width, ctx.height, ctx.tile_size, tile_width, tile_height,
                               ptr(isect_offsets), ptr(flatten_ids), ptr(render_alphas), ptr(last_ids),
                               ptr(v_render_colors), ptr(v_render_alphas), ptr(v_abs), ptr(v_means2d),
@@ -639,4 +703,4 @@ class _RasterizeToPixels(torch.autograd.Function):
         v_backgrounds = None
         if ctx.needs_input_grad[4]:
             v_backgrounds = (v_render_colors * (1.0 - render_alphas).float()).sum(dim=(1, 2))
-        return (v_means2d, v_conics, v_colors, v_opacities, v_backgrounds) + (None,) * 7
+        return (v_means2d, v_conics, v_colors, v_opacities, v_backgrounds) + (None,) * 8

@@ -20,6 +20,31 @@ import torch.distributed as dist
 from torch import Tensor
 
 
+class _HostTrace:
+    """Optional CPU-side phase timer (GSPLAT_B200_TRACE=1): where the launching thread spends its time."""
+
+    def __init__(self):
+        self.enabled = os.environ.get("GSPLAT_B200_TRACE", "0") == "1"
+        self.acc, self.t = {}, None
+
+    def mark(self, name=None):
+        if not self.enabled:
+            return
+        import time
+
+        now = time.perf_counter()
+        if name is not None and self.t is not None:
+            c, tot = self.acc.get(name, (0, 0.0))
+            self.acc[name] = (c + 1, tot + now - self.t)
+        self.t = now
+
+    def summary(self):
+        return {k: round(1e6 * tot / max(c, 1), 1) for k, (c, tot) in self.acc.items()}
+
+
+host_trace = _HostTrace()
+
+
 def _as_int_list(values: Sequence[Union[int, Tensor]]) -> List[int]:
     return [int(v.item()) if isinstance(v, Tensor) else int(v) for v in values]
 
@@ -39,29 +64,88 @@ def all_gather_int32(world_size: int, value: Union[int, Tensor], device: Optiona
     return out.tolist() if scalar else list(out.unbind())
 
 
-_HOST_GROUP = None
+class HostBoard:
+    """Host-side all-gather of one integer per rank through a shared-memory file per rank (one node).
+
+    `all_gather_int32` on a CUDA tensor costs a device-to-host read-back: the CPU waits for every queued kernel
+    of the previous step and the next forward's launches are exposed. The count of Gaussians is host data
+    already, so the ranks post it on a board in /dev/shm instead: microseconds, no GPU involvement, the CPU
+    keeps running ahead of the GPU. Slot layout per rank: int64[2][3] = (sequence, value, check) for even / odd
+    sequence numbers (a rank can be at most one gather ahead of a peer that has not read it yet).
+    """
+
+    _MAGIC = 0x5DEECE66D
+
+    def __init__(self, group=None):
+        import mmap
+        import tempfile
+        import uuid
+
+        import numpy as np
+
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        root = "/dev/shm" if os.path.isdir("/dev/shm") else tempfile.gettempdir()
+        name = [f"gsb_board_{os.getpid()}_{uuid.uuid4().hex[:12]}"]
+        dist.broadcast_object_list(name, src=0, group=group)
+        self.paths = [os.path.join(root, f"{name[0]}_{r}") for r in range(self.world)]
+        with open(self.paths[self.rank], "wb") as f:
+            f.write(b"\0" * 64)
+        dist.barrier(group)  # every rank's file exists
+        self.maps, self.slots = [], []
+        for path in self.paths:
+            f = open(path, "r+b")
+            m = mmap.mmap(f.fileno(), 64)
+            f.close()
+            self.maps.append(m)
+            self.slots.append(np.frombuffer(m, dtype=np.int64, count=6).reshape(2, 3))
+        dist.barrier(group)  # every rank has mapped every file: the names can go
+        try:
+            os.unlink(self.paths[self.rank])
+        except OSError:
+            pass
+        self.seq = 0
+
+    def all_gather(self, value: int, timeout_s: float = 300.0) -> List[int]:
+        import time
+
+        self.seq += 1
+        seq, p = self.seq, self.seq & 1
+        mine = self.slots[self.rank]
+        mine[p, 1] = int(value)
+        mine[p, 2] = (int(value) ^ (seq * self._MAGIC)) & 0x7FFFFFFFFFFFFFFF
+        mine[p, 0] = seq
+        out = []
+        for r in range(self.world):
+            slot = self.slots[r]
+            spins, t0 = 0, None
+            while True:
+                s, v, c = int(slot[p, 0]), int(slot[p, 1]), int(slot[p, 2])
+                if s == seq and c == (v ^ (seq * self._MAGIC)) & 0x7FFFFFFFFFFFFFFF:
+                    out.append(v)
+                    break
+                spins += 1
+                if spins > 2000:
+                    if t0 is None:
+                        t0 = time.monotonic()
+                    elif time.monotonic() - t0 > timeout_s:
+                        raise RuntimeError(f"gsplat b200 host board: rank {r} did not post gather {seq}")
+                    time.sleep(20e-6)
+        return out
+
+
+_HOST_BOARD = None
 
 
 def all_gather_int_host(world_size: int, value: int) -> List[int]:
-    """Gathers one host integer from every rank WITHOUT touching the GPU stream.
-
-    `all_gather_int32` on a CUDA tensor costs a device-to-host read-back, i.e. the CPU waits for all queued
-    kernels of the previous step and the next forward's launches are exposed. The count of Gaussians is host
-    data already, so it travels over a host-side (gloo) group created on first use: the CPU keeps running ahead
-    of the GPU. Collective: every rank must call it."""
-    global _HOST_GROUP
+    """Gathers one host integer from every rank of this node without touching the GPU (see HostBoard).
+    Collective: every rank must call it."""
+    global _HOST_BOARD
     if world_size == 1:
         return [int(value)]
-    if dist.get_backend() == "gloo":
-        group = None
-    else:
-        if _HOST_GROUP is None:
-            _HOST_GROUP = dist.new_group(backend="gloo")
-        group = _HOST_GROUP
-    mine = torch.tensor([int(value)], dtype=torch.int64)
-    out = [torch.empty(1, dtype=torch.int64) for _ in range(world_size)]
-    dist.all_gather(out, mine, group=group)
-    return [int(t.item()) for t in out]
+    if _HOST_BOARD is None:
+        _HOST_BOARD = HostBoard()
+    return _HOST_BOARD.all_gather(int(value))
 
 
 def all_to_all_int32(world_size: int, values: List[Union[int, Tensor]], device: Optional[torch.device] = None):

@@ -50,6 +50,7 @@ from .distributed import (
     all_to_all_rows,
     all_to_all_tensor_list,
     interleave_camera_major,
+    host_trace,
     pack_rows,
     peer_exchange_available,
     peer_exchange_rows,
@@ -130,16 +131,19 @@ def rasterization(
         assert not distributed, "AbsGrad is not supported in distributed mode."
 
     # Distributed: Gaussians are sharded over ranks for projection, cameras for compositing.
+    host_trace.mark()
     if distributed:
         world_rank = torch.distributed.get_rank()
         world_size = torch.distributed.get_world_size()
-        if BACKEND == "b200" and os.environ.get("GSPLAT_B200_HOST_COUNTS", "1") == "1":
+        if BACKEND == "b200" and peer_exchange_available() and os.environ.get("GSPLAT_B200_HOST_COUNTS", "1") == "1":
             N_world = all_gather_int_host(world_size, N)  # host-side channel: no GPU read-back per step
         else:
             N_world = all_gather_int32(world_size, N, device=device)
+        host_trace.mark("us_counts")
         C_world = [C] * world_size  # every rank must bring the same number of cameras
         viewmats, Ks = all_gather_tensor_list(world_size, [viewmats, Ks])
         C = len(viewmats)  # global camera count from here on
+        host_trace.mark("us_cameras")
 
     proj_results = fully_fused_projection(
         means, covars, quats, scales, viewmats, Ks, width, height,
@@ -194,6 +198,7 @@ def rasterization(
                 colors = spherical_harmonics(sh_degree, dirs, shs, masks=radii > 0)  # [C, N, 3]
             colors = torch.clamp_min(colors + 0.5, 0.0)  # as rendering.py:408
 
+    host_trace.mark("us_project_colors")
     # Distributed: hand every projected Gaussian to the rank that owns its camera.
     if distributed:
         D = colors.shape[-1]
@@ -228,6 +233,7 @@ def rasterization(
             means2d, conics, colors = (t.reshape(C, N_total, -1) for t in (means2d, conics, colors))
             depths, opacities, radii = (t.reshape(C, N_total) for t in (depths, opacities, radii))
 
+    host_trace.mark("us_exchange")
     if render_mode in ("RGB+D", "RGB+ED"):
         colors = torch.cat((colors, depths[..., None]), dim=-1)
         if backgrounds is not None:
@@ -240,11 +246,48 @@ def rasterization(
     # Tile intersection, sort, per-tile ranges
     tile_width = math.ceil(width / float(tile_size))
     tile_height = math.ceil(height / float(tile_size))
-    tiles_per_gauss, isect_ids, flatten_ids = isect_tiles(
-        means2d, radii, depths, tile_size, tile_width, tile_height,
-        packed=packed, n_cameras=C, camera_ids=camera_ids, gaussian_ids=gaussian_ids,
-    )
-    isect_offsets = isect_offset_encode(isect_ids, C, tile_width, tile_height)
+    def intersect(speculate):
+        out = isect_tiles(
+            means2d, radii, depths, tile_size, tile_width, tile_height,
+            packed=packed, n_cameras=C, camera_ids=camera_ids, gaussian_ids=gaussian_ids,
+            **({"_speculate": True} if speculate else {}),
+        )
+        if speculate and out[4] is not None:
+            return out  # (tiles_per_gauss, isect_ids, flatten_ids, isect_offsets, pending count)
+        return out[0], out[1], out[2], isect_offset_encode(out[1], C, tile_width, tile_height), None
+
+    # b200: intersection buffers sized from the previous call's count, the real count is read back only after
+    # the compositor has been queued (no GPU bubble at the reference's `.item()`, isect_tiles.py:102)
+    speculate = BACKEND == "b200" and os.environ.get("GSPLAT_B200_SPECULATE", "1") == "1"
+    tiles_per_gauss, isect_ids, flatten_ids, isect_offsets, pending = intersect(speculate)
+    host_trace.mark("us_isect")
+
+    # Composite
+    def composite(colors_c, backgrounds_c):
+        return rasterize_to_pixels(
+            means2d, conics, colors_c, opacities, width, height, tile_size, isect_offsets, flatten_ids,
+            backgrounds=backgrounds_c, packed=packed, absgrad=absgrad,
+        )
+
+    def composite_all():
+        if colors.shape[-1] > channel_chunk:
+            chunks, alphas = [], None
+            for lo in range(0, colors.shape[-1], channel_chunk):
+                bg = backgrounds[..., lo:lo + channel_chunk] if backgrounds is not None else None
+                rc, ra = composite(colors[..., lo:lo + channel_chunk], bg)
+                chunks.append(rc)
+                alphas = ra if alphas is None else alphas
+            return torch.cat(chunks, dim=-1), alphas
+        return composite(colors, backgrounds)
+
+    render_colors, render_alphas = composite_all()
+    if pending is not None:
+        n_isects = pending.wait()
+        if n_isects > pending.capacity:  # the estimate was too small: redo this part with exact sizes
+            tiles_per_gauss, isect_ids, flatten_ids, isect_offsets, pending = intersect(False)
+            render_colors, render_alphas = composite_all()
+        else:
+            isect_ids, flatten_ids = isect_ids[:n_isects], flatten_ids[:n_isects]
     meta.update({
         "tile_width": tile_width,
         "tile_height": tile_height,
@@ -257,24 +300,7 @@ def rasterization(
         "tile_size": tile_size,
         "n_cameras": C,
     })
-
-    # Composite
-    def composite(colors_c, backgrounds_c):
-        return rasterize_to_pixels(
-            means2d, conics, colors_c, opacities, width, height, tile_size, isect_offsets, flatten_ids,
-            backgrounds=backgrounds_c, packed=packed, absgrad=absgrad,
-        )
-
-    if colors.shape[-1] > channel_chunk:
-        chunks, render_alphas = [], None
-        for lo in range(0, colors.shape[-1], channel_chunk):
-            bg = backgrounds[..., lo:lo + channel_chunk] if backgrounds is not None else None
-            rc, ra = composite(colors[..., lo:lo + channel_chunk], bg)
-            chunks.append(rc)
-            render_alphas = ra if render_alphas is None else render_alphas
-        render_colors = torch.cat(chunks, dim=-1)
-    else:
-        render_colors, render_alphas = composite(colors, backgrounds)
+    host_trace.mark("us_composite")
 
     if render_mode in ("ED", "RGB+ED"):
         render_colors = torch.cat(

@@ -157,6 +157,19 @@ int gsb_sort_pairs_u32(int64_t n, int end_bit, int32_t *keys, int32_t *keys_alt,
 int gsb_isect_finalize(int64_t n_isects, const int32_t *tile_keys, const int32_t *flatten_ids, const float *depths,
                        int C, int tile_width, int tile_height, int tile_n_bits, int64_t *isect_ids, int32_t *offsets,
                        cudaStream_t stream);
+/* Speculatively sized variants (no host read-back of n_isects before the compositor is launched): buffers hold
+ * `capacity` slots, the real count stays on the device (`n_isects_dev`, the total written by gsb_isect_count_perm).
+ * emit writes only slots < capacity and pads [n_isects, capacity) with 0xffffffff keys (they sort last); finalize
+ * treats min(*n_isects_dev, capacity) as the count. The caller reads the count back later and, if it exceeded
+ * the capacity, redoes the step with exact sizes. */
+int gsb_isect_emit_perm_cap(int64_t P, int N, int packed, const int32_t *perm, const float *means2d,
+                            const int32_t *radii, const int64_t *camera_ids, int tile_size, int tile_width,
+                            int tile_height, int tile_n_bits, const int32_t *tiles_per_gauss,
+                            const int64_t *block_offsets, int32_t *tile_keys, int32_t *flatten_ids,
+                            int64_t capacity, const int64_t *n_isects_dev, cudaStream_t stream);
+int gsb_isect_finalize_cap(int64_t n_isects, const int64_t *n_isects_dev, const int32_t *tile_keys,
+                           const int32_t *flatten_ids, const float *depths, int C, int tile_width, int tile_height,
+                           int tile_n_bits, int64_t *isect_ids, int32_t *offsets, cudaStream_t stream);
 
 /* ---- rasterize_to_pixels ----------------------------------------------------------------------
  * replaces triton_impl/rasterize_to_pixels_fwd.py:200-275 / :21-196, rasterize_to_pixels_bwd.py:341-430
@@ -172,6 +185,13 @@ int gsb_rasterize_fwd(int C, int64_t n_isects, int D, const float *recA, const f
                       const float *backgrounds, const uint8_t *masks, int width, int height, int tile_size,
                       int tile_width, int tile_height, const int32_t *isect_offsets, const int32_t *flatten_ids,
                       float *render_colors, float *render_alphas, int32_t *last_ids, cudaStream_t stream);
+/* same, for speculatively sized intersection buffers: n_isects = capacity of flatten_ids, the real count is
+ * min(*n_isects_dev, n_isects) (NULL: n_isects is exact). See gsb_isect_emit_perm_cap. */
+int gsb_rasterize_fwd_cap(int C, int64_t n_isects, const int64_t *n_isects_dev, int D, const float *recA,
+                          const float *recB, const float *colors, const float *backgrounds, const uint8_t *masks,
+                          int width, int height, int tile_size, int tile_width, int tile_height,
+                          const int32_t *isect_offsets, const int32_t *flatten_ids, float *render_colors,
+                          float *render_alphas, int32_t *last_ids, cudaStream_t stream);
 /* diagnostics: counts[C,H,W] = number of Gaussians composited into each pixel (ones: float[P] of 1.0f);
  * same traversal as gsb_rasterize_fwd with D = 1. Used by bench.py for the useful-work roofline. */
 int gsb_rasterize_count(int C, int64_t n_isects, const float *recA, const float *recB, const float *ones, int width,

@@ -106,3 +106,16 @@ def test_world_size_one_is_identity():
     assert all_gather_int32(1, 7) == [7]
     assert all_gather_tensor_list(1, t) is t and all_to_all_tensor_list(1, t, [2]) is t
     assert cli(lambda lr, wr, ws, a: (lr, wr, ws, a), "x", world_size=1) == (0, 0, 1, "x")
+
+
+def _host_board(rank, world):
+    from gsplat.distributed import all_gather_int_host
+
+    # shared-memory board: many gathers in a row (slot parity reuse), values change every call
+    for i in range(200):
+        assert all_gather_int_host(world, 1000 * rank + i) == [1000 * r + i for r in range(world)]
+    assert all_gather_int_host(world, (1 << 40) + rank) == [(1 << 40) + r for r in range(world)]
+
+
+def test_host_board_all_gather():
+    _spawn("_host_board")

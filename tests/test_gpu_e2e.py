@@ -251,3 +251,42 @@ def test_distributed_peer_exchange_two_gpus():
         capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "MISMATCH" not in r.stdout
+
+
+@pytest.mark.parametrize("packed", [False, True])
+def test_speculative_intersection_buffers_match_exact(packed, monkeypatch):
+    """rasterization() sizes the intersection buffers from the previous call's count and reads the real count
+    back after the compositor is queued. Same ids / offsets / images / gradients as the exact path, also when the
+    estimate is too small (overflow -> exact redo) and when nothing is visible."""
+    from gsplat.b200_impl import _wrapper as Wp
+    from gsplat.rendering import rasterization
+
+    means, quats, scales, opac, colors, viewmats, Ks, W, H = _scene(step=40, cams=2)
+    args = [t.to(DEV) for t in (means, quats, scales, opac, colors, viewmats, Ks)]
+
+    def run(speculate, estimate=None, shift=0.0):
+        monkeypatch.setenv("GSPLAT_B200_SPECULATE", "1" if speculate else "0")
+        Wp._ISECT_ESTIMATE.clear()
+        if estimate is not None:
+            Wp._ISECT_ESTIMATE[(torch.cuda.current_device(), 2, -(-W // 16), -(-H // 16), 16, packed)] = estimate
+        p = [t.clone().requires_grad_(True) for t in args[:5]]
+        p[0].data[:, 2] += shift
+        rc, ra, meta = rasterization(*p, args[5], args[6], W, H, packed=packed)
+        (rc.sum() + 2 * ra.sum()).backward()
+        return rc, ra, meta, [t.grad for t in p]
+
+    rc0, ra0, m0, g0 = run(False)
+    n = m0["flatten_ids"].numel()
+    assert n > 0
+    for estimate in (n, n * 2, n // 3, 0):  # exact fit (+margin), oversized, overflow -> redo, tiny
+        rc, ra, m, g = run(True, estimate)
+        for k in ("isect_ids", "flatten_ids", "isect_offsets", "tiles_per_gauss"):
+            assert torch.equal(m[k], m0[k]), (estimate, k)
+        assert torch.equal(rc, rc0) and torch.equal(ra, ra0), estimate
+        for a, b in zip(g, g0):
+            assert torch.allclose(a, b, rtol=1e-4, atol=1e-6 + 1e-4 * b.abs().max().item()), estimate
+        assert Wp._ISECT_ESTIMATE, "the count must be remembered for the next call"
+    # nothing visible (all Gaussians far behind the cameras) with a stale, large estimate
+    rc, ra, m, _ = run(True, n, shift=-1e4)
+    assert m["flatten_ids"].numel() == 0 and m["isect_ids"].numel() == 0
+    assert float(ra.abs().max()) == 0.0 and int(m["isect_offsets"].abs().max()) == 0

@@ -16,7 +16,11 @@ def test_projection_matches_reference(golden):
         radii, means2d, depths, conics, comps = O.fully_fused_projection(
             g["means"], covars, g["viewmats"], g["Ks"], g["width"], g["height"], eps2d=0.3,
             calc_compensations=True, camera_model=model)
-        assert torch.equal(radii, g[f"{model}_radii"])  # bit-exact integer output
+        # integer output: equal to the frozen reference values, except that a radius sitting exactly on a
+        # ceil() boundary may flip by one when the CPU matmuls reduce in another order (thread count / load):
+        # the reference's own tolerance (triton_tests/test_fused_proj.py:116, atol=1)
+        diff = (radii - g[f"{model}_radii"]).abs()
+        assert int(diff.max()) <= 1 and float((diff > 0).float().mean()) < 1e-3
         v = radii > 0
         assert v.sum() > 100
         _close(means2d[v], g[f"{model}_means2d"][v])
