@@ -110,8 +110,11 @@ __device__ __forceinline__ void copy_run(const float *__restrict__ src, float *_
 __global__ void __launch_bounds__(kThreads)
 put_fwd_kernel(PeerTable peers, Fields fields, int world, int rank, int C_local, int64_t N_local, int64_t N_total,
                int64_t n_base, int64_t region_offset, unsigned long long epoch) {
-    const int f = blockIdx.y % fields.count;
-    const int c = blockIdx.y / fields.count;
+    // segment order: camera fastest and rotated by rank, so the CTAs in flight at any moment cover every
+    // destination and no two senders start on the same one (an 8-to-1 incast would share one ingress port)
+    const int n_cam = world * C_local;
+    const int f = blockIdx.y / n_cam;
+    const int c = (blockIdx.y % n_cam + (rank + 1) * C_local) % n_cam;
     const int dest = c / C_local, c_local = c - dest * C_local;
     const int w = fields.width[f];
     const float *src = fields.src[f] + (int64_t)c * N_local * w;
@@ -126,9 +129,11 @@ put_fwd_kernel(PeerTable peers, Fields fields, int world, int rank, int C_local,
 __global__ void __launch_bounds__(kThreads)
 put_bwd_kernel(PeerTable peers, Fields fields, RankBases bases, int world, int rank, int C_local, int64_t N_total,
                int64_t region_offset, unsigned long long epoch) {
-    const int f = blockIdx.y % fields.count;
-    const int q = blockIdx.y / fields.count;
-    const int dest = q % world, c_local = q / world;
+    // destination fastest and rotated by rank (see put_fwd_kernel)
+    const int n_seg = world * C_local;
+    const int f = blockIdx.y / n_seg;
+    const int q = blockIdx.y % n_seg;
+    const int dest = (q + rank + 1) % world, c_local = q / world;
     const int w = fields.width[f];
     const int64_t b0 = bases.base[dest], N_dest = bases.base[dest + 1] - b0;
     const float *src = fields.src[f] ? fields.src[f] + ((int64_t)c_local * N_total + b0) * w : nullptr;
