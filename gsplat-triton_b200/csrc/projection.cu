@@ -16,7 +16,7 @@
 namespace {
 
 constexpr int kThreads = 256;
-enum { MODEL_PINHOLE = 0, MODEL_ORTHO = 1 };
+enum { MODEL_PINHOLE = 0, MODEL_ORTHO = 1, MODEL_FISHEYE = 2 };
 
 struct Sym3 {
     float xx, xy, xz, yy, yz, zz;
@@ -140,6 +140,52 @@ __device__ __forceinline__ PinholeJ pinhole_jacobian(const Camera &c, float tx, 
     return j;
 }
 
+// Equidistant fisheye (reference: _torch_impl._fisheye_proj :123-182, Utils.cuh:554-592): with r = |(x, y)|,
+// theta = atan2(r, z), the image point is f * (x, y) * g + c where g = theta / r. Its 2x3 Jacobian is
+//   [ fx (g + x^2 h)   fx x y h        -fx x k ]        h = (dg/dr) / r = z k / r^2 - theta / r^3
+//   [ fy x y h         fy (g + y^2 h)  -fy y k ]        k = 1 / (r^2 + z^2)
+// and every derivative of J (backward) needs only one more radial function m = (dh/dr) / r plus dh/dz = 2 k^2.
+// Near the optical axis (r < 0.3 z) g, h, m are evaluated by their series in t = r/z, where the closed forms cancel
+// catastrophically (the reference guards that region with eps = 1e-7 instead; differences stay below 1e-5).
+struct FisheyeJ {
+    float g, h, k, m;
+    float j00, j01, j02, j10, j11, j12;
+};
+
+__device__ __forceinline__ FisheyeJ fisheye_jacobian(const Camera &c, float x, float y, float z) {
+    FisheyeJ j;
+    const float r2 = x * x + y * y, r = sqrtf(r2);
+    j.k = 1.0f / (r2 + z * z);
+    if (z > 0.f && r < 0.3f * z) {
+        // atan(t)/t = sum_n a_n t^2n, a_n = (-1)^n / (2n+1):  g = sum a_n t^2n / z,
+        // h = sum_{n>=1} 2n a_n t^(2n-2) / z^3,  m = sum_{n>=2} 2n (2n-2) a_n t^(2n-4) / z^5   (10 terms: < 1e-6 at t = .3)
+        const float iz = 1.0f / z, t2 = r2 * iz * iz, iz2 = iz * iz;
+        float sg = 0.f, sh = 0.f, sm = 0.f;
+#pragma unroll
+        for (int n = 9; n >= 0; --n) {
+            const float a = ((n & 1) ? -1.0f : 1.0f) / (float)(2 * n + 1);
+            sg = fmaf(sg, t2, a);
+            if (n >= 1) sh = fmaf(sh, t2, (float)(2 * n) * a);
+            if (n >= 2) sm = fmaf(sm, t2, (float)(2 * n * (2 * n - 2)) * a);
+        }
+        j.g = iz * sg;
+        j.h = iz * iz2 * sh;
+        j.m = iz * iz2 * iz2 * sm;
+    } else {
+        const float theta = atan2f(r, z), ir = 1.0f / r, ir2 = ir * ir;
+        j.g = theta * ir;
+        j.h = z * j.k * ir2 - theta * ir2 * ir;
+        j.m = -2.0f * z * j.k * j.k * ir2 - 3.0f * z * j.k * ir2 * ir2 + 3.0f * theta * ir2 * ir2 * ir;
+    }
+    j.j00 = c.fx * (j.g + x * x * j.h);
+    j.j01 = c.fx * x * y * j.h;
+    j.j02 = -c.fx * x * j.k;
+    j.j10 = c.fy * x * y * j.h;
+    j.j11 = c.fy * (j.g + y * y * j.h);
+    j.j12 = -c.fy * y * j.k;
+    return j;
+}
+
 template <int MODEL>
 __device__ __forceinline__ Proj2D project_one(const Camera &c, float px, float py, float pz, const Sym3 &S,
                                               const ProjParams &p) {
@@ -158,6 +204,20 @@ __device__ __forceinline__ Proj2D project_one(const Camera &c, float px, float p
         v_yy = j.jyy * Sc.yy * j.jyy + 2.0f * j.jyy * Sc.yz * j.jyz + j.jyz * Sc.zz * j.jyz;
         o.mx = c.fx * tx * j.iz + c.cx;
         o.my = c.fy * ty * j.iz + c.cy;
+    } else if (MODEL == MODEL_FISHEYE) {
+        const FisheyeJ j = fisheye_jacobian(c, tx, ty, tz);
+        // rows of J * Sigma_c
+        const float a0 = j.j00 * Sc.xx + j.j01 * Sc.xy + j.j02 * Sc.xz;
+        const float a1 = j.j00 * Sc.xy + j.j01 * Sc.yy + j.j02 * Sc.yz;
+        const float a2 = j.j00 * Sc.xz + j.j01 * Sc.yz + j.j02 * Sc.zz;
+        const float b0 = j.j10 * Sc.xx + j.j11 * Sc.xy + j.j12 * Sc.xz;
+        const float b1 = j.j10 * Sc.xy + j.j11 * Sc.yy + j.j12 * Sc.yz;
+        const float b2 = j.j10 * Sc.xz + j.j11 * Sc.yz + j.j12 * Sc.zz;
+        v_xx = a0 * j.j00 + a1 * j.j01 + a2 * j.j02;
+        v_xy = a0 * j.j10 + a1 * j.j11 + a2 * j.j12;
+        v_yy = b0 * j.j10 + b1 * j.j11 + b2 * j.j12;
+        o.mx = c.fx * tx * j.g + c.cx;
+        o.my = c.fy * ty * j.g + c.cy;
     } else {
         v_xx = c.fx * c.fx * Sc.xx;
         v_xy = c.fx * c.fy * Sc.xy;
@@ -280,6 +340,41 @@ __device__ __forceinline__ void project_one_vjp(const Camera &c, float px, float
         tmp -= j.clamp_x ? v_jxz * j.jxz : 0.0f;
         tmp -= j.clamp_y ? v_jyz * j.jyz : 0.0f;
         v_tz -= j.iz * tmp;
+    } else if (MODEL == MODEL_FISHEYE) {
+        const FisheyeJ j = fisheye_jacobian(c, tx, ty, tz);
+        // v_Sigma_c = J^T d J (d symmetric)
+        const float e00 = d_xx * j.j00 + d_xy * j.j10, e01 = d_xx * j.j01 + d_xy * j.j11, e02 = d_xx * j.j02 + d_xy * j.j12;
+        const float e10 = d_xy * j.j00 + d_yy * j.j10, e11 = d_xy * j.j01 + d_yy * j.j11, e12 = d_xy * j.j02 + d_yy * j.j12;
+        vSc.xx = j.j00 * e00 + j.j10 * e10;
+        vSc.xy = j.j00 * e01 + j.j10 * e11;
+        vSc.xz = j.j00 * e02 + j.j10 * e12;
+        vSc.yy = j.j01 * e01 + j.j11 * e11;
+        vSc.yz = j.j01 * e02 + j.j11 * e12;
+        vSc.zz = j.j02 * e02 + j.j12 * e12;
+        // mean path: v_t = J^T v_mean2d
+        v_tx = j.j00 * g.v_mx + j.j10 * g.v_my;
+        v_ty = j.j01 * g.v_mx + j.j11 * g.v_my;
+        v_tz = j.j02 * g.v_mx + j.j12 * g.v_my;
+        // Jacobian path: v_J = 2 d (J Sigma_c), then v_t += sum_ij v_J[i][j] dJ[i][j]/dt
+        const float a0 = j.j00 * Sc.xx + j.j01 * Sc.xy + j.j02 * Sc.xz;
+        const float a1 = j.j00 * Sc.xy + j.j01 * Sc.yy + j.j02 * Sc.yz;
+        const float a2 = j.j00 * Sc.xz + j.j01 * Sc.yz + j.j02 * Sc.zz;
+        const float b0 = j.j10 * Sc.xx + j.j11 * Sc.xy + j.j12 * Sc.xz;
+        const float b1 = j.j10 * Sc.xy + j.j11 * Sc.yy + j.j12 * Sc.yz;
+        const float b2 = j.j10 * Sc.xz + j.j11 * Sc.yz + j.j12 * Sc.zz;
+        const float q00 = 2.0f * c.fx * (d_xx * a0 + d_xy * b0), q01 = 2.0f * c.fx * (d_xx * a1 + d_xy * b1);
+        const float q02 = 2.0f * c.fx * (d_xx * a2 + d_xy * b2);  // v_J row 0, pre-multiplied by fx
+        const float q10 = 2.0f * c.fy * (d_xy * a0 + d_yy * b0), q11 = 2.0f * c.fy * (d_xy * a1 + d_yy * b1);
+        const float q12 = 2.0f * c.fy * (d_xy * a2 + d_yy * b2);  // v_J row 1, pre-multiplied by fy
+        const float x = tx, y = ty, z = tz, h = j.h, m = j.m, k = j.k, k2 = 2.0f * j.k * j.k;
+        const float xx = x * x, yy = y * y, xy = x * y;
+        // d/dx, d/dy, d/dz of the unit-focal entries (g + x^2 h, x y h, -x k ; x y h, g + y^2 h, -y k)
+        v_tx += q00 * (3.0f * x * h + xx * x * m) + (q01 + q10) * (y * h + xx * y * m) + q02 * (xx * k2 - k) +
+                q11 * (x * h + x * yy * m) + q12 * (xy * k2);
+        v_ty += q00 * (y * h + xx * y * m) + (q01 + q10) * (x * h + x * yy * m) + q02 * (xy * k2) +
+                q11 * (3.0f * y * h + yy * y * m) + q12 * (yy * k2 - k);
+        v_tz += q00 * (xx * k2 - k) + (q01 + q10) * (xy * k2) + q02 * (x * z * k2) + q11 * (yy * k2 - k) +
+                q12 * (y * z * k2);
     } else {
         vSc.xx = c.fx * c.fx * d_xx;
         vSc.yy = c.fy * c.fy * d_yy;
@@ -616,8 +711,9 @@ projection_finalize_kernel(int N, const float *__restrict__ acc, const float *__
 }
 
 int check_model(int camera_model) {
-    if (camera_model != MODEL_PINHOLE && camera_model != MODEL_ORTHO) {
-        gsb_set_error("camera_model %d is not supported by the b200 backend (0=pinhole, 1=ortho)", camera_model);
+    if (camera_model != MODEL_PINHOLE && camera_model != MODEL_ORTHO && camera_model != MODEL_FISHEYE) {
+        gsb_set_error("camera_model %d is not supported by the b200 backend (0=pinhole, 1=ortho, 2=fisheye)",
+                      camera_model);
         return GSB_ERR_UNSUPPORTED;
     }
     return GSB_OK;
@@ -629,8 +725,11 @@ int check_model(int camera_model) {
     if ((model) == MODEL_PINHOLE) {                        \
         constexpr int M = MODEL_PINHOLE;                   \
         __VA_ARGS__;                                       \
-    } else {                                               \
+    } else if ((model) == MODEL_ORTHO) {                   \
         constexpr int M = MODEL_ORTHO;                     \
+        __VA_ARGS__;                                       \
+    } else {                                               \
+        constexpr int M = MODEL_FISHEYE;                   \
         __VA_ARGS__;                                       \
     }
 

@@ -18,13 +18,13 @@ from torch import Tensor
 
 from ._lib import lib, ptr, require_cuda, stream_of
 
-_CAMERA_MODELS = {"pinhole": 0, "ortho": 1}
+_CAMERA_MODELS = {"pinhole": 0, "ortho": 1, "fisheye": 2}
 _RASTER_CHANNELS = (1, 2, 3, 4, 8, 16, 32)
 
 
 def _camera_model_id(camera_model: str) -> int:
     if camera_model not in _CAMERA_MODELS:
-        # the Triton reference only has pinhole (triton_impl/_wrapper.py:322-323)
+        # (the Triton reference only has pinhole, triton_impl/_wrapper.py:322-323; the CUDA one has these three)
         raise NotImplementedError(f"camera_model={camera_model!r} is not implemented by the b200 backend")
     return _CAMERA_MODELS[camera_model]
 

@@ -33,6 +33,7 @@ typedef struct CUstream_st *cudaStream_t;
 
 #define GSB_CAMERA_PINHOLE 0
 #define GSB_CAMERA_ORTHO 1
+#define GSB_CAMERA_FISHEYE 2
 
 /* library identity / diagnostics */
 const char *gsb_last_error(void);

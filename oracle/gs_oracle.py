@@ -8,7 +8,7 @@ Each function restates, in plain float32 torch/numpy on the CPU, the reference a
 cites (paths relative to the reference checkout, hieu1999210/gsplat-triton @ 46beece):
 
   quat_scale_to_covar      gsplat/cuda/_torch_impl.py:10-75   (_quat_to_rotmat, _quat_scale_to_covar_preci)
-  fully_fused_projection   gsplat/cuda/_torch_impl.py:78-122 (_persp_proj), :203-216 (_ortho_proj),
+  fully_fused_projection   gsplat/cuda/_torch_impl.py:78-122 (_persp_proj), :123-182 (_fisheye_proj), :203-216 (_ortho_proj),
                            :219-247 (_world_to_cam), :250-328 (_fully_fused_projection),
                            + radius_clip from triton_impl/fused_projection_fwd.py:215-221
   sh_bases / spherical_harmonics   gsplat/cuda/_torch_impl.py:620-714
@@ -108,6 +108,19 @@ def fully_fused_projection(
     elif camera_model == "ortho":  # _ortho_proj :203-216
         J = torch.stack([fx + O, O, O, O, fy + O, O], dim=-1).reshape(C, N, 2, 3)
         means2d = torch.stack([fx * tx + cx, fy * ty + cy], dim=-1)
+    elif camera_model == "fisheye":  # _fisheye_proj :123-182 (equidistant model, the reference's eps placement)
+        eps = 0.0000001
+        xy_len = (tx**2 + ty**2) ** 0.5 + eps
+        theta = torch.atan2(xy_len, tz + eps)
+        means2d = torch.stack([tx * fx * theta / xy_len + cx, ty * fy * theta / xy_len + cy], dim=-1)
+        x2, y2, xy = tx * tx + eps, ty * ty, tx * ty
+        x2y2 = x2 + y2
+        x2y2z2_inv = 1.0 / (x2y2 + tz * tz)
+        b_ = torch.atan2(xy_len, tz) / xy_len / x2y2
+        a_ = tz * x2y2z2_inv / x2y2
+        J = torch.stack([fx * (x2 * a_ + y2 * b_), fx * xy * (a_ - b_), -fx * tx * x2y2z2_inv,
+                         fy * xy * (a_ - b_), fy * (y2 * a_ + x2 * b_), -fy * ty * x2y2z2_inv],
+                        dim=-1).reshape(C, N, 2, 3)
     else:
         raise NotImplementedError(camera_model)
     cov2d = J @ covars_c @ J.transpose(-1, -2)

@@ -161,6 +161,41 @@ def case_projection(T):
     return out
 
 
+def case_projection_fisheye(T):
+    """Same scene as case_projection, camera_model="fisheye": reference _fully_fused_projection (-> _fisheye_proj,
+    _torch_impl.py:123-182) fwd + autograd grads. Kept in its own file (projection_fisheye.npz)."""
+    from gsplat._helper import load_test_data
+
+    torch.manual_seed(42)
+    means, quats, scales, opacities, colors, viewmats, Ks, W, H = load_test_data(device="cpu")
+    sel = slice(0, None, 40)
+    means, quats, scales = means[sel], quats[sel], scales[sel] * 3.0 + 0.002
+    p = [t.clone().requires_grad_(True) for t in (means, quats, scales, viewmats)]
+    covars, _ = T._quat_scale_to_covar_preci(p[1], p[2], True, False, triu=False)
+    radii, means2d, depths, conics, comps = T._fully_fused_projection(
+        p[0], covars, p[3], Ks, W, H, eps2d=0.3, calc_compensations=True, camera_model="fisheye")
+    o_radii, o_means2d, o_depths, o_conics, o_comps = O.fully_fused_projection(
+        means, O.quat_scale_to_covar(quats, scales), viewmats, Ks, W, H, eps2d=0.3, calc_compensations=True,
+        camera_model="fisheye")
+    assert torch.equal(radii, o_radii), "fisheye: oracle radii differ from reference"
+    v = radii > 0
+    _close(o_means2d[v], means2d[v], what="fisheye means2d")
+    _close(o_depths[v], depths[v], what="fisheye depths")
+    _close(o_conics[v], conics[v], what="fisheye conics")
+    _close(o_comps[v], comps[v], what="fisheye comps")
+    g = torch.Generator().manual_seed(7)
+    w2, wd, wc, wp = (torch.randn(t.shape, generator=g) for t in (means2d, depths, conics, comps))
+    mask = v.float()
+    loss = ((means2d * w2 * 1e-2).sum(-1) * mask + depths * wd * mask + (conics * wc).sum(-1) * mask
+            + comps * wp * mask).sum()
+    grads = torch.autograd.grad(loss, p)
+    np.savez_compressed(os.path.join(GOLD, "projection_fisheye.npz"), **_np(
+        means=means, quats=quats, scales=scales, viewmats=viewmats, Ks=Ks, width=W, height=H,
+        radii=radii, means2d=means2d, depths=depths, conics=conics, comps=comps, w_means2d=w2 * 1e-2, w_depths=wd,
+        w_conics=wc, w_comps=wp, v_means=grads[0], v_quats=grads[1], v_scales=grads[2], v_viewmats=grads[3]))
+    print("projection_fisheye: N=%d visible=%d" % (means.shape[0], int(v.sum())))
+
+
 def case_sh(T):
     """triton_tests/test_sh.py protocol (seed 43), degrees 0-4: reference _spherical_harmonics fwd + grads."""
     torch.manual_seed(43)
@@ -255,7 +290,11 @@ def main():
     import gsplat.cuda._torch_impl as T
 
     os.makedirs(GOLD, exist_ok=True)
+    if len(sys.argv) > 1 and sys.argv[1] == "fisheye":  # only the fisheye vectors (the others stay frozen)
+        case_projection_fisheye(T)
+        return
     proj = case_projection(T)
+    case_projection_fisheye(T)
     case_sh(T)
     case_isect(T, proj)
     case_raster(T)

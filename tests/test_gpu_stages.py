@@ -76,6 +76,42 @@ def test_projection_backward(golden, model):
         _close_frac(got, ref, rtol=tol[name], atol=tol[name] * float(ref.abs().max()) * 1e-2 + 1e-6)
 
 
+def test_projection_fisheye(golden):
+    """camera_model="fisheye" (reference: cuda backend only, Utils.cuh:554-693; golden from _torch_impl._fisheye_proj)
+    forward + backward, unpacked and packed."""
+    from gsplat.b200_impl import fully_fused_projection
+
+    g = golden("projection_fisheye")
+    p = [t.requires_grad_(True) for t in _cu(g, "means", "quats", "scales", "viewmats")]
+    Ks, W, H = g["Ks"].to(DEV), g["width"], g["height"]
+    radii, means2d, depths, conics, comps = fully_fused_projection(
+        p[0], None, p[1], p[2], p[3], Ks, W, H, calc_compensations=True, camera_model="fisheye")
+    ref = g["radii"]
+    diff = (radii.cpu() - ref).abs()
+    assert int(diff.max()) <= 1 and float((diff > 0).float().mean()) < 2e-3
+    assert int((ref > 0).sum()) > 1000
+    v = (radii.cpu() > 0) & (ref > 0)
+    _close(means2d.detach().cpu()[v], g["means2d"][v], rtol=1e-4, atol=1e-3)
+    _close(depths.detach().cpu()[v], g["depths"][v])
+    _close_frac(conics.detach().cpu()[v], g["conics"][v], rtol=1e-4, atol=1e-5, max_bad=1e-3)
+    _close_frac(comps.detach().cpu()[v], g["comps"][v], rtol=1e-4, atol=1e-3, max_bad=1e-3)
+    m = (ref > 0).float().to(DEV) * (radii > 0).float()
+    w2, wd, wc, wp = _cu(g, "w_means2d", "w_depths", "w_conics", "w_comps")
+    loss = ((means2d * w2).sum(-1) * m + depths * wd * m + (conics * wc).sum(-1) * m + comps * wp * m).sum()
+    grads = torch.autograd.grad(loss, p)
+    tol = {"v_means": 1e-3, "v_quats": 5e-3, "v_scales": 5e-2, "v_viewmats": 1e-3}
+    for got, name in zip(grads, ("v_means", "v_quats", "v_scales", "v_viewmats")):
+        r = g[name]
+        _close_frac(got, r, rtol=tol[name], atol=tol[name] * float(r.abs().max()) * 1e-2 + 1e-6)
+    # packed rows == the visible unpacked rows
+    cam, gid, radii_p, means2d_p, _, conics_p, _ = fully_fused_projection(
+        p[0].detach(), None, p[1].detach(), p[2].detach(), p[3].detach(), Ks, W, H, packed=True,
+        calc_compensations=True, camera_model="fisheye")
+    sel = radii > 0
+    assert torch.equal(radii_p, radii[sel]) and torch.equal(means2d_p, means2d.detach()[sel])
+    assert torch.equal(conics_p, conics.detach()[sel])
+
+
 def test_projection_covars_input_and_packed(golden):
     from gsplat.b200_impl import fully_fused_projection
 

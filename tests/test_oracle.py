@@ -29,6 +29,25 @@ def test_projection_matches_reference(golden):
         _close(comps[v], g[f"{model}_comps"][v])
 
 
+def test_projection_fisheye_matches_reference(golden):
+    g = golden("projection_fisheye")
+    p = [g[k].clone().requires_grad_(True) for k in ("means", "quats", "scales", "viewmats")]
+    radii, means2d, depths, conics, comps = O.fully_fused_projection(
+        p[0], O.quat_scale_to_covar(p[1], p[2]), p[3], g["Ks"], g["width"], g["height"], calc_compensations=True,
+        camera_model="fisheye")
+    diff = (radii - g["radii"]).abs()
+    assert int(diff.max()) <= 1 and float((diff > 0).float().mean()) < 1e-3
+    v = (radii > 0) & (g["radii"] > 0)
+    for got, name in ((means2d, "means2d"), (depths, "depths"), (conics, "conics"), (comps, "comps")):
+        _close(got[v], g[name][v])
+    m = (g["radii"] > 0).float()
+    loss = ((means2d * g["w_means2d"]).sum(-1) * m + depths * g["w_depths"] * m
+            + (conics * g["w_conics"]).sum(-1) * m + comps * g["w_comps"] * m).sum()
+    grads = torch.autograd.grad(loss, p)
+    for got, name in zip(grads, ("v_means", "v_quats", "v_scales", "v_viewmats")):
+        _close(got, g[name], rtol=1e-3, atol=1e-3 * float(g[name].abs().max()))
+
+
 def test_projection_gradients_match_reference(golden):
     g = golden("projection")
     p = [g[k].clone().requires_grad_(True) for k in ("means", "quats", "scales", "viewmats")]
