@@ -313,3 +313,69 @@ def test_rasterization_fisheye_matches_oracle():
     _close_frac(ra, o_ra, rtol=1e-4, atol=1e-4)
     for a, b, tol in zip(grads, o_grads, (1e-3, 5e-3, 5e-2, 1e-3, 1e-3)):
         _close_frac(a, b, rtol=tol, atol=tol * float(b.abs().max()) * 1e-2 + 1e-6, max_bad=5e-3)
+
+
+@pytest.mark.parametrize("packed,absgrad", [(False, False), (True, True)])
+def test_training_loop_contract(packed, absgrad):
+    """The trainer's use of rasterization() (examples/simple_trainer.py:483-560 + strategy/default.py:140-262):
+    activations outside, `info["means2d"].retain_grad()` before backward, `.grad` / `.absgrad`, `radii`,
+    `gaussian_ids`, `width/height/n_cameras` after it, Adam steps on the raw parameters. The L1 loss against
+    a target rendered from perturbed parameters must drop, the densification statistics must be sane, and a
+    changing Gaussian count (prune) must be accepted from one step to the next."""
+    from gsplat.rendering import rasterization
+
+    means, quats, scales, opac, colors, viewmats, Ks, W, H = _scene(step=80, cams=2)
+    dev = DEV
+    viewmats, Ks = viewmats.to(dev), Ks.to(dev)
+    g = torch.Generator().manual_seed(11)
+    sh0 = ((colors - 0.5) / 0.2820947917738781)[:, None, :]
+    shN = torch.zeros(len(means), 3, 3)
+
+    def render(p, **kw):
+        return rasterization(p["means"], p["quats"], torch.exp(p["scales"]), torch.sigmoid(p["opacities"]),
+                             torch.cat([p["sh0"], p["shN"]], 1), viewmats, Ks, W, H, sh_degree=1, packed=packed,
+                             absgrad=absgrad, **kw)
+
+    truth = {"means": means, "quats": quats, "scales": torch.log(scales), "opacities": torch.logit(opac * 0.9 + 0.05),
+             "sh0": sh0, "shN": shN}
+    truth = {k: v.to(dev) for k, v in truth.items()}
+    with torch.no_grad():
+        target, _, _ = render(truth)
+    params = {k: v.clone() for k, v in truth.items()}
+    params["means"] += 0.01 * torch.randn(means.shape, generator=g).to(dev)
+    params["sh0"] += 0.5 * torch.randn(sh0.shape, generator=g).to(dev)
+    params["opacities"] -= 1.0
+    params = {k: v.requires_grad_(True) for k, v in params.items()}
+    opt = torch.optim.Adam([{"params": [v], "lr": lr} for v, lr in zip(
+        params.values(), (1e-4, 1e-3, 5e-3, 5e-2, 2.5e-2, 1e-3))])
+    state = {"grad2d": torch.zeros(len(means), device=dev), "count": torch.zeros(len(means), device=dev)}
+    losses = []
+    for step in range(40):
+        rc, ra, info = render(params)
+        info["means2d"].retain_grad()  # strategy.step_pre_backward
+        loss = (rc - target).abs().mean()
+        loss.backward()
+        losses.append(float(loss))
+        for key in ("width", "height", "n_cameras", "radii", "gaussian_ids", "means2d"):  # _update_state
+            assert key in info
+        grads = (info["means2d"].absgrad if absgrad else info["means2d"].grad).clone()
+        assert grads.shape == info["means2d"].shape and bool(torch.isfinite(grads).all())
+        grads[..., 0] *= info["width"] / 2.0 * info["n_cameras"]
+        grads[..., 1] *= info["height"] / 2.0 * info["n_cameras"]
+        if packed:
+            ids = info["gaussian_ids"]
+        else:
+            sel = info["radii"] > 0
+            ids, grads = torch.where(sel)[1], grads[sel]
+        state["grad2d"].index_add_(0, ids, grads.norm(dim=-1))
+        state["count"].index_add_(0, ids, torch.ones_like(ids, dtype=torch.float32))
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+    assert losses[-1] < 0.6 * losses[0], (losses[0], losses[-1])
+    assert float(state["count"].max()) == 2 * 40 and float(state["grad2d"].sum()) > 0
+    # prune (a new Gaussian count from one call to the next) and render again
+    keepers = torch.sigmoid(params["opacities"]) > 0.2
+    pruned = {k: v.detach()[keepers].requires_grad_(True) for k, v in params.items()}
+    rc, ra, info = render(pruned)
+    rc.mean().backward()
+    assert pruned["means"].grad.shape == pruned["means"].shape and bool(torch.isfinite(rc).all())
