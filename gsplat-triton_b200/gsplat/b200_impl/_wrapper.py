@@ -467,14 +467,11 @@ def _isect_presorted(means2d, radii, depths, camera_ids, C, N, P, packed, tile_s
     tiles_per_gauss = torch.empty(radii.shape, dtype=torch.int32, device=dev)
     nblk = int(lib.gsb_isect_num_blocks(P))
     rows = torch.empty((P,), dtype=torch.int32, device=dev)
-    if C == 1:
-        # one camera: the row key is the depth bit pattern itself (positive floats order like their bits)
-        lib.gsb_isect_row_keys(P, N, int(packed), ptr(depths), ptr(camera_ids), None, ptr(rows), st)
-        _, perm = _sort_pairs_u32(depths.reshape(-1).view(torch.int32).clone(), rows, 32)
-    else:
-        row_keys = torch.empty((P,), dtype=torch.int64, device=dev)
-        lib.gsb_isect_row_keys(P, N, int(packed), ptr(depths), ptr(camera_ids), ptr(row_keys), ptr(rows), st)
-        _, perm = _sort_pairs(row_keys, rows, 32 + cb)
+    # the row key is the depth bit pattern itself (positive floats order like their bits). Cameras need no bits
+    # here: rows are emitted in global depth order and the (camera | tile) sort below is stable, so inside every
+    # (camera, tile) bucket the intersections stay depth-ordered, ties by ascending row like the reference's sort.
+    lib.gsb_isect_row_keys(P, N, int(packed), ptr(depths), ptr(camera_ids), None, ptr(rows), st)
+    _, perm = _sort_pairs_u32(depths.reshape(-1).view(torch.int32).clone(), rows, 32)
     block_sums = torch.empty((max(nblk, 1),), dtype=torch.int32, device=dev)
     block_offsets = torch.empty((nblk + 1,), dtype=torch.int64, device=dev)
     lib.gsb_isect_count_perm(P, ptr(perm), ptr(means2d), ptr(radii), tile_size, tile_width, tile_height,
@@ -496,10 +493,13 @@ def _isect_presorted(means2d, radii, depths, camera_ids, C, N, P, packed, tile_s
     tile_keys = torch.empty((n_isects,), dtype=torch.int32, device=dev)
     flatten_ids = torch.empty((n_isects,), dtype=torch.int32, device=dev)
     if n_isects > 0:
+        # the hand-written sort takes the device-side count itself; the library sort needs the tail padded with
+        # keys that sort last
+        pad = n_dev if not _own_sort() else None
         lib.gsb_isect_emit_perm_cap(P, N, int(packed), ptr(perm), ptr(means2d), ptr(radii), ptr(camera_ids),
                                     tile_size, tile_width, tile_height, tb, ptr(tiles_per_gauss), ptr(block_offsets),
-                                    ptr(tile_keys), ptr(flatten_ids), n_isects, n_dev, st)
-        tile_keys, flatten_ids = _sort_pairs_u32(tile_keys, flatten_ids, tb + cb)
+                                    ptr(tile_keys), ptr(flatten_ids), n_isects, pad, st)
+        tile_keys, flatten_ids = _sort_pairs_u32(tile_keys, flatten_ids, tb + cb, n_dev)
     lib.gsb_isect_finalize_cap(n_isects, n_dev if n_isects > 0 else None, ptr(tile_keys), ptr(flatten_ids),
                                ptr(depths), C, tile_width, tile_height, tb, ptr(isect_ids), ptr(offsets), st)
     if pending is None:
@@ -510,10 +510,34 @@ def _isect_presorted(means2d, radii, depths, camera_ids, C, N, P, packed, tile_s
     return tiles_per_gauss, isect_ids, flatten_ids, offsets, pending
 
 
+def _own_sort() -> bool:
+    # GSPLAT_B200_SORT_IMPL=cub keeps the library sort for A/B measurements (tools/sort_bench.py)
+    return os.environ.get("GSPLAT_B200_SORT_IMPL", "onesweep") != "cub"
+
+
+def _radix_sort(keys: Tensor, vals: Tensor, end_bit: int, n_dev: Optional[int] = None) -> Tuple[Tensor, Tensor]:
+    """Stable LSD radix sort of (uint32|int64 bit pattern, int32) pairs over bits [0, end_bit) with the hand-written
+    onesweep kernels (csrc/radix_sort.cu). `n_dev`: device address of an int64 item count (<= keys.numel())."""
+    import ctypes
+
+    n = keys.numel()
+    keys_alt = torch.empty_like(keys)
+    vals_alt = torch.empty_like(vals)
+    temp_bytes = int(lib.gsb_radix_temp_bytes(n, end_bit))
+    temp = torch.empty((max(temp_bytes, 1),), dtype=torch.uint8, device=keys.device)
+    in_alt = ctypes.c_int(0)
+    fn = lib.gsb_radix_sort_pairs_u32 if keys.dtype == torch.int32 else lib.gsb_radix_sort_pairs_u64
+    fn(n, n_dev, end_bit, ptr(keys), ptr(keys_alt), ptr(vals), ptr(vals_alt), ptr(temp), temp_bytes,
+       ctypes.addressof(in_alt), stream_of(keys))
+    return (keys_alt, vals_alt) if in_alt.value else (keys, vals)
+
+
 def _sort_pairs(keys: Tensor, vals: Tensor, end_bit: int) -> Tuple[Tensor, Tensor]:
     """Stable LSD radix sort of (int64, int32) pairs over bits [0, end_bit) (radix_sort.cu:10-62)."""
     import ctypes
 
+    if _own_sort():
+        return _radix_sort(keys, vals, end_bit)
     n = keys.numel()
     keys_alt = torch.empty_like(keys)
     vals_alt = torch.empty_like(vals)
@@ -525,10 +549,12 @@ def _sort_pairs(keys: Tensor, vals: Tensor, end_bit: int) -> Tuple[Tensor, Tenso
     return (keys_alt, vals_alt) if in_alt.value else (keys, vals)
 
 
-def _sort_pairs_u32(keys: Tensor, vals: Tensor, end_bit: int) -> Tuple[Tensor, Tensor]:
+def _sort_pairs_u32(keys: Tensor, vals: Tensor, end_bit: int, n_dev: Optional[int] = None) -> Tuple[Tensor, Tensor]:
     """Stable LSD radix sort of (uint32 bit pattern, int32) pairs over bits [0, end_bit)."""
     import ctypes
 
+    if _own_sort():
+        return _radix_sort(keys, vals, end_bit, n_dev)
     n = keys.numel()
     keys_alt = torch.empty_like(keys)
     vals_alt = torch.empty_like(vals)

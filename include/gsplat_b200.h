@@ -208,6 +208,21 @@ int gsb_rasterize_bwd(int C, int64_t n_isects, int D, const float *recA, const f
                       const float *v_render_alphas, float *v_means2d_abs, float *v_means2d, float *v_conics,
                       float *v_colors, float *v_opacities, cudaStream_t stream);
 
+/* ---- stable LSD radix sort of (key, int32 value) pairs, hand-written onesweep (csrc/radix_sort.cu) ------------
+ * replaces triton_impl/radix_sort/radix_sort.cu:10-62 / cub::DeviceRadixSort in IntersectTile.cu. Sorts over key
+ * bits [0, end_bit), 8 bits per pass, one kernel per pass + one histogram kernel + one memset of `temp`
+ * (gsb_radix_temp_bytes(n, end_bit) bytes, caller-allocated). n < 2^30. `n_dev` (NULL or a device int64): the
+ * number of valid leading items is min(n, *n_dev) - the rest of the buffers is neither read nor written, so a
+ * speculatively sized caller pays for the real count only. keys_alt / vals_alt: ping-pong buffers of n items;
+ * *result_in_alt_host (host int, written at call time) tells which pair of buffers holds the result. */
+int64_t gsb_radix_temp_bytes(int64_t n, int end_bit);
+int gsb_radix_sort_pairs_u32(int64_t n, const int64_t *n_dev, int end_bit, int32_t *keys, int32_t *keys_alt,
+                             int32_t *vals, int32_t *vals_alt, void *temp, int64_t temp_bytes,
+                             int *result_in_alt_host, cudaStream_t stream);
+int gsb_radix_sort_pairs_u64(int64_t n, const int64_t *n_dev, int end_bit, int64_t *keys, int64_t *keys_alt,
+                             int32_t *vals, int32_t *vals_alt, void *temp, int64_t temp_bytes,
+                             int *result_in_alt_host, cudaStream_t stream);
+
 /* ---- distributed exchange rows (rendering.py:413-494, distributed.py:170-257) -----------------
  * One fused row per projected Gaussian: means2d(2) depths(1) conics(3) opacities(1) colors(D)
  * radii(1, int32 bit pattern) = (8+D) 4-byte words, so a single all-to-all per direction

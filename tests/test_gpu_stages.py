@@ -186,3 +186,50 @@ def test_projection_culling_parameters():
         d = (radii.cpu() - ref).abs()
         flips = ((radii.cpu() > 0) != (ref > 0)).float().mean()
         assert float(flips) < 3e-3 and int(d[(radii.cpu() > 0) & (ref > 0)].max()) <= 1
+
+
+# ---------------------------------------------------------------------------------------------
+# hand-written radix sort (csrc/radix_sort.cu) against torch's stable sort
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n", [0, 1, 255, 4096, 4097, 70001, 1 << 20])
+@pytest.mark.parametrize("wide", [False, True])
+def test_radix_sort_pairs_is_a_stable_sort(n, wide):
+    from gsplat.b200_impl import _wrapper as Wp
+
+    g = torch.Generator().manual_seed(n + 17)
+    for end_bit in ((5, 13, 32) if not wide else (9, 45, 64)):
+        hi = min(end_bit, 62)
+        keys = torch.randint(0, 1 << hi, (n,), generator=g, dtype=torch.int64)
+        if n > 100:
+            keys[: n // 3] = keys[0]  # long runs of equal keys: stability matters
+        junk = torch.randint(0, 1 << 20, (n,), generator=g, dtype=torch.int64) << end_bit if end_bit < 40 else 0
+        stored = keys | junk if not wide or end_bit < 40 else keys  # bits above end_bit must be ignored
+        vals = torch.arange(n, dtype=torch.int32)
+        order = torch.sort(keys, stable=True).indices
+        if wide:
+            k_dev = stored.to(DEV)
+        else:
+            k_dev = (stored & 0xFFFFFFFF).to(torch.int64)
+            k_dev = torch.where(k_dev >= (1 << 31), k_dev - (1 << 32), k_dev).to(torch.int32).to(DEV)
+        sk, sv = Wp._radix_sort(k_dev.clone(), vals.to(DEV), end_bit)
+        assert torch.equal(sv.cpu().long(), order), (n, end_bit)
+        assert torch.equal(sk.cpu(), k_dev.cpu()[order]), (n, end_bit)
+
+
+def test_radix_sort_device_side_count():
+    from gsplat.b200_impl import _wrapper as Wp
+
+    g = torch.Generator().manual_seed(5)
+    cap, n = 50000, 31234
+    keys = torch.randint(0, 1 << 13, (cap,), generator=g, dtype=torch.int32)
+    vals = torch.arange(cap, dtype=torch.int32)
+    n_dev = torch.tensor([n], dtype=torch.int64, device=DEV)
+    sk, sv = Wp._radix_sort(keys.to(DEV), vals.to(DEV), 13, n_dev.data_ptr())
+    order = torch.sort(keys[:n].long(), stable=True).indices
+    assert torch.equal(sv[:n].cpu().long(), order) and torch.equal(sk[:n].cpu(), keys[:n][order])
+    for count in (0, cap + 999):  # empty, and a count beyond the capacity (clamped)
+        n_dev.fill_(count)
+        sk, sv = Wp._radix_sort(keys.to(DEV), vals.to(DEV), 13, n_dev.data_ptr())
+        m = min(count, cap)
+        order = torch.sort(keys[:m].long(), stable=True).indices
+        assert torch.equal(sv[:m].cpu().long(), order)
