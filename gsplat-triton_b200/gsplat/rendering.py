@@ -60,6 +60,15 @@ from .distributed import (
 _RENDER_MODES = ("RGB", "D", "ED", "RGB+D", "RGB+ED")
 
 
+def _rows_of(table: Tensor, ids: Tensor) -> Tensor:
+    """`table[ids]` (packed rows -> their Gaussian's attribute); the b200 build uses an index_add backward."""
+    if BACKEND == "b200":
+        from .b200_impl._wrapper import gather_rows
+
+        return gather_rows(table, ids)
+    return table[ids]
+
+
 def rasterization(
     means: Tensor,  # [N, 3]
     quats: Tensor,  # [N, 4]
@@ -153,7 +162,7 @@ def rasterization(
     )
     if packed:
         camera_ids, gaussian_ids, radii, means2d, depths, conics, compensations = proj_results
-        opacities = opacities[gaussian_ids]  # [nnz]
+        opacities = _rows_of(opacities, gaussian_ids)  # [nnz]
     else:
         radii, means2d, depths, conics, compensations = proj_results
         opacities = opacities.repeat(C, 1)  # [C, N]
@@ -174,7 +183,7 @@ def rasterization(
     # Colours -> [C, N, D] or [nnz, D]
     if sh_degree is None:
         if packed:
-            colors = colors[gaussian_ids] if colors.dim() == 2 else colors[camera_ids, gaussian_ids]
+            colors = _rows_of(colors, gaussian_ids) if colors.dim() == 2 else colors[camera_ids, gaussian_ids]
         elif colors.dim() == 2:
             colors = colors.expand(C, -1, -1)
     else:
@@ -183,6 +192,11 @@ def rasterization(
             from .b200_impl._wrapper import view_dependent_colors
 
             colors = view_dependent_colors(sh_degree, means, viewmats, colors, radii)  # [C, N, 3]
+        elif BACKEND == "b200" and packed and colors.dim() == 3 and not viewmats.requires_grad:
+            # same kernels over the dense [C, N] grid (mask scattered from the packed ids); only colours are gathered
+            from .b200_impl._wrapper import view_dependent_colors_packed
+
+            colors = view_dependent_colors_packed(sh_degree, means, viewmats, colors, camera_ids, gaussian_ids)
         else:
             camtoworlds = torch.inverse(viewmats)
             if packed:
