@@ -156,8 +156,15 @@ def _stage_table(summary, steps, meta, n_local, C, D, K, work, peaks, sm_mhz):
         "gsb_sh_bwd": 24 * P + P + 12 * K * n_local,
         "gsb_isect_count": 12 * P + 4 * P,
         "gsb_isect_row_keys": 4 * P + 12 * P,
-        "gsb_isect_count_perm": 4 * P + 12 * P + 4 * P,
+        "gsb_isect_row_tiles": 12 * P + 24 * P,
+        "gsb_isect_count_perm": 4 * P + 4 * P,
         "gsb_isect_emit_perm": 20 * P + 8 * I,
+        "gsb_isect_emit_perm_cap": 20 * P + 8 * I,  # perm 4 + one 16-byte record per row, 8 per intersection out
+        "gsb_radix_sort_pairs_u32": 4 * 16 * P + 4 * P + math.ceil((bits - 32) / 8) * 16 * I + 4 * I,
+        "gsb_isect_finalize_cap": 8 * I + 4 * I + 8 * I + 4 * C * n_tiles,
+        "gsb_a2a_put_fwd": 2 * (8 + D) * 4 * P,
+        "gsb_a2a_put_bwd": 2 * (7 + D) * 4 * P,
+        "gsb_a2a_wait_copy": (2 * (8 + D) + 2 * (7 + D)) * 4 * P,
         "gsb_sort_pairs_u32": math.ceil((bits - 32) / 8) * 16 * I + 4 * I,
         "gsb_isect_finalize": 8 * I + 4 * I + 8 * I + 4 * C * n_tiles,
         "gsb_isect_emit": 20 * P + 12 * I,

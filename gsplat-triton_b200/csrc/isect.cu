@@ -189,6 +189,31 @@ row_keys_kernel(int64_t P, int N, const float *__restrict__ depths, const int64_
     rows[i] = (int32_t)i;
 }
 
+// natural order (coalesced): rows[i] = i, the tile count of row i and, for the depth-ordered emission, ONE 16-byte
+// record per row (x0 | y0 << 16, width, camera << tile_bits, count): the emit pass then gathers a single sector per
+// row instead of four (means2d, radius, count, camera id)
+template <bool PACKED>
+__global__ void __launch_bounds__(kThreads)
+row_tiles_kernel(int64_t P, int N, const float *__restrict__ means2d, const int32_t *__restrict__ radii,
+                 const int64_t *__restrict__ camera_ids, int tile_size, int tw, int th, int tile_n_bits,
+                 int32_t *__restrict__ rows, int32_t *__restrict__ tiles_per_gauss, int4 *__restrict__ records) {
+    int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (i >= P) return;
+    int cnt = 0;
+    int4 rec = make_int4(0, 0, 0, 0);
+    const int r = radii[i];
+    if (r > 0) {
+        float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * i);
+        TileBox b = tile_box(m.x, m.y, r, tile_size, tw, th);
+        cnt = (b.x1 - b.x0) * (b.y1 - b.y0);
+        const uint32_t cam = (uint32_t)(PACKED ? camera_ids[i] : (i / N));
+        rec = make_int4(b.x0 | (b.y0 << 16), b.x1 - b.x0, (int)(cam << tile_n_bits), cnt);
+    }
+    rows[i] = (int32_t)i;
+    tiles_per_gauss[i] = cnt;
+    if (records != nullptr) records[i] = rec;
+}
+
 // k-th thread handles row perm[k]: tile count (also stored in natural order) + block sums in permuted order
 __global__ void __launch_bounds__(kThreads)
 count_perm_kernel(int64_t P, const int32_t *__restrict__ perm, const float *__restrict__ means2d,
@@ -199,13 +224,17 @@ count_perm_kernel(int64_t P, const int32_t *__restrict__ perm, const float *__re
     int cnt = 0;
     if (k < P) {
         int64_t i = perm[k];
-        int r = radii[i];
-        if (r > 0) {
-            float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * i);
-            TileBox b = tile_box(m.x, m.y, r, tile_size, tw, th);
-            cnt = (b.x1 - b.x0) * (b.y1 - b.y0);
+        if (means2d == nullptr) {
+            cnt = tiles_per_gauss[i];  // counted in natural order by row_tiles_kernel: one 4-byte gather per row
+        } else {
+            int r = radii[i];
+            if (r > 0) {
+                float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * i);
+                TileBox b = tile_box(m.x, m.y, r, tile_size, tw, th);
+                cnt = (b.x1 - b.x0) * (b.y1 - b.y0);
+            }
+            tiles_per_gauss[i] = cnt;
         }
-        tiles_per_gauss[i] = cnt;
     }
     int sum = cnt;
 #pragma unroll
@@ -220,32 +249,63 @@ count_perm_kernel(int64_t P, const int32_t *__restrict__ perm, const float *__re
     }
 }
 
+// Block-cooperative emission: the CTA's 256 rows (in permuted = depth order) describe their tile rectangles in shared
+// memory, then the threads walk the CTA's OUTPUT range slot by slot (binary search for the owning row), so every
+// store instruction writes 32 consecutive words, whatever the spread of tiles per row.
 template <bool PACKED>
 __global__ void __launch_bounds__(kThreads)
 emit_perm_kernel(int64_t P, int N, const int32_t *__restrict__ perm, const float *__restrict__ means2d,
                  const int32_t *__restrict__ radii, const int64_t *__restrict__ camera_ids, int tile_size, int tw,
                  int th, int tile_n_bits, const int32_t *__restrict__ tiles_per_gauss,
                  const int64_t *__restrict__ block_offsets, uint32_t *__restrict__ tile_keys,
-                 int32_t *__restrict__ flatten_ids, int64_t capacity) {
+                 int32_t *__restrict__ flatten_ids, int64_t capacity, const int4 *__restrict__ records) {
     __shared__ int s_warp[kThreads / 32];
-    int64_t k = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    __shared__ int s_start[kThreads];  // first output slot of each row inside the CTA's range
+    __shared__ int s_xy[kThreads];     // x0 | y0 << 16
+    __shared__ int s_w[kThreads];
+    __shared__ int s_row[kThreads];
+    __shared__ uint32_t s_hi[kThreads];
+    const int tid = threadIdx.x;
+    int64_t k = (int64_t)blockIdx.x * kThreads + tid;
     int64_t i = k < P ? perm[k] : 0;
-    int cnt = k < P ? tiles_per_gauss[i] : 0;
+    int cnt = 0;
+    if (records != nullptr) {
+        int4 rec = make_int4(0, 0, 0, 0);
+        if (k < P) rec = __ldg(records + i);
+        cnt = rec.w;
+        s_xy[tid] = rec.x;
+        s_w[tid] = rec.y;
+        s_hi[tid] = (uint32_t)rec.z;
+    } else {
+        cnt = k < P ? tiles_per_gauss[i] : 0;
+        if (cnt > 0) {
+            float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * i);
+            TileBox b = tile_box(m.x, m.y, radii[i], tile_size, tw, th);
+            s_xy[tid] = b.x0 | (b.y0 << 16);
+            s_w[tid] = b.x1 - b.x0;
+            s_hi[tid] = (uint32_t)(PACKED ? camera_ids[i] : (i / N)) << tile_n_bits;
+        }
+    }
+    s_row[tid] = (int)i;
     int block_total;
-    int local = block_exclusive_scan(cnt, s_warp, block_total);
-    if (cnt == 0) return;
-    int64_t out = block_offsets[blockIdx.x] + local;
-    float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * i);
-    TileBox b = tile_box(m.x, m.y, radii[i], tile_size, tw, th);
-    uint32_t cam = (uint32_t)(PACKED ? camera_ids[i] : (i / N));
-    uint32_t hi = cam << tile_n_bits;
-    for (int y = b.y0; y < b.y1; ++y) {
-        for (int x = b.x0; x < b.x1; ++x) {
-            if (out < capacity) {  // speculative capacity (gsb_isect_emit_perm_cap): never write past the buffers
-                tile_keys[out] = hi | (uint32_t)(y * tw + x);
-                flatten_ids[out] = (int32_t)i;
-            }
-            ++out;
+    s_start[tid] = block_exclusive_scan(cnt, s_warp, block_total);
+    __syncthreads();
+    const int64_t base = block_offsets[blockIdx.x];
+    for (int j = tid; j < block_total; j += kThreads) {
+        // last row r with s_start[r] <= j (rows without tiles share their successor's start and are skipped)
+        int lo = 0, hi_ = kThreads;  // invariant: s_start[lo] <= j < s_start[hi_] (s_start[kThreads] = block_total)
+#pragma unroll
+        for (int step = 0; step < 8; ++step) {
+            const int mid = (lo + hi_) >> 1;
+            if (s_start[mid] <= j) lo = mid; else hi_ = mid;
+        }
+        const int t = j - s_start[lo];
+        const int w = s_w[lo], xy = s_xy[lo];
+        const int dy = t / w, dx = t - dy * w;
+        const int64_t out = base + j;
+        if (out < capacity) {  // speculative capacity (gsb_isect_emit_perm_cap): never write past the buffers
+            tile_keys[out] = s_hi[lo] | (uint32_t)(((xy >> 16) + dy) * tw + (xy & 0xffff) + dx);
+            flatten_ids[out] = s_row[lo];
         }
     }
 }
@@ -400,6 +460,27 @@ extern "C" int gsb_isect_row_keys(int64_t P, int N, int packed, const float *dep
     return gsb_check_launch("isect_row_keys");
 }
 
+extern "C" int gsb_isect_row_tiles(int64_t P, int N, int packed, const float *means2d, const int32_t *radii,
+                                   const int64_t *camera_ids, int tile_size, int tile_width, int tile_height,
+                                   int tile_n_bits, int32_t *rows, int32_t *tiles_per_gauss, int32_t *row_records,
+                                   cudaStream_t stream) {
+    GSB_REQUIRE(P >= 0 && tile_size > 0 && tile_width >= 0 && tile_height >= 0, "bad sizes");
+    GSB_REQUIRE(P < ((int64_t)1 << 31), "more than 2^31-1 rows");
+    GSB_REQUIRE(!packed || camera_ids != nullptr || P == 0 || row_records == nullptr, "camera_ids required when packed");
+    GSB_REQUIRE(packed || N > 0 || P == 0, "N required when not packed");
+    GSB_REQUIRE(tile_width < 65536 && tile_height < 32768, "tile grid too large");
+    if (P == 0) return GSB_OK;
+    const unsigned nblk = (unsigned)gsb_isect_num_blocks(P);
+    auto recs = reinterpret_cast<int4 *>(row_records);
+    if (packed)
+        row_tiles_kernel<true><<<nblk, kThreads, 0, stream>>>(P, N, means2d, radii, camera_ids, tile_size, tile_width,
+                                                              tile_height, tile_n_bits, rows, tiles_per_gauss, recs);
+    else
+        row_tiles_kernel<false><<<nblk, kThreads, 0, stream>>>(P, N, means2d, radii, camera_ids, tile_size, tile_width,
+                                                               tile_height, tile_n_bits, rows, tiles_per_gauss, recs);
+    return gsb_check_launch("isect_row_tiles");
+}
+
 extern "C" int gsb_isect_count_perm(int64_t P, const int32_t *perm, const float *means2d, const int32_t *radii,
                                     int tile_size, int tile_width, int tile_height, int32_t *tiles_per_gauss,
                                     int32_t *block_sums, int64_t *block_offsets, int64_t *n_isects_out,
@@ -422,29 +503,32 @@ extern "C" int gsb_isect_emit_perm(int64_t P, int N, int packed, const int32_t *
                                    cudaStream_t stream) {
     return gsb_isect_emit_perm_cap(P, N, packed, perm, means2d, radii, camera_ids, tile_size, tile_width, tile_height,
                                    tile_n_bits, tiles_per_gauss, block_offsets, tile_keys, flatten_ids,
-                                   INT64_MAX, nullptr, stream);
+                                   INT64_MAX, nullptr, nullptr, stream);
 }
 
 extern "C" int gsb_isect_emit_perm_cap(int64_t P, int N, int packed, const int32_t *perm, const float *means2d,
                                        const int32_t *radii, const int64_t *camera_ids, int tile_size, int tile_width,
                                        int tile_height, int tile_n_bits, const int32_t *tiles_per_gauss,
                                        const int64_t *block_offsets, int32_t *tile_keys, int32_t *flatten_ids,
-                                       int64_t capacity, const int64_t *n_isects_dev, cudaStream_t stream) {
+                                       int64_t capacity, const int64_t *n_isects_dev, const int32_t *row_records,
+                                       cudaStream_t stream) {
     GSB_REQUIRE(P >= 0 && tile_size > 0 && capacity >= 0, "bad sizes");
     GSB_REQUIRE(!packed || camera_ids != nullptr || P == 0, "camera_ids required when packed");
     auto tk = reinterpret_cast<uint32_t *>(tile_keys);
+    auto recs = reinterpret_cast<const int4 *>(row_records);
+    GSB_REQUIRE(tile_width < 65536 && tile_height < 32768, "tile grid too large");
     if (P > 0) {
         unsigned nblk = (unsigned)gsb_isect_num_blocks(P);
         if (packed)
             emit_perm_kernel<true><<<nblk, kThreads, 0, stream>>>(P, N, perm, means2d, radii, camera_ids, tile_size,
                                                                   tile_width, tile_height, tile_n_bits,
                                                                   tiles_per_gauss, block_offsets, tk, flatten_ids,
-                                                                  capacity);
+                                                                  capacity, recs);
         else
             emit_perm_kernel<false><<<nblk, kThreads, 0, stream>>>(P, N, perm, means2d, radii, camera_ids, tile_size,
                                                                    tile_width, tile_height, tile_n_bits,
                                                                    tiles_per_gauss, block_offsets, tk, flatten_ids,
-                                                                   capacity);
+                                                                   capacity, recs);
         if (int e = gsb_check_launch("isect_emit_perm")) return e;
     }
     if (n_isects_dev != nullptr && capacity > 0) {

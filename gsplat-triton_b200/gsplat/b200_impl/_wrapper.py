@@ -539,11 +539,14 @@ def _isect_presorted(means2d, radii, depths, camera_ids, C, N, P, packed, tile_s
     # the row key is the depth bit pattern itself (positive floats order like their bits). Cameras need no bits
     # here: rows are emitted in global depth order and the (camera | tile) sort below is stable, so inside every
     # (camera, tile) bucket the intersections stay depth-ordered, ties by ascending row like the reference's sort.
-    lib.gsb_isect_row_keys(P, N, int(packed), ptr(depths), ptr(camera_ids), None, ptr(rows), st)
+    # tile counts are taken in natural order (coalesced); the depth-ordered passes only gather them
+    records = torch.empty((P, 4), dtype=torch.int32, device=dev)
+    lib.gsb_isect_row_tiles(P, N, int(packed), ptr(means2d), ptr(radii), ptr(camera_ids), tile_size, tile_width,
+                            tile_height, tb, ptr(rows), ptr(tiles_per_gauss), ptr(records), st)
     _, perm = _sort_pairs_u32(depths.reshape(-1).view(torch.int32).clone(), rows, 32)
     block_sums = torch.empty((max(nblk, 1),), dtype=torch.int32, device=dev)
     block_offsets = torch.empty((nblk + 1,), dtype=torch.int64, device=dev)
-    lib.gsb_isect_count_perm(P, ptr(perm), ptr(means2d), ptr(radii), tile_size, tile_width, tile_height,
+    lib.gsb_isect_count_perm(P, ptr(perm), None, None, tile_size, tile_width, tile_height,
                              ptr(tiles_per_gauss), ptr(block_sums), ptr(block_offsets),
                              block_offsets.data_ptr() + 8 * nblk, st)
     key = (dev.index, C, tile_width, tile_height, tile_size, bool(packed))
@@ -567,7 +570,7 @@ def _isect_presorted(means2d, radii, depths, camera_ids, C, N, P, packed, tile_s
         pad = n_dev if not _own_sort() else None
         lib.gsb_isect_emit_perm_cap(P, N, int(packed), ptr(perm), ptr(means2d), ptr(radii), ptr(camera_ids),
                                     tile_size, tile_width, tile_height, tb, ptr(tiles_per_gauss), ptr(block_offsets),
-                                    ptr(tile_keys), ptr(flatten_ids), n_isects, pad, st)
+                                    ptr(tile_keys), ptr(flatten_ids), n_isects, pad, ptr(records), st)
         tile_keys, flatten_ids = _sort_pairs_u32(tile_keys, flatten_ids, tb + cb, n_dev)
     lib.gsb_isect_finalize_cap(n_isects, n_dev if n_isects > 0 else None, ptr(tile_keys), ptr(flatten_ids),
                                ptr(depths), C, tile_width, tile_height, tb, ptr(isect_ids), ptr(offsets), st)

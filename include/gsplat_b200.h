@@ -145,6 +145,12 @@ int gsb_isect_offsets(int64_t n_isects, const int64_t *isect_ids, int C, int til
  * reference's own key). tile_bits + camera_bits must be <= 32. */
 int gsb_isect_row_keys(int64_t P, int N, int packed, const float *depths, const int64_t *camera_ids, int64_t *keys,
                        int32_t *rows, cudaStream_t stream);
+/* natural-order (coalesced) part of steps 1-2: rows[i] = i, tiles_per_gauss[i] = tile count of row i and (optional)
+ * row_records int32[P,4] = (x0 | y0 << 16, width, camera << tile_n_bits, count) for gsb_isect_emit_perm_cap. With it,
+ * gsb_isect_count_perm may be called with means2d = radii = NULL and only gathers the 4-byte counts. */
+int gsb_isect_row_tiles(int64_t P, int N, int packed, const float *means2d, const int32_t *radii,
+                        const int64_t *camera_ids, int tile_size, int tile_width, int tile_height, int tile_n_bits,
+                        int32_t *rows, int32_t *tiles_per_gauss, int32_t *row_records, cudaStream_t stream);
 int gsb_isect_count_perm(int64_t P, const int32_t *perm, const float *means2d, const int32_t *radii, int tile_size,
                          int tile_width, int tile_height, int32_t *tiles_per_gauss, int32_t *block_sums,
                          int64_t *block_offsets, int64_t *n_isects_out, cudaStream_t stream);
@@ -162,12 +168,14 @@ int gsb_isect_finalize(int64_t n_isects, const int32_t *tile_keys, const int32_t
  * `capacity` slots, the real count stays on the device (`n_isects_dev`, the total written by gsb_isect_count_perm).
  * emit writes only slots < capacity and pads [n_isects, capacity) with 0xffffffff keys (they sort last); finalize
  * treats min(*n_isects_dev, capacity) as the count. The caller reads the count back later and, if it exceeded
- * the capacity, redoes the step with exact sizes. */
+ * the capacity, redoes the step with exact sizes. row_records (or NULL): the per-row records of
+ * gsb_isect_row_tiles; with them emit gathers one 16-byte record per row instead of means2d/radii/camera_ids. */
 int gsb_isect_emit_perm_cap(int64_t P, int N, int packed, const int32_t *perm, const float *means2d,
                             const int32_t *radii, const int64_t *camera_ids, int tile_size, int tile_width,
                             int tile_height, int tile_n_bits, const int32_t *tiles_per_gauss,
                             const int64_t *block_offsets, int32_t *tile_keys, int32_t *flatten_ids,
-                            int64_t capacity, const int64_t *n_isects_dev, cudaStream_t stream);
+                            int64_t capacity, const int64_t *n_isects_dev, const int32_t *row_records,
+                            cudaStream_t stream);
 int gsb_isect_finalize_cap(int64_t n_isects, const int64_t *n_isects_dev, const int32_t *tile_keys,
                            const int32_t *flatten_ids, const float *depths, int C, int tile_width, int tile_height,
                            int tile_n_bits, int64_t *isect_ids, int32_t *offsets, cudaStream_t stream);
