@@ -174,7 +174,8 @@ def _stage_table(summary, steps, meta, n_local, C, D, K, work, peaks, sm_mhz):
     }
     fp32_peak = SM_COUNT * FP32_LANES * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12  # TFLOP/s at max clock, FMA = 2
     evals, hits = work if work is not None else (None, None)
-    flops = {} if hits is None else {"gsb_rasterize_fwd": 2 * SLOTS_FWD * hits, "gsb_rasterize_bwd": 2 * SLOTS_BWD * hits}
+    flops = {} if hits is None else {"gsb_rasterize_fwd": 2 * SLOTS_FWD * hits, "gsb_rasterize_fwd_cap": 2 * SLOTS_FWD * hits,
+                                     "gsb_rasterize_bwd": 2 * SLOTS_BWD * hits}
     out = {}
     for name, (calls, ms) in summary.items():
         per_step = ms / steps

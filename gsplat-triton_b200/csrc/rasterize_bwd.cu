@@ -70,7 +70,10 @@ __device__ __forceinline__ void reduce_chunk(int count, int lane, const float2 *
     float abs_x = 0.f, abs_y = 0.f;
     const int j = s_cj[s < count ? s : 0];
     const float4 mu = s_P[j];  // (x, y, sorted index, -)
-    const float4 b4 = s_B[j];
+    float4 b4 = s_B[j];        // staged (pre-scaled) conic -> conic
+    b4.x *= kUnscaleDiag;
+    b4.y *= kUnscaleOff;
+    b4.z *= kUnscaleDiag;
     const float ux = mu.x - bcx, uy = mu.y - bcy;
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
@@ -221,7 +224,7 @@ rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
         const int slot = stage_slot(mask != 0u, s_wcnt, total);  // syncs: previous batch fully consumed
         if (mask != 0u) {
             s_P[slot] = make_float4(A.x, A.y, __int_as_float(idx), __uint_as_float(mask));
-            s_B[slot] = B;
+            s_B[slot] = stage_conic(B);
             const float *cp = colors + (size_t)g * D;
 #pragma unroll
             for (int k = 0; k < CS; ++k) s_col[slot * CS + k] = k < D ? cp[k] : 0.f;
@@ -244,11 +247,10 @@ rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
                 const float4 p4 = s_P[j];
                 const float4 b4 = s_B[j];
                 const float dx = p4.x - pxf, dy = p4.y - pyf;
-                const float sigma = 0.5f * (b4.x * dx * dx + b4.z * dy * dy) + b4.y * dx * dy;
-                const float vis = __expf(-sigma);
-                const float ov = b4.w * vis;
+                const float ex = gauss_log2(b4, dx, dy);  // log2(e^-sigma), same expression as the forward pass
+                const float ov = b4.w * exp2f(ex);
                 const float alpha = fminf(kAlphaMax, ov);
-                const bool hit = (__float_as_int(p4.z) <= bin_final) && !(sigma < 0.f) && !(alpha < kAlphaMin);
+                const bool hit = (__float_as_int(p4.z) <= bin_final) && !(ex > 0.f) && !(alpha < kAlphaMin);
                 if (!__any_sync(0xffffffffu, hit)) continue;
 
                 float w1 = 0.f, w2 = 0.f;

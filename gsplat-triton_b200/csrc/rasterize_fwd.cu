@@ -94,7 +94,7 @@ rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
             const int slot = stage_slot(mask != 0u, s_wcnt, total);
             if (mask != 0u) {
                 st.P[slot] = make_float4(A.x, A.y, __int_as_float(idx), __uint_as_float(mask));
-                st.B[slot] = B;
+                st.B[slot] = stage_conic(B);
                 const float *cp = colors + (size_t)g * D;
                 if (kPacked) {
                     float4 c4 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -120,10 +120,10 @@ rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
                     const float4 p4 = st.P[j];
                     const float4 b4 = st.B[j];
                     const float dx = p4.x - pxf, dy = p4.y - pyf;
-                    const float sigma = 0.5f * (b4.x * dx * dx + b4.z * dy * dy) + b4.y * dx * dy;
-                    const float alpha = fminf(kAlphaMax, b4.w * __expf(-sigma));
-                    const float next_T = T * (1.0f - alpha);  // < 0 on finished pixels
-                    if (!(sigma < 0.f) && !(alpha < kAlphaMin)) {
+                    const float ex = gauss_log2(b4, dx, dy);  // log2(e^-sigma)
+                    const float alpha = fminf(kAlphaMax, b4.w * exp2f(ex));
+                    const float next_T = fmaf(-T, alpha, T);  // T (1 - alpha); < 0 on finished pixels
+                    if (!(ex > 0.f) && !(alpha < kAlphaMin)) {
                         if (next_T <= kTmin) {
                             T = -fabsf(T);  // stop *before* this splat; no-op when already finished
                         } else {
