@@ -28,11 +28,14 @@ namespace {
 #ifndef GSB_SORT_MIN_BLOCKS
 #define GSB_SORT_MIN_BLOCKS 3
 #endif
+#ifndef GSB_SORT_ITEMS
+#define GSB_SORT_ITEMS 8
+#endif
 constexpr int kThreads = 512;
 constexpr int kWarps = kThreads / 32;
 template <typename KeyT>
 struct TileOf {
-    static constexpr int kItems = 8;
+    static constexpr int kItems = GSB_SORT_ITEMS;
     static constexpr int kTile = kThreads * kItems;  // 4096 pairs
     static constexpr size_t kSmem = sizeof(uint32_t) * kWarps * 256 + sizeof(int64_t) * 256 +
                                     sizeof(KeyT) * kTile + sizeof(int32_t) * kTile;
@@ -298,7 +301,7 @@ int sort_pairs(int64_t n, const int64_t *n_dev, int end_bit, KeyT *keys, KeyT *k
 
 extern "C" int64_t gsb_radix_temp_bytes(int64_t n, int end_bit) {
     const int passes = (end_bit + 7) / 8;
-    const int64_t tiles = (n + TileOf<unsigned long long>::kTile - 1) / TileOf<unsigned long long>::kTile;  // the smaller tile
+    const int64_t tiles = (n + TileOf<unsigned long long>::kTile - 1) / TileOf<unsigned long long>::kTile;
     return scratch_words(passes > 0 ? passes : 1, tiles > 0 ? tiles : 1) * 4;
 }
 
