@@ -137,15 +137,21 @@ class HostBoard:
 _HOST_BOARD = None
 
 
+def _group_key():
+    """Identity of the current default process group (boards / mailboxes do not outlive it)."""
+    return (id(dist.distributed_c10d._get_default_group()), dist.get_world_size(), dist.get_rank())
+
+
 def all_gather_int_host(world_size: int, value: int) -> List[int]:
     """Gathers one host integer from every rank of this node without touching the GPU (see HostBoard).
     Collective: every rank must call it."""
     global _HOST_BOARD
     if world_size == 1:
         return [int(value)]
-    if _HOST_BOARD is None:
-        _HOST_BOARD = HostBoard()
-    return _HOST_BOARD.all_gather(int(value))
+    key = _group_key()
+    if _HOST_BOARD is None or _HOST_BOARD[0] != key:  # a new process group (init/destroy cycle): new board
+        _HOST_BOARD = (key, HostBoard())
+    return _HOST_BOARD[1].all_gather(int(value))
 
 
 def all_to_all_int32(world_size: int, values: List[Union[int, Tensor]], device: Optional[torch.device] = None):
@@ -459,9 +465,10 @@ def peer_exchange_available() -> bool:
 
 
 def get_mailbox(group=None) -> PeerMailbox:
-    key = id(group) if group is not None else None
+    key = (id(group),) if group is not None else _group_key()
     box = _MAILBOXES.get(key)
     if box is None:
+        close_mailboxes()  # mailboxes of a process group that no longer exists
         box = _MAILBOXES[key] = PeerMailbox(group)
     return box
 
