@@ -7,6 +7,7 @@ from ._wrapper import (  # noqa: F401
     fully_fused_projection,
     isect_offset_encode,
     isect_tiles,
+    rasterize_to_indices_in_range,
     rasterize_to_pixels,
     spherical_harmonics,
 )

@@ -802,3 +802,50 @@ class _RasterizeToPixels(torch.autograd.Function):
         if ctx.needs_input_grad[4]:
             v_backgrounds = (v_render_colors * (1.0 - render_alphas).float()).sum(dim=(1, 2))
         return (v_means2d, v_conics, v_colors, v_opacities, v_backgrounds) + (None,) * 8
+
+
+# --------------------------------------------------------------------------------------------
+# rasterize_to_indices_in_range
+# --------------------------------------------------------------------------------------------
+@torch.no_grad()
+def rasterize_to_indices_in_range(
+    range_start: int,
+    range_end: int,
+    transmittances: Tensor,  # [C, image_height, image_width]
+    means2d: Tensor,  # [C, N, 2]
+    conics: Tensor,  # [C, N, 3]
+    opacities: Tensor,  # [C, N]
+    image_width: int,
+    image_height: int,
+    tile_size: int,
+    isect_offsets: Tensor,  # [C, tile_height, tile_width]
+    flatten_ids: Tensor,  # [n_isects]
+) -> Tuple[Tensor, Tensor, Tensor]:
+    """The (Gaussian, pixel, camera) index lists of the pairs the compositor blends for the sorted-intersection
+    batches `[range_start, range_end)` of every tile. Contract: cuda/_wrapper.py:577-648 (the op the reference's
+    pure-torch compositor `_torch_impl._rasterize_to_pixels` iterates on). Returns int64 `[M]` tensors."""
+    C, N, _ = means2d.shape
+    assert conics.shape == (C, N, 3), conics.shape
+    assert opacities.shape == (C, N), opacities.shape
+    assert isect_offsets.shape[0] == C, isect_offsets.shape
+    assert transmittances.shape == (C, image_height, image_width), transmittances.shape
+    tile_height, tile_width = isect_offsets.shape[1:3]
+    assert tile_height * tile_size >= image_height, f"Assert Failed: {tile_height} * {tile_size} >= {image_height}"
+    assert tile_width * tile_size >= image_width, f"Assert Failed: {tile_width} * {tile_size} >= {image_width}"
+    require_cuda(transmittances, means2d, conics, opacities, isect_offsets, flatten_ids)
+    dev, st = means2d.device, stream_of(means2d)
+    range_end = int(min(range_end, 2**31 - 1))
+    args = (C, N, flatten_ids.numel(), int(range_start), range_end, ptr(_f32(transmittances)), ptr(_f32(means2d)),
+            ptr(_f32(conics)), ptr(_f32(opacities)), image_width, image_height, tile_size, tile_width, tile_height,
+            ptr(isect_offsets.contiguous().int()), ptr(flatten_ids.contiguous().int()))
+    counts = torch.empty((C * image_height * image_width,), dtype=torch.int32, device=dev)
+    lib.gsb_rasterize_indices_count(*args, ptr(counts), st)
+    ends = torch.cumsum(counts, dim=0, dtype=torch.int64)
+    total = int(ends[-1].item()) if ends.numel() else 0
+    starts = (ends - counts).contiguous()
+    gaussian_ids = torch.empty((total,), dtype=torch.int64, device=dev)
+    indices = torch.empty((total,), dtype=torch.int64, device=dev)
+    if total > 0:
+        lib.gsb_rasterize_indices_write(*args, ptr(starts), ptr(gaussian_ids), ptr(indices), st)
+    per_camera = image_width * image_height
+    return gaussian_ids, indices % per_camera, indices // per_camera

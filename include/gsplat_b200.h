@@ -216,6 +216,24 @@ int gsb_rasterize_bwd(int C, int64_t n_isects, int D, const float *recA, const f
                       const float *v_render_alphas, float *v_means2d_abs, float *v_means2d, float *v_conics,
                       float *v_colors, float *v_opacities, cudaStream_t stream);
 
+/* ---- rasterize_to_indices_in_range (cuda/_wrapper.py:577-648, RasterizeToIndices3DGS.cu:14-170) ---------------
+ * the (Gaussian, pixel) pairs the compositor blends for sorted-intersection batches [range_start, range_end) of
+ * every tile (batch = tile_size^2 intersections), starting from transmittances[C,H,W]. Pass 1 writes counts[C*H*W];
+ * the caller scans them (exclusive, int64) into pixel_starts and sizes the outputs; pass 2 writes
+ * gaussian_ids (within-camera id) and indices (camera*H*W + pixel), pixel-major, sorted order inside a pixel.
+ * Any tile_size (the grid of isect_offsets must cover the image). */
+int gsb_rasterize_indices_count(int C, int N, int64_t n_isects, int range_start, int range_end,
+                                const float *transmittances, const float *means2d, const float *conics,
+                                const float *opacities, int width, int height, int tile_size, int tile_width,
+                                int tile_height, const int32_t *isect_offsets, const int32_t *flatten_ids,
+                                int32_t *counts, cudaStream_t stream);
+int gsb_rasterize_indices_write(int C, int N, int64_t n_isects, int range_start, int range_end,
+                                const float *transmittances, const float *means2d, const float *conics,
+                                const float *opacities, int width, int height, int tile_size, int tile_width,
+                                int tile_height, const int32_t *isect_offsets, const int32_t *flatten_ids,
+                                const int64_t *pixel_starts, int64_t *gaussian_ids, int64_t *indices,
+                                cudaStream_t stream);
+
 /* ---- stable LSD radix sort of (key, int32 value) pairs, hand-written onesweep (csrc/radix_sort.cu) ------------
  * replaces triton_impl/radix_sort/radix_sort.cu:10-62 / cub::DeviceRadixSort in IntersectTile.cu. Sorts over key
  * bits [0, end_bit), 8 bits per pass, one kernel per pass + one histogram kernel + one memset of `temp`

@@ -65,47 +65,7 @@ def _install_nerfacc_stub():
     sys.modules["nerfacc"] = m
 
 
-@torch.no_grad()
-def _indices_in_range_cpu(range_start, range_end, transmittances, means2d, conics, opacities, image_width,
-                          image_height, tile_size, isect_offsets, flatten_ids):
-    """RasterizeToIndices3DGS.cu:14-170 on the CPU, one pixel at a time (grouped by camera, pixel)."""
-    C, N, _ = means2d.shape
-    th, tw = isect_offsets.shape[1:]
-    n_isects = flatten_ids.numel()
-    offs = torch.cat([isect_offsets.flatten().long(), torch.tensor([n_isects])]).numpy()
-    fid = flatten_ids.long().numpy()
-    m = means2d.reshape(-1, 2).numpy()
-    cn = conics.reshape(-1, 3).numpy()
-    op = opacities.reshape(-1).numpy()
-    block = tile_size * tile_size
-    gs, px, cam = [], [], []
-    for c in range(C):
-        for i in range(image_height):
-            for j in range(image_width):
-                t = (c * th + i // tile_size) * tw + j // tile_size
-                lo, hi = int(offs[t]), int(offs[t + 1])
-                lo2 = lo + block * range_start
-                hi2 = min(hi, lo + block * range_end)
-                if lo2 >= hi2:
-                    continue
-                g = fid[lo2:hi2]
-                dx = m[g, 0] - np.float32(j + 0.5)
-                dy = m[g, 1] - np.float32(i + 0.5)
-                sigma = np.float32(0.5) * (cn[g, 0] * dx * dx + cn[g, 2] * dy * dy) + cn[g, 1] * dx * dy
-                alpha = np.minimum(np.float32(0.999), op[g] * np.exp(-sigma))
-                T = np.float32(transmittances[c, i, j].item())
-                for k in range(g.shape[0]):
-                    if sigma[k] < 0 or alpha[k] < np.float32(1.0 / 255.0):
-                        continue
-                    nT = T * (np.float32(1.0) - alpha[k])
-                    if nT <= np.float32(1e-4):
-                        break
-                    gs.append(int(g[k]) % N)
-                    px.append(i * image_width + j)
-                    cam.append(c)
-                    T = nT
-    return (torch.tensor(gs, dtype=torch.long), torch.tensor(px, dtype=torch.long),
-            torch.tensor(cam, dtype=torch.long))
+_indices_in_range_cpu = O.rasterize_to_indices_in_range  # RasterizeToIndices3DGS.cu:14-170 on the CPU
 
 
 def _close(a, b, rtol=1e-4, atol=1e-4, what=""):

@@ -281,3 +281,33 @@ def test_raster_masks_empty_and_last_tile():
     rc, ra = rasterize_to_pixels(means2d.to(DEV), conics.to(DEV), colors.to(DEV), opac.to(DEV), W, H, ts,
                                  torch.zeros_like(offs).to(DEV), e, backgrounds=bg.to(DEV))
     assert float(ra.abs().max()) == 0.0 and torch.equal(rc[0, 0, 0].cpu(), bg[0])
+
+
+def test_rasterize_to_indices_in_range_matches_oracle(golden):
+    """b200 rasterize_to_indices_in_range (cuda/_wrapper.py:577) vs the CPU restatement, whole range and in two
+    steps with the transmittance carried over, per-pixel counts and the lists themselves."""
+    from gsplat.b200_impl import rasterize_to_indices_in_range
+
+    g = golden("raster")
+    C, H, W, ts = g["means2d"].shape[0], g["height"], g["width"], g["tile_size"]
+    dev = "cuda"
+    args = [g[k].to(dev) for k in ("means2d", "conics", "opacities")]
+    tail = (W, H, ts, g["offsets"].to(dev), g["flatten_ids"].to(dev))
+    o_tail = (W, H, ts, g["offsets"], g["flatten_ids"])
+    T0 = torch.ones(C, H, W)
+    for lo, hi, T in ((0, 1 << 30, T0), (0, 1, T0), (1, 3, T0 * 0.5)):
+        gs, px, cam = rasterize_to_indices_in_range(lo, hi, T.to(dev), *args, *tail)
+        o_gs, o_px, o_cam = O.rasterize_to_indices_in_range(lo, hi, T, g["means2d"], g["conics"], g["opacities"],
+                                                            *o_tail)
+        assert gs.dtype == torch.int64 and px.dtype == torch.int64 and cam.dtype == torch.int64
+        key, o_key = (cam * H * W + px).cpu(), o_cam * H * W + o_px
+        cnt = torch.bincount(key, minlength=C * H * W)
+        o_cnt = torch.bincount(o_key, minlength=C * H * W)
+        # exp() differs by an ulp between the two sides: a pair sitting on the 1/255 or 1e-4 threshold may flip
+        assert float((cnt != o_cnt).float().mean()) < 5e-3, (lo, hi)
+        assert abs(gs.numel() - o_gs.numel()) <= 5e-3 * max(o_gs.numel(), 1) + 2
+        same = (cnt == o_cnt)
+        keep, o_keep = same[key], same[o_key]
+        assert torch.equal(gs.cpu()[keep], o_gs[o_keep]) and torch.equal(key[keep], o_key[o_keep]), (lo, hi)
+    empty = rasterize_to_indices_in_range(5000, 5001, T0.to(dev), *args, *tail)
+    assert all(t.numel() == 0 for t in empty)

@@ -153,3 +153,25 @@ def test_whole_path_runs_on_garden_subset():
     assert rc.shape == (1, H, W, 3) and ra.shape == (1, H, W, 1)
     assert float(ra.max()) <= 1.0 and float(ra.max()) > 0.0
     assert int(meta["isect_offsets"][-1, -1, -1]) <= meta["flatten_ids"].numel()
+
+
+def test_indices_in_range_agree_with_the_compositor(golden):
+    """rasterize_to_indices_in_range restatement (RasterizeToIndices3DGS.cu:14-170): the pairs it lists, blended
+    with w = alpha * prod(1 - alpha), reproduce the oracle compositor's alpha image; batches partition the list."""
+    g = golden("raster")
+    C, H, W, ts = g["means2d"].shape[0], g["height"], g["width"], g["tile_size"]
+    T0 = torch.ones(C, H, W)
+    gs, px, cam = O.rasterize_to_indices_in_range(0, 1 << 20, T0, g["means2d"], g["conics"], g["opacities"], W, H, ts,
+                                                  g["offsets"], g["flatten_ids"])
+    assert gs.numel() > 1000 and int(gs.max()) < g["means2d"].shape[1]
+    key = cam * H * W + px
+    assert bool((key[1:] >= key[:-1]).all())  # pixel-major
+    d = g["means2d"][cam, gs] - torch.stack([px % W + 0.5, px // W + 0.5], -1)
+    cn = g["conics"][cam, gs]
+    sigma = 0.5 * (cn[:, 0] * d[:, 0] ** 2 + cn[:, 2] * d[:, 1] ** 2) + cn[:, 1] * d[:, 0] * d[:, 1]
+    alpha = torch.clamp_max(g["opacities"][cam, gs] * torch.exp(-sigma), 0.999)
+    logT = torch.zeros(C * H * W).index_add_(0, key, torch.log1p(-alpha))
+    _close(1.0 - torch.exp(logT).reshape(C, H, W, 1), g["render_alphas"], atol=1e-4)
+    first = O.rasterize_to_indices_in_range(0, 1, T0, g["means2d"], g["conics"], g["opacities"], W, H, ts,
+                                            g["offsets"], g["flatten_ids"])
+    assert 0 < first[0].numel() <= gs.numel()
