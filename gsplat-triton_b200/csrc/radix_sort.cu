@@ -209,26 +209,32 @@ onesweep_kernel(int64_t n, const int64_t *__restrict__ n_dev, const KeyT *__rest
         uint32_t prefix = 0u;
         bool done = (tile == 0);
         int64_t t = tile - 1;
-        while (!done) {
-#pragma unroll
-            for (int j = 0; j < kLook; ++j) {
-                if (done) break;
-                if ((look[j] >> 30) == 0u) {  // not published yet: poll this one
-                    const volatile uint32_t *st = states + (t - j) * kBins + d;
-                    unsigned spins = 0;
-                    while (((look[j] = *st) >> 30) == 0u) {
-                        if (++spins > (1u << 26)) __trap();  // a preceding tile never published: fail loudly, never hang
-                    }
+        auto consume = [&](uint32_t v, int64_t at) {
+            if ((v >> 30) == 0u) {  // not published yet: poll this one
+                const volatile uint32_t *st = states + at * kBins + d;
+                unsigned spins = 0;
+                while (((v = *st) >> 30) == 0u) {
+                    if (++spins > (1u << 26)) __trap();  // a preceding tile never published: fail loudly, never hang
                 }
-                prefix += look[j] & kValueMask;
-                done = (look[j] & kFlagPrefix) != 0u;
             }
-            t -= kLook;
-            if (!done) {
+            prefix += v & kValueMask;
+            done = (v & kFlagPrefix) != 0u;
+        };
 #pragma unroll
-                for (int j = 0; j < kLook; ++j)
-                    look[j] = (t - j >= 0) ? __ldcv(states + (t - j) * kBins + d) : kFlagPrefix;
-            }
+        for (int j = 0; j < kLook; ++j)
+            if (!done) consume(look[j], t - j);
+        t -= kLook;
+        // further back: 16 states per round trip (key[] / rank[] are dead by now, the registers are free). With a whole
+        // wave of tiles starting at once the frontier of finished prefixes grows quadratically in round trips.
+        constexpr int kWide = 16;
+        while (!done) {
+            uint32_t far[kWide];
+#pragma unroll
+            for (int j = 0; j < kWide; ++j) far[j] = (t - j >= 0) ? __ldcv(states + (t - j) * kBins + d) : kFlagPrefix;
+#pragma unroll
+            for (int j = 0; j < kWide; ++j)
+                if (!done) consume(far[j], t - j);
+            t -= kWide;
         }
         if (tile != 0) __stcg(states + tile * kBins + d, kFlagPrefix | ((prefix + total) & kValueMask));
         s_global[d] = (int32_t)(hbase + prefix) - (int32_t)bucket;  // n < 2^30: positions fit 32 bits
