@@ -1,7 +1,7 @@
 """gsplat (b200 build): `rasterization()` and its five backend stages on hand-written sm_100a kernels.
 
 Only the hot path of the reference is provided: `gsplat.rendering.rasterization`,
-`gsplat.distributed`, `gsplat.b200_impl`. For parity runs against the reference's own backends set
+`gsplat.distributed`, `gsplat.b200_impl`, plus `gsplat.optimizers.SelectiveAdam` (section 8f). For parity runs against the reference's own backends set
 GSPLAT_REFERENCE_PATH=<checkout of hieu1999210/gsplat-triton>: its `gsplat/` directory is appended to this
 package's search path so `gsplat.triton_impl`, `gsplat.cuda`, `gsplat._helper` resolve there while
 `gsplat.rendering`, `gsplat.distributed`, `gsplat.b200_impl` stay ours.
@@ -28,4 +28,12 @@ def __getattr__(name):
         from . import rendering
 
         return getattr(rendering, name)
+    if name == "rasterize_to_indices_in_range":
+        from .b200_impl import rasterize_to_indices_in_range
+
+        return rasterize_to_indices_in_range
+    if name == "SelectiveAdam":
+        from .optimizers import SelectiveAdam
+
+        return SelectiveAdam
     raise AttributeError(f"module 'gsplat' has no attribute {name!r}")

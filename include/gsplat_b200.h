@@ -234,6 +234,17 @@ int gsb_rasterize_indices_write(int C, int N, int64_t n_isects, int range_start,
                                 const int64_t *pixel_starts, int64_t *gaussian_ids, int64_t *indices,
                                 cudaStream_t stream);
 
+/* ---- selective fused Adam (optimizers/selective_adam.py, AdamCUDA.cu:13-52) ------------------------------------
+ * in-place update of param / exp_avg / exp_avg_sq [N, M] for the Gaussians with visibility[n] != 0 (uint8[N], or
+ * NULL = all): m = b1 m + (1-b1) g, v = b2 v + (1-b2) g^2, p -= lr m / (sqrt(v) + eps); no bias correction. */
+int gsb_selective_adam(int64_t N, int64_t M, float *param, const float *grad, float *exp_avg, float *exp_avg_sq,
+                       const uint8_t *visibility, float lr, float b1, float b2, float eps, cudaStream_t stream);
+
+/* ---- MCMC relocation (relocation.py:10-50, RelocationCUDA.cu:13-45) ---------------------------------------------
+ * per Gaussian split into ratios[n] (1..n_max) copies: new_opacities [N], new_scales [N,3]; binoms [n_max,n_max]. */
+int gsb_relocation(int64_t N, const float *opacities, const float *scales, const int32_t *ratios,
+                   const float *binoms, int n_max, float *new_opacities, float *new_scales, cudaStream_t stream);
+
 /* ---- stable LSD radix sort of (key, int32 value) pairs, hand-written onesweep (csrc/radix_sort.cu) ------------
  * replaces triton_impl/radix_sort/radix_sort.cu:10-62 / cub::DeviceRadixSort in IntersectTile.cu. Sorts over key
  * bits [0, end_bit), 8 bits per pass, one kernel per pass + one histogram kernel + one memset of `temp`

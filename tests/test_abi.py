@@ -83,3 +83,19 @@ def test_product_never_imports_the_oracle():
                 text = open(os.path.join(dirpath, f)).read()
                 assert "gs_oracle" not in text and "import oracle" not in text, os.path.join(dirpath, f)
     assert os.path.isdir(os.path.join(ROOT, "oracle"))
+
+
+def test_optimizer_ops_refuse_cpu_tensors():
+    """SelectiveAdam / compute_relocation have no CPU path either: CPU tensors raise instead of falling back."""
+    import pytest
+    import torch
+    from gsplat.optimizers import SelectiveAdam
+    from gsplat.relocation import compute_relocation
+
+    p = torch.zeros(4, 3, requires_grad=True)
+    p.grad = torch.ones(4, 3)
+    opt = SelectiveAdam([{"params": [p], "lr": 1e-3}], eps=1e-15, betas=(0.9, 0.999))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        opt.step(visibility=torch.ones(4, dtype=torch.bool))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        compute_relocation(torch.rand(4), torch.rand(4, 3), torch.ones(4, dtype=torch.int64), torch.ones(5, 5))

@@ -379,3 +379,66 @@ def test_training_loop_contract(packed, absgrad):
     rc, ra, info = render(pruned)
     rc.mean().backward()
     assert pruned["means"].grad.shape == pruned["means"].shape and bool(torch.isfinite(rc).all())
+
+
+def test_selective_adam_matches_the_formula():
+    """gsplat.optimizers.SelectiveAdam (reference optimizers/selective_adam.py + AdamCUDA.cu:13-52): visible rows
+    follow m, v, p -= lr m / (sqrt(v) + eps); invisible rows keep parameter and moments, for [N], [N,3], [N,K,3]."""
+    from gsplat.optimizers import SelectiveAdam
+
+    g = torch.Generator().manual_seed(9)
+    N = 1000
+    vis = torch.rand(N, generator=g) > 0.4
+    for shape, lr in (((N,), 1e-2), ((N, 3), 1e-3), ((N, 16, 3), 2.5e-3)):
+        p0 = torch.randn(shape, generator=g)
+        param = p0.clone().to(DEV).requires_grad_(True)
+        opt = SelectiveAdam([{"params": [param], "lr": lr}], eps=1e-15, betas=(0.9, 0.999))
+        m, v, ref = torch.zeros(shape), torch.zeros(shape), p0.clone()
+        sel = vis.reshape((N,) + (1,) * (len(shape) - 1)).expand(shape)
+        for _ in range(3):
+            grad = torch.randn(shape, generator=g)
+            param.grad = grad.to(DEV)
+            opt.step(visibility=vis.to(DEV))
+            m_new, v_new = 0.9 * m + 0.1 * grad, 0.999 * v + 0.001 * grad * grad
+            m, v = torch.where(sel, m_new, m), torch.where(sel, v_new, v)
+            ref = torch.where(sel, ref - lr * m / (v.sqrt() + 1e-15), ref)
+        torch.testing.assert_close(param.detach().cpu(), ref, rtol=1e-5, atol=1e-6)
+        st = opt.state[param]
+        torch.testing.assert_close(st["exp_avg"].cpu(), m, rtol=1e-5, atol=1e-7)
+        torch.testing.assert_close(st["exp_avg_sq"].cpu(), v, rtol=1e-5, atol=1e-9)
+        assert torch.equal(param.detach().cpu()[~vis], p0[~vis])
+
+
+def test_compute_relocation_matches_equation_9():
+    """gsplat.relocation.compute_relocation (reference relocation.py:10-50, RelocationCUDA.cu:13-45) against a
+    float64 restatement of eq. 9; ratios beyond the table are clamped in place as the reference does."""
+    import math
+
+    from gsplat.relocation import compute_relocation
+
+    g = torch.Generator().manual_seed(11)
+    N, n_max = 4096, 51
+    binoms = torch.zeros(n_max, n_max)
+    for n in range(n_max):
+        for k in range(n + 1):
+            binoms[n, k] = math.comb(n, k)
+    opac = torch.rand(N, generator=g) * 0.98 + 0.01
+    scales = torch.rand(N, 3, generator=g) * 0.1
+    ratios = torch.randint(0, 60, (N,), generator=g)
+    r_dev = ratios.to(DEV)
+    new_o, new_s = compute_relocation(opac.to(DEV), scales.to(DEV), r_dev, binoms.to(DEV))
+    assert int(r_dev.min()) >= 1 and int(r_dev.max()) <= n_max
+    n = ratios.clamp(1, n_max).double()
+    o = opac.double()
+    ref_o = 1.0 - (1.0 - o) ** (1.0 / n)
+    denom = torch.zeros(N, dtype=torch.float64)
+    B = binoms.double()
+    for i in range(1, n_max + 1):
+        for k in range(i):
+            term = B[i - 1, k] * ((-1.0) ** k / math.sqrt(k + 1)) * ref_o ** (k + 1)
+            denom += torch.where(n >= i, term, torch.zeros_like(term))
+    ref_s = (o / denom)[:, None] * scales.double()
+    # float32 cancellation in 1 - (1 - o)^(1/n) for small o and large n costs ~1e-4 relative (emulated on the CPU)
+    torch.testing.assert_close(new_o.cpu().double(), ref_o, rtol=2e-3, atol=1e-7)
+    torch.testing.assert_close(new_s.cpu().double(), ref_s, rtol=2e-3, atol=1e-8)
+    assert torch.isfinite(new_s).all()
