@@ -82,6 +82,31 @@ histogram_kernel(int64_t n, const int64_t *__restrict__ n_dev, const KeyT *__res
     }
 }
 
+// Lanes of the warp holding the same digit (dead lanes, digit kBins, match only each other).
+// GSB_SORT_MATCH=1: one vote per digit bit, intersected (ALU/vote pipe only); 0: one match.any per item.
+#ifndef GSB_SORT_MATCH
+#define GSB_SORT_MATCH 1
+#endif
+__device__ __forceinline__ uint32_t match_digit(int digit, bool live, int bits) {
+#if GSB_SORT_MATCH
+    uint32_t peers = __ballot_sync(0xffffffffu, live);
+    if (!live) peers = ~peers;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        if (b < bits) {  // warp-uniform
+            const bool one = (digit >> b) & 1;
+            const uint32_t with_one = __ballot_sync(0xffffffffu, one);
+            peers &= one ? with_one : ~with_one;
+        }
+    }
+    return peers;
+#else
+    (void)live;
+    (void)bits;
+    return __match_any_sync(0xffffffffu, digit);
+#endif
+}
+
 template <typename KeyT>
 __global__ void __launch_bounds__(kThreads, sizeof(KeyT) == 4 ? GSB_SORT_MIN_BLOCKS : 2)
 onesweep_kernel(int64_t n, const int64_t *__restrict__ n_dev, const KeyT *__restrict__ keys_in,
@@ -127,7 +152,7 @@ onesweep_kernel(int64_t n, const int64_t *__restrict__ n_dev, const KeyT *__rest
     for (int i = 0; i < kItems; ++i) {
         const bool live = chunk + i * 32 + lane < count;
         // dead slots take a digit of their own (kBins: never equal to a live digit) so they match only each other
-        peers[i] = __match_any_sync(0xffffffffu, live ? digit_of(key[i], shift, mask) : kBins);
+        peers[i] = match_digit(live ? digit_of(key[i], shift, mask) : kBins, live, bits);
     }
 #pragma unroll
     for (int i = 0; i < kItems; ++i) {

@@ -17,7 +17,7 @@
 //     forward kernel;
 //   * two-phase reduction without a cross-lane reduction tree. Phase 1 (lane = pixel, sequential over
 //     the warp's splats because of the transmittance recurrence) only produces two scalars per
-//     (pixel, splat): w1 = d loss / d sigma and w2 = alpha T, parked in a per-warp shared table.
+//     (pixel, splat): w1 = -d loss / d sigma and w2 = alpha T, parked in a per-warp shared table.
 //     Phase 2 (every 16 splats; lane = splat x half block) walks the 32 pixels of the block and
 //     accumulates in registers the moments of w1 about the block centre (sum w1 {1, x, y, x^2, xy, y^2})
 //     and sum w2 v_out; the conic / mean / opacity gradients are closed forms of those moments.
@@ -45,17 +45,17 @@ struct BwdSmem {
                                     + sizeof(float) * kThreads * CS                     // s_col
                                     + sizeof(float2) * kWarps * kChunk * kChunkStride   // s_w
                                     + sizeof(float) * kWarps * (32 * DP + 4)            // s_vout
-                                    + sizeof(int) * (kWarps * kChunk + 2 * kWarps);     // s_cj, counters
+                                    + sizeof(int) * (2 * kWarps);                       // counters
 };
 
 // Second half of the backward pass for up to kChunk splats of ONE warp (8x4 pixel block):
 // lane (s = lane & 15, h = lane >> 4) owns splat s and sums over the 16 pixels of block rows 2h, 2h+1.
-// Inputs per (splat, pixel): w1 = d loss / d sigma, w2 = alpha * T (weight of the colour cotangent).
+// Inputs per (splat, pixel): w1 = -d loss / d sigma (sign folded into the epilogue), w2 = alpha * T (weight of the colour cotangent).
 // Geometry gradients come from the moments of w1 over the block, taken about the block centre:
 //   sum w1 dx = ux M0 - Mx, sum w1 dx^2 = ux^2 M0 - 2 ux Mx + Mxx, ...   (dx = ux - cx, ux = mu_x - centre_x)
 template <int D, bool ABS>
 __device__ __forceinline__ void reduce_chunk(int count, int lane, const float2 *s_w, const float *s_vout,
-                                             const int *s_cj, const float4 *s_P, const float4 *s_B,
+                                             int chunk_j, const float4 *s_P, const float4 *s_B,
                                              const int32_t *__restrict__ flatten_ids,
                                              float bcx, float bcy, const GradTargets &out) {
     constexpr int DP = BwdSmem<D>::DP;
@@ -68,7 +68,8 @@ __device__ __forceinline__ void reduce_chunk(int count, int lane, const float2 *
 #pragma unroll
     for (int k = 0; k < D; ++k) col[k] = 0.f;
     float abs_x = 0.f, abs_y = 0.f;
-    const int j = s_cj[s < count ? s : 0];
+    // lane n holds the staged slot of the chunk's n-th splat (slots past `count` repeat the first: masked below)
+    const int j = __shfl_sync(0xffffffffu, chunk_j, s < count ? s : 0);
     const float4 mu = s_P[j];  // (x, y, sorted index, -)
     float4 b4 = s_B[j];        // staged (pre-scaled) conic -> conic
     b4.x *= kUnscaleDiag;
@@ -121,12 +122,13 @@ __device__ __forceinline__ void reduce_chunk(int count, int lane, const float2 *
         const float Syy = fmaf(uy, fmaf(uy, M0, -2.f * My), Myy);
         const float Sxy = fmaf(ux, fmaf(uy, M0, -My), fmaf(-uy, Mx, Mxy));
         float v[6];
-        v[0] = b4.x * Sx + b4.y * Sy;
-        v[1] = b4.y * Sx + b4.z * Sy;
-        v[2] = 0.5f * Sxx;
-        v[3] = Sxy;
-        v[4] = 0.5f * Syy;
-        v[5] = -__fdividef(M0, b4.w);  // v_opacity = sum e^-sigma v_alpha = -sum w1 / opacity
+        // the moments are of -w1 (phase 1 stores -d loss / d sigma): the signs are folded in here
+        v[0] = -(b4.x * Sx + b4.y * Sy);
+        v[1] = -(b4.y * Sx + b4.z * Sy);
+        v[2] = -0.5f * Sxx;
+        v[3] = -Sxy;
+        v[4] = -0.5f * Syy;
+        v[5] = __fdividef(M0, b4.w);  // v_opacity = sum e^-sigma v_alpha = -sum w1 / opacity
         if (v[0] != 0.f) atomicAdd(out.v_means2d + 2 * g, v[0]);
         if (v[1] != 0.f) atomicAdd(out.v_means2d + 2 * g + 1, v[1]);
         if (v[2] != 0.f) atomicAdd(out.v_conics + 3 * g, v[2]);
@@ -162,8 +164,7 @@ rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
     float *s_col = reinterpret_cast<float *>(s_B + kThreads);
     float2 *s_w_all = reinterpret_cast<float2 *>(s_col + kThreads * CS);
     float *s_vout_all = reinterpret_cast<float *>(s_w_all + kWarps * kChunk * kChunkStride);
-    int *s_cj_all = reinterpret_cast<int *>(s_vout_all + kWarps * (32 * DP + 4));
-    int *s_wcnt = s_cj_all + kWarps * kChunk;
+    int *s_wcnt = reinterpret_cast<int *>(s_vout_all + kWarps * (32 * DP + 4));
     int *s_red = s_wcnt + kWarps;
 
     const TileGeom tg = tile_geometry(n_isects, W, H, tw, th, C, offsets);
@@ -172,7 +173,6 @@ rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
     const float pxf = (float)tg.px + 0.5f, pyf = (float)tg.py + 0.5f;
     float2 *s_w = s_w_all + warp * kChunk * kChunkStride;
     float *s_vout = s_vout_all + warp * (32 * DP + 4);
-    int *s_cj = s_cj_all + warp * kChunk;
     // centre of this warp's 8x4 block, in pixel-centre coordinates
     const float bcx = (float)(tg.tile_x * kTile + (warp & 1) * 8) + 4.0f;
     const float bcy = (float)(tg.tile_y * kTile + (warp >> 1) * 4) + 2.0f;
@@ -181,20 +181,20 @@ rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
     const float T_final = tg.inside ? 1.0f - render_alphas[tg.pix_id] : 1.0f;
     float T = T_final;
     const int bin_final = tg.inside ? last_ids[tg.pix_id] : -1;
-    float S[D], v_out[D];
+    float v_out[D];
     float v_out_a = 0.f, bg_dot = 0.f;
 #pragma unroll
-    for (int k = 0; k < D; ++k) {
-        S[k] = 0.f;
-        v_out[k] = tg.inside ? v_render_colors[tg.pix_id * D + k] : 0.f;
-    }
+    for (int k = 0; k < D; ++k) v_out[k] = tg.inside ? v_render_colors[tg.pix_id * D + k] : 0.f;
     if (tg.inside) v_out_a = v_render_alphas[tg.pix_id];
     if (backgrounds != nullptr) {
 #pragma unroll
         for (int k = 0; k < D; ++k) bg_dot = fmaf(backgrounds[(size_t)tg.cam * D + k], v_out[k], bg_dot);
     }
     // d(out)/d(alpha_i) carries T_final/(1-alpha_i) * (v_alpha_out - bg . v_out)
-    const float tail = T_final * (v_out_a - bg_dot);
+    // Everything behind splat i reaches v_alpha_i only through the scalar
+    //   u_i = T_final (v_alpha_out - bg . v_out) - sum_{j behind i} w2_j (c_j . v_out):
+    // v_alpha_i = (c_i . v_out) T_i + u_i / (1 - alpha_i). One recurrence instead of one per channel.
+    float u = T_final * (v_out_a - bg_dot);
     {   // colour cotangents of the block's pixels, for the splat-parallel pass
         float *dst = s_vout + lane * DP + (lane >> 4) * 4;
 #pragma unroll
@@ -231,7 +231,8 @@ rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
         }
         __syncthreads();
 
-        int n_chunk = 0;
+        int n_chunk = 0, chunk_j = 0;
+        float2 *w_slot = s_w + lane;  // this lane's entry of the chunk row being filled
         for (int c0 = 0; c0 < total; c0 += 32) {
             const int jl = c0 + lane;
             // this warp's splats of the chunk: may touch its 8x4 block and not behind every pixel's last id
@@ -253,31 +254,30 @@ rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
                 const bool hit = (__float_as_int(p4.z) <= bin_final) && !(ex > 0.f) && !(alpha < kAlphaMin);
                 if (!__any_sync(0xffffffffu, hit)) continue;
 
-                float w1 = 0.f, w2 = 0.f;
-                if (hit) {
-                    const float ra = __fdividef(1.0f, 1.0f - alpha);
-                    T *= ra;
-                    w2 = alpha * T;
-                    float v_alpha = 0.f;
+                // branch-free over the lanes: a lane without a hit runs the same arithmetic with alpha = 0
+                // (1 / (1 - 0) and T * 1 are exact, w2 = 0 leaves u alone) and a zero weight on v_alpha
+                const float alpha_h = hit ? alpha : 0.f;
+                const float ov_h = ov <= kAlphaMax ? alpha_h : 0.f;  // = ov on a hit; no gradient through the clamp
+                const float ra = __fdividef(1.0f, 1.0f - alpha_h);
+                T *= ra;
+                const float w2 = alpha_h * T;
+                float cv = 0.f;
 #pragma unroll
-                    for (int k = 0; k < D; ++k) {
-                        const float c = s_col[j * CS + k];
-                        v_alpha = fmaf(c * T - S[k] * ra, v_out[k], v_alpha);
-                        S[k] = fmaf(c, w2, S[k]);
-                    }
-                    v_alpha = fmaf(tail, ra, v_alpha);
-                    if (ov <= kAlphaMax) w1 = -ov * v_alpha;  // no gradient through the alpha clamp
-                }
-                s_w[n_chunk * kChunkStride + lane] = make_float2(w1, w2);
-                if (lane == 0) s_cj[n_chunk] = j;
+                for (int k = 0; k < D; ++k) cv = fmaf(s_col[j * CS + k], v_out[k], cv);
+                const float w1 = ov_h * fmaf(cv, T, u * ra);  // = -d loss / d sigma: reduce_chunk flips the sign once
+                u = fmaf(-cv, w2, u);
+                *w_slot = make_float2(w1, w2);
+                w_slot += kChunkStride;
+                chunk_j = lane == n_chunk ? j : chunk_j;  // the chunk's splat slots live in lanes 0..15, not in memory
                 if (++n_chunk == kChunk) {
-                    reduce_chunk<D, ABS>(n_chunk, lane, s_w, s_vout, s_cj, s_P, s_B, flatten_ids, bcx, bcy, out);
+                    reduce_chunk<D, ABS>(n_chunk, lane, s_w, s_vout, chunk_j, s_P, s_B, flatten_ids, bcx, bcy, out);
                     n_chunk = 0;
+                    w_slot = s_w + lane;
                 }
             }
         }
         if (n_chunk > 0)
-            reduce_chunk<D, ABS>(n_chunk, lane, s_w, s_vout, s_cj, s_P, s_B, flatten_ids, bcx, bcy, out);
+            reduce_chunk<D, ABS>(n_chunk, lane, s_w, s_vout, chunk_j, s_P, s_B, flatten_ids, bcx, bcy, out);
     }
 }
 
