@@ -20,6 +20,6 @@ void gsb_set_error(const char *fmt, ...) {
 void gsb_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 extern "C" const char *gsb_last_error(void) { return g_error; }
-extern "C" int gsb_abi_version(void) { return 1; }
+extern "C" int gsb_abi_version(void) { return 2; }
 extern "C" int64_t gsb_launch_count(void) { return (int64_t)g_launches.load(std::memory_order_relaxed); }
 extern "C" void gsb_reset_launch_count(void) { g_launches.store(0, std::memory_order_relaxed); }

@@ -153,8 +153,8 @@ rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
                      const uint8_t *__restrict__ masks, int W, int H, int tw, int th,
                      const int32_t *__restrict__ offsets, const int32_t *__restrict__ flatten_ids,
                      const float *__restrict__ render_alphas, const int32_t *__restrict__ last_ids,
-                     const float *__restrict__ v_render_colors, const float *__restrict__ v_render_alphas,
-                     GradTargets out) {
+                     const uint8_t *__restrict__ block_masks, const float *__restrict__ v_render_colors,
+                     const float *__restrict__ v_render_alphas, GradTargets out) {
     constexpr int DP = BwdSmem<D>::DP;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int CS = BwdSmem<D>::CS;
@@ -215,10 +215,21 @@ rasterize_bwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
         int g = 0;
         float4 A, B;
         if (idx >= tg.range_start) {
-            g = flatten_ids[idx];
-            A = __ldg(recA + g);
-            B = __ldg(recB + g);
-            mask = splat_block_mask(A, B, tg.tile_x * kTile, tg.tile_y * kTile);
+            if (block_masks != nullptr) {
+                // culling result of the forward pass (every intersection up to the tile's last contributor was
+                // staged there): culled intersections cost one byte, no record gathers and no arithmetic
+                mask = block_masks[idx];
+                if (mask != 0u) {
+                    g = flatten_ids[idx];
+                    A = __ldg(recA + g);
+                    B = __ldg(recB + g);
+                }
+            } else {
+                g = flatten_ids[idx];
+                A = __ldg(recA + g);
+                B = __ldg(recB + g);
+                mask = splat_block_mask(A, B, tg.tile_x * kTile, tg.tile_y * kTile);
+            }
         }
         int total;
         const int slot = stage_slot(mask != 0u, s_wcnt, total);  // syncs: previous batch fully consumed
@@ -285,8 +296,8 @@ template <int D, bool ABS>
 int launch_bwd(int C, int64_t n_isects, const float *recA, const float *recB, const float *colors,
                const float *backgrounds, const uint8_t *masks, int W, int H, int tw, int th,
                const int32_t *offsets, const int32_t *flatten_ids, const float *render_alphas,
-               const int32_t *last_ids, const float *v_render_colors, const float *v_render_alphas,
-               GradTargets out, cudaStream_t stream) {
+               const int32_t *last_ids, const uint8_t *block_masks, const float *v_render_colors,
+               const float *v_render_alphas, GradTargets out, cudaStream_t stream) {
     constexpr size_t smem = BwdSmem<D>::bytes;
     auto kernel = rasterize_bwd_kernel<D, ABS>;
     static bool configured = false;  // one instantiation per (D, ABS)
@@ -301,7 +312,7 @@ int launch_bwd(int C, int64_t n_isects, const float *recA, const float *recB, co
     dim3 grid(tw, th, C);
     kernel<<<grid, kThreads, smem, stream>>>(C, n_isects, reinterpret_cast<const float4 *>(recA),
                                              reinterpret_cast<const float4 *>(recB), colors, backgrounds, masks, W,
-                                             H, tw, th, offsets, flatten_ids, render_alphas, last_ids,
+                                             H, tw, th, offsets, flatten_ids, render_alphas, last_ids, block_masks,
                                              v_render_colors, v_render_alphas, out);
     return gsb_check_launch("rasterize_bwd");
 }
@@ -310,14 +321,15 @@ template <int D>
 int dispatch_abs(bool abs, int C, int64_t n_isects, const float *recA, const float *recB, const float *colors,
                  const float *backgrounds, const uint8_t *masks, int W, int H, int tw, int th,
                  const int32_t *offsets, const int32_t *flatten_ids, const float *render_alphas,
-                 const int32_t *last_ids, const float *v_render_colors, const float *v_render_alphas,
-                 GradTargets out, cudaStream_t stream) {
+                 const int32_t *last_ids, const uint8_t *block_masks, const float *v_render_colors,
+                 const float *v_render_alphas, GradTargets out, cudaStream_t stream) {
     if (abs)
         return launch_bwd<D, true>(C, n_isects, recA, recB, colors, backgrounds, masks, W, H, tw, th, offsets,
-                                   flatten_ids, render_alphas, last_ids, v_render_colors, v_render_alphas, out,
-                                   stream);
+                                   flatten_ids, render_alphas, last_ids, block_masks, v_render_colors,
+                                   v_render_alphas, out, stream);
     return launch_bwd<D, false>(C, n_isects, recA, recB, colors, backgrounds, masks, W, H, tw, th, offsets,
-                                flatten_ids, render_alphas, last_ids, v_render_colors, v_render_alphas, out, stream);
+                                flatten_ids, render_alphas, last_ids, block_masks, v_render_colors, v_render_alphas,
+                                out, stream);
 }
 
 }  // namespace raster
@@ -326,8 +338,8 @@ extern "C" int gsb_rasterize_bwd(int C, int64_t n_isects, int D, const float *re
                                  const float *colors, const float *backgrounds, const uint8_t *masks, int width,
                                  int height, int tile_size, int tile_width, int tile_height,
                                  const int32_t *isect_offsets, const int32_t *flatten_ids,
-                                 const float *render_alphas, const int32_t *last_ids, const float *v_render_colors,
-                                 const float *v_render_alphas, float *v_means2d_abs, float *v_means2d,
+                                 const float *render_alphas, const int32_t *last_ids, const uint8_t *block_masks,
+                                 const float *v_render_colors, const float *v_render_alphas, float *v_means2d_abs, float *v_means2d,
                                  float *v_conics, float *v_colors, float *v_opacities, cudaStream_t stream) {
     GSB_REQUIRE(C >= 0 && n_isects >= 0 && width > 0 && height > 0, "bad sizes");
     GSB_REQUIRE(n_isects < ((int64_t)1 << 31), "more than 2^31-1 intersections");
@@ -343,8 +355,8 @@ extern "C" int gsb_rasterize_bwd(int C, int64_t n_isects, int D, const float *re
     case DD:                                                                                                      \
         return raster::dispatch_abs<DD>(abs, C, n_isects, recA, recB, colors, backgrounds, masks, width,     \
                                              height, tile_width, tile_height, isect_offsets, flatten_ids,         \
-                                             render_alphas, last_ids, v_render_colors, v_render_alphas, out,      \
-                                             stream);
+                                             render_alphas, last_ids, block_masks, v_render_colors,               \
+                                             v_render_alphas, out, stream);
     switch (D) {
         GSB_BWD_CASE(1)
         GSB_BWD_CASE(2)

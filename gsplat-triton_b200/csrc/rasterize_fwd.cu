@@ -46,7 +46,8 @@ rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
                      const uint8_t *__restrict__ masks, int W, int H, int tw, int th,
                      const int32_t *__restrict__ offsets, const int32_t *__restrict__ flatten_ids,
                      float *__restrict__ out_colors, float *__restrict__ out_alphas,
-                     int32_t *__restrict__ last_ids, const int64_t *__restrict__ n_isects_dev) {
+                     int32_t *__restrict__ last_ids, const int64_t *__restrict__ n_isects_dev,
+                     uint8_t *__restrict__ block_masks) {
     // speculatively sized intersection buffers: n_isects is their capacity, the count lives on the device
     if (n_isects_dev != nullptr) n_isects = min(n_isects, (int64_t)*n_isects_dev);
     // staged batch: three float4 arrays with the same 16-byte stride, so one address computation serves all
@@ -89,6 +90,8 @@ rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
                 A = __ldg(recA + g);
                 B = __ldg(recB + g);
                 mask = splat_block_mask(A, B, tg.tile_x * kTile, tg.tile_y * kTile);
+                // the backward pass re-stages the same intersections: hand it the culling result (one byte each)
+                if (block_masks != nullptr) block_masks[idx] = (uint8_t)mask;
             }
             int total;
             const int slot = stage_slot(mask != 0u, s_wcnt, total);
@@ -167,11 +170,12 @@ template <int D>
 int launch_fwd(int C, int64_t n_isects, const float *recA, const float *recB, const float *colors,
                const float *backgrounds, const uint8_t *masks, int W, int H, int tw, int th,
                const int32_t *offsets, const int32_t *flatten_ids, float *out_colors, float *out_alphas,
-               int32_t *last_ids, const int64_t *n_isects_dev, cudaStream_t stream) {
+               int32_t *last_ids, const int64_t *n_isects_dev, uint8_t *block_masks, cudaStream_t stream) {
     dim3 grid(tw, th, C);
     rasterize_fwd_kernel<D><<<grid, kThreads, 0, stream>>>(
         C, n_isects, reinterpret_cast<const float4 *>(recA), reinterpret_cast<const float4 *>(recB), colors,
-        backgrounds, masks, W, H, tw, th, offsets, flatten_ids, out_colors, out_alphas, last_ids, n_isects_dev);
+        backgrounds, masks, W, H, tw, th, offsets, flatten_ids, out_colors, out_alphas, last_ids, n_isects_dev,
+        block_masks);
     return gsb_check_launch("rasterize_fwd");
 }
 
@@ -193,7 +197,7 @@ extern "C" int gsb_rasterize_fwd(int C, int64_t n_isects, int D, const float *re
                                  float *render_alphas, int32_t *last_ids, cudaStream_t stream) {
     return gsb_rasterize_fwd_cap(C, n_isects, nullptr, D, recA, recB, colors, backgrounds, masks, width, height,
                                  tile_size, tile_width, tile_height, isect_offsets, flatten_ids, render_colors,
-                                 render_alphas, last_ids, stream);
+                                 render_alphas, last_ids, nullptr, stream);
 }
 
 extern "C" int gsb_rasterize_fwd_cap(int C, int64_t n_isects, const int64_t *n_isects_dev, int D, const float *recA,
@@ -201,7 +205,7 @@ extern "C" int gsb_rasterize_fwd_cap(int C, int64_t n_isects, const int64_t *n_i
                                      const uint8_t *masks, int width, int height, int tile_size, int tile_width,
                                      int tile_height, const int32_t *isect_offsets, const int32_t *flatten_ids,
                                      float *render_colors, float *render_alphas, int32_t *last_ids,
-                                     cudaStream_t stream) {
+                                     uint8_t *block_masks, cudaStream_t stream) {
     GSB_REQUIRE(C >= 0 && n_isects >= 0 && width > 0 && height > 0, "bad sizes");
     GSB_REQUIRE(n_isects < ((int64_t)1 << 31), "more than 2^31-1 intersections");
     if (tile_size != raster::kTile) {
@@ -215,7 +219,7 @@ extern "C" int gsb_rasterize_fwd_cap(int C, int64_t n_isects, const int64_t *n_i
     case DD:                                                                                                      \
         return raster::launch_fwd<DD>(C, n_isects, recA, recB, colors, backgrounds, masks, width, height,         \
                                       tile_width, tile_height, isect_offsets, flatten_ids, render_colors,         \
-                                      render_alphas, last_ids, n_isects_dev, stream);
+                                      render_alphas, last_ids, n_isects_dev, block_masks, stream);
     switch (D) {
         GSB_FWD_CASE(1)
         GSB_FWD_CASE(2)
@@ -243,6 +247,6 @@ extern "C" int gsb_rasterize_count(int C, int64_t n_isects, const float *recA, c
     raster::rasterize_fwd_kernel<1, true><<<grid, raster::kThreads, 0, stream>>>(
         C, n_isects, reinterpret_cast<const float4 *>(recA), reinterpret_cast<const float4 *>(recB), ones, nullptr,
         nullptr, width, height, tile_width, tile_height, isect_offsets, flatten_ids, counts, render_alphas, last_ids,
-        nullptr);
+        nullptr, nullptr);
     return gsb_check_launch("rasterize_count");
 }

@@ -760,12 +760,17 @@ class _RasterizeToPixels(torch.autograd.Function):
         n_dev = ptr(pending.n_dev) if (pending is not None and pending.n is None) else None
         if pending is not None and pending.n is not None:
             n_isects = min(n_isects, pending.n)
+        # per-intersection culling result (which 8x4 blocks of the tile the Gaussian reaches), kept for the backward
+        # pass; only needed when a gradient will be asked for
+        needs_grad = any(ctx.needs_input_grad[:5])
+        block_masks = torch.empty((max(flatten_ids.numel(), 1),), dtype=torch.uint8, device=dev) if needs_grad else None
         lib.gsb_rasterize_fwd_cap(C, n_isects, n_dev, D, ptr(rec[0]), ptr(rec[1]), ptr(colors), ptr(backgrounds),
                                   ptr(m8), width, height, tile_size, tile_width, tile_height, ptr(isect_offsets),
-                                  ptr(flatten_ids), ptr(render_colors), ptr(render_alphas), ptr(last_ids), st)
+                                  ptr(flatten_ids), ptr(render_colors), ptr(render_alphas), ptr(last_ids),
+                                  ptr(block_masks), st)
         ctx.pending = pending
         ctx.save_for_backward(means2d, rec, colors, backgrounds, m8, isect_offsets, flatten_ids, render_alphas,
-                              last_ids)
+                              last_ids, block_masks)
         ctx.width, ctx.height, ctx.tile_size, ctx.absgrad = width, height, tile_size, absgrad
         ctx.shapes = (conics.shape, opacities.shape)
         return render_colors, render_alphas
@@ -773,7 +778,7 @@ class _RasterizeToPixels(torch.autograd.Function):
     @staticmethod
     def backward(ctx, v_render_colors, v_render_alphas):
         (means2d, rec, colors, backgrounds, m8, isect_offsets, flatten_ids, render_alphas,
-         last_ids) = ctx.saved_tensors
+         last_ids, block_masks) = ctx.saved_tensors
         C, tile_height, tile_width = isect_offsets.shape
         D = colors.shape[-1]
         dev = means2d.device
@@ -794,7 +799,7 @@ class _RasterizeToPixels(torch.autograd.Function):
         lib.gsb_rasterize_bwd(C, n_isects, D, ptr(rec[0]), ptr(rec[1]), ptr(colors), ptr(backgrounds),
                               ptr(m8), ctx.width, ctx.height, ctx.tile_size, tile_width, tile_height,
                               ptr(isect_offsets), ptr(flatten_ids), ptr(render_alphas), ptr(last_ids),
-                              ptr(v_render_colors), ptr(v_render_alphas), ptr(v_abs), ptr(v_means2d),
+                              ptr(block_masks), ptr(v_render_colors), ptr(v_render_alphas), ptr(v_abs), ptr(v_means2d),
                               ptr(v_conics), ptr(v_colors), ptr(v_opacities), stream_of(means2d))
         if ctx.absgrad:
             means2d.absgrad = v_abs

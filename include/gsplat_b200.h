@@ -195,12 +195,14 @@ int gsb_rasterize_fwd(int C, int64_t n_isects, int D, const float *recA, const f
                       int tile_width, int tile_height, const int32_t *isect_offsets, const int32_t *flatten_ids,
                       float *render_colors, float *render_alphas, int32_t *last_ids, cudaStream_t stream);
 /* same, for speculatively sized intersection buffers: n_isects = capacity of flatten_ids, the real count is
- * min(*n_isects_dev, n_isects) (NULL: n_isects is exact). See gsb_isect_emit_perm_cap. */
+ * min(*n_isects_dev, n_isects) (NULL: n_isects is exact). See gsb_isect_emit_perm_cap.
+ * block_masks uint8[n_isects] or NULL: receives, for every intersection the pass stages, which of the tile's eight
+ * 8x4 pixel blocks the Gaussian can reach (0 = culled); gsb_rasterize_bwd reuses it instead of recomputing. */
 int gsb_rasterize_fwd_cap(int C, int64_t n_isects, const int64_t *n_isects_dev, int D, const float *recA,
                           const float *recB, const float *colors, const float *backgrounds, const uint8_t *masks,
                           int width, int height, int tile_size, int tile_width, int tile_height,
                           const int32_t *isect_offsets, const int32_t *flatten_ids, float *render_colors,
-                          float *render_alphas, int32_t *last_ids, cudaStream_t stream);
+                          float *render_alphas, int32_t *last_ids, uint8_t *block_masks, cudaStream_t stream);
 /* diagnostics: counts[C,H,W] = number of Gaussians composited into each pixel (ones: float[P] of 1.0f);
  * same traversal as gsb_rasterize_fwd with D = 1. Used by bench.py for the useful-work roofline. */
 int gsb_rasterize_count(int C, int64_t n_isects, const float *recA, const float *recB, const float *ones, int width,
@@ -208,13 +210,14 @@ int gsb_rasterize_count(int C, int64_t n_isects, const float *recA, const float 
                         const int32_t *flatten_ids, float *counts, float *render_alphas, int32_t *last_ids,
                         cudaStream_t stream);
 /* v_means2d[P,2], v_conics[P,3], v_colors[P,D], v_opacities[P] must be ZERO-filled by the caller
- * (the kernel accumulates with atomics); v_means2d_abs[P,2] (zero-filled) or NULL. */
+ * (the kernel accumulates with atomics); v_means2d_abs[P,2] (zero-filled) or NULL.
+ * block_masks: what gsb_rasterize_fwd_cap wrote for the same inputs, or NULL (recomputed). */
 int gsb_rasterize_bwd(int C, int64_t n_isects, int D, const float *recA, const float *recB, const float *colors,
                       const float *backgrounds, const uint8_t *masks, int width, int height, int tile_size,
                       int tile_width, int tile_height, const int32_t *isect_offsets, const int32_t *flatten_ids,
-                      const float *render_alphas, const int32_t *last_ids, const float *v_render_colors,
-                      const float *v_render_alphas, float *v_means2d_abs, float *v_means2d, float *v_conics,
-                      float *v_colors, float *v_opacities, cudaStream_t stream);
+                      const float *render_alphas, const int32_t *last_ids, const uint8_t *block_masks,
+                      const float *v_render_colors, const float *v_render_alphas, float *v_means2d_abs,
+                      float *v_means2d, float *v_conics, float *v_colors, float *v_opacities, cudaStream_t stream);
 
 /* ---- rasterize_to_indices_in_range (cuda/_wrapper.py:577-648, RasterizeToIndices3DGS.cu:14-170) ---------------
  * the (Gaussian, pixel) pairs the compositor blends for sorted-intersection batches [range_start, range_end) of
