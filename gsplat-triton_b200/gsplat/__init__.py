@@ -32,6 +32,10 @@ def __getattr__(name):
         from .b200_impl import rasterize_to_indices_in_range
 
         return rasterize_to_indices_in_range
+    if name == "accumulate":
+        from .b200_impl import accumulate
+
+        return accumulate
     if name == "SelectiveAdam":
         from .optimizers import SelectiveAdam
 

@@ -311,3 +311,40 @@ def test_rasterize_to_indices_in_range_matches_oracle(golden):
         assert torch.equal(gs.cpu()[keep], o_gs[o_keep]) and torch.equal(key[keep], o_key[o_keep]), (lo, hi)
     empty = rasterize_to_indices_in_range(5000, 5001, T0.to(dev), *args, *tail)
     assert all(t.numel() == 0 for t in empty)
+
+
+def test_torch_compositor_over_our_index_kernel_equals_the_fused_compositor():
+    """The reference's pure-PyTorch compositor (_torch_impl._rasterize_to_pixels :522-617 = batches of
+    rasterize_to_indices_in_range + accumulate, autograd gradients), restated without nerfacc on top of OUR index
+    kernel, against the fused b200 compositor: several batches per tile, one and many batches per iteration."""
+    from gsplat.b200_impl import rasterize_to_pixels, rasterize_to_pixels_torch
+
+    C, N, W, H, ts, D = 2, 2500, 70, 50, 16, 3
+    means2d, conics, colors, opac, radii, depths = _random_splats(C, N, W, H, D, seed=5)
+    tw, th = -(-W // ts), -(-H // ts)
+    _, ids, flat = O.isect_tiles(means2d, radii, depths, ts, tw, th)
+    offs = O.isect_offset_encode(ids, C, tw, th)
+    per_tile = torch.diff(torch.cat([offs.flatten(), torch.tensor([flat.numel()])]))
+    assert int(per_tile.max()) > 2 * ts * ts  # more than two batches somewhere
+    backgrounds = torch.rand(C, D)
+    gw = torch.Generator().manual_seed(7)
+    w_c, w_a = torch.randn(C, H, W, D, generator=gw).to(DEV), torch.randn(C, H, W, 1, generator=gw).to(DEV)
+
+    # The reference's loop re-arms the stop rule T (1 - alpha) <= 1e-4 with every call of the index op, so it equals
+    # the fused compositor when one iteration covers the whole tile (default: 100 batches) or when no pixel stops
+    # (faint scene, any batching) -- tests/test_oracle.py::test_torch_compositor_loop_batches shows the same on the CPU.
+    for scale, batch_per_iter in ((1.0, 100), (0.02, 1)):
+        opac_s = opac * scale
+
+        def run(fn, **kw):
+            p = [t.clone().to(DEV).requires_grad_(True) for t in (means2d, conics, colors, opac_s)]
+            b = backgrounds.clone().to(DEV).requires_grad_(True)
+            rc, ra = fn(p[0], p[1], p[2], p[3], W, H, ts, offs.to(DEV), flat.to(DEV), backgrounds=b, **kw)
+            return rc, ra, torch.autograd.grad((rc * w_c).sum() + (ra * w_a).sum(), p + [b])
+
+        rc, ra, grads = run(rasterize_to_pixels)
+        t_rc, t_ra, t_grads = run(rasterize_to_pixels_torch, batch_per_iter=batch_per_iter)
+        _close_frac(t_rc, rc, rtol=1e-4, atol=1e-5, max_bad=3e-3)
+        _close_frac(t_ra, ra, rtol=1e-4, atol=1e-5, max_bad=3e-3)
+        for a, b in zip(t_grads, grads):
+            _close_frac(a, b, rtol=1e-3, atol=1e-5 * float(b.abs().max()) + 1e-6, max_bad=5e-3)
