@@ -145,12 +145,14 @@ rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
                             T = next_T;
                         }
                     }
-                    if (__all_sync(0xffffffffu, T < 0.f)) {
-                        warp_done = true;
-                        break;
-                    }
                 }
-                if (warp_done) break;
+                // all 32 pixels finished? Checked once per 32 staged splats (about every 4th of this warp's pairs), not
+                // per pair: a finished pixel ignores further splats (next_T < 0 keeps T), so the few extra pairs are
+                // harmless and cost less than three instructions on every pair.
+                if (__all_sync(0xffffffffu, T < 0.f)) {
+                    warp_done = true;
+                    break;
+                }
             }
         }
     }
