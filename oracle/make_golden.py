@@ -13,6 +13,8 @@ need (i) the third-party package `nerfacc` (absent, un-vendored) and (ii) the CU
 reference's compositor math (`accumulate`, `_rasterize_to_pixels`) executes unmodified on top
 of them. The outputs are stored as the golden vectors the `-m "not gpu"` tests check the oracle
 against and the `-m gpu` tests check the CUDA kernels against.
+`case_e2e` additionally runs the reference's end-to-end pure-torch pipeline `gsplat.rendering._rasterization`
+(rendering.py:601-760) with its backend-dispatched calls pointed at the same `_torch_impl` functions.
 """
 import os
 import sys
@@ -243,7 +245,70 @@ def case_raster(T):
         depths=depths, offsets=offs, flatten_ids=flat, isect_ids=ids, width=Wd, height=Ht, tile_size=ts,
         render_colors=rc, render_alphas=ra, w_colors=w_c, w_alphas=w_a, v_means2d=grads[0], v_conics=grads[1],
         v_colors=grads[2], v_opacities=grads[3], v_backgrounds=grads[4]))
-    print("raster: n_isects=%d mean alpha=%.3f" % (flat.numel(), float(ra.mean())))
+    print("raster: n_isects=%d mean alpha=%.3f" % (flat.numel(), float(ra.detach().mean())))
+
+
+def case_e2e(T):
+    """The reference's own end-to-end pure-torch pipeline, `gsplat.rendering._rasterization` (rendering.py:601-760),
+    on a reduced garden scene, fwd + autograd gradients, for SH colours (degree 3, RGB+ED) and plain colours
+    (antialiased, background). Its three backend-dispatched calls are pointed at the reference's own `_torch_impl`
+    versions (`_isect_tiles`, `_isect_offset_encode`, `_spherical_harmonics`), the compositor runs on the nerfacc /
+    index-op restatements above. The oracle's `rasterization()` must reproduce it."""
+    import gsplat.cuda._wrapper as W_
+    import gsplat.rendering as R
+
+    _install_nerfacc_stub()
+    W_.rasterize_to_indices_in_range = _indices_in_range_cpu
+
+    def sh(degree, dirs, coeffs, masks=None):
+        out = T._spherical_harmonics(degree, dirs, coeffs)
+        return out if masks is None else torch.where(masks[..., None], out, torch.zeros_like(out))
+
+    R.isect_tiles = lambda m, r, d, ts, tw, th, **kw: T._isect_tiles(m, r, d, ts, tw, th)
+    R.isect_offset_encode = T._isect_offset_encode
+    R.spherical_harmonics = sh
+
+    data = np.load(os.path.join(GOLD, "test_garden.npz"))
+    means = torch.from_numpy(data["means3d"]).float()
+    rgb = torch.from_numpy(data["colors"] / 255.0).float()
+    keep = ((means >= -2) & (means <= 2)).all(dim=-1)
+    means, rgb = means[keep][::40].contiguous(), rgb[keep][::40].contiguous()
+    g = torch.Generator().manual_seed(7)
+    N = means.shape[0]
+    scales = torch.rand(N, 3, generator=g) * 0.06 + 0.004
+    quats = torch.nn.functional.normalize(torch.randn(N, 4, generator=g), dim=-1)
+    opacities = torch.rand(N, generator=g)
+    shs = torch.randn(N, 16, 3, generator=g) * 0.3
+    shs[:, 0] += 0.5
+    viewmats = torch.from_numpy(data["viewmats"]).float()[:2].contiguous()
+    Ks = torch.from_numpy(data["Ks"]).float()[:2].clone()
+    W, H = int(data["width"]) // 4, int(data["height"]) // 4
+    Ks[:, :2, :] *= 0.25
+    backgrounds = torch.rand(2, 3, generator=g)
+    out = dict(means=means, quats=quats, scales=scales, opacities=opacities, rgb=rgb, shs=shs, viewmats=viewmats,
+               Ks=Ks, width=W, height=H, backgrounds=backgrounds)
+    cases = {
+        "sh": dict(colors=shs, kw=dict(sh_degree=3, render_mode="RGB+ED")),
+        "rgb": dict(colors=rgb, kw=dict(rasterize_mode="antialiased", backgrounds=backgrounds)),
+    }
+    for name, case in cases.items():
+        leaves = [t.clone().requires_grad_(True) for t in (means, quats, scales, opacities, case["colors"])]
+        rc, ra, _ = R._rasterization(*leaves, viewmats, Ks, W, H, **case["kw"])
+        w_c, w_a = torch.randn(rc.shape, generator=g), torch.randn(ra.shape, generator=g)
+        grads = torch.autograd.grad((rc * w_c).sum() + (ra * w_a).sum(), leaves)
+        o_leaves = [t.clone().requires_grad_(True) for t in (means, quats, scales, opacities, case["colors"])]
+        o_rc, o_ra, _ = O.rasterization(*o_leaves, viewmats, Ks, W, H, bits_rule="cuda", **case["kw"])
+        o_grads = torch.autograd.grad((o_rc * w_c).sum() + (o_ra * w_a).sum(), o_leaves)
+        _close(o_rc, rc, what=name + " render_colors")
+        _close(o_ra, ra, what=name + " render_alphas")
+        for gname, a, b in zip(("means", "quats", "scales", "opacities", "colors"), o_grads, grads):
+            _close(a, b, rtol=1e-3, atol=1e-4 * float(b.abs().max()) + 1e-6, what=f"{name} v_{gname}")
+        out.update({f"{name}_render_colors": rc, f"{name}_render_alphas": ra, f"{name}_w_colors": w_c,
+                    f"{name}_w_alphas": w_a})
+        out.update({f"{name}_v_{gname}": gr for gname, gr in
+                    zip(("means", "quats", "scales", "opacities", "colors"), grads)})
+        print("e2e %s: N=%d mean alpha=%.3f" % (name, N, float(ra.detach().mean())))
+    np.savez_compressed(os.path.join(GOLD, "e2e.npz"), **_np(**out))
 
 
 def main():
@@ -253,11 +318,15 @@ def main():
     if len(sys.argv) > 1 and sys.argv[1] == "fisheye":  # only the fisheye vectors (the others stay frozen)
         case_projection_fisheye(T)
         return
+    if len(sys.argv) > 1 and sys.argv[1] == "e2e":  # only the end-to-end vectors
+        case_e2e(T)
+        return
     proj = case_projection(T)
     case_projection_fisheye(T)
     case_sh(T)
     case_isect(T, proj)
     case_raster(T)
+    case_e2e(T)
     print("golden vectors written to", GOLD)
 
 

@@ -1,5 +1,6 @@
 """CPU: the oracle (oracle/gs_oracle.py) against the golden vectors frozen from the reference's
 own `_torch_impl` by oracle/make_golden.py, plus the literal known-answer vectors of the reference."""
+import pytest
 import torch
 
 import gs_oracle as O
@@ -234,3 +235,25 @@ def test_torch_compositor_loop_batches(monkeypatch):
         assert bad < 3e-3, (batch_per_iter, bad)
         bad = ((ra - o_ra).abs() > 1e-5 + 1e-4 * o_ra.abs()).float().mean().item()
         assert bad < 3e-3, (batch_per_iter, bad)
+
+
+@pytest.mark.parametrize("case", ["sh", "rgb"])
+def test_oracle_pipeline_reproduces_the_reference_end_to_end(golden, case):
+    """tests/golden/e2e.npz holds the outputs and autograd gradients of the REFERENCE's own pure-torch pipeline
+    (`gsplat.rendering._rasterization`, rendering.py:601-760, run by oracle/make_golden.py::case_e2e): SH degree 3 with
+    RGB+ED, and plain colours antialiased over a background. The oracle's rasterization() -- what the GPU tests hold
+    the CUDA path against -- must reproduce them."""
+    g = golden("e2e")
+    W, H = int(g["width"]), int(g["height"])
+    colors = g["shs"] if case == "sh" else g["rgb"]
+    kw = dict(sh_degree=3, render_mode="RGB+ED") if case == "sh" else dict(rasterize_mode="antialiased",
+                                                                            backgrounds=g["backgrounds"])
+    leaves = [g[k].clone().requires_grad_(True) for k in ("means", "quats", "scales", "opacities")]
+    leaves.append(colors.clone().requires_grad_(True))
+    rc, ra, _ = O.rasterization(*leaves, g["viewmats"], g["Ks"], W, H, **kw)
+    _close(rc, g[f"{case}_render_colors"])
+    _close(ra, g[f"{case}_render_alphas"])
+    grads = torch.autograd.grad((rc * g[f"{case}_w_colors"]).sum() + (ra * g[f"{case}_w_alphas"]).sum(), leaves)
+    for name, got in zip(("means", "quats", "scales", "opacities", "colors"), grads):
+        want = g[f"{case}_v_{name}"]
+        _close(got, want, rtol=1e-3, atol=1e-4 * float(want.abs().max()) + 1e-6)
