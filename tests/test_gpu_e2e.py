@@ -444,3 +444,30 @@ def test_compute_relocation_matches_equation_9():
     torch.testing.assert_close(new_o.cpu().double(), ref_o, rtol=2e-3, atol=1e-7)
     torch.testing.assert_close(new_s.cpu().double(), ref_s, rtol=2e-3, atol=1e-8)
     assert torch.isfinite(new_s).all()
+
+
+@pytest.mark.xfail(strict=False, reason="written after this round's GPU budget ran out: not yet observed on a B200 "
+                                        "(the same comparison passes transitively: CUDA path == oracle pipeline on the "
+                                        "GPU, oracle pipeline == these vectors on the CPU); drop the marker once green")
+@pytest.mark.parametrize("case", ["sh", "rgb"])
+def test_rasterization_matches_the_reference_end_to_end_vectors(golden, case):
+    """The CUDA path against tests/golden/e2e.npz: outputs and autograd gradients of the REFERENCE's own pure-torch
+    `_rasterization` (rendering.py:601-760, frozen by oracle/make_golden.py::case_e2e)."""
+    from gsplat.rendering import rasterization
+
+    g = golden("e2e")
+    W, H = int(g["width"]), int(g["height"])
+    colors = g["shs"] if case == "sh" else g["rgb"]
+    kw = dict(sh_degree=3, render_mode="RGB+ED") if case == "sh" else dict(rasterize_mode="antialiased",
+                                                                            backgrounds=g["backgrounds"].to(DEV))
+    leaves = [g[k].clone().to(DEV).requires_grad_(True) for k in ("means", "quats", "scales", "opacities")]
+    leaves.append(colors.clone().to(DEV).requires_grad_(True))
+    rc, ra, _ = rasterization(*leaves, g["viewmats"].to(DEV), g["Ks"].to(DEV), W, H, **kw)
+    _close_frac(rc, g[f"{case}_render_colors"], rtol=1e-4, atol=1e-4)
+    _close_frac(ra, g[f"{case}_render_alphas"], rtol=1e-4, atol=1e-4)
+    loss = (rc * g[f"{case}_w_colors"].to(DEV)).sum() + (ra * g[f"{case}_w_alphas"].to(DEV)).sum()
+    grads = torch.autograd.grad(loss, leaves)
+    tol = {"means": 1e-3, "quats": 5e-3, "scales": 5e-2, "opacities": 1e-3, "colors": 1e-3}
+    for name, got in zip(tol, grads):
+        want = g[f"{case}_v_{name}"]
+        _close_frac(got, want, rtol=tol[name], atol=tol[name] * 1e-2 * float(want.abs().max()) + 1e-7, max_bad=1e-2)
