@@ -298,15 +298,18 @@ int sort_pairs(int64_t n, const int64_t *n_dev, int end_bit, KeyT *keys, KeyT *k
         gsb_set_error("radix sort: memset: %s", cudaGetErrorString(e));
         return GSB_ERR_CUDA;
     }
-    static bool configured = false;  // one instantiation per key type
-    if (!configured) {
+    // one instantiation per key type; the attribute is per DEVICE: bit d = configured on device d
+    static unsigned long long configured = 0ull;
+    int device = 0;
+    cudaGetDevice(&device);
+    if (!((configured >> (device & 63)) & 1ull)) {
         e = cudaFuncSetAttribute(onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)TileOf<KeyT>::kSmem);
         if (e != cudaSuccess) {
             gsb_set_error("radix sort: shared memory: %s", cudaGetErrorString(e));
             return GSB_ERR_CUDA;
         }
-        configured = true;
+        configured |= 1ull << (device & 63);
     }
     uint32_t *hist = reinterpret_cast<uint32_t *>(temp);
     uint32_t *tickets = hist + (int64_t)passes * kBins;

@@ -300,14 +300,17 @@ int launch_bwd(int C, int64_t n_isects, const float *recA, const float *recB, co
                const float *v_render_alphas, GradTargets out, cudaStream_t stream) {
     constexpr size_t smem = BwdSmem<D>::bytes;
     auto kernel = rasterize_bwd_kernel<D, ABS>;
-    static bool configured = false;  // one instantiation per (D, ABS)
-    if (!configured) {
+    // one instantiation per (D, ABS); the attribute is per DEVICE: bit d = configured on device d
+    static unsigned long long configured = 0ull;
+    int device = 0;
+    cudaGetDevice(&device);
+    if (!((configured >> (device & 63)) & 1ull)) {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) {
             gsb_set_error("rasterize_bwd: cannot reserve %zu B of shared memory: %s", smem, cudaGetErrorString(e));
             return GSB_ERR_CUDA;
         }
-        configured = true;
+        configured |= 1ull << (device & 63);
     }
     dim3 grid(tw, th, C);
     kernel<<<grid, kThreads, smem, stream>>>(C, n_isects, reinterpret_cast<const float4 *>(recA),
