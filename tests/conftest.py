@@ -23,6 +23,16 @@ os.environ.setdefault("GSPLAT_BACKEND", "b200")
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    # a fresh checkout has no built library (it is git-ignored): build it once if the toolchain is here
+    lib_path = os.path.join(PKG, "lib", "libgsplat_b200.so")
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    if not os.path.exists(lib_path) and os.path.exists(nvcc):
+        import importlib.util
+
+        spec = importlib.util.spec_from_file_location("_gsb_build", os.path.join(PKG, "build.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        mod.build()
 
 
 def pytest_collection_modifyitems(config, items):
