@@ -99,3 +99,34 @@ def test_optimizer_ops_refuse_cpu_tensors():
         opt.step(visibility=torch.ones(4, dtype=torch.bool))
     with pytest.raises(RuntimeError, match="CUDA"):
         compute_relocation(torch.rand(4), torch.rand(4, 3), torch.ones(4, dtype=torch.int64), torch.ones(5, 5))
+
+
+def test_rasterization_argument_validation_matches_the_reference():
+    """Shape / mode checks fire before anything touches the GPU, with the reference's conditions and messages
+    (rendering.py:242-293); valid CPU arguments then hit the no-CPU-path error, not a fallback."""
+    import pytest
+    import torch
+    from gsplat.rendering import rasterization
+
+    N, C = 8, 2
+    ok = dict(means=torch.zeros(N, 3), quats=torch.ones(N, 4), scales=torch.ones(N, 3), opacities=torch.ones(N),
+              colors=torch.ones(N, 3), viewmats=torch.eye(4).expand(C, 4, 4), Ks=torch.eye(3).expand(C, 3, 3),
+              width=32, height=32)
+
+    def call(**over):
+        a = dict(ok, **over)
+        return rasterization(a.pop("means"), a.pop("quats"), a.pop("scales"), a.pop("opacities"), a.pop("colors"),
+                             a.pop("viewmats"), a.pop("Ks"), a.pop("width"), a.pop("height"), **a)
+
+    for bad in (dict(means=torch.zeros(N, 2)), dict(quats=torch.ones(N, 3)), dict(scales=torch.ones(N + 1, 3)),
+                dict(opacities=torch.ones(N, 1)), dict(viewmats=torch.eye(4).expand(C, 4, 4)[:, :3]),
+                dict(Ks=torch.eye(3).expand(C + 1, 3, 3)), dict(render_mode="RGBD"), dict(colors=torch.ones(N + 1, 3)),
+                dict(colors=torch.ones(N, 4, 3), sh_degree=2), dict(covars=torch.ones(N, 3, 2))):
+        with pytest.raises(AssertionError):
+            call(**bad)
+    with pytest.raises(AssertionError, match="AbsGrad is not supported in distributed mode"):
+        call(absgrad=True, distributed=True)
+    with pytest.raises(AssertionError, match="per-Gaussian colors"):
+        call(colors=torch.ones(C, N, 3), distributed=True)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        call()
