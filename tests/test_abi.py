@@ -130,3 +130,39 @@ def test_rasterization_argument_validation_matches_the_reference():
         call(colors=torch.ones(C, N, 3), distributed=True)
     with pytest.raises(RuntimeError, match="CUDA"):
         call()
+
+
+def test_stage_functions_validate_like_the_reference_wrappers():
+    """The five backend functions check their arguments where the reference wrappers do (triton_impl/_wrapper.py:
+    225-277, 511-523; cuda/_wrapper.py:260-300, 505-530) -- before any GPU work, so it can be seen on the CPU."""
+    import pytest
+    import torch
+    from gsplat.b200_impl import fully_fused_projection, isect_tiles, rasterize_to_pixels, spherical_harmonics
+
+    N, C = 6, 2
+    means, quats, scales = torch.zeros(N, 3), torch.ones(N, 4), torch.ones(N, 3)
+    viewmats, Ks = torch.eye(4).expand(C, 4, 4), torch.eye(3).expand(C, 3, 3)
+    with pytest.raises(AssertionError):
+        fully_fused_projection(means[:, :2], None, quats, scales, viewmats, Ks, 32, 32)
+    with pytest.raises(AssertionError, match="covars or quats is required"):
+        fully_fused_projection(means, None, None, scales, viewmats, Ks, 32, 32)
+    with pytest.raises(AssertionError):
+        fully_fused_projection(means, torch.ones(N, 3, 3), None, None, viewmats, Ks, 32, 32)  # covars are [N, 6] here
+    with pytest.raises(AssertionError, match="sparse_grad is only supported when packed is True"):
+        fully_fused_projection(means, None, quats, scales, viewmats, Ks, 32, 32, sparse_grad=True)
+    with pytest.raises((NotImplementedError, ValueError, AssertionError)):
+        fully_fused_projection(means, None, quats, scales, viewmats, Ks, 32, 32, camera_model="equirectangular")
+    means2d, conics, colors, opac = torch.zeros(C, N, 2), torch.ones(C, N, 3), torch.ones(C, N, 3), torch.ones(C, N)
+    offsets, flat = torch.zeros(C, 2, 2, dtype=torch.int32), torch.zeros(0, dtype=torch.int32)
+    with pytest.raises(AssertionError):
+        rasterize_to_pixels(means2d, conics[:, :, :2], colors, opac, 32, 32, 16, offsets, flat)
+    with pytest.raises(AssertionError):
+        rasterize_to_pixels(means2d, conics, colors, opac, 32, 32, 16, offsets, flat, backgrounds=torch.ones(C, 4))
+    with pytest.raises(AssertionError, match="Assert Failed"):
+        rasterize_to_pixels(means2d, conics, colors, opac, 64, 32, 16, offsets, flat)  # tile grid smaller than image
+    with pytest.raises(ValueError, match="Unsupported number of color channels"):
+        rasterize_to_pixels(means2d, conics, torch.ones(C, N, 600), opac, 32, 32, 16, offsets, flat)
+    with pytest.raises(AssertionError):
+        isect_tiles(means2d, torch.ones(C, N + 1, dtype=torch.int32), torch.ones(C, N), 16, 2, 2)
+    with pytest.raises(AssertionError):
+        spherical_harmonics(3, torch.ones(N, 3), torch.ones(N, 9, 3))  # (degree + 1)^2 coefficients needed
