@@ -117,7 +117,7 @@ def _raster_work_counts(meta, device):
     (SURVEY 8d); Hits = pixel-Gaussian pairs actually composited (alpha >= 1/255, before termination)."""
     from gsplat.b200_impl._lib import lib, ptr, stream_of
 
-    means2d, conics, opac = meta["means2d"].detach(), meta["conics"].detach(), meta["opacities"].detach()
+    means2d, conics, opac = (meta[k].detach().contiguous() for k in ("means2d", "conics", "opacities"))
     offs, flat = meta["isect_offsets"], meta["flatten_ids"]
     C, th, tw = offs.shape
     P, W, H = opac.numel(), meta["width"], meta["height"]
@@ -126,8 +126,7 @@ def _raster_work_counts(meta, device):
     cnt, ra = torch.empty((C, H, W), device=device), torch.empty((C, H, W), device=device)
     last = torch.empty((C, H, W), dtype=torch.int32, device=device)
     st = stream_of(rec)
-    lib.gsb_rasterize_pack(P, ptr(means2d.contiguous()), ptr(conics.contiguous()), ptr(opac.contiguous()),
-                           ptr(rec[0]), ptr(rec[1]), st)
+    lib.gsb_rasterize_pack(P, ptr(means2d), ptr(conics), ptr(opac), ptr(rec[0]), ptr(rec[1]), st)
     lib.gsb_rasterize_count(C, flat.numel(), ptr(rec[0]), ptr(rec[1]), ptr(ones), W, H, 16, tw, th, ptr(offs),
                             ptr(flat), ptr(cnt), ptr(ra), ptr(last), st)
     hits = int(cnt.double().sum().item())

@@ -143,10 +143,14 @@ class _FullyFusedProjection(torch.autograd.Function):
         v_viewmats = torch.empty_like(viewmats) if need[4] else None
         if compensations is None:
             v_compensations = None
+        # converted cotangents stay bound until after the launch (a temporary freed before the launch could be
+        # handed to the next conversion by the caching allocator and overwritten on the same stream)
+        v_means2d, v_depths, v_conics, v_compensations = (
+            _f32(t) for t in (v_means2d, v_depths, v_conics, v_compensations))
         lib.gsb_projection_bwd(
             C, N, ptr(means), ptr(covars), ptr(quats), ptr(scales), ptr(viewmats), ptr(Ks), ctx.width,
             ctx.height, ctx.eps2d, ctx.model, ptr(radii), ptr(conics), ptr(compensations),
-            ptr(_f32(v_means2d)), ptr(_f32(v_depths)), ptr(_f32(v_conics)), ptr(_f32(v_compensations)),
+            ptr(v_means2d), ptr(v_depths), ptr(v_conics), ptr(v_compensations),
             ptr(v_means), ptr(v_covars), ptr(v_quats), ptr(v_scales), ptr(v_viewmats), stream_of(means),
         )
         return (v_means, v_covars, v_quats, v_scales, v_viewmats) + (None,) * 9
@@ -212,11 +216,13 @@ class _FullyFusedProjectionPacked(torch.autograd.Function):
         acc = None if sparse else torch.empty((N, 9), dtype=torch.float32, device=dev)
         if compensations is None:
             v_compensations = None
+        v_means2d, v_depths, v_conics, v_compensations = (
+            _f32(t) for t in (v_means2d, v_depths, v_conics, v_compensations))  # bound past the launch
         lib.gsb_projection_packed_bwd(
             C, N, nnz, ptr(means), ptr(covars), ptr(quats), ptr(scales), ptr(viewmats), ptr(Ks), ctx.width,
             ctx.height, ctx.eps2d, ctx.model, ptr(camera_ids), ptr(gaussian_ids), ptr(conics),
-            ptr(compensations), ptr(_f32(v_means2d)), ptr(_f32(v_depths)), ptr(_f32(v_conics)),
-            ptr(_f32(v_compensations)), int(sparse), ptr(acc), ptr(v_means), ptr(v_covars), ptr(v_quats),
+            ptr(compensations), ptr(v_means2d), ptr(v_depths), ptr(v_conics),
+            ptr(v_compensations), int(sparse), ptr(acc), ptr(v_means), ptr(v_covars), ptr(v_quats),
             ptr(v_scales), ptr(v_viewmats), stream_of(means),
         )
         if sparse:
@@ -296,8 +302,9 @@ class _SphericalHarmonics(torch.autograd.Function):
         v_dirs = torch.empty_like(dirs) if ctx.needs_input_grad[1] else None
         if n_rows == 0 or n_batch == 0:
             v_coeffs.zero_()
+        v_colors = _f32(v_colors)
         lib.gsb_sh_bwd(ctx.sh_degree, n_rows, n_batch, K, ptr(dirs), ptr(coeffs), ptr(m8),
-                       ptr(_f32(v_colors)), ptr(v_coeffs), ptr(v_dirs), stream_of(dirs))
+                       ptr(v_colors), ptr(v_coeffs), ptr(v_dirs), stream_of(dirs))
         if not ctx.needs_input_grad[2]:
             v_coeffs = None
         return None, v_dirs, v_coeffs, None
@@ -340,8 +347,9 @@ class _ViewColors(torch.autograd.Function):
         C, N = radii.shape
         v_coeffs = torch.empty_like(coeffs)
         v_means = torch.empty_like(means) if ctx.needs_input_grad[1] else None
+        v_colors = _f32(v_colors)
         lib.gsb_sh_colors_bwd(ctx.sh_degree, N, C, coeffs.shape[1], ptr(means), ptr(campos), ptr(coeffs), ptr(radii),
-                              ptr(_f32(v_colors)), ptr(v_coeffs), ptr(v_means), stream_of(means))
+                              ptr(v_colors), ptr(v_coeffs), ptr(v_means), stream_of(means))
         return None, v_means, None, (v_coeffs if ctx.needs_input_grad[3] else None), None
 
 
@@ -840,9 +848,12 @@ def rasterize_to_indices_in_range(
     require_cuda(transmittances, means2d, conics, opacities, isect_offsets, flatten_ids)
     dev, st = means2d.device, stream_of(means2d)
     range_end = int(min(range_end, 2**31 - 1))
-    args = (C, N, flatten_ids.numel(), int(range_start), range_end, ptr(_f32(transmittances)), ptr(_f32(means2d)),
-            ptr(_f32(conics)), ptr(_f32(opacities)), image_width, image_height, tile_size, tile_width, tile_height,
-            ptr(isect_offsets.contiguous().int()), ptr(flatten_ids.contiguous().int()))
+    # every converted copy stays bound to a local until both launches are queued
+    transmittances, means2d, conics, opacities = (_f32(t) for t in (transmittances, means2d, conics, opacities))
+    isect_offsets, flatten_ids = isect_offsets.contiguous().int(), flatten_ids.contiguous().int()
+    args = (C, N, flatten_ids.numel(), int(range_start), range_end, ptr(transmittances), ptr(means2d),
+            ptr(conics), ptr(opacities), image_width, image_height, tile_size, tile_width, tile_height,
+            ptr(isect_offsets), ptr(flatten_ids))
     counts = torch.empty((C * image_height * image_width,), dtype=torch.int32, device=dev)
     lib.gsb_rasterize_indices_count(*args, ptr(counts), st)
     ends = torch.cumsum(counts, dim=0, dtype=torch.int64)

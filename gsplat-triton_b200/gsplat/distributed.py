@@ -271,8 +271,11 @@ class _PackRows(torch.autograd.Function):
         require_cuda(means2d)
         P, D = depths.numel(), colors.shape[-1]
         rows = torch.empty((P, 8 + D), dtype=torch.float32, device=means2d.device)
-        lib.gsb_a2a_pack(P, D, ptr(means2d.contiguous()), ptr(depths.contiguous()), ptr(conics.contiguous()),
-                         ptr(opacities.contiguous()), ptr(colors.contiguous()), ptr(radii.contiguous()),
+        # contiguous copies stay bound to locals until the launch is queued (never `ptr(x.contiguous())`: the
+        # temporary would be freed, and possibly reused by the next copy, before the kernel reads it)
+        means2d, depths, conics, opacities, colors, radii = (
+            t.contiguous() for t in (means2d, depths, conics, opacities, colors, radii))
+        lib.gsb_a2a_pack(P, D, ptr(means2d), ptr(depths), ptr(conics), ptr(opacities), ptr(colors), ptr(radii),
                          ptr(rows), stream_of(means2d))
         ctx.D = D
         return rows
@@ -312,9 +315,11 @@ class _UnpackRows(torch.autograd.Function):
         P, D = v_depths.numel(), ctx.D
         rows = torch.empty((P, 8 + D), dtype=torch.float32, device=v_depths.device)
         zeros = torch.zeros((max(P, 1),), dtype=torch.int32, device=v_depths.device)
-        lib.gsb_a2a_pack(P, D, ptr(v_means2d.contiguous()), ptr(v_depths.contiguous()), ptr(v_conics.contiguous()),
-                         ptr(v_opacities.contiguous()), ptr(v_colors.contiguous()), ptr(zeros), ptr(rows),
-                         stream_of(rows))
+        # e.g. RGB+ED hands v_colors / v_depths over as narrow views of one cat() gradient: two copies back to back
+        v_means2d, v_depths, v_conics, v_opacities, v_colors = (
+            t.float().contiguous() for t in (v_means2d, v_depths, v_conics, v_opacities, v_colors))
+        lib.gsb_a2a_pack(P, D, ptr(v_means2d), ptr(v_depths), ptr(v_conics), ptr(v_opacities), ptr(v_colors),
+                         ptr(zeros), ptr(rows), stream_of(rows))
         return rows, None
 
 
@@ -513,9 +518,10 @@ class _PeerExchangeRows(torch.autograd.Function):
         st = stream_of(means2d)
         epoch = box.next_epoch(0)
         region = box.region(0, epoch)
-        lib.gsb_a2a_put_fwd(world, rank, C_local, N_local, N_total, bases[rank], D, ptr(means2d.contiguous()),
-                            ptr(depths.contiguous()), ptr(conics.contiguous()), ptr(opacities.contiguous()),
-                            ptr(colors.contiguous()), ptr(radii.contiguous()), box.peer_array, region, epoch, st)
+        means2d, depths, conics, opacities, colors, radii = (
+            t.contiguous() for t in (means2d, depths, conics, opacities, colors, radii))  # bound past the launch
+        lib.gsb_a2a_put_fwd(world, rank, C_local, N_local, N_total, bases[rank], D, ptr(means2d), ptr(depths),
+                            ptr(conics), ptr(opacities), ptr(colors), ptr(radii), box.peer_array, region, epoch, st)
         rows = C_local * N_total
         out, views = _region_views(rows, D, True, dev)
         lib.gsb_a2a_wait_copy(world, 0, epoch, box.local, region, out.numel(), ptr(out), box.timeout_flag, st)

@@ -400,9 +400,14 @@ def rasterization(
     means, quats, scales, opacities, colors, viewmats, Ks, width, height,
     near_plane=0.01, far_plane=1e10, radius_clip=0.0, eps2d=0.3, sh_degree=None, tile_size=16,
     backgrounds=None, render_mode="RGB", rasterize_mode="classic", camera_model="pinhole", covars=None,
-    bits_rule="triton",
+    bits_rule="triton", compositor="torch", pixel_weight=None,
 ):
-    """CPU restatement of rendering.py:44-598 for packed=False, distributed=False."""
+    """CPU restatement of rendering.py:44-598 for packed=False, distributed=False.
+
+    `compositor="c"` composites with oracle/gs_compositor.c (OpenMP; full-size scenes in seconds) instead of the
+    torch-autograd restatement above; `meta` then also carries `margin` (per-pixel distance of the closest
+    threshold decision, see gs_compositor.c) and `last_ids`, and `pixel_weight` (bool [C,H,W]) removes pixels
+    from the backward pass."""
     C = viewmats.shape[0]
     if covars is None:
         covars = quat_scale_to_covar(quats, scales)
@@ -432,14 +437,25 @@ def rasterization(
     tw, th = math.ceil(width / float(tile_size)), math.ceil(height / float(tile_size))
     tiles_per_gauss, isect_ids, flatten_ids = isect_tiles(means2d, radii, depths, tile_size, tw, th, bits_rule=bits_rule)
     offsets = isect_offset_encode(isect_ids, C, tw, th, bits_rule=bits_rule)
-    render_colors, render_alphas = rasterize_to_pixels(
-        means2d, conics, cols, opac, width, height, tile_size, offsets, flatten_ids, backgrounds=backgrounds
-    )
+    extra = {}
+    if compositor == "c":
+        import c_oracle
+
+        render_colors, render_alphas, last_ids, margin = c_oracle.rasterize_to_pixels(
+            means2d, conics, cols, opac, width, height, tile_size, offsets, flatten_ids, backgrounds=backgrounds,
+            return_last_ids=True, return_margin=True, pixel_weight=pixel_weight)
+        extra = {"margin": margin, "last_ids": last_ids}
+    else:
+        assert pixel_weight is None
+        render_colors, render_alphas = rasterize_to_pixels(
+            means2d, conics, cols, opac, width, height, tile_size, offsets, flatten_ids, backgrounds=backgrounds
+        )
     if render_mode in ("ED", "RGB+ED"):
         render_colors = torch.cat(
             [render_colors[..., :-1], render_colors[..., -1:] / render_alphas.clamp(min=1e-10)], dim=-1
         )
     meta = {"radii": radii, "means2d": means2d, "depths": depths, "conics": conics, "opacities": opac,
             "tiles_per_gauss": tiles_per_gauss, "isect_ids": isect_ids, "flatten_ids": flatten_ids,
-            "isect_offsets": offsets, "tile_width": tw, "tile_height": th}
+            "isect_offsets": offsets, "tile_width": tw, "tile_height": th, "colors": cols}
+    meta.update(extra)
     return render_colors, render_alphas, meta

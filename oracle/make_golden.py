@@ -70,6 +70,54 @@ def _install_nerfacc_stub():
 _indices_in_range_cpu = O.rasterize_to_indices_in_range  # RasterizeToIndices3DGS.cu:14-170 on the CPU
 
 
+def _indices_in_range_tiles(range_start, range_end, transmittances, means2d, conics, opacities, image_width,
+                            image_height, tile_size, isect_offsets, flatten_ids):
+    """Same enumeration as `_indices_in_range_cpu` (RasterizeToIndices3DGS.cu:14-170), vectorised per tile in
+    float32 numpy so the full-size garden scene finishes in minutes; `main()` asserts both give the same lists."""
+    C, N, _ = means2d.shape
+    th, tw = isect_offsets.shape[1:]
+    n_isects = flatten_ids.numel()
+    offs = torch.cat([isect_offsets.flatten().long(), torch.tensor([n_isects])]).numpy()
+    fid = flatten_ids.long().numpy()
+    m, cn, op = (x.detach().numpy() for x in (means2d.reshape(-1, 2), conics.reshape(-1, 3), opacities.reshape(-1)))
+    Tin = transmittances.detach().numpy()
+    block = tile_size * tile_size
+    f = np.float32
+    gs, px, cam = [], [], []
+    for c in range(C):
+        for ty in range(th):
+            for tx in range(tw):
+                t = (c * th + ty) * tw + tx
+                lo, hi = int(offs[t]), int(offs[t + 1])
+                lo2, hi2 = lo + block * range_start, min(hi, lo + block * range_end)
+                if lo2 >= hi2:
+                    continue
+                y0, x0 = ty * tile_size, tx * tile_size
+                ys = np.arange(y0, min(y0 + tile_size, image_height))
+                xs = np.arange(x0, min(x0 + tile_size, image_width))
+                yy, xx = np.meshgrid(ys, xs, indexing="ij")
+                yy, xx = yy.reshape(-1), xx.reshape(-1)
+                g = fid[lo2:hi2]
+                dx = m[g, 0][None, :] - (xx.astype(f) + f(0.5))[:, None]
+                dy = m[g, 1][None, :] - (yy.astype(f) + f(0.5))[:, None]
+                sigma = f(0.5) * (cn[g, 0] * dx * dx + cn[g, 2] * dy * dy) + cn[g, 1] * dx * dy
+                alpha = np.minimum(f(0.999), op[g][None, :] * np.exp(-sigma))
+                valid = ~(sigma < 0) & ~(alpha < f(1.0 / 255.0))
+                one_m = np.where(valid, f(1.0) - alpha, f(1.0)).astype(f)
+                T_incl = Tin[c, yy, xx][:, None] * np.cumprod(one_m, axis=1, dtype=f)  # sequential float32 products
+                stop = np.maximum.accumulate(valid & (T_incl <= f(1e-4)), axis=1)
+                pi, gi = np.nonzero(valid & ~stop)  # row-major: grouped by pixel, Gaussians in sorted order
+                gs.append(g[gi] % N)
+                px.append(yy[pi] * image_width + xx[pi])
+                cam.append(np.full(pi.shape, c, dtype=np.int64))
+    if not gs:
+        z = torch.zeros(0, dtype=torch.long)
+        return z, z.clone(), z.clone()
+    gs, px, cam = np.concatenate(gs), np.concatenate(px), np.concatenate(cam)
+    order = np.lexsort((np.arange(gs.size), px, cam))  # the op returns pairs grouped by (camera, pixel)
+    return torch.from_numpy(gs[order]), torch.from_numpy(px[order]), torch.from_numpy(cam[order])
+
+
 def _close(a, b, rtol=1e-4, atol=1e-4, what=""):
     torch.testing.assert_close(a, b, rtol=rtol, atol=atol, msg=lambda m: f"{what}: {m}")
 
@@ -311,6 +359,47 @@ def case_e2e(T):
     np.savez_compressed(os.path.join(GOLD, "e2e.npz"), **_np(**out))
 
 
+def case_cfg1(T):
+    """BASELINE configs[0] at FULL size: the reference's pure-torch `_rasterization` (rendering.py:601-814) on
+    `load_test_data` (N = 111 785, seed 42, `_helper.py:9-55`), camera 0, 648x420, colours [N,3], fwd + autograd
+    gradients. Frozen: image, alpha, the per-pixel decision margin of the C oracle on the same inputs, and every
+    16th row of each parameter gradient. Takes a few minutes (the reference's `_isect_tiles` is a Python loop)."""
+    import time
+
+    import gsplat.cuda._wrapper as W_
+    import gsplat.rendering as R
+    from gsplat._helper import load_test_data
+
+    _install_nerfacc_stub()
+    W_.rasterize_to_indices_in_range = _indices_in_range_tiles
+    R.isect_tiles = lambda m, r, d, ts, tw, th, **kw: T._isect_tiles(m, r, d, ts, tw, th)
+    R.isect_offset_encode = T._isect_offset_encode
+    torch.manual_seed(42)
+    means, quats, scales, opacities, colors, viewmats, Ks, W, H = load_test_data(device="cpu")
+    viewmats, Ks = viewmats[:1].contiguous(), Ks[:1].contiguous()
+    g = torch.Generator().manual_seed(1)
+    leaves = [t.clone().requires_grad_(True) for t in (means, quats, scales, opacities, colors)]
+    t0 = time.time()
+    rc, ra, _ = R._rasterization(*leaves, viewmats, Ks, W, H)
+    w_c, w_a = torch.rand(rc.shape, generator=g), torch.rand(ra.shape, generator=g)
+    grads = torch.autograd.grad((rc * w_c).sum() + (ra * w_a).sum(), leaves)
+    print("cfg1 reference fwd+bwd: %.1f s, mean alpha %.3f" % (time.time() - t0, float(ra.mean())))
+    o_leaves = [t.clone().requires_grad_(True) for t in (means, quats, scales, opacities, colors)]
+    o_rc, o_ra, o_meta = O.rasterization(*o_leaves, viewmats, Ks, W, H, bits_rule="cuda", compositor="c")
+    o_grads = torch.autograd.grad((o_rc * w_c).sum() + (o_ra * w_a).sum(), o_leaves)
+    bad = ((o_rc - rc.detach()).abs() > 1e-4 + 1e-4 * rc.detach().abs()).any(-1)
+    print("cfg1 oracle(C) vs reference: image max err %.2e, pixels beyond 1e-4: %d (margin < 1e-4 on %d of them)" % (
+        float((o_rc - rc.detach()).abs().max()), int(bad.sum()), int((bad & (o_meta["margin"] < 1e-4)).sum())))
+    assert bool((~bad | (o_meta["margin"] < 1e-4)).all()), "an oracle/reference image difference is not a threshold flip"
+    out = dict(width=W, height=H, n=means.shape[0], render_colors=rc, render_alphas=ra, margin=o_meta["margin"],
+               n_isects=o_meta["flatten_ids"].numel(), checksum=torch.stack([t.double().sum() for t in leaves]))
+    for gname, a, b in zip(("means", "quats", "scales", "opacities", "colors"), o_grads, grads):
+        rel = float((a - b).abs().max() / b.abs().max())
+        print("  v_%s: oracle(C) vs reference max err / max |g| = %.2e" % (gname, rel))
+        out["v_" + gname] = b[::16].contiguous()
+    np.savez_compressed(os.path.join(GOLD, "cfg1.npz"), **_np(**out))
+
+
 def main():
     import gsplat.cuda._torch_impl as T
 
@@ -321,12 +410,16 @@ def main():
     if len(sys.argv) > 1 and sys.argv[1] == "e2e":  # only the end-to-end vectors
         case_e2e(T)
         return
+    if len(sys.argv) > 1 and sys.argv[1] == "cfg1":  # only the full-size garden vectors
+        case_cfg1(T)
+        return
     proj = case_projection(T)
     case_projection_fisheye(T)
     case_sh(T)
     case_isect(T, proj)
     case_raster(T)
     case_e2e(T)
+    case_cfg1(T)
     print("golden vectors written to", GOLD)
 
 
