@@ -8,8 +8,15 @@ per GPU, NCCL): the same 1M-Gaussian scene strided over the ranks (`means[rank::
 rank, `distributed=True` (per-camera all-to-all of the projected rows) — per-GPU work is constant
 (weak scaling); `value` = camera renders (fwd+bwd) per second over all ranks.
 
-One JSON line on stdout (rank 0): see the keys in `main`. `--impl reference` times the CPU oracle
-port of the reference's torch path (oracle/gs_oracle.py) on the host cores instead.
+`--config cfg1` (N=1 only) runs BASELINE.json configs[0] instead: the garden fixture (N = 111 785, camera 0, 648x420,
+colours [N,3], `gsplat/_helper.py:9-55` protocol), the only configuration the reference's pure-torch CPU path runs end
+to end.
+
+One JSON line on stdout (rank 0): see the keys in `main`. `--impl reference` times WHOLE iterations of the CPU port of
+the reference's pure-torch path on the host cores (oracle/gs_oracle.py for projection / SH / intersection,
+oracle/gs_compositor.c for the compositor: the reference's own `_rasterize_to_pixels` cannot run anywhere without the
+un-vendored nerfacc and a CUDA op) — no sampling, no extrapolation; it stops early only at a wall budget and then
+reports the number of whole iterations it measured as `steps`.
 """
 import argparse
 import json
@@ -54,10 +61,55 @@ def make_cfg2(device="cpu", n=N_GAUSS, seed=0):
     return s
 
 
-def loss_weights(device, seed=1):
+def make_cfg1(device="cpu"):
+    """BASELINE configs[0]: the reference's `load_test_data` protocol (gsplat/_helper.py:9-55, seed 42) on the
+    committed copy of its only fixture (tests/golden/test_garden.npz), camera 0."""
+    import numpy as np
+
+    data = np.load(os.path.join(ROOT, "tests", "golden", "test_garden.npz"))
+    means = torch.from_numpy(data["means3d"]).float()
+    colors = torch.from_numpy(data["colors"] / 255.0).float()
+    sel = ((means >= -2) & (means <= 2)).all(dim=-1)
+    means, colors = means[sel].contiguous(), colors[sel].contiguous()
+    g = torch.Generator().manual_seed(42)
+    n = means.shape[0]
+    scales = torch.rand((n, 3), generator=g) * 0.02
+    quats = torch.nn.functional.normalize(torch.randn((n, 4), generator=g), dim=-1)
+    opacities = torch.rand((n,), generator=g)
+    s = dict(means=means, quats=quats, scales=scales, opacities=opacities, colors=colors,
+             viewmats=torch.from_numpy(data["viewmats"]).float()[:1].contiguous(),
+             Ks=torch.from_numpy(data["Ks"]).float()[:1].contiguous())
+    s = {k: t.to(device) for k, t in s.items()}
+    s.update(width=int(data["width"]), height=int(data["height"]))
+    return s
+
+
+WORKLOADS = {
+    "cfg2": "cfg2: 1M Gaussians SH deg 3, 1920x1080, 1 camera per GPU, packed=False",
+    "cfg1": "cfg1: garden fixture N=111785 colours [N,3], 648x420, camera 0, packed=False",
+}
+METRICS = {
+    "cfg2": "fwd+bwd render iters/s (1M Gaussians, 1080p)",
+    "cfg1": "fwd+bwd render iters/s (garden 111785 Gaussians, 648x420)",
+}
+
+
+def workload_string(config, world):
+    return WORKLOADS[config] + (f", Gaussians strided over {world} ranks, distributed=True" if world > 1 else "")
+
+
+def make_scene(config, device="cpu"):
+    """-> (scene dict, ordered parameter names, rasterization kwargs)."""
+    if config == "cfg1":
+        return make_cfg1(device), ("means", "quats", "scales", "opacities", "colors"), dict(packed=False)
+    return (make_cfg2(device), ("means", "quats", "scales", "opacities", "shs"),
+            dict(packed=False, sh_degree=SH_DEGREE))
+
+
+def loss_weights(device, seed=1, width=WIDTH, height=HEIGHT):
     g = torch.Generator().manual_seed(seed)
-    G = torch.rand(1, HEIGHT, WIDTH, 3, generator=g)
-    a = torch.rand(1, HEIGHT, WIDTH, 1, generator=g)
+    G = torch.rand(1, height, width, 3, generator=g)
+    a = torch.rand(1, height, width, 1, generator=g)
     return G.to(device), a.to(device)
 
 
@@ -102,19 +154,31 @@ class ClockSampler:
 
 
 def measured_peaks():
+    """Roofline denominators: HBM from the driver-written MEASURED_PEAKS.json; FP32-FMA / MUFU.EX2 from
+    profiles/peaks_fp32.json (tools/peak_fp32.cu run on this pool's B200), else the arithmetic figure."""
+    out = {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0, "source": "fallback"}
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         d = json.load(open(p))
-        return {"hbm_gbs": float(d["hbm_gbs"]), "sm_max_mhz": float(d.get("sm_max_mhz", 1965.0)), "source": "measured"}
-    return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0, "source": "fallback"}
+        out.update(hbm_gbs=float(d["hbm_gbs"]), sm_max_mhz=float(d.get("sm_max_mhz", 1965.0)), source="measured")
+    out["fp32_tflops"] = SM_COUNT * FP32_LANES * 2 * out["sm_max_mhz"] * 1e6 / 1e12
+    out["fp32_source"] = "arithmetic: 148 SMs * 128 lanes * 2 * sm_max_mhz (profiles/peaks_fp32.json absent)"
+    p = os.path.join(ROOT, "profiles", "peaks_fp32.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        out["fp32_tflops"] = float(d["fp32_fma"]["burst"])
+        out["mufu_tops"] = float(d["mufu_ex2"]["burst"])
+        out["fp32_source"] = "measured: profiles/peaks_fp32.json fp32_fma.burst (tools/peak_fp32.cu on this pool's B200)"
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
 # the b200 arm
 # ------------------------------------------------------------------------------------------------
 def _raster_work_counts(meta, device):
-    """(E, Hits): E = reference-algorithm evaluations 256 * sum_tiles(last contributing index - tile start + 1)
-    (SURVEY 8d); Hits = pixel-Gaussian pairs actually composited (alpha >= 1/255, before termination)."""
+    """(E, hits, lane_evals): E = reference-algorithm evaluations 256 * sum_tiles(last contributing index - tile
+    start + 1) (SURVEY 8d); hits = pixel-Gaussian pairs actually composited (alpha >= 1/255, before termination);
+    lane_evals = 32 x the (warp, splat) pairs the forward kernel walks = evaluations the kernels EXECUTE."""
     from gsplat.b200_impl._lib import lib, ptr, stream_of
 
     means2d, conics, opac = (meta[k].detach().contiguous() for k in ("means2d", "conics", "opacities"))
@@ -125,10 +189,11 @@ def _raster_work_counts(meta, device):
     ones = torch.ones((P,), device=device)
     cnt, ra = torch.empty((C, H, W), device=device), torch.empty((C, H, W), device=device)
     last = torch.empty((C, H, W), dtype=torch.int32, device=device)
+    pairs = torch.zeros((1,), dtype=torch.int64, device=device)
     st = stream_of(rec)
     lib.gsb_rasterize_pack(P, ptr(means2d), ptr(conics), ptr(opac), ptr(rec[0]), ptr(rec[1]), st)
     lib.gsb_rasterize_count(C, flat.numel(), ptr(rec[0]), ptr(rec[1]), ptr(ones), W, H, 16, tw, th, ptr(offs),
-                            ptr(flat), ptr(cnt), ptr(ra), ptr(last), st)
+                            ptr(flat), ptr(cnt), ptr(ra), ptr(last), ptr(pairs), st)
     hits = int(cnt.double().sum().item())
     last = torch.where(cnt > 0, last, torch.full_like(last, -1))
     pad_h, pad_w = th * 16 - H, tw * 16 - W
@@ -136,14 +201,13 @@ def _raster_work_counts(meta, device):
     tile_last = last.reshape(C, th, 16, tw, 16).amax(dim=(2, 4))
     work = (tile_last - offs + 1).clamp(min=0)
     work = torch.where(tile_last >= 0, work, torch.zeros_like(work))
-    return 256 * int(work.sum().item()), hits
+    return 256 * int(work.sum().item()), hits, 32 * int(pairs.item())
 
 
 def _stage_table(summary, steps, meta, n_local, C, D, K, work, peaks, sm_mhz):
     """Per-entry-point ms/step, algorithmic bytes (SURVEY 8d formulas) or FP32 slots, achieved vs peak."""
     P = C * n_local
     I = meta["flatten_ids"].numel()
-    px = C * meta["width"] * meta["height"]
     n_tiles = meta["tile_width"] * meta["tile_height"]
     bits = 32 + (n_tiles - 1).bit_length() + max(C - 1, 0).bit_length()
     hbm = {
@@ -171,10 +235,8 @@ def _stage_table(summary, steps, meta, n_local, C, D, K, work, peaks, sm_mhz):
         "gsb_isect_offsets": 8 * I + 4 * C * n_tiles,
         "gsb_rasterize_pack": 24 * P + 32 * P,
     }
-    fp32_peak = SM_COUNT * FP32_LANES * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12  # TFLOP/s at max clock, FMA = 2
-    evals, hits = work if work is not None else (None, None)
-    flops = {} if hits is None else {"gsb_rasterize_fwd": 2 * SLOTS_FWD * hits, "gsb_rasterize_fwd_cap": 2 * SLOTS_FWD * hits,
-                                     "gsb_rasterize_bwd": 2 * SLOTS_BWD * hits}
+    fp32_peak = peaks["fp32_tflops"]
+    slots = {"gsb_rasterize_fwd": SLOTS_FWD, "gsb_rasterize_fwd_cap": SLOTS_FWD, "gsb_rasterize_bwd": SLOTS_BWD}
     out = {}
     for name, (calls, ms) in summary.items():
         per_step = ms / steps
@@ -183,15 +245,22 @@ def _stage_table(summary, steps, meta, n_local, C, D, K, work, peaks, sm_mhz):
             a = hbm[name] / (per_step * 1e-3) / 1e9
             row.update(bound="hbm", achieved=round(a, 1), peak=peaks["hbm_gbs"], unit="GB/s",
                        frac=round(a / peaks["hbm_gbs"], 4), algorithmic_bytes=hbm[name])
-        elif name in flops and per_step > 0:
-            a = flops[name] / (per_step * 1e-3) / 1e12
-            # headline = SURVEY 8(d): slots x the reference algorithm's evaluations E (every pixel of a tile against
-            # every Gaussian up to the tile's last contributor). The kernels cull most of E exactly, so this can
-            # exceed 1; `frac_composited_pairs` counts only the pairs that really blend (strict lower bound).
-            a_ref = a * evals / max(hits, 1)
-            row.update(bound="fp32", achieved=round(a_ref, 2), peak=round(fp32_peak, 2), unit="TFLOP/s",
-                       frac=round(a_ref / fp32_peak, 4), reference_evaluations=evals, composited_pairs=hits,
-                       achieved_composited_pairs=round(a, 2), frac_composited_pairs=round(a / fp32_peak, 4))
+        elif name in slots and per_step > 0 and work is not None:
+            # Three counts of pixel-Gaussian evaluations, each x the SURVEY 8(d) FP32 issue slots per evaluation:
+            #   frac                      what the kernel EXECUTES: 32 lanes x the (warp, splat) pairs it walks
+            #                             (counted in-kernel by gsb_rasterize_count) -- the roofline fraction;
+            #   frac_composited_pairs     only the pairs that really blend (alpha >= 1/255 before termination):
+            #                             useful work, a strict lower bound;
+            #   frac_reference_algorithm  the reference's dense loop E (every pixel of a tile x every Gaussian up to
+            #                             the tile's last contributor). The kernels cull most of E exactly, so this
+            #                             one can exceed 1: it is a speed-up over the dense algorithm, not a fraction.
+            evals, hits, lane_evals = work
+            to_tf = 2 * slots[name] / (per_step * 1e-3) / 1e12
+            row.update(bound="fp32", achieved=round(lane_evals * to_tf, 2), peak=round(fp32_peak, 2), unit="TFLOP/s",
+                       frac=round(lane_evals * to_tf / fp32_peak, 4), executed_lane_evaluations=lane_evals,
+                       composited_pairs=hits, frac_composited_pairs=round(hits * to_tf / fp32_peak, 4),
+                       reference_evaluations=evals, frac_reference_algorithm=round(evals * to_tf / fp32_peak, 4),
+                       issue_slots_per_evaluation=slots[name])
         out[name] = row
     return out
 
@@ -211,19 +280,20 @@ def run_b200(args):
     from gsplat.b200_impl._lib import lib, timing
     from gsplat.rendering import rasterization
 
-    host = make_cfg2("cpu")
-    names = ("means", "quats", "scales", "opacities", "shs")
+    config = args.config
+    assert config == "cfg2" or world == 1, "--config cfg1 is a single-GPU configuration"
+    host, names, render_kw = make_scene(config, "cpu")
+    WIDTH, HEIGHT = host["width"], host["height"]
     host_params = [host[k][rank::world].contiguous().pin_memory() for k in names]
     viewmats, Ks = host["viewmats"].to(dev), host["Ks"].to(dev)
-    G, gA = loss_weights(dev)
+    G, gA = loss_weights(dev, width=WIDTH, height=HEIGHT)
     n_local = host_params[0].shape[0]
 
     from gsplat.distributed import host_trace
 
-    def iteration(params):
+    def iteration(params, distributed=(world > 1)):
         host_trace.mark()
-        rc, ra, meta = rasterization(*params, viewmats, Ks, WIDTH, HEIGHT, sh_degree=SH_DEGREE, packed=False,
-                                     distributed=(world > 1))
+        rc, ra, meta = rasterization(*params, viewmats, Ks, WIDTH, HEIGHT, distributed=distributed, **render_kw)
         host_trace.mark()
         loss = (rc * G).sum() + (ra * gA).sum()
         loss.backward()
@@ -283,6 +353,7 @@ def run_b200(args):
     out_a = torch.empty((1, HEIGHT, WIDTH, 1), dtype=torch.float32).pin_memory()
     h2d = sum(t.numel() * t.element_size() for t in host_params)
     d2h = out_c.numel() * 4 + out_a.numel() * 4 + 4
+    assert all(t.is_pinned() for t in host_params) and out_c.is_pinned()
 
     # double-buffered: step i+1's host->device copy (copy stream) overlaps step i's kernels; every step
     # still copies all of its inputs from pinned host memory and reads its image + loss back to the host
@@ -353,33 +424,58 @@ def run_b200(args):
     # one more (untimed) iteration on EVERY rank (it contains collectives) to read the stage geometry from `meta`
     for p in params:
         p.grad = None
-    _, _, _, meta = iteration(params)
+    rc_d, ra_d, _, meta = iteration(params)
+    barrier()
+    parity = None
+    if world > 1 and rank == 0:
+        # multi-GPU parity, checked in every recorded run: rank 0 renders its camera from the WHOLE scene on its own
+        # GPU (distributed=False) and compares the distributed image / alpha and the gradients of its shard. Every
+        # rank holds the same camera and loss weights here, so the shard's distributed gradient is world x the
+        # single-camera one.
+        full = [host[k].to(dev).requires_grad_(True) for k in names]
+        rc_s, ra_s, _, _ = iteration(full, distributed=False)
+        g_rel = max(float(((p.grad - world * f.grad[rank::world]).abs().max()
+                           / (world * f.grad[rank::world].abs().max() + 1e-30)).item())
+                    for p, f in zip(params, full))
+        bad = ((rc_d - rc_s).abs() > 1e-4 + 1e-4 * rc_s.abs()).any(-1).float().mean()
+        parity = {"img_max_err": float((rc_d - rc_s).abs().max()), "alpha_max_err": float((ra_d - ra_s).abs().max()),
+                  "img_frac_beyond_1e-4": float(bad), "grad_max_rel": g_rel,
+                  "what": "rank 0: distributed render of its camera vs its own single-GPU render of the whole scene; "
+                          "gradients of its Gaussian shard vs world x the single-GPU ones (max |diff| / max |grad|)"}
+        del full
     barrier()
     if rank == 0:
+        # exchange rows are re-laid out after `meta` is filled when distributed: count on a single GPU only
         # exchange rows are re-laid out after `meta` is filled when distributed: count on a single GPU only
         work = _raster_work_counts(meta, dev) if world == 1 else None
         peaks = measured_peaks()
         clk = clocks.summary()
-        C_local, D, K = 1, 3, (SH_DEGREE + 1) ** 2
+        C_local, D = 1, 3
+        K = (SH_DEGREE + 1) ** 2 if config == "cfg2" else 0
         n_rows = meta["means2d"].shape[1]
         stages = _stage_table(stage_summary, stage_steps, meta, n_rows, C_local, D, K, work, peaks, clk["sm_mhz"])
         top = max((k for k in stages if "bound" in stages[k]), key=lambda k: stages[k]["ms_per_step"])
         roof = {k: stages[top][k] for k in ("bound", "achieved", "peak", "unit", "frac")}
+        for k in ("frac_composited_pairs", "frac_reference_algorithm"):
+            if k in stages[top]:
+                roof[k] = stages[top][k]
         traffic_file = os.path.join(ROOT, "profiles", "ncu_traffic.json")
-        traffic = json.load(open(traffic_file)).get(top) if os.path.exists(traffic_file) else None
-        roof.update(kernel=top, traffic=traffic, peak_source=(
-            "148 SMs*128 lanes*2*sm_max_mhz (no measured FP32 peak in MEASURED_PEAKS.json)"
-            if roof["bound"] == "fp32" else peaks["source"] + " MEASURED_PEAKS.json hbm_gbs"),
-            share_of_step=round(stages[top]["ms_per_step"] / ms_step, 4))
+        traffic = json.load(open(traffic_file)).get(top) if os.path.exists(traffic_file) and config == "cfg2" else None
+        roof.update(kernel=top, traffic=traffic,
+                    traffic_source="profiles/ncu_traffic.json: dram__bytes_read+write per launch from a separate "
+                                   "`ncu --set full` capture of this workload, NOT measured in this run",
+                    peak_source=(peaks["fp32_source"] if roof["bound"] == "fp32"
+                                 else peaks["source"] + " MEASURED_PEAKS.json hbm_gbs"),
+                    share_of_step=round(stages[top]["ms_per_step"] / ms_step, 4))
         line = {
-            "metric": "fwd+bwd render iters/s (1M Gaussians, 1080p)", "value": round(world * 1e3 / ms_step, 3),
+            "metric": METRICS[config], "value": round(world * 1e3 / ms_step, 3),
             "unit": "iters/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "cfg2: 1M Gaussians SH deg 3, 1920x1080, 1 camera per GPU, packed=False"
-                       + (f", Gaussians strided over {world} ranks, distributed=True" if world > 1 else ""),
+            "dtype": "f32", "data": "synthetic" if config == "cfg2" else "reference fixture (garden) + seeded random attributes",
+            "config": {"workload": workload_string(config, world),
                        "n_gaussians_per_gpu": n_local, "n_isects": meta["flatten_ids"].numel(),
-                       "l2": "inputs 236 MB/step > 126 MB L2 and a 256 MB flush write between steps (untimed)",
+                       "l2": "a 256 MB flush write between steps (untimed)"
+                             + ("; inputs 236 MB/step > 126 MB L2" if config == "cfg2" else ""),
                        "timing": "sum of per-step CUDA-event times on the launch stream, max over ranks"},
             "e2e": {"value": round(world * 1e3 / ms_e2e, 3), "unit": "iters/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": round(ms_e2e, 4),
@@ -390,10 +486,12 @@ def run_b200(args):
             "gpu_launches": launches, "wall_s_timed_region": round(wall_s, 3), "clocks": clk,
             "roofline": roof, "stages": stages,
         }
+        if parity is not None:
+            line["parity"] = parity
         if host_trace.enabled:
             line["host_trace_us"] = host_resident
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(rows=2, gauss_stride=8)
+            line["cpu_baseline"] = cpu_baseline(config)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -401,112 +499,171 @@ def run_b200(args):
 
 
 # ------------------------------------------------------------------------------------------------
-# the CPU arm: oracle port of the reference's pure-torch path (_torch_impl) on the host cores
+# the CPU arm: WHOLE iterations of the port of the reference's pure-torch path on the host cores
 # ------------------------------------------------------------------------------------------------
-_WARM = []
-
-
-def _cpu_reference_step(scene, O, rows, gauss_stride):
-    """One bounded sample of a cfg2 fwd+bwd iteration on the CPU; returns the estimated full-iteration seconds.
-
-    Sample: (A) covariance + projection + SH colour forward and backward on every `gauss_stride`-th
-    Gaussian (linear in N, scaled by gauss_stride); (B) tile intersection + sort + offsets on the full
-    scene (unscaled); (C) compositor forward+backward on `rows` of the 68 tile rows (scaled by 68/rows).
-    """
-    W, H = scene["width"], scene["height"]
-    names = ("means", "quats", "scales", "opacities", "shs")
-    t = {}
-    def stage_a():
-        sub = [scene[k][::gauss_stride].clone().requires_grad_(True) for k in names]
-        t0 = time.perf_counter()
-        cov = O.quat_scale_to_covar(sub[1], sub[2])
-        radii, means2d, depths, conics, _ = O.fully_fused_projection(sub[0], cov, scene["viewmats"], scene["Ks"], W, H)
-        dirs = sub[0][None] - torch.inverse(scene["viewmats"])[:, None, :3, 3]
-        col = torch.clamp_min(O.spherical_harmonics(SH_DEGREE, dirs, sub[4][None], masks=radii > 0) + 0.5, 0.0)
-        opac = sub[3][None]
-        t1 = time.perf_counter()
-        outs = [means2d, conics, col, opac]
-        torch.autograd.backward(outs, [torch.ones_like(x) for x in outs])
-        return t1 - t0, time.perf_counter() - t1
-
-    if not _WARM:
-        stage_a()  # first call pays thread-pool / einsum-plan start-up: not part of the baseline
-        _WARM.append(True)
-    t["A_fwd"], t["A_bwd"] = stage_a()
-
-    with torch.no_grad():  # full-size projected splats for (B) and (C)
-        cov = O.quat_scale_to_covar(scene["quats"], scene["scales"])
-        radii, means2d, depths, conics, _ = O.fully_fused_projection(scene["means"], cov, scene["viewmats"],
-                                                                     scene["Ks"], W, H)
-        col = torch.rand(1, radii.shape[1], 3)
-        opac = scene["opacities"][None]
-    tw, th = -(-W // 16), -(-H // 16)
-    t0 = time.perf_counter()
-    _, ids, flat = O.isect_tiles(means2d, radii, depths, 16, tw, th)
-    offs = O.isect_offset_encode(ids, 1, tw, th)
-    t["B_isect"] = time.perf_counter() - t0
-    masks = torch.zeros(1, th, tw, dtype=torch.bool)
-    pick = [int(round((i + 0.5) * th / rows)) for i in range(rows)]
-    masks[0, pick, :] = True
-    p = [x.clone().requires_grad_(True) for x in (means2d, conics, col, opac)]
-    t0 = time.perf_counter()
-    rc, ra = O.rasterize_to_pixels(p[0], p[1], p[2], p[3], W, H, 16, offs, flat, masks=masks)
-    (rc.sum() + ra.sum()).backward()
-    t["C_raster_sample"] = time.perf_counter() - t0
-    # masked-out tiles still cost the python loop a little; measure that overhead and remove it
-    t0 = time.perf_counter()
-    O.rasterize_to_pixels(means2d, conics, col, opac, W, H, 16, offs, flat, masks=torch.zeros_like(masks))
-    t["C_loop_overhead"] = time.perf_counter() - t0
-    raster = max(t["C_raster_sample"] - t["C_loop_overhead"] * (th - rows) / th, 1e-6) * th / rows
-    est = gauss_stride * (t["A_fwd"] + t["A_bwd"]) + t["B_isect"] + raster
-    return est, t
-
-
 def _load_oracle():
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import c_oracle
     import gs_oracle
 
+    c_oracle.build()
     return gs_oracle
 
 
-def cpu_baseline(rows=2, gauss_stride=8):
-    O = _load_oracle()
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    scene = make_cfg2("cpu")
-    est, parts = _cpu_reference_step(scene, O, rows, gauss_stride)
-    return {"value": round(1.0 / est, 6), "unit": "iters/s", "cores": cores, "kind": "port",
-            "sample": (f"oracle/gs_oracle.py (port of the reference's _torch_impl path): projection+SH fwd+bwd on every "
-                       f"{gauss_stride}th Gaussian (x{gauss_stride}), isect+sort+offsets on the full 1M scene, compositor "
-                       f"fwd+bwd on {rows} of 68 tile rows (x68/{rows}); estimated full iteration {est:.1f} s"),
-            "parts_s": {k: round(v, 3) for k, v in parts.items()}}
+def _load_reference_torch_impl():
+    """The reference's own gsplat/cuda/_torch_impl.py from baseline/_ref (tools/install_reference.sh), loaded as a
+    stand-alone module (its only package-relative import sits in `_rasterize_to_pixels`, which cannot run: nerfacc +
+    a CUDA op). None when baseline/_ref is absent."""
+    import importlib.util
+
+    path = os.path.join(ROOT, "baseline", "_ref", "gsplat", "cuda", "_torch_impl.py")
+    if not os.path.exists(path):
+        return None
+    spec = importlib.util.spec_from_file_location("_gsplat_ref_torch_impl", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+class CpuArm:
+    """One fwd+bwd iteration of `rasterization()` on the CPU, same inputs and loss as the b200 arm.
+
+    cfg2: oracle/gs_oracle.py (restated `_torch_impl` projection / SH / vectorised isect_tiles / offsets) +
+          oracle/gs_compositor.c (OpenMP) — kind "port".
+    cfg1: the reference's OWN `_torch_impl` functions for covariance, projection and offsets when baseline/_ref is
+          present (else the restatement), the vectorised isect_tiles restatement (the reference's is a Python double
+          loop: timed once and reported beside), the C compositor. `impl` in the report says which ran per stage."""
+
+    def __init__(self, config):
+        self.O = _load_oracle()
+        self.config = config
+        self.scene, self.names, kw = make_scene(config, "cpu")
+        self.kw = {k: v for k, v in kw.items() if k != "packed"}
+        self.G, self.gA = loss_weights("cpu", width=self.scene["width"], height=self.scene["height"])
+        self.T = _load_reference_torch_impl() if config == "cfg1" else None
+        self.cores = os.cpu_count() or 1
+        torch.set_num_threads(self.cores)
+        self.impl = {
+            "covariance+projection": "reference gsplat/cuda/_torch_impl.py (baseline/_ref)" if self.T else
+                                     "port oracle/gs_oracle.py",
+            "spherical_harmonics": "port oracle/gs_oracle.py" if config == "cfg2" else "n/a (colours [N,3])",
+            "isect_tiles": "port oracle/gs_oracle.py (vectorised; the reference's is a Python double loop)",
+            "isect_offset_encode": "reference _torch_impl.py" if self.T else "port oracle/gs_oracle.py",
+            "rasterize_to_pixels fwd+bwd": "port oracle/gs_compositor.c (OpenMP, all cores)",
+        }
+
+    def step(self):
+        """-> (seconds, per-stage forward seconds)."""
+        s, O = self.scene, self.O
+        leaves = [s[k].clone().requires_grad_(True) for k in self.names]
+        timers = {}
+        t0 = time.perf_counter()
+        if self.T is None:
+            rc, ra, _ = O.rasterization(*leaves, s["viewmats"], s["Ks"], s["width"], s["height"], compositor="c",
+                                        timers=timers, **self.kw)
+        else:
+            rc, ra = self._reference_pipeline(leaves, timers)
+        t1 = time.perf_counter()
+        ((rc * self.G).sum() + (ra * self.gA).sum()).backward()
+        t2 = time.perf_counter()
+        timers.update(forward_s=t1 - t0, backward_s=t2 - t1)
+        return t2 - t0, timers
+
+    def _reference_pipeline(self, leaves, timers):
+        import c_oracle
+
+        s, O, T = self.scene, self.O, self.T
+        means, quats, scales, opac, colors = leaves
+        W, H, C = s["width"], s["height"], s["viewmats"].shape[0]
+        t0 = time.perf_counter()
+        covars, _ = T._quat_scale_to_covar_preci(quats, scales, True, False, triu=False)
+        radii, means2d, depths, conics, _ = T._fully_fused_projection(means, covars, s["viewmats"], s["Ks"], W, H)
+        t1 = time.perf_counter()
+        tw, th = -(-W // 16), -(-H // 16)
+        _, ids, flat = O.isect_tiles(means2d.detach(), radii, depths.detach(), 16, tw, th, bits_rule="cuda")
+        offs = T._isect_offset_encode(ids, C, tw, th)
+        t2 = time.perf_counter()
+        rc, ra = c_oracle.rasterize_to_pixels(means2d, conics, colors.expand(C, -1, -1), opac.repeat(C, 1), W, H, 16,
+                                              offs, flat)
+        timers.update(projection_colors_fwd_s=t1 - t0, isect_sort_offsets_s=t2 - t1,
+                      compositor_fwd_s=time.perf_counter() - t2)
+        self._projected = (means2d.detach(), radii, depths.detach(), tw, th)
+        return rc, ra
+
+    def reference_isect_loop_seconds(self):
+        """The reference's own `_isect_tiles` (Python double loop, _torch_impl.py:331) on the projected scene."""
+        if self.T is None or not hasattr(self, "_projected"):
+            return None
+        m, r, d, tw, th = self._projected
+        t0 = time.perf_counter()
+        self.T._isect_tiles(m, r, d, 16, tw, th)
+        return time.perf_counter() - t0
+
+    def describe(self, steps_measured, seconds):
+        return (f"{steps_measured} WHOLE fwd+bwd iteration(s) of {WORKLOADS[self.config]} on {self.cores} host threads "
+                f"({seconds:.1f} s measured), nothing sampled or extrapolated")
+
+
+def cpu_baseline(config="cfg2", budget_s=25.0):
+    """The `cpu_baseline` object of the b200 line: whole CPU iterations (one warm-up, then as many as fit the
+    budget, at least one)."""
+    arm = CpuArm(config)
+    arm.step()
+    times, parts = [], {}
+    while not times or (sum(times) + times[-1] < budget_s and len(times) < 20):
+        t, parts = arm.step()
+        times.append(t)
+    mean = sum(times) / len(times)
+    out = {"value": round(1.0 / mean, 6), "unit": "iters/s", "cores": arm.cores, "kind": "port",
+           "sample": arm.describe(len(times), sum(times)), "steps_measured": len(times),
+           "s_per_step": round(mean, 3), "impl": arm.impl, "parts_s": {k: round(v, 3) for k, v in parts.items()}}
+    if config == "cfg1":
+        loop = arm.reference_isect_loop_seconds()
+        if loop is not None:
+            out["reference_isect_tiles_python_loop_s"] = round(loop, 2)
+    return out
 
 
 def run_reference(args):
-    """`--impl reference`: the reference's CPU path for cfg2 (oracle port) on all host cores, rank 0 only."""
+    """`--impl reference`: whole CPU iterations of the same workload, rank 0 only, on all host cores."""
     if int(os.environ.get("RANK", 0)) != 0:
         return
-    O = _load_oracle()
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    scene = make_cfg2("cpu")
-    total = args.steps + args.warmup
-    rows, stride = (2, 8) if total <= 12 else (1, 16)
+    config = args.config
+    arm = CpuArm(config)
+    budget = float(os.environ.get("GSPLAT_BENCH_CPU_BUDGET_S", 420.0))
+    t_begin = time.perf_counter()
+    warm = 0
     for _ in range(args.warmup):
-        _cpu_reference_step(scene, O, rows, stride)
-    ests = [_cpu_reference_step(scene, O, rows, stride)[0] for _ in range(args.steps)]
-    est = sum(ests) / len(ests)
-    value = round(1.0 / est, 6)
-    sample = (f"per step: projection+SH fwd+bwd on every {stride}th Gaussian (x{stride}), isect+sort+offsets on the "
-              f"full scene, compositor fwd+bwd on {rows} of 68 tile rows (x68/{rows}); oracle/gs_oracle.py")
+        # warm-ups are whole iterations too; they stop early when they would eat more than a third of the budget
+        if warm and time.perf_counter() - t_begin > budget / 3:
+            break
+        arm.step()
+        warm += 1
+    times, parts = [], {}
+    for _ in range(args.steps):
+        t, parts = arm.step()
+        times.append(t)
+        if time.perf_counter() - t_begin + t > budget:
+            break
+    mean = sum(times) / len(times)
+    value = round(1.0 / mean, 6)
+    base = {"value": value, "unit": "iters/s", "cores": arm.cores, "kind": "port",
+            "sample": arm.describe(len(times), sum(times)), "impl": arm.impl,
+            "parts_s": {k: round(v, 3) for k, v in parts.items()}}
+    if config == "cfg1":
+        loop = arm.reference_isect_loop_seconds()
+        if loop is not None:
+            base["reference_isect_tiles_python_loop_s"] = round(loop, 2)
     print(json.dumps({
-        "impl": "reference", "metric": "fwd+bwd render iters/s (1M Gaussians, 1080p)", "value": value,
-        "unit": "iters/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": round(est * 1e3, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "cfg2: 1M Gaussians SH deg 3, 1920x1080, 1 camera, packed=False (CPU, extrapolated "
-                               "from a bounded sample per step)"},
-        "cpu_baseline": {"value": value, "unit": "iters/s", "cores": cores, "kind": "port", "sample": sample},
+        "impl": "reference", "metric": METRICS[config], "value": value,
+        "unit": "iters/s", "n_gpus": args.gpus, "steps": len(times), "steps_requested": args.steps,
+        "warmup": warm, "warmup_requested": args.warmup,
+        "ms_per_step": round(mean * 1e3, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic" if config == "cfg2" else "reference fixture (garden) + seeded random attributes",
+        "config": {"workload": workload_string(config, args.gpus),
+                   "cpu_arm": "whole iterations on the host cores of rank 0 (one camera render per iteration); "
+                              f"wall budget {budget:.0f} s: `steps` is the number of whole iterations measured"},
+        "cpu_baseline": base,
         "e2e": {"value": value, "unit": "iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }), flush=True)
@@ -518,6 +675,8 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="cfg2", choices=["cfg2", "cfg1"],
+                    help="cfg2 = BASELINE configs[1] (the metric's configuration); cfg1 = configs[0] (garden, N=1 only)")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the CPU leg (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -47,7 +47,7 @@ rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
                      const int32_t *__restrict__ offsets, const int32_t *__restrict__ flatten_ids,
                      float *__restrict__ out_colors, float *__restrict__ out_alphas,
                      int32_t *__restrict__ last_ids, const int64_t *__restrict__ n_isects_dev,
-                     uint8_t *__restrict__ block_masks) {
+                     uint8_t *__restrict__ block_masks, unsigned long long *__restrict__ warp_pairs) {
     // speculatively sized intersection buffers: n_isects is their capacity, the count lives on the device
     if (n_isects_dev != nullptr) n_isects = min(n_isects, (int64_t)*n_isects_dev);
     // staged batch: three float4 arrays with the same 16-byte stride, so one address computation serves all
@@ -72,6 +72,7 @@ rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
     // |T| is the transmittance; T < 0 marks a finished pixel (saturated, or outside the image)
     float T = tg.inside ? 1.0f : -1.0f;
     int cur = 0;
+    unsigned n_pairs = 0;  // COUNT only: (warp, splat) pairs this warp walked
 
     const bool render = (masks == nullptr) || masks[tg.tile_id];
     if (render) {
@@ -120,6 +121,7 @@ rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
                 while (todo) {
                     const int j = c0 + __ffs(todo) - 1;
                     todo &= todo - 1u;
+                    if (COUNT) ++n_pairs;
                     const float4 p4 = st.P[j];
                     const float4 b4 = st.B[j];
                     const float dx = p4.x - pxf, dy = p4.y - pyf;
@@ -157,6 +159,7 @@ rasterize_fwd_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, c
         }
     }
     T = fabsf(T);
+    if (COUNT && warp_pairs != nullptr && lane == 0 && n_pairs) atomicAdd(warp_pairs, (unsigned long long)n_pairs);
 
     if (tg.inside) {
         float *oc = out_colors + tg.pix_id * D;
@@ -177,7 +180,7 @@ int launch_fwd(int C, int64_t n_isects, const float *recA, const float *recB, co
     rasterize_fwd_kernel<D><<<grid, kThreads, 0, stream>>>(
         C, n_isects, reinterpret_cast<const float4 *>(recA), reinterpret_cast<const float4 *>(recB), colors,
         backgrounds, masks, W, H, tw, th, offsets, flatten_ids, out_colors, out_alphas, last_ids, n_isects_dev,
-        block_masks);
+        block_masks, nullptr);
     return gsb_check_launch("rasterize_fwd");
 }
 
@@ -240,7 +243,8 @@ extern "C" int gsb_rasterize_fwd_cap(int C, int64_t n_isects, const int64_t *n_i
 extern "C" int gsb_rasterize_count(int C, int64_t n_isects, const float *recA, const float *recB, const float *ones,
                                    int width, int height, int tile_size, int tile_width, int tile_height,
                                    const int32_t *isect_offsets, const int32_t *flatten_ids, float *counts,
-                                   float *render_alphas, int32_t *last_ids, cudaStream_t stream) {
+                                   float *render_alphas, int32_t *last_ids, int64_t *warp_pairs,
+                                   cudaStream_t stream) {
     GSB_REQUIRE(C >= 0 && n_isects >= 0 && width > 0 && height > 0, "bad sizes");
     GSB_REQUIRE(tile_size == raster::kTile, "tile_size must be 16");
     GSB_REQUIRE(tile_width * tile_size >= width && tile_height * tile_size >= height, "tile grid smaller than image");
@@ -249,6 +253,6 @@ extern "C" int gsb_rasterize_count(int C, int64_t n_isects, const float *recA, c
     raster::rasterize_fwd_kernel<1, true><<<grid, raster::kThreads, 0, stream>>>(
         C, n_isects, reinterpret_cast<const float4 *>(recA), reinterpret_cast<const float4 *>(recB), ones, nullptr,
         nullptr, width, height, tile_width, tile_height, isect_offsets, flatten_ids, counts, render_alphas, last_ids,
-        nullptr, nullptr);
+        nullptr, nullptr, reinterpret_cast<unsigned long long *>(warp_pairs));
     return gsb_check_launch("rasterize_count");
 }

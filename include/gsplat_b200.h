@@ -204,11 +204,13 @@ int gsb_rasterize_fwd_cap(int C, int64_t n_isects, const int64_t *n_isects_dev, 
                           const int32_t *isect_offsets, const int32_t *flatten_ids, float *render_colors,
                           float *render_alphas, int32_t *last_ids, uint8_t *block_masks, cudaStream_t stream);
 /* diagnostics: counts[C,H,W] = number of Gaussians composited into each pixel (ones: float[P] of 1.0f);
- * same traversal as gsb_rasterize_fwd with D = 1. Used by bench.py for the useful-work roofline. */
+ * same traversal as gsb_rasterize_fwd with D = 1. warp_pairs (zero-filled int64[1] or NULL) receives the number of
+ * (warp, splat) pairs the kernel walked: x 32 lanes = the pixel-Gaussian evaluations it EXECUTED (bench.py's
+ * executed-work roofline). */
 int gsb_rasterize_count(int C, int64_t n_isects, const float *recA, const float *recB, const float *ones, int width,
                         int height, int tile_size, int tile_width, int tile_height, const int32_t *isect_offsets,
                         const int32_t *flatten_ids, float *counts, float *render_alphas, int32_t *last_ids,
-                        cudaStream_t stream);
+                        int64_t *warp_pairs, cudaStream_t stream);
 /* v_means2d[P,2], v_conics[P,3], v_colors[P,D], v_opacities[P] must be ZERO-filled by the caller
  * (the kernel accumulates with atomics); v_means2d_abs[P,2] (zero-filled) or NULL.
  * block_masks: what gsb_rasterize_fwd_cap wrote for the same inputs, or NULL (recomputed). */

@@ -400,14 +400,17 @@ def rasterization(
     means, quats, scales, opacities, colors, viewmats, Ks, width, height,
     near_plane=0.01, far_plane=1e10, radius_clip=0.0, eps2d=0.3, sh_degree=None, tile_size=16,
     backgrounds=None, render_mode="RGB", rasterize_mode="classic", camera_model="pinhole", covars=None,
-    bits_rule="triton", compositor="torch", pixel_weight=None,
+    bits_rule="triton", compositor="torch", pixel_weight=None, timers=None,
 ):
     """CPU restatement of rendering.py:44-598 for packed=False, distributed=False.
 
     `compositor="c"` composites with oracle/gs_compositor.c (OpenMP; full-size scenes in seconds) instead of the
     torch-autograd restatement above; `meta` then also carries `margin` (per-pixel distance of the closest
     threshold decision, see gs_compositor.c) and `last_ids`, and `pixel_weight` (bool [C,H,W]) removes pixels
-    from the backward pass."""
+    from the backward pass. `timers` (dict) receives the forward wall time of the three stage groups."""
+    import time
+
+    t_start = time.perf_counter()
     C = viewmats.shape[0]
     if covars is None:
         covars = quat_scale_to_covar(quats, scales)
@@ -435,8 +438,10 @@ def rasterization(
         if backgrounds is not None:
             backgrounds = torch.zeros(C, 1)
     tw, th = math.ceil(width / float(tile_size)), math.ceil(height / float(tile_size))
+    t_proj = time.perf_counter()
     tiles_per_gauss, isect_ids, flatten_ids = isect_tiles(means2d, radii, depths, tile_size, tw, th, bits_rule=bits_rule)
     offsets = isect_offset_encode(isect_ids, C, tw, th, bits_rule=bits_rule)
+    t_isect = time.perf_counter()
     extra = {}
     if compositor == "c":
         import c_oracle
@@ -450,6 +455,9 @@ def rasterization(
         render_colors, render_alphas = rasterize_to_pixels(
             means2d, conics, cols, opac, width, height, tile_size, offsets, flatten_ids, backgrounds=backgrounds
         )
+    if timers is not None:
+        timers.update(projection_colors_fwd_s=t_proj - t_start, isect_sort_offsets_s=t_isect - t_proj,
+                      compositor_fwd_s=time.perf_counter() - t_isect)
     if render_mode in ("ED", "RGB+ED"):
         render_colors = torch.cat(
             [render_colors[..., :-1], render_colors[..., -1:] / render_alphas.clamp(min=1e-10)], dim=-1

@@ -8,8 +8,8 @@ the reference's Python-loop `_isect_tiles`; it is compared with the oracle pipel
 inputs and end to end.
 
 Tolerances (north_star): forward rtol 1e-4 (+ atol 1e-4, tests/test_rasterization.py:88-89 of the reference),
-gradients rtol 1e-3 (quats 5e-3, scales 5e-2 as triton_tests/test_fused_proj.py:159-162) + 2e-4 of the largest
-gradient entry. No blanket outlier allowance: see tests/parity.py.
+gradients rtol 1e-3 (quats 5e-3, scales 5e-2 as triton_tests/test_fused_proj.py:159-162) + 1e-4 of the largest
+gradient entry (measured on a B200: <= 6e-5, profiles/r02a_parity_report.txt). No blanket outlier allowance: see tests/parity.py.
 """
 import os
 import sys
@@ -25,6 +25,20 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda"
 GRAD_TOL = {"means": 1e-3, "quats": 5e-3, "scales": 5e-2, "opacities": 1e-3, "colors": 1e-3}
 NAMES = tuple(GRAD_TOL)
+
+
+def _check_radii(r_gpu, r_cpu, what):
+    """SURVEY 8a hazard 1: radii are not bit-exact between any two implementations (the reference's tests allow
+    atol=1). Reported: exact-match rate, max |delta| where both sides keep the Gaussian, and visibility flips (one
+    side culls what the other keeps: a cull test sitting on its threshold)."""
+    r_gpu, r_cpu = r_gpu.cpu().long(), r_cpu.long()
+    both = (r_gpu > 0) & (r_cpu > 0)
+    rep = {"what": what, "exact_match_rate": float((r_gpu == r_cpu).float().mean()),
+           "max_abs_delta_both_visible": int((r_gpu - r_cpu).abs()[both].max()) if both.any() else 0,
+           "visibility_flips": int(((r_gpu > 0) != (r_cpu > 0)).sum()), "n": r_gpu.numel()}
+    print("PARITY radii", rep)
+    assert rep["exact_match_rate"] > 1 - 1e-3 and rep["max_abs_delta_both_visible"] <= 1, rep
+    assert rep["visibility_flips"] <= 1e-5 * rep["n"] + 1, rep
 
 
 def _loss_weights(shape_c, shape_a, seed=1):
@@ -77,13 +91,10 @@ def test_cfg1_full_size_matches_the_reference_golden_and_oracle():
     # (2) and against the oracle pipeline
     assert_close_classified(rc, o_rc, flag, 1e-4, 1e-4, "cfg1 colours vs oracle")
     # (3) radii: exact-match rate and max |delta| (SURVEY 8a hazard 1; reference tests allow atol=1 everywhere)
-    r_gpu, r_cpu = meta["radii"].cpu().long(), o_meta["radii"].long()
-    mism = (r_gpu != r_cpu)
-    print("PARITY radii", {"exact_match_rate": 1 - float(mism.float().mean()), "max_abs_delta": int((r_gpu - r_cpu).abs().max())})
-    assert float(mism.float().mean()) < 1e-3 and int((r_gpu - r_cpu).abs().max()) <= 1
+    _check_radii(meta["radii"], o_meta["radii"], "cfg1 radii vs oracle")
     # (4) gradients, flagged pixels removed from the loss on both sides: zero outliers
     for name, a, b in zip(NAMES, grads, o_grads):
-        assert_grads_close(a, b, GRAD_TOL[name], 2e-4, f"cfg1 v_{name} vs oracle (masked loss)")
+        assert_grads_close(a, b, GRAD_TOL[name], 1e-4, f"cfg1 v_{name} vs oracle (masked loss)")
     # (5) gradients under the FULL loss against the reference's frozen rows (every 16th Gaussian): flips stay in
     leaves = [t.clone().to(DEV).requires_grad_(True) for t in cpu]
     from gsplat.rendering import rasterization
@@ -108,7 +119,7 @@ def test_cfg1_three_cameras_packed_and_unpacked(packed):
     assert_close_classified(rc[..., 3:], o_rc[..., 3:], flag, 1e-4, 1e-4, "3-camera expected depth vs oracle")
     assert_close_classified(ra, o_ra, flag, 1e-4, 1e-4, "3-camera alphas vs oracle")
     for name, a, b in zip(NAMES, grads, o_grads):
-        assert_grads_close(a, b, GRAD_TOL[name], 2e-4, f"3-camera v_{name} vs oracle (masked loss)")
+        assert_grads_close(a, b, GRAD_TOL[name], 1e-4, f"3-camera v_{name} vs oracle (masked loss)")
 
 
 def test_cfg2_full_size_stagewise_and_end_to_end():
@@ -125,11 +136,8 @@ def test_cfg2_full_size_stagewise_and_end_to_end():
     assert_close_classified(rc, o_rc, flag, 1e-4, 1e-4, "cfg2 colours vs oracle")
     assert_close_classified(ra, o_ra, flag, 1e-4, 1e-4, "cfg2 alphas vs oracle")
     for name, a, b in zip(NAMES, grads, o_grads):
-        assert_grads_close(a, b, GRAD_TOL[name], 2e-4, f"cfg2 v_{name} vs oracle (masked loss)")
-    r_gpu, r_cpu = meta["radii"].cpu().long(), o_meta["radii"].long()
-    print("PARITY radii", {"exact_match_rate": float((r_gpu == r_cpu).float().mean()),
-                           "max_abs_delta": int((r_gpu - r_cpu).abs().max())})
-    assert float((r_gpu != r_cpu).float().mean()) < 1e-3 and int((r_gpu - r_cpu).abs().max()) <= 1
+        assert_grads_close(a, b, GRAD_TOL[name], 1e-4, f"cfg2 v_{name} vs oracle (masked loss)")
+    _check_radii(meta["radii"], o_meta["radii"], "cfg2 radii vs oracle")
 
     # stage-wise on IDENTICAL inputs: the oracle's projection outputs through the CUDA intersection stage are
     # bit-exact (protocol of triton_tests/test_isect.py:66-89) ...
