@@ -19,7 +19,7 @@ import torch
 
 import gs_oracle as O
 from conftest import garden_scene, load_golden
-from parity import assert_close_classified, assert_grads_close, flagged_pixels, tile_list_hash
+from parity import assert_close_classified, assert_grads_close, flagged_pixels, run_pair
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
@@ -46,34 +46,9 @@ def _loss_weights(shape_c, shape_a, seed=1):
     return torch.rand(shape_c, generator=g), torch.rand(shape_a, generator=g)
 
 
-def _global_ids(meta, N):
-    """flatten_ids as indices into the dense [C, N] grid (packed rows are mapped through their ids)."""
-    flat = meta["flatten_ids"].long()
-    if meta.get("camera_ids") is not None:
-        flat = (meta["camera_ids"].long() * N + meta["gaussian_ids"].long())[flat]
-    return flat
-
-
 def _run_pair(cpu_leaves, viewmats, Ks, W, H, kw, packed=False):
-    """GPU rasterization() and the oracle pipeline (C compositor) on the same inputs, gradients under a loss from
-    which the flagged pixels are removed on both sides. Returns everything the assertions need."""
-    from gsplat.rendering import rasterization
-
-    N = cpu_leaves[0].shape[0]
-    leaves = [t.clone().to(DEV).requires_grad_(True) for t in cpu_leaves]
-    rc, ra, meta = rasterization(*leaves, viewmats.to(DEV), Ks.to(DEV), W, H, packed=packed, **kw)
-    o_leaves = [t.clone().requires_grad_(True) for t in cpu_leaves]
-    o_rc, o_ra, o_meta = O.rasterization(*o_leaves, viewmats, Ks, W, H, compositor="c", **kw)
-    h_gpu = tile_list_hash(_global_ids(meta, N), meta["isect_offsets"])
-    h_cpu = tile_list_hash(o_meta["flatten_ids"], o_meta["isect_offsets"])
-    flag, info = flagged_pixels(o_meta["margin"], H, W, 16, h_gpu, h_cpu)
-    print("PARITY flags", info)
-    w_c, w_a = _loss_weights(o_rc.shape, o_ra.shape)
-    keep = (~flag)[..., None].float()
-    w_c, w_a = w_c * keep, w_a * keep
-    grads = torch.autograd.grad((rc * w_c.to(DEV)).sum() + (ra * w_a.to(DEV)).sum(), leaves)
-    o_grads = torch.autograd.grad((o_rc * w_c).sum() + (o_ra * w_a).sum(), o_leaves)
-    return rc, ra, meta, grads, o_rc, o_ra, o_meta, o_grads, flag
+    r = run_pair(cpu_leaves, viewmats, Ks, W, H, kw, packed=packed)
+    return (r["rc"], r["ra"], r["meta"], r["grads"], r["o_rc"], r["o_ra"], r["o_meta"], r["o_grads"], r["flag"])
 
 
 def test_cfg1_full_size_matches_the_reference_golden_and_oracle():

@@ -25,7 +25,9 @@ def _close(a, b, rtol=1e-4, atol=1e-4, **kw):
 def _close_frac(a, b, rtol, atol, max_bad=1e-3):
     """assert_close allowing a tiny fraction of outliers (threshold flips near alpha=1/255 etc.)."""
     a, b = a.cpu().double(), b.cpu().double()
-    bad = ((a - b).abs() > atol + rtol * b.abs()).double().mean().item()
+    err = (a - b).abs()
+    bad = (err > atol + rtol * b.abs()).double().mean().item()
+    print("PARITY stage", {"outlier_frac": bad, "n": a.numel(), "max_err": float(err.max()), "max_ref": float(b.abs().max())})
     assert bad <= max_bad, f"{bad:.2e} of the elements differ beyond rtol={rtol} atol={atol}"
 
 
