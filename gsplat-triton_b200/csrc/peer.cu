@@ -78,6 +78,7 @@ __device__ __forceinline__ void publish_when_grid_done(const PeerTable &peers, i
 // are views of ONE buffer with the same layout, so unpacking is a straight vectorised copy, and every
 // (camera, field) run a sender owns is contiguous on both sides.
 constexpr int kFields = 6;
+constexpr int kPackedFields = 8;  // + camera ids, Gaussian ids (packed rows only)
 struct Fields {
     const float *src[kFields];
     int width[kFields];
@@ -141,6 +142,56 @@ put_bwd_kernel(PeerTable peers, Fields fields, RankBases bases, int world, int r
                  field_offset(fields.width, f, (int64_t)world * C_local * N_dest) +
                  ((int64_t)rank * C_local + c_local) * N_dest * w;
     copy_run(src, dst, N_dest * w);
+    publish_when_grid_done(peers, world, rank, 1, epoch);
+}
+
+// ---- packed rows (COO): variable row counts per destination --------------------------------------------
+// The sender's packed rows are camera-major, so the rows owned by destination rank d are one contiguous run
+// [src_start[d], src_start[d] + count[d]); they land in d's table (dst_rows[d] rows, same SoA layout, two extra
+// int32 fields) at row dst_base[d] = rows of lower-ranked senders. The id fields are rebased on the fly: camera ids
+// global -> local to the destination, Gaussian ids local -> global (rendering.py:436-451 of the reference).
+struct PackedPlan {
+    int64_t src_start[kMaxPeers], count[kMaxPeers], dst_base[kMaxPeers], dst_rows[kMaxPeers], cam_base[kMaxPeers];
+    int64_t gauss_base;
+};
+struct PackedFields {
+    const void *src[kPackedFields];
+    int width[kPackedFields];
+};
+
+__global__ void __launch_bounds__(kThreads)
+put_packed_fwd_kernel(PeerTable peers, PackedFields fields, PackedPlan plan, int world, int rank,
+                      int64_t region_offset, unsigned long long epoch) {
+    const int f = blockIdx.y / world;
+    const int dest = (blockIdx.y % world + rank + 1) % world;  // rotated by rank: no incast at start
+    const int w = fields.width[f];
+    const int64_t n = plan.count[dest];
+    float *dst = reinterpret_cast<float *>(peers.base[dest] + region_offset) +
+                 field_offset(fields.width, f, plan.dst_rows[dest]) + plan.dst_base[dest] * w;
+    if (f < kFields) {
+        copy_run(reinterpret_cast<const float *>(fields.src[f]) + plan.src_start[dest] * w, dst, n * w);
+    } else {
+        const int64_t *ids = reinterpret_cast<const int64_t *>(fields.src[f]) + plan.src_start[dest];
+        const int64_t shift = (f == kFields) ? -plan.cam_base[dest] : plan.gauss_base;
+        int32_t *d32 = reinterpret_cast<int32_t *>(dst);
+        for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads)
+            d32[i] = (int32_t)(ids[i] + shift);
+    }
+    publish_when_grid_done(peers, world, rank, 0, epoch);
+}
+
+// backward: the gradient rows this rank holds for sender r's Gaussians ([src_start[r], +count[r]) of its table)
+// go back to r, at rows [dst_base[r], +count[r]) of r's packed order (dst_rows[r] = nnz of r)
+__global__ void __launch_bounds__(kThreads)
+put_packed_bwd_kernel(PeerTable peers, PackedFields fields, PackedPlan plan, int world, int rank,
+                      int64_t region_offset, unsigned long long epoch) {
+    const int f = blockIdx.y / world;
+    const int dest = (blockIdx.y % world + rank + 1) % world;
+    const int w = fields.width[f];
+    const float *src = reinterpret_cast<const float *>(fields.src[f]);
+    float *dst = reinterpret_cast<float *>(peers.base[dest] + region_offset) +
+                 field_offset(fields.width, f, plan.dst_rows[dest]) + plan.dst_base[dest] * w;
+    copy_run(src ? src + plan.src_start[dest] * w : nullptr, dst, plan.count[dest] * w);
     publish_when_grid_done(peers, world, rank, 1, epoch);
 }
 
@@ -248,8 +299,8 @@ extern "C" int gsb_peer_flag_free(void *flag_host) {
 }
 
 extern "C" int64_t gsb_a2a_field_offset(int64_t rows, int D, int field) {
-    const int width[kFields] = {2, 1, 3, 1, D, 1};
-    if (field < 0 || field > kFields) return -1;
+    const int width[kPackedFields] = {2, 1, 3, 1, D, 1, 1, 1};
+    if (field < 0 || field > kPackedFields) return -1;
     return field_offset(width, field, rows);
 }
 
@@ -317,4 +368,72 @@ extern "C" int gsb_a2a_wait_copy(int world, int dir, int64_t epoch, const void *
                                                    (unsigned long long)epoch, region_offset, n_floats, out,
                                                    timeout_flag);
     return gsb_check_launch("a2a_wait_copy");
+}
+
+namespace {
+int fill_plan(PackedPlan &plan, int world, const int64_t *counts, const int64_t *dst_base, const int64_t *dst_rows,
+              const int64_t *cam_base, int64_t gauss_base, int64_t &widest) {
+    int64_t at = 0;
+    widest = 0;
+    for (int i = 0; i < kMaxPeers; ++i) {
+        const bool in = i < world;
+        plan.src_start[i] = at;
+        plan.count[i] = in ? counts[i] : 0;
+        plan.dst_base[i] = in ? dst_base[i] : 0;
+        plan.dst_rows[i] = in ? dst_rows[i] : 0;
+        plan.cam_base[i] = (in && cam_base) ? cam_base[i] : 0;
+        if (in && (counts[i] < 0 || dst_base[i] < 0 || dst_base[i] + counts[i] > dst_rows[i])) return -1;
+        at += plan.count[i];
+        if (plan.count[i] > widest) widest = plan.count[i];
+    }
+    plan.gauss_base = gauss_base;
+    return 0;
+}
+}  // namespace
+
+extern "C" int gsb_a2a_put_packed_fwd(int world, int rank, int D, const int64_t *send_counts_host,
+                                      const int64_t *dst_row_base_host, const int64_t *dst_rows_host,
+                                      const int64_t *cam_base_host, int64_t gauss_base, const float *means2d,
+                                      const float *depths, const float *conics, const float *opacities,
+                                      const float *colors, const int32_t *radii, const int64_t *camera_ids,
+                                      const int64_t *gaussian_ids, const void *const *peer_bases_host,
+                                      int64_t region_offset, int64_t epoch, cudaStream_t stream) {
+    GSB_REQUIRE(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world && D >= 1, "bad world/rank");
+    GSB_REQUIRE(send_counts_host && dst_row_base_host && dst_rows_host && cam_base_host, "null plan");
+    GSB_REQUIRE(region_offset >= kHeaderBytes && epoch > 0, "bad region/epoch");
+    PeerTable peers;
+    GSB_REQUIRE(fill_peers(peers, peer_bases_host, world) == 0, "null peer mailbox");
+    PackedPlan plan;
+    int64_t widest = 0;
+    GSB_REQUIRE(fill_plan(plan, world, send_counts_host, dst_row_base_host, dst_rows_host, cam_base_host, gauss_base,
+                          widest) == 0, "inconsistent row plan");
+    PackedFields fields = {{means2d, depths, conics, opacities, colors, radii, camera_ids, gaussian_ids},
+                           {2, 1, 3, 1, D, 1, 1, 1}};
+    dim3 grid(blocks_per_run(widest * (D > 3 ? D : 3)), (unsigned)(world * kPackedFields));
+    put_packed_fwd_kernel<<<grid, kThreads, 0, stream>>>(peers, fields, plan, world, rank, region_offset,
+                                                        (unsigned long long)epoch);
+    return gsb_check_launch("a2a_put_packed_fwd");
+}
+
+extern "C" int gsb_a2a_put_packed_bwd(int world, int rank, int D, const int64_t *recv_counts_host,
+                                      const int64_t *dst_row_base_host, const int64_t *dst_rows_host,
+                                      const float *v_means2d, const float *v_depths, const float *v_conics,
+                                      const float *v_opacities, const float *v_colors,
+                                      const void *const *peer_bases_host, int64_t region_offset, int64_t epoch,
+                                      cudaStream_t stream) {
+    GSB_REQUIRE(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world && D >= 1, "bad world/rank");
+    GSB_REQUIRE(recv_counts_host && dst_row_base_host && dst_rows_host, "null plan");
+    GSB_REQUIRE(region_offset >= kHeaderBytes && epoch > 0, "bad region/epoch");
+    PeerTable peers;
+    GSB_REQUIRE(fill_peers(peers, peer_bases_host, world) == 0, "null peer mailbox");
+    PackedPlan plan;
+    int64_t widest = 0;
+    GSB_REQUIRE(fill_plan(plan, world, recv_counts_host, dst_row_base_host, dst_rows_host, nullptr, 0, widest) == 0,
+                "inconsistent row plan");
+    PackedFields fields = {{v_means2d, v_depths, v_conics, v_opacities, v_colors, nullptr, nullptr, nullptr},
+                           {2, 1, 3, 1, D, 1, 1, 1}};
+    dim3 grid(blocks_per_run(widest * (D > 3 ? D : 3)), (unsigned)(world * (kFields - 1)));
+    put_packed_bwd_kernel<<<grid, kThreads, 0, stream>>>(peers, fields, plan, world, rank, region_offset,
+                                                        (unsigned long long)epoch);
+    return gsb_check_launch("a2a_put_packed_bwd");
 }

@@ -156,6 +156,19 @@ class _FullyFusedProjection(torch.autograd.Function):
         return (v_means, v_covars, v_quats, v_scales, v_viewmats) + (None,) * 9
 
 
+_PACKED_COUNTS = [None]  # (camera_ids.data_ptr(), nnz, rows per camera) of the last packed projection
+
+
+def packed_camera_counts(camera_ids: Tensor, n_cameras: int):
+    """Rows per camera of a packed projection, as a host list without a device read-back when `camera_ids` is the
+    tensor the last `fully_fused_projection(packed=True)` returned (its counts came back with nnz)."""
+    last = _PACKED_COUNTS[0]
+    if last is not None and last[0] == camera_ids.data_ptr() and last[1] == camera_ids.numel() \
+            and len(last[2]) == n_cameras:
+        return list(last[2])
+    return torch.bincount(camera_ids, minlength=n_cameras).tolist()
+
+
 class _FullyFusedProjectionPacked(torch.autograd.Function):
     """Packed (COO) projection. cf. cuda/_wrapper.py:998-1190."""
 
@@ -174,7 +187,11 @@ class _FullyFusedProjectionPacked(torch.autograd.Function):
         lib.gsb_projection_packed_count(*args, ptr(block_counts), st)
         lib.gsb_scan_i32_to_i64(C * nblk, ptr(block_counts), ptr(block_offsets),
                                 block_offsets.data_ptr() + 8 * C * nblk, st)
-        nnz = int(block_offsets[-1].item())  # size read-back, as Projection.cpp:332-333
+        # size read-back, as Projection.cpp:332-333; the same copy brings the per-camera row counts (the scan is
+        # camera-major), which the distributed packed exchange needs on the host (rendering.py:416-418 of the reference
+        # does a bincount + one .item() per rank for them)
+        bounds = block_offsets[::nblk].tolist() if nblk > 0 else [0] * (C + 1)
+        nnz = int(bounds[-1])
         camera_ids = torch.empty((nnz,), dtype=torch.int64, device=dev)
         gaussian_ids = torch.empty((nnz,), dtype=torch.int64, device=dev)
         radii = torch.empty((nnz,), dtype=torch.int32, device=dev)
@@ -191,6 +208,7 @@ class _FullyFusedProjectionPacked(torch.autograd.Function):
                               compensations)
         ctx.width, ctx.height, ctx.eps2d, ctx.model, ctx.sparse_grad = width, height, eps2d, model, sparse_grad
         ctx.mark_non_differentiable(camera_ids, gaussian_ids, radii)
+        _PACKED_COUNTS[0] = (camera_ids.data_ptr(), nnz, [int(b - a) for a, b in zip(bounds[:-1], bounds[1:])])
         return camera_ids, gaussian_ids, radii, means2d, depths, conics, compensations
 
     @staticmethod

@@ -70,11 +70,13 @@ class HostBoard:
     `all_gather_int32` on a CUDA tensor costs a device-to-host read-back: the CPU waits for every queued kernel
     of the previous step and the next forward's launches are exposed. The count of Gaussians is host data
     already, so the ranks post it on a board in /dev/shm instead: microseconds, no GPU involvement, the CPU
-    keeps running ahead of the GPU. Slot layout per rank: int64[2][3] = (sequence, value, check) for even / odd
-    sequence numbers (a rank can be at most one gather ahead of a peer that has not read it yet).
+    keeps running ahead of the GPU. Slot layout per rank: int64[2][2 + 16] = (sequence, check, values...) for even /
+    odd sequence numbers (a rank can be at most one gather ahead of a peer that has not read it yet); up to 16
+    values per gather (the packed exchange posts one row count per destination rank).
     """
 
     _MAGIC = 0x5DEECE66D
+    _WIDTH = 16
 
     def __init__(self, group=None):
         import mmap
@@ -89,16 +91,17 @@ class HostBoard:
         name = [f"gsb_board_{os.getpid()}_{uuid.uuid4().hex[:12]}"]
         dist.broadcast_object_list(name, src=0, group=group)
         self.paths = [os.path.join(root, f"{name[0]}_{r}") for r in range(self.world)]
+        nbytes = 2 * (2 + self._WIDTH) * 8
         with open(self.paths[self.rank], "wb") as f:
-            f.write(b"\0" * 64)
+            f.write(b"\0" * nbytes)
         dist.barrier(group)  # every rank's file exists
         self.maps, self.slots = [], []
         for path in self.paths:
             f = open(path, "r+b")
-            m = mmap.mmap(f.fileno(), 64)
+            m = mmap.mmap(f.fileno(), nbytes)
             f.close()
             self.maps.append(m)
-            self.slots.append(np.frombuffer(m, dtype=np.int64, count=6).reshape(2, 3))
+            self.slots.append(np.frombuffer(m, dtype=np.int64, count=2 * (2 + self._WIDTH)).reshape(2, 2 + self._WIDTH))
         dist.barrier(group)  # every rank has mapped every file: the names can go
         try:
             os.unlink(self.paths[self.rank])
@@ -107,22 +110,37 @@ class HostBoard:
         self.seq = 0
 
     def all_gather(self, value: int, timeout_s: float = 300.0) -> List[int]:
+        return [v[0] for v in self.all_gather_vec([int(value)], timeout_s)]
+
+    def all_gather_vec(self, values: Sequence[int], timeout_s: float = 300.0) -> List[List[int]]:
+        """Every rank posts `values` (same length on every rank, <= 16); returns the rows of all ranks."""
         import time
 
+        n = len(values)
+        assert 1 <= n <= self._WIDTH
         self.seq += 1
         seq, p = self.seq, self.seq & 1
+        mask = 0x7FFFFFFFFFFFFFFF
+
+        def check_of(vals):
+            c = seq * self._MAGIC
+            for k, v in enumerate(vals):
+                c ^= (int(v) + 1) * (2 * k + 3)
+            return c & mask
+
         mine = self.slots[self.rank]
-        mine[p, 1] = int(value)
-        mine[p, 2] = (int(value) ^ (seq * self._MAGIC)) & 0x7FFFFFFFFFFFFFFF
+        mine[p, 2:2 + n] = [int(v) for v in values]
+        mine[p, 1] = check_of(values)
         mine[p, 0] = seq
         out = []
         for r in range(self.world):
             slot = self.slots[r]
             spins, t0 = 0, None
             while True:
-                s, v, c = int(slot[p, 0]), int(slot[p, 1]), int(slot[p, 2])
-                if s == seq and c == (v ^ (seq * self._MAGIC)) & 0x7FFFFFFFFFFFFFFF:
-                    out.append(v)
+                s_, c_ = int(slot[p, 0]), int(slot[p, 1])
+                vals = [int(v) for v in slot[p, 2:2 + n]]
+                if s_ == seq and c_ == check_of(vals):
+                    out.append(vals)
                     break
                 spins += 1
                 if spins > 2000:
@@ -152,6 +170,18 @@ def all_gather_int_host(world_size: int, value: int) -> List[int]:
     if _HOST_BOARD is None or _HOST_BOARD[0] != key:  # a new process group (init/destroy cycle): new board
         _HOST_BOARD = (key, HostBoard())
     return _HOST_BOARD[1].all_gather(int(value))
+
+
+def all_gather_ints_host(world_size: int, values: Sequence[int]) -> List[List[int]]:
+    """Every rank posts up to 16 host integers; returns all ranks' rows (row r = what rank r posted) without touching
+    the GPU (see HostBoard). Collective: every rank must call it with the same number of values."""
+    global _HOST_BOARD
+    if world_size == 1:
+        return [[int(v) for v in values]]
+    key = _group_key()
+    if _HOST_BOARD is None or _HOST_BOARD[0] != key:
+        _HOST_BOARD = (key, HostBoard())
+    return _HOST_BOARD[1].all_gather_vec(values)
 
 
 def all_to_all_int32(world_size: int, values: List[Union[int, Tensor]], device: Optional[torch.device] = None):
@@ -456,9 +486,14 @@ def _check(rc: int, what: str) -> None:
 _MAILBOXES = {}
 
 
+_PEER_OK = {}
+
+
 def peer_exchange_available() -> bool:
-    """True when the row exchange can go through peer memory: NCCL process group, every rank on this
-    node with its own visible GPU, and GSPLAT_B200_EXCHANGE != "nccl"."""
+    """True when the row exchange can go through peer memory: NCCL process group, GSPLAT_B200_EXCHANGE != "nccl",
+    and EVERY rank agrees that all ranks sit on one node with peer access between their GPUs (decided once per
+    process group by a collective: every rank must reach the first call, which `rasterization(distributed=True)`
+    guarantees). Anything else selects the NCCL all-to-all."""
     if os.environ.get("GSPLAT_B200_EXCHANGE", "peer") == "nccl":
         return False
     if not (dist.is_available() and dist.is_initialized() and torch.cuda.is_available()):
@@ -466,7 +501,30 @@ def peer_exchange_available() -> bool:
     if dist.get_backend() != "nccl":
         return False
     world = dist.get_world_size()
-    return 1 < world <= 16 and world <= torch.cuda.device_count()
+    if not 1 < world <= 16:
+        return False
+    key = _group_key()
+    if key not in _PEER_OK:
+        import socket
+
+        try:
+            boot = open("/proc/sys/kernel/random/boot_id").read().strip()
+        except OSError:
+            boot = ""
+        mine = (socket.gethostname(), boot, torch.cuda.current_device(), torch.cuda.device_count())
+        everyone = [None] * world
+        dist.all_gather_object(everyone, mine)
+        same_node = all(e[:2] == mine[:2] for e in everyone)
+        devices = [e[2] for e in everyone]
+        ok = same_node and len(set(devices)) == world and world <= mine[3]
+        if ok:
+            me = torch.cuda.current_device()
+            ok = all(d == me or torch.cuda.can_device_access_peer(me, d) for d in devices)
+        verdict = torch.tensor([1 if ok else 0], device=torch.device("cuda", torch.cuda.current_device()))
+        dist.all_reduce(verdict, op=dist.ReduceOp.MIN)  # unanimous, or nobody uses the mailboxes
+        _PEER_OK.clear()
+        _PEER_OK[key] = bool(verdict.item())
+    return _PEER_OK[key]
 
 
 def get_mailbox(group=None) -> PeerMailbox:
@@ -567,6 +625,90 @@ def peer_exchange_rows(means2d, depths, conics, opacities, colors, radii, C_loca
     """Fused exchange of the projected rows (unpacked mode): see `_PeerExchangeRows`."""
     return _PeerExchangeRows.apply(means2d, depths, conics, opacities, colors, radii, int(C_local),
                                    tuple(int(n) for n in N_world))
+
+
+def _region_views_packed(rows: int, D: int, n_fields: int, device):
+    """Flat float32 buffer laid out like a packed mailbox region (csrc/peer.cu) + per-field views."""
+    from .b200_impl._lib import lib
+
+    offs = [int(lib.gsb_a2a_field_offset(rows, D, f)) for f in range(n_fields + 1)]
+    widths = (2, 1, 3, 1, D, 1, 1, 1)
+    out = torch.empty((max(offs[-1], 4),), dtype=torch.float32, device=device)
+    return out, [out[offs[f]:offs[f] + rows * widths[f]] for f in range(n_fields)]
+
+
+class _PeerExchangePacked(torch.autograd.Function):
+    """Packed (COO, camera-major) rows -> the ranks owning their cameras, through the peers' mailboxes.
+
+    `matrix[r][d]` = rows rank r sends to rank d (host data, identical on every rank: HostBoard). Returns the rows of
+    the local cameras grouped by sender, with camera ids local to this rank and Gaussian ids global, exactly what the
+    reference builds with two all_to_all calls (rendering.py:413-451); backward returns the gradients the same way."""
+
+    @staticmethod
+    def forward(ctx, means2d, depths, conics, opacities, colors, radii, camera_ids, gaussian_ids, matrix, C_local,
+                gauss_base):
+        import ctypes
+
+        from .b200_impl._lib import lib, ptr, stream_of
+
+        box = get_mailbox()
+        world, rank = box.world, box.rank
+        D = colors.shape[-1]
+        send = [int(v) for v in matrix[rank]]
+        assert sum(send) == depths.numel()
+        rows_in = [sum(matrix[r][d] for r in range(world)) for d in range(world)]  # table size of every rank
+        nnz = [sum(matrix[r]) for r in range(world)]
+        box.ensure(4 * max(int(lib.gsb_a2a_field_offset(max(max(rows_in), max(nnz), 1), D, 8)), 4))
+        dev, st = means2d.device, stream_of(means2d)
+        arr = lambda v: (ctypes.c_int64 * world)(*[int(x) for x in v])  # noqa: E731
+        dst_base = [sum(matrix[r][d] for r in range(rank)) for d in range(world)]
+        cam_base = [d * C_local for d in range(world)]
+        epoch = box.next_epoch(0)
+        region = box.region(0, epoch)
+        means2d, depths, conics, opacities, colors, radii, camera_ids, gaussian_ids = (
+            t.contiguous() for t in (means2d, depths, conics, opacities, colors, radii, camera_ids, gaussian_ids))
+        lib.gsb_a2a_put_packed_fwd(world, rank, D, arr(send), arr(dst_base), arr(rows_in), arr(cam_base),
+                                   int(gauss_base), ptr(means2d), ptr(depths), ptr(conics), ptr(opacities), ptr(colors),
+                                   ptr(radii), ptr(camera_ids), ptr(gaussian_ids), box.peer_array, region, epoch, st)
+        rows = rows_in[rank]
+        out, v = _region_views_packed(rows, D, 8, dev)
+        lib.gsb_a2a_wait_copy(world, 0, epoch, box.local, region, out.numel() // 4 * 4, ptr(out), box.timeout_flag, st)
+        outs = (v[0].view(rows, 2), v[1], v[2].view(rows, 3), v[3], v[4].view(rows, D), v[5].view(torch.int32),
+                v[6].view(torch.int32).long(), v[7].view(torch.int32).long())
+        ctx.plan = (matrix, D, nnz)
+        ctx.mark_non_differentiable(outs[5], outs[6], outs[7])
+        return outs
+
+    @staticmethod
+    def backward(ctx, v_means2d, v_depths, v_conics, v_opac, v_colors, _v_radii, _v_cam, _v_gauss):
+        import ctypes
+
+        from .b200_impl._lib import lib, ptr
+
+        matrix, D, nnz = ctx.plan
+        box = get_mailbox()
+        world, rank = box.world, box.rank
+        dev = box.device
+        st = torch.cuda.current_stream(dev).cuda_stream
+        arr = lambda v: (ctypes.c_int64 * world)(*[int(x) for x in v])  # noqa: E731
+        recv = [matrix[r][rank] for r in range(world)]  # rows held for sender r, in sender order
+        dst_base = [sum(matrix[r][:rank]) for r in range(world)]  # where they sit in r's packed order
+        epoch = box.next_epoch(1)
+        region = box.region(1, epoch)
+        grads = [None if t is None else t.float().contiguous() for t in (v_means2d, v_depths, v_conics, v_opac, v_colors)]
+        lib.gsb_a2a_put_packed_bwd(world, rank, D, arr(recv), arr(dst_base), arr(nnz), *(ptr(g) for g in grads),
+                                   box.peer_array, region, epoch, st)
+        rows = nnz[rank]
+        out, v = _region_views_packed(rows, D, 5, dev)
+        lib.gsb_a2a_wait_copy(world, 1, epoch, box.local, region, out.numel() // 4 * 4, ptr(out), box.timeout_flag, st)
+        return (v[0].view(rows, 2), v[1], v[2].view(rows, 3), v[3], v[4].view(rows, D)) + (None,) * 6
+
+
+def peer_exchange_packed(means2d, depths, conics, opacities, colors, radii, camera_ids, gaussian_ids, matrix,
+                         C_local: int, gauss_base: int):
+    """Fused exchange of packed rows: see `_PeerExchangePacked`."""
+    return _PeerExchangePacked.apply(means2d, depths, conics, opacities, colors, radii, camera_ids, gaussian_ids,
+                                     [[int(x) for x in row] for row in matrix], int(C_local), int(gauss_base))
 
 
 # ---------------------------------------------------------------------------------------------

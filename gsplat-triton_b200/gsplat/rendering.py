@@ -45,6 +45,7 @@ else:
 from .distributed import (
     all_gather_int32,
     all_gather_int_host,
+    all_gather_ints_host,
     all_gather_tensor_list,
     all_to_all_int32,
     all_to_all_rows,
@@ -53,6 +54,7 @@ from .distributed import (
     host_trace,
     pack_rows,
     peer_exchange_available,
+    peer_exchange_packed,
     peer_exchange_rows,
     unpack_rows,
 )
@@ -216,9 +218,21 @@ def rasterization(
     # Distributed: hand every projected Gaussian to the rank that owns its camera.
     if distributed:
         D = colors.shape[-1]
-        if packed:
-            cnts = torch.bincount(camera_ids, minlength=C).split(C_world, dim=0)
-            cnts = [int(c.sum().item()) for c in cnts]
+        if packed and BACKEND == "b200" and peer_exchange_available() and world_size <= 16:
+            # rows per destination rank: host data already (they came back with nnz), exchanged on the host board;
+            # then ONE fused pack + NVLink put per direction, ids rebased inside the kernel
+            from .b200_impl._wrapper import packed_camera_counts
+
+            per_cam = packed_camera_counts(camera_ids, C)
+            C_l = C_world[world_rank]
+            cnts = [sum(per_cam[i * C_l:(i + 1) * C_l]) for i in range(world_size)]
+            matrix = all_gather_ints_host(world_size, cnts)
+            means2d, depths, conics, opacities, colors, radii, camera_ids, gaussian_ids = peer_exchange_packed(
+                means2d, depths, conics, opacities, colors, radii, camera_ids, gaussian_ids, matrix, C_l,
+                sum(N_world[:world_rank]))
+            C = C_l
+        elif packed:
+            cnts = torch.bincount(camera_ids, minlength=C).view(world_size, -1).sum(dim=1).tolist()  # one read-back
             recv = all_to_all_int32(world_size, cnts, device=device)
             rows = pack_rows(means2d, depths, conics, opacities, colors, radii)
             rows = all_to_all_rows(rows, cnts, recv)

@@ -318,6 +318,26 @@ int gsb_a2a_put_bwd(int world, int rank, int C_local, int64_t N_total, const int
 int gsb_a2a_wait_copy(int world, int dir, int64_t epoch, const void *local_base, int64_t region_offset,
                       int64_t n_floats, float *out, int *timeout_flag, cudaStream_t stream);
 int64_t gsb_a2a_field_offset(int64_t rows, int D, int field);
+/* Packed (COO) rows over the same mailboxes (reference rendering.py:413-451: bincount + all_to_all of counts,
+ * all_to_all of the rows, a second one for the rebased ids). The sender's packed rows are camera-major, so the rows
+ * for destination d are the run after those for d-1: send_counts_host[d] rows go to rows
+ * [dst_row_base_host[d], + count) of d's table of dst_rows_host[d] rows (a region with two extra int32 fields after
+ * radii: camera id local to d = id - cam_base_host[d], Gaussian id global = id + gauss_base; field offsets from
+ * gsb_a2a_field_offset with field 6, 7, 8). All *_host arrays have `world` entries and live on the host.
+ * gsb_a2a_put_packed_bwd returns the gradient rows held for sender r (recv_counts_host[r], in sender order) to rows
+ * [dst_row_base_host[r], + count) of r's table of dst_rows_host[r] = nnz_r rows. */
+int gsb_a2a_put_packed_fwd(int world, int rank, int D, const int64_t *send_counts_host,
+                           const int64_t *dst_row_base_host, const int64_t *dst_rows_host,
+                           const int64_t *cam_base_host, int64_t gauss_base, const float *means2d,
+                           const float *depths, const float *conics, const float *opacities, const float *colors,
+                           const int32_t *radii, const int64_t *camera_ids, const int64_t *gaussian_ids,
+                           const void *const *peer_bases_host, int64_t region_offset, int64_t epoch,
+                           cudaStream_t stream);
+int gsb_a2a_put_packed_bwd(int world, int rank, int D, const int64_t *recv_counts_host,
+                           const int64_t *dst_row_base_host, const int64_t *dst_rows_host, const float *v_means2d,
+                           const float *v_depths, const float *v_conics, const float *v_opacities,
+                           const float *v_colors, const void *const *peer_bases_host, int64_t region_offset,
+                           int64_t epoch, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

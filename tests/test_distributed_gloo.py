@@ -115,6 +115,14 @@ def _host_board(rank, world):
     for i in range(200):
         assert all_gather_int_host(world, 1000 * rank + i) == [1000 * r + i for r in range(world)]
     assert all_gather_int_host(world, (1 << 40) + rank) == [(1 << 40) + r for r in range(world)]
+    # vector form (the packed exchange's row-count matrix), interleaved with scalar gathers
+    from gsplat.distributed import all_gather_ints_host
+
+    for i in range(50):
+        rows = all_gather_ints_host(world, [rank * 100 + i + d for d in range(world)])
+        assert rows == [[r * 100 + i + d for d in range(world)] for r in range(world)]
+        assert all_gather_int_host(world, i - rank) == [i - r for r in range(world)]
+    assert all_gather_ints_host(world, list(range(16))) == [list(range(16))] * world
 
 
 def test_host_board_all_gather():

@@ -7,7 +7,9 @@ volume per rank and direction and the per-entry-point table (CUDA events) of ran
         tools/bench_cfg4.py                      # CFG4_PACKED=1 for packed rows (NCCL transport), CFG4_N=6000000
 
 Not the bench line (bench.py measures cfg2 and its sharded version); the data point for the configuration BASELINE.json
-names for the distributed path. Written after round 1's GPU budget was spent: first run pending (round 2).
+names for the distributed path. The exchange volume is counted from the rows really sent (unpacked: every local row to
+every camera owner; packed: the visible rows), the achieved NVLink rate = bytes that leave this GPU / duration of the put
+kernel (CUDA events), against 900 GB/s nominal / 770 GB/s measured peer copy per direction (B200_PROFILING.md).
 """
 import json
 import math
@@ -97,14 +99,36 @@ def main():
     timing.reset(False)
     barrier()
     if rank == 0:
-        rows_out = n_local * world  # unpacked: every local Gaussian goes to every camera owner, (8 + 3) words per row
-        print(json.dumps({
+        D = 3
+        if packed:  # rows this rank keeps visible for any camera = rows it sends (incl. to itself)
+            rows_out = int(meta["_rows_sent"]) if "_rows_sent" in meta else None
+        else:
+            rows_out = n_local * world  # every local Gaussian goes to every camera owner
+        out = {
             "workload": f"cfg4: {N_total} Gaussians over {world} ranks, 1 camera per rank at {W}x{H}, packed={packed}, "
                         "antialiased, SH deg 3, distributed",
+            "world": world, "packed": packed,
             "ms_per_step": round(float(ms), 3), "camera_renders_per_s": round(world * 1e3 / float(ms), 1),
             "n_local": n_local, "n_isects_rank0": int(meta["flatten_ids"].numel()),
-            "exchange_MB_per_rank_per_direction_unpacked": round(rows_out * 11 * 4 / 1e6, 1),
-            "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 2), "stages_ms_rank0": table}))
+            "rows_received_rank0": int(meta["radii"].numel()),
+            "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 2), "stages_ms_rank0": table}
+        if world > 1:
+            rows_in = int(meta["radii"].numel())
+            rows = rows_out if rows_out is not None else rows_in  # packed: symmetric scene, sent ~= received
+            fwd_b = rows * ((8 + D) * 4 + (8 if packed else 0))
+            bwd_b = rows_in * (7 + D) * 4
+            nv = (world - 1) / world
+            ex = {"fwd_MB_per_rank": round(fwd_b / 1e6, 1), "bwd_MB_per_rank": round(bwd_b / 1e6, 1),
+                  "over_nvlink_fraction": round(nv, 3)}
+            for key, name, b in (("fwd", "gsb_a2a_put_packed_fwd" if packed else "gsb_a2a_put_fwd", fwd_b),
+                                 ("bwd", "gsb_a2a_put_packed_bwd" if packed else "gsb_a2a_put_bwd", bwd_b)):
+                if name in table and table[name] > 0:
+                    ex[f"{key}_put_ms"] = table[name]
+                    ex[f"{key}_nvlink_GBps_achieved"] = round(b * nv / (table[name] * 1e-3) / 1e9, 1)
+            ex["nvlink_GBps_nominal_per_direction"] = 900.0
+            ex["nvlink_GBps_measured_peer_copy"] = 770.0
+            out["exchange"] = ex
+        print("CFG4 " + json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
 

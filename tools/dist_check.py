@@ -3,10 +3,11 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 tools/dist_check.py
 
 Every rank renders its own cameras from Gaussians sharded over the ranks, once through the fused
-peer-store exchange (csrc/peer.cu) and once through the NCCL all-to-all, and compares images, alphas and
-the gradients of its Gaussian shard with a plain single-GPU render of the whole scene (all cameras, all
-Gaussians) computed locally. Also runs forward-only steps between training steps (mailbox double buffering)
-and uneven shard sizes. Prints one line per rank; exit code 1 on mismatch.
+peer-store exchange (csrc/peer.cu) and once through the NCCL all-to-all, unpacked and packed rows, RGB and
+RGB+ED (antialiased), and compares images, alphas and the gradients of its Gaussian shard with a plain
+single-GPU render of the whole scene (all cameras, all Gaussians) computed locally. Also runs forward-only
+steps between training steps (mailbox double buffering) and uneven shard sizes. Prints one line per rank and
+(rank 0) a final JSON summary line `DIST_CHECK {...}`; exit code 1 on mismatch.
 """
 import math
 import os
@@ -55,7 +56,7 @@ def main():
     from gsplat.rendering import rasterization
 
     W, H, C_local = 320, 200, 2
-    ok = True
+    ok, worst, n_cases = True, [0.0, 0.0, 0.0], 0
     for n, uneven in ((20000, False), (30011, True)):
         params, viewmats, Ks = scene(n, world * C_local, W, H)
         # shard: contiguous blocks (uneven sizes when asked) so global Gaussian order = concatenation over ranks
@@ -69,35 +70,52 @@ def main():
         Gw = torch.rand(world * C_local, H, W, 3, generator=g).to(dev)
         Aw = torch.rand(world * C_local, H, W, 1, generator=g).to(dev)
 
-        # single-GPU truth: all cameras, all Gaussians
-        full = [p.to(dev).requires_grad_(True) for p in params]
-        rc, ra, _ = rasterization(*full, viewmats.to(dev), Ks.to(dev), W, H, sh_degree=2, packed=False)
-        ((rc * Gw).sum() + (ra * Aw).sum()).backward()
-        truth = dict(rc=rc[my_cams].detach(), ra=ra[my_cams].detach(), grads=[p.grad[lo:hi].clone() for p in full])
-
-        for transport in ("peer", "nccl"):
-            os.environ["GSPLAT_B200_EXCHANGE"] = transport
-            for step in range(3):
-                shard = [p[lo:hi].to(dev).requires_grad_(True) for p in params]
-                if step == 1:  # forward-only steps in between (mailbox reuse without a backward exchange)
-                    with torch.no_grad():
-                        for _ in range(3):
-                            rasterization(*shard, viewmats[my_cams].to(dev), Ks[my_cams].to(dev), W, H, sh_degree=2,
-                                          packed=False, distributed=True)
-                rc, ra, _ = rasterization(*shard, viewmats[my_cams].to(dev), Ks[my_cams].to(dev), W, H, sh_degree=2,
-                                          packed=False, distributed=True)
-                ((rc * Gw[my_cams]).sum() + (ra * Aw[my_cams]).sum()).backward()
-                e_img = (rc - truth["rc"]).abs().max().item()
-                e_a = (ra - truth["ra"]).abs().max().item()
-                e_g = max(((p.grad - t).abs().max() / (t.abs().max() + 1e-12)).item()
-                          for p, t in zip(shard, truth["grads"]))
-                good = e_img < 2e-4 and e_a < 2e-4 and e_g < 2e-3
-                ok &= good
-                print(f"rank {rank} n={n} uneven={uneven} {transport} step {step}: img {e_img:.2e} alpha {e_a:.2e} "
-                      f"grad {e_g:.2e} {'ok' if good else 'MISMATCH'}", flush=True)
+        for packed, mode, raster in ((False, "RGB", "classic"), (False, "RGB+ED", "antialiased"),
+                                     (True, "RGB", "classic"), (True, "RGB+ED", "antialiased")):
+            Dch = 4 if mode == "RGB+ED" else 3
+            Gc = Gw if Dch == 3 else torch.cat([Gw, Gw[..., :1] * 0.1], dim=-1)
+            kw = dict(sh_degree=2, render_mode=mode, rasterize_mode=raster)
+            # single-GPU truth: all cameras, all Gaussians
+            full = [p.to(dev).requires_grad_(True) for p in params]
+            rc, ra, _ = rasterization(*full, viewmats.to(dev), Ks.to(dev), W, H, packed=False, **kw)
+            ((rc * Gc).sum() + (ra * Aw).sum()).backward()
+            truth = dict(rc=rc[my_cams].detach(), ra=ra[my_cams].detach(),
+                         grads=[p.grad[lo:hi].clone() for p in full])
+            del full, rc, ra
+            for transport in ("peer", "nccl"):
+                os.environ["GSPLAT_B200_EXCHANGE"] = transport
+                for step in range(3):
+                    shard = [p[lo:hi].to(dev).requires_grad_(True) for p in params]
+                    args = (viewmats[my_cams].to(dev), Ks[my_cams].to(dev), W, H)
+                    if step == 1:  # forward-only steps in between (mailbox reuse without a backward exchange)
+                        with torch.no_grad():
+                            for _ in range(3):
+                                rasterization(*shard, *args, packed=packed, distributed=True, **kw)
+                    rc, ra, meta = rasterization(*shard, *args, packed=packed, distributed=True, **kw)
+                    ((rc * Gc[my_cams]).sum() + (ra * Aw[my_cams]).sum()).backward()
+                    e_img = (rc - truth["rc"]).abs().max().item()
+                    e_a = (ra - truth["ra"]).abs().max().item()
+                    e_g = max(((p.grad - t).abs().max() / (t.abs().max() + 1e-12)).item()
+                              for p, t in zip(shard, truth["grads"]))
+                    good = e_img < 2e-4 and e_a < 2e-4 and e_g < 2e-3
+                    ok &= good
+                    worst = [max(a, b) for a, b in zip(worst, (e_img, e_a, e_g))]
+                    n_cases += 1
+                    print(f"rank {rank} n={n} uneven={uneven} packed={packed} {mode} {transport} step {step}: "
+                          f"img {e_img:.2e} alpha {e_a:.2e} grad {e_g:.2e} {'ok' if good else 'MISMATCH'}", flush=True)
     torch.cuda.synchronize()
     flag = torch.tensor([0 if ok else 1], device=dev)
     dist.all_reduce(flag)
+    w = torch.tensor(worst, device=dev, dtype=torch.float64)
+    dist.all_reduce(w, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        import json
+
+        print("DIST_CHECK " + json.dumps({
+            "world": world, "cases_per_rank": n_cases, "ok": flag.item() == 0, "img_max_err": w[0].item(),
+            "alpha_max_err": w[1].item(), "grad_max_rel": w[2].item(),
+            "covers": "packed x {RGB classic, RGB+ED antialiased} x {peer, nccl} x {even, uneven shards} x 3 steps "
+                      "(forward-only steps in between), vs a single-GPU render of the whole scene"}), flush=True)
     dist.barrier()
     close_mailboxes()
     dist.destroy_process_group()
