@@ -178,7 +178,7 @@ def measured_peaks():
 def _raster_work_counts(meta, device):
     """(E, hits, lane_evals): E = reference-algorithm evaluations 256 * sum_tiles(last contributing index - tile
     start + 1) (SURVEY 8d); hits = pixel-Gaussian pairs actually composited (alpha >= 1/255, before termination);
-    lane_evals = 32 x the (warp, splat) pairs the forward kernel walks = evaluations the kernels EXECUTE."""
+    lane_evals = per kernel, the evaluations it EXECUTES: lanes x the inner-loop iterations counted in-kernel."""
     from gsplat.b200_impl._lib import lib, ptr, stream_of
 
     means2d, conics, opac = (meta[k].detach().contiguous() for k in ("means2d", "conics", "opacities"))
@@ -195,13 +195,24 @@ def _raster_work_counts(meta, device):
     lib.gsb_rasterize_count(C, flat.numel(), ptr(rec[0]), ptr(rec[1]), ptr(ones), W, H, 16, tw, th, ptr(offs),
                             ptr(flat), ptr(cnt), ptr(ra), ptr(last), ptr(pairs), st)
     hits = int(cnt.double().sum().item())
+    lane_evals = {"gsb_rasterize_bwd": 32 * int(pairs.item())}
+    if int(lib.gsb_get_option(0)) == 2:  # forward v2: one loop iteration = 2 blocks x 32 pixels
+        iters = torch.zeros((1,), dtype=torch.int64, device=device)
+        s1, s2 = torch.empty_like(cnt), torch.empty_like(ra)
+        s3 = torch.empty_like(last)
+        lib.gsb_rasterize_fwd2_count(C, flat.numel(), ptr(rec[0]), ptr(rec[1]), ptr(ones), W, H, tw, th, ptr(offs),
+                                     ptr(flat), ptr(s1), ptr(s2), ptr(s3), ptr(iters), st)
+        lane_evals["gsb_rasterize_fwd_cap"] = 64 * int(iters.item())
+    else:
+        lane_evals["gsb_rasterize_fwd_cap"] = 32 * int(pairs.item())
+    lane_evals["gsb_rasterize_fwd"] = lane_evals["gsb_rasterize_fwd_cap"]
     last = torch.where(cnt > 0, last, torch.full_like(last, -1))
     pad_h, pad_w = th * 16 - H, tw * 16 - W
     last = torch.nn.functional.pad(last, (0, pad_w, 0, pad_h), value=-1)
     tile_last = last.reshape(C, th, 16, tw, 16).amax(dim=(2, 4))
     work = (tile_last - offs + 1).clamp(min=0)
     work = torch.where(tile_last >= 0, work, torch.zeros_like(work))
-    return 256 * int(work.sum().item()), hits, 32 * int(pairs.item())
+    return 256 * int(work.sum().item()), hits, lane_evals
 
 
 def _stage_table(summary, steps, meta, n_local, C, D, K, work, peaks, sm_mhz):
@@ -254,7 +265,7 @@ def _stage_table(summary, steps, meta, n_local, C, D, K, work, peaks, sm_mhz):
             #   frac_reference_algorithm  the reference's dense loop E (every pixel of a tile x every Gaussian up to
             #                             the tile's last contributor). The kernels cull most of E exactly, so this
             #                             one can exceed 1: it is a speed-up over the dense algorithm, not a fraction.
-            evals, hits, lane_evals = work
+            evals, hits, lane_evals = work[0], work[1], work[2][name]
             to_tf = 2 * slots[name] / (per_step * 1e-3) / 1e12
             row.update(bound="fp32", achieved=round(lane_evals * to_tf, 2), peak=round(fp32_peak, 2), unit="TFLOP/s",
                        frac=round(lane_evals * to_tf / fp32_peak, 4), executed_lane_evaluations=lane_evals,

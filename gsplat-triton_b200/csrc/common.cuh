@@ -9,6 +9,8 @@
 void gsb_set_error(const char *fmt, ...);
 // bumps the counter behind gsb_launch_count()
 void gsb_count_launch(int n);
+// current value of a GSB_OPT_* switch (gsb_set_option)
+int gsb_option(int which);
 
 static inline int gsb_check_launch(const char *what) {
     gsb_count_launch(1);

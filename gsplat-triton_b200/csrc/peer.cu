@@ -91,19 +91,30 @@ __host__ __device__ __forceinline__ int64_t field_offset(const int *width, int f
     return off;
 }
 
-// copies `len` floats src -> dst with this CTA column (blockIdx.x of gridDim.x); src == NULL stores zeros
+// copies `len` floats src -> dst with this CTA column (blockIdx.x of gridDim.x); src == NULL stores zeros.
+// The stores are what crosses NVLink: they are always 16-byte vectors on the 16-byte aligned body of dst (a scalar
+// head / tail of < 4 floats around it); the loads are vectors when src has the same alignment phase (unpacked rows
+// always; packed runs start at arbitrary rows) and four scalar loads otherwise.
 __device__ __forceinline__ void copy_run(const float *__restrict__ src, float *__restrict__ dst, int64_t len) {
     const int64_t tid = (int64_t)blockIdx.x * kThreads + threadIdx.x, step = (int64_t)gridDim.x * kThreads;
-    const bool vec = (((uintptr_t)dst & 15) == 0) && (src == nullptr || ((uintptr_t)src & 15) == 0);
-    if (vec) {
-        const int64_t n4 = len >> 2;
-        const float4 *s4 = reinterpret_cast<const float4 *>(src);
-        float4 *d4 = reinterpret_cast<float4 *>(dst);
-        for (int64_t i = tid; i < n4; i += step) d4[i] = src ? __ldg(s4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int64_t i = (n4 << 2) + tid; i < len; i += step) dst[i] = src ? src[i] : 0.f;
+    int64_t head = (4 - (int64_t)(((uintptr_t)dst >> 2) & 3)) & 3;  // floats before dst is 16-byte aligned
+    if (head > len) head = len;
+    const int64_t n4 = (len - head) >> 2;
+    float4 *d4 = reinterpret_cast<float4 *>(dst + head);
+    if (src == nullptr) {
+        for (int64_t i = tid; i < n4; i += step) d4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    } else if ((((uintptr_t)(src + head)) & 15) == 0) {
+        const float4 *s4 = reinterpret_cast<const float4 *>(src + head);
+        for (int64_t i = tid; i < n4; i += step) d4[i] = __ldg(s4 + i);
     } else {
-        for (int64_t i = tid; i < len; i += step) dst[i] = src ? src[i] : 0.f;
+        const float *s = src + head;
+        for (int64_t i = tid; i < n4; i += step)
+            d4[i] = make_float4(__ldg(s + 4 * i), __ldg(s + 4 * i + 1), __ldg(s + 4 * i + 2), __ldg(s + 4 * i + 3));
     }
+    // head and tail: fewer than 8 floats in total
+    if (tid < head) dst[tid] = src ? src[tid] : 0.f;
+    const int64_t tail0 = head + (n4 << 2);
+    if (tid < len - tail0) dst[tail0 + tid] = src ? src[tail0 + tid] : 0.f;
 }
 
 // forward: segment (camera c of all world*C_local cameras, field f): N_local rows -> the rank owning camera c,
@@ -174,8 +185,18 @@ put_packed_fwd_kernel(PeerTable peers, PackedFields fields, PackedPlan plan, int
         const int64_t *ids = reinterpret_cast<const int64_t *>(fields.src[f]) + plan.src_start[dest];
         const int64_t shift = (f == kFields) ? -plan.cam_base[dest] : plan.gauss_base;
         int32_t *d32 = reinterpret_cast<int32_t *>(dst);
-        for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads)
-            d32[i] = (int32_t)(ids[i] + shift);
+        const int64_t tid = (int64_t)blockIdx.x * kThreads + threadIdx.x, step = (int64_t)gridDim.x * kThreads;
+        int64_t head = (4 - (int64_t)(((uintptr_t)d32 >> 2) & 3)) & 3;
+        if (head > n) head = n;
+        const int64_t n4 = (n - head) >> 2;
+        int4 *d4 = reinterpret_cast<int4 *>(d32 + head);
+        const int64_t *s = ids + head;
+        for (int64_t i = tid; i < n4; i += step)
+            d4[i] = make_int4((int32_t)(s[4 * i] + shift), (int32_t)(s[4 * i + 1] + shift),
+                              (int32_t)(s[4 * i + 2] + shift), (int32_t)(s[4 * i + 3] + shift));
+        if (tid < head) d32[tid] = (int32_t)(ids[tid] + shift);
+        const int64_t tail0 = head + (n4 << 2);
+        if (tid < n - tail0) d32[tail0 + tid] = (int32_t)(ids[tail0 + tid] + shift);
     }
     publish_when_grid_done(peers, world, rank, 0, epoch);
 }

@@ -186,6 +186,13 @@ int launch_fwd(int C, int64_t n_isects, const float *recA, const float *recB, co
 
 }  // namespace raster
 
+// rasterize_fwd2.cu
+int gsb_rasterize_fwd2_dispatch(int C, int64_t n_isects, const int64_t *n_isects_dev, int D, const float *recA,
+                                const float *recB, const float *colors, const float *backgrounds,
+                                const uint8_t *masks, int width, int height, int tile_width, int tile_height,
+                                const int32_t *isect_offsets, const int32_t *flatten_ids, float *render_colors,
+                                float *render_alphas, int32_t *last_ids, uint8_t *block_masks, cudaStream_t stream);
+
 extern "C" int gsb_rasterize_pack(int64_t P, const float *means2d, const float *conics, const float *opacities,
                                   float *recA, float *recB, cudaStream_t stream) {
     GSB_REQUIRE(P >= 0, "negative size");
@@ -220,6 +227,10 @@ extern "C" int gsb_rasterize_fwd_cap(int C, int64_t n_isects, const int64_t *n_i
     GSB_REQUIRE(tile_width * tile_size >= width && tile_height * tile_size >= height, "tile grid smaller than image");
     GSB_REQUIRE(tile_height <= 65535 && C <= 65535, "grid too large");
     if (C == 0) return GSB_OK;
+    if (D <= 4 && gsb_option(GSB_OPT_FWD_VARIANT) == 2)
+        return gsb_rasterize_fwd2_dispatch(C, n_isects, n_isects_dev, D, recA, recB, colors, backgrounds, masks, width,
+                                           height, tile_width, tile_height, isect_offsets, flatten_ids,
+                                           render_colors, render_alphas, last_ids, block_masks, stream);
 #define GSB_FWD_CASE(DD)                                                                                          \
     case DD:                                                                                                      \
         return raster::launch_fwd<DD>(C, n_isects, recA, recB, colors, backgrounds, masks, width, height,         \

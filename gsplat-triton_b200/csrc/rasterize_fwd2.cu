@@ -1,0 +1,293 @@
+// rasterize_to_pixels forward, second generation ("v2"): half-warp per 8x4 pixel block, two pixels per lane,
+// Blackwell packed FP32 (FFMA2 / FMUL2 / FADD2, PTX `*.f32x2`).
+//
+// Same semantics, same staging, same exact block culling and the SAME arithmetic per (pixel, Gaussian) pair as
+// rasterize_fwd.cu (every rounding identical: the two kernels produce bit-identical images; tests assert it). What
+// changes is the issue-slot economy, the measured limiter of v1 (ncu: 79 % issue-active, FMA pipe 34 %):
+//   * a warp owns TWO 8x4 blocks of the tile (lanes 0-15: block 2w, lanes 16-31: block 2w+1); each half walks the
+//     ballot list of its own block, so one loop iteration composites two different Gaussians onto 2 x 32 pixels;
+//   * a lane owns two vertically adjacent pixels and evaluates them with packed instructions (one FFMA2 = two
+//     FMAs, per-Gaussian scalars enter as broadcast operands at no cost), so the list bookkeeping, the three 16-byte
+//     shared-memory loads and most of the arithmetic are issued once per two pixels;
+//   * the blend is branch-free (select, zero weight) — no divergence between the two halves or the two pixels.
+// ~47 issued instructions per iteration (64 pixel-Gaussian evaluations) against 37 per 32 in v1.
+#include "rasterize_common.cuh"
+
+namespace raster {
+
+typedef unsigned long long f32x2;
+
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 bcast2(float a) { return pack2(a, a); }
+// acc += a * b (accumulate form: no register moves around the asm)
+__device__ __forceinline__ void fma2_acc(f32x2 &acc, f32x2 a, f32x2 b) {
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
+}
+__device__ __forceinline__ float4 lds128(unsigned addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+
+constexpr int kThreads2 = 128;  // 4 warps x 2 blocks
+constexpr int kWarps2 = kThreads2 / 32;
+
+#ifndef GSB_FWD2_MIN_BLOCKS
+#define GSB_FWD2_MIN_BLOCKS 8
+#endif
+
+// COUNT (diagnostics): `warp_iters` receives the number of loop iterations (each = 64 lane evaluations)
+template <int D, bool COUNT = false>
+__global__ void __launch_bounds__(kThreads2, GSB_FWD2_MIN_BLOCKS)
+rasterize_fwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, const float4 *__restrict__ recB,
+                      const float *__restrict__ colors, const float *__restrict__ backgrounds,
+                      const uint8_t *__restrict__ masks, int W, int H, int tw, int th,
+                      const int32_t *__restrict__ offsets, const int32_t *__restrict__ flatten_ids,
+                      float *__restrict__ out_colors, float *__restrict__ out_alphas,
+                      int32_t *__restrict__ last_ids, const int64_t *__restrict__ n_isects_dev,
+                      uint8_t *__restrict__ block_masks, unsigned long long *__restrict__ warp_iters) {
+    static_assert(D >= 1 && D <= 4, "v2 keeps the colour of a staged splat in one float4");
+    if (n_isects_dev != nullptr) n_isects = min(n_isects, (int64_t)*n_isects_dev);
+    // Staged batch. Entry 0 of every array is a zeroed pad: a half-warp whose list is exhausted reads it (index
+    // c0 + ffs(0) = c0, harmless finite values, discarded through a zero opacity) while the other half goes on.
+    struct __align__(16) Stage {
+        float4 P[kThreads2 + 32];   // x, y, sorted index, block mask
+        float4 B[kThreads2 + 32];   // staged conic (A', B', C'), MINUS opacity
+        float4 Cq[kThreads2 + 32];  // colour
+        int wcnt[kWarps2];
+    };
+    __shared__ Stage st;
+    for (int i = threadIdx.x; i < kThreads2 + 32; i += kThreads2) {
+        st.P[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        st.B[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        st.Cq[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    const unsigned sP = (unsigned)__cvta_generic_to_shared(st.P);
+    constexpr unsigned kOffB = sizeof(float4) * (kThreads2 + 32), kOffC = 2 * kOffB;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, half = lane >> 4, l16 = lane & 15;
+    const int cam = blockIdx.z, tile_y = blockIdx.y, tile_x = blockIdx.x;
+    const int64_t tile_id = ((int64_t)cam * th + tile_y) * tw + tile_x;
+    const int range_start = offsets[tile_id];
+    const int range_end = (tile_id + 1 < (int64_t)C * th * tw) ? offsets[tile_id + 1] : (int)n_isects;
+    // block (bx = half, by = warp) of the tile: the same numbering as v1's warps, bit 2*warp + half of the mask
+    const int px = tile_x * kTile + half * 8 + (l16 & 7);
+    const int py0 = tile_y * kTile + warp * 4 + (l16 >> 3) * 2, py1 = py0 + 1;
+    const bool in0 = (px < W) & (py0 < H), in1 = (px < W) & (py1 < H);
+
+    f32x2 pix[D];
+#pragma unroll
+    for (int k = 0; k < D; ++k) pix[k] = pack2(0.f, 0.f);  // holds MINUS the colour sums
+    // |T| is the transmittance; T < 0 marks a finished pixel (saturated, or outside the image)
+    float T0 = in0 ? 1.0f : -1.0f, T1 = in1 ? 1.0f : -1.0f;
+    int cur0 = 0, cur1 = 0;
+    unsigned n_iters = 0;
+
+    const bool render = (masks == nullptr) || masks[tile_id];
+    if (render) {
+        const float pxf = (float)px + 0.5f;
+        const f32x2 npy = pack2(-((float)py0 + 0.5f), -((float)py1 + 0.5f));
+        bool warp_done = __all_sync(0xffffffffu, (T0 < 0.f) & (T1 < 0.f));
+        const int bit0 = 2 * warp, bit1 = 2 * warp + 1;
+
+        for (int base = range_start; base < range_end; base += kThreads2) {
+            if (__syncthreads_count((T0 < 0.f) & (T1 < 0.f)) == kThreads2) break;
+            const int idx = base + tid;
+            unsigned mask = 0u;
+            int g = 0;
+            float4 A, B;
+            if (idx < range_end) {
+                g = flatten_ids[idx];
+                A = __ldg(recA + g);
+                B = __ldg(recB + g);
+                mask = splat_block_mask(A, B, tile_x * kTile, tile_y * kTile);
+                if (block_masks != nullptr) block_masks[idx] = (uint8_t)mask;
+            }
+            // compacting append (4 warps)
+            const unsigned ballot = __ballot_sync(0xffffffffu, mask != 0u);
+            if (lane == 0) st.wcnt[warp] = __popc(ballot);
+            __syncthreads();
+            int slot = 0, total = 0;
+#pragma unroll
+            for (int w = 0; w < kWarps2; ++w) {
+                const int c = st.wcnt[w];
+                slot += (w < warp) ? c : 0;
+                total += c;
+            }
+            slot += __popc(ballot & ((1u << lane) - 1u)) + 1;  // entry 0 is the pad
+            if (mask != 0u) {
+                st.P[slot] = make_float4(A.x, A.y, __int_as_float(idx), __uint_as_float(mask));
+                float4 sb = stage_conic(B);
+                sb.w = -sb.w;
+                st.B[slot] = sb;
+                const float *cp = colors + (size_t)g * D;
+                float4 c4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                c4.x = cp[0];
+                if (D > 1) c4.y = cp[1];
+                if (D > 2) c4.z = cp[2];
+                if (D > 3) c4.w = cp[3];
+                st.Cq[slot] = c4;
+            }
+            __syncthreads();
+            if (warp_done) continue;
+            for (int c0 = 0; c0 < total; c0 += 32) {
+                const int jl = c0 + lane;
+                const unsigned m = jl < total ? __float_as_uint(st.P[jl + 1].w) : 0u;
+                unsigned todo0 = __ballot_sync(0xffffffffu, (m >> bit0) & 1u);
+                unsigned todo1 = __ballot_sync(0xffffffffu, (m >> bit1) & 1u);
+                while (todo0 | todo1) {
+                    const unsigned todo = half ? todo1 : todo0;
+                    const unsigned addr = sP + 16u * (unsigned)(c0 + __ffs(todo));  // entry c0 + ffs (pad-shifted)
+                    todo0 &= todo0 - 1u;
+                    todo1 &= todo1 - 1u;
+                    if (COUNT) ++n_iters;
+                    const float4 p4 = lds128(addr);
+                    const float4 b4 = lds128(addr + kOffB);
+                    const float4 c4 = lds128(addr + kOffC);
+                    const float dx = p4.x - pxf;
+                    const f32x2 dy = add2(bcast2(p4.y), npy);
+                    // log2(e^-sigma) = dx (A' dx + B' dy) + C' dy^2: the expression (and every rounding) of gauss_log2
+                    const f32x2 t = fma2(bcast2(b4.y), dy, bcast2(b4.x * dx));
+                    const f32x2 ex = fma2(mul2(bcast2(b4.z), dy), dy, mul2(bcast2(dx), t));
+                    float ex0, ex1;
+                    unpack2(ex, ex0, ex1);
+                    // MINUS alpha; an exhausted half composites the pad with opacity 0: never a hit
+                    const float nopac = todo != 0u ? b4.w : 0.f;
+                    float na0, na1;
+                    unpack2(mul2(bcast2(nopac), pack2(exp2f(ex0), exp2f(ex1))), na0, na1);
+                    na0 = fmaxf(-kAlphaMax, na0);
+                    na1 = fmaxf(-kAlphaMax, na1);
+                    const f32x2 na = pack2(na0, na1), T2 = pack2(T0, T1);
+                    float nT0, nT1;  // T (1 - alpha); < 0 on finished pixels
+                    unpack2(fma2(T2, na, T2), nT0, nT1);
+                    const bool hit0 = !(ex0 > 0.f) & !(na0 > -kAlphaMin);
+                    const bool hit1 = !(ex1 > 0.f) & !(na1 > -kAlphaMin);
+                    const bool go0 = hit0 & !(nT0 <= kTmin), go1 = hit1 & !(nT1 <= kTmin);
+                    float w0, w1;  // MINUS alpha T
+                    unpack2(mul2(na, T2), w0, w1);
+                    const f32x2 wn = pack2(go0 ? w0 : 0.f, go1 ? w1 : 0.f);
+#ifdef GSB_FWD2_ACC_ASM
+                    fma2_acc(pix[0], bcast2(c4.x), wn);
+                    if (D > 1) fma2_acc(pix[1], bcast2(c4.y), wn);
+                    if (D > 2) fma2_acc(pix[2], bcast2(c4.z), wn);
+                    if (D > 3) fma2_acc(pix[3], bcast2(c4.w), wn);
+#else
+                    pix[0] = fma2(bcast2(c4.x), wn, pix[0]);
+                    if (D > 1) pix[1] = fma2(bcast2(c4.y), wn, pix[1]);
+                    if (D > 2) pix[2] = fma2(bcast2(c4.z), wn, pix[2]);
+                    if (D > 3) pix[3] = fma2(bcast2(c4.w), wn, pix[3]);
+#endif
+                    const int sidx = __float_as_int(p4.z);
+                    cur0 = go0 ? sidx : cur0;
+                    cur1 = go1 ? sidx : cur1;
+                    // a hit that is not composited stops the pixel *before* this splat: set the sign bit (a no-op
+                    // on finished pixels, whose T (1 - alpha) < 0 always lands here)
+                    T0 = go0 ? nT0 : __uint_as_float(__float_as_uint(T0) | (hit0 ? 0x80000000u : 0u));
+                    T1 = go1 ? nT1 : __uint_as_float(__float_as_uint(T1) | (hit1 ? 0x80000000u : 0u));
+                }
+                if (__all_sync(0xffffffffu, (T0 < 0.f) & (T1 < 0.f))) {
+                    warp_done = true;
+                    break;
+                }
+            }
+        }
+    }
+    T0 = fabsf(T0);
+    T1 = fabsf(T1);
+    if (COUNT && warp_iters != nullptr && lane == 0 && n_iters) atomicAdd(warp_iters, (unsigned long long)n_iters);
+
+    const float *bg = backgrounds != nullptr ? backgrounds + (size_t)cam * D : nullptr;
+    float c0v[D], c1v[D];
+#pragma unroll
+    for (int k = 0; k < D; ++k) {
+        unpack2(pix[k], c0v[k], c1v[k]);
+        c0v[k] = -c0v[k];
+        c1v[k] = -c1v[k];
+    }
+    if (in0) {
+        const int64_t p = ((int64_t)cam * H + py0) * W + px;
+#pragma unroll
+        for (int k = 0; k < D; ++k) out_colors[p * D + k] = bg != nullptr ? fmaf(T0, bg[k], c0v[k]) : c0v[k];
+        out_alphas[p] = 1.0f - T0;
+        last_ids[p] = cur0;
+    }
+    if (in1) {
+        const int64_t p = ((int64_t)cam * H + py1) * W + px;
+#pragma unroll
+        for (int k = 0; k < D; ++k) out_colors[p * D + k] = bg != nullptr ? fmaf(T1, bg[k], c1v[k]) : c1v[k];
+        out_alphas[p] = 1.0f - T1;
+        last_ids[p] = cur1;
+    }
+}
+
+template <int D>
+int launch_fwd2(int C, int64_t n_isects, const float *recA, const float *recB, const float *colors,
+                const float *backgrounds, const uint8_t *masks, int W, int H, int tw, int th,
+                const int32_t *offsets, const int32_t *flatten_ids, float *out_colors, float *out_alphas,
+                int32_t *last_ids, const int64_t *n_isects_dev, uint8_t *block_masks, cudaStream_t stream) {
+    dim3 grid(tw, th, C);
+    rasterize_fwd2_kernel<D><<<grid, kThreads2, 0, stream>>>(
+        C, n_isects, reinterpret_cast<const float4 *>(recA), reinterpret_cast<const float4 *>(recB), colors,
+        backgrounds, masks, W, H, tw, th, offsets, flatten_ids, out_colors, out_alphas, last_ids, n_isects_dev,
+        block_masks, nullptr);
+    return gsb_check_launch("rasterize_fwd2");
+}
+
+}  // namespace raster
+
+// D <= 4 only; returns GSB_ERR_UNSUPPORTED otherwise (the caller falls back to v1's instantiations)
+int gsb_rasterize_fwd2_dispatch(int C, int64_t n_isects, const int64_t *n_isects_dev, int D, const float *recA,
+                                const float *recB, const float *colors, const float *backgrounds,
+                                const uint8_t *masks, int width, int height, int tile_width, int tile_height,
+                                const int32_t *isect_offsets, const int32_t *flatten_ids, float *render_colors,
+                                float *render_alphas, int32_t *last_ids, uint8_t *block_masks, cudaStream_t stream) {
+#define GSB_FWD2_CASE(DD)                                                                                         \
+    case DD:                                                                                                      \
+        return raster::launch_fwd2<DD>(C, n_isects, recA, recB, colors, backgrounds, masks, width, height,        \
+                                       tile_width, tile_height, isect_offsets, flatten_ids, render_colors,        \
+                                       render_alphas, last_ids, n_isects_dev, block_masks, stream);
+    switch (D) {
+        GSB_FWD2_CASE(1)
+        GSB_FWD2_CASE(2)
+        GSB_FWD2_CASE(3)
+        GSB_FWD2_CASE(4)
+        default:
+            return GSB_ERR_UNSUPPORTED;
+    }
+#undef GSB_FWD2_CASE
+}
+
+// diagnostics for bench.py: iterations of the v2 inner loop (x 64 = executed lane evaluations)
+int gsb_rasterize_fwd2_count(int C, int64_t n_isects, const float *recA, const float *recB, const float *ones,
+                             int width, int height, int tile_width, int tile_height, const int32_t *isect_offsets,
+                             const int32_t *flatten_ids, float *scratch_colors, float *scratch_alphas,
+                             int32_t *scratch_last, int64_t *warp_iters, cudaStream_t stream) {
+    dim3 grid(tile_width, tile_height, C);
+    raster::rasterize_fwd2_kernel<1, true><<<grid, raster::kThreads2, 0, stream>>>(
+        C, n_isects, reinterpret_cast<const float4 *>(recA), reinterpret_cast<const float4 *>(recB), ones, nullptr,
+        nullptr, width, height, tile_width, tile_height, isect_offsets, flatten_ids, scratch_colors, scratch_alphas,
+        scratch_last, nullptr, nullptr, reinterpret_cast<unsigned long long *>(warp_iters));
+    return gsb_check_launch("rasterize_fwd2_count");
+}

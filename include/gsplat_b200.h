@@ -41,6 +41,15 @@ int gsb_abi_version(void);
 /* number of kernels launched by this library since load (or since gsb_reset_launch_count) */
 int64_t gsb_launch_count(void);
 void gsb_reset_launch_count(void);
+/* kernel-variant switches, for A/B measurements only (the defaults are the tuned path):
+ *   GSB_OPT_FWD_VARIANT  1 = rasterize_fwd.cu (warp per 8x4 block, scalar FP32)
+ *                        2 = rasterize_fwd2.cu (half-warp per block, 2 pixels per lane, packed FFMA2) [default, D <= 4]
+ *   GSB_OPT_BWD_VARIANT  1 = rasterize_bwd.cu [default] */
+#define GSB_OPT_FWD_VARIANT 0
+#define GSB_OPT_BWD_VARIANT 1
+#define GSB_OPT_COUNT 2
+int gsb_set_option(int which, int value);
+int gsb_get_option(int which);
 
 /* ---- fully_fused_projection ------------------------------------------------------------------
  * replaces triton_impl/fused_projection_fwd.py:232-300 (launcher) / :18-228 (kernel) and
@@ -211,6 +220,11 @@ int gsb_rasterize_count(int C, int64_t n_isects, const float *recA, const float 
                         int height, int tile_size, int tile_width, int tile_height, const int32_t *isect_offsets,
                         const int32_t *flatten_ids, float *counts, float *render_alphas, int32_t *last_ids,
                         int64_t *warp_pairs, cudaStream_t stream);
+/* diagnostics: iterations of the v2 forward kernel's inner loop (x 64 lanes = executed evaluations), D = 1 */
+int gsb_rasterize_fwd2_count(int C, int64_t n_isects, const float *recA, const float *recB, const float *ones,
+                             int width, int height, int tile_width, int tile_height, const int32_t *isect_offsets,
+                             const int32_t *flatten_ids, float *scratch_colors, float *scratch_alphas,
+                             int32_t *scratch_last, int64_t *warp_iters, cudaStream_t stream);
 /* v_means2d[P,2], v_conics[P,3], v_colors[P,D], v_opacities[P] must be ZERO-filled by the caller
  * (the kernel accumulates with atomics); v_means2d_abs[P,2] (zero-filled) or NULL.
  * block_masks: what gsb_rasterize_fwd_cap wrote for the same inputs, or NULL (recomputed). */

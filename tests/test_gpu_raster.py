@@ -266,6 +266,40 @@ def test_raster_channels_against_oracle(D, bg, absgrad):
         assert int(bad.sum()) == 0, int(bad.sum())
 
 
+@pytest.mark.parametrize("D,bg", [(1, False), (3, True), (4, True)])
+def test_forward_kernel_variants_are_bit_identical(D, bg):
+    """rasterize_fwd2.cu (half-warp per block, two pixels per lane, packed FFMA2) performs the same arithmetic per
+    (pixel, Gaussian) pair as rasterize_fwd.cu: images, alphas and the gradients' inputs (last ids through the
+    backward pass) must be identical bit for bit, also on partial tiles and with masks."""
+    from gsplat.b200_impl import rasterize_to_pixels
+    from gsplat.b200_impl._lib import lib
+
+    C, N, W, H, ts = 2, 4000, 200, 117, 16
+    means2d, conics, colors, opac, radii, depths = _random_splats(C, N, W, H, D, seed=11 + D)
+    tw, th = -(-W // ts), -(-H // ts)
+    _, ids, flat = O.isect_tiles(means2d, radii, depths, ts, tw, th)
+    offs = O.isect_offset_encode(ids, C, tw, th)
+    masks = torch.ones(C, th, tw, dtype=torch.bool)
+    masks[1, 2, 3] = False
+    backgrounds = torch.rand(C, D) if bg else None
+    g = torch.Generator().manual_seed(5)
+    w_c, w_a = torch.randn(C, H, W, D, generator=g).to(DEV), torch.randn(C, H, W, 1, generator=g).to(DEV)
+    outs = {}
+    try:
+        for variant in (1, 2):
+            assert lib.gsb_set_option(0, variant) == 0
+            p = [t.clone().to(DEV).requires_grad_(True) for t in (means2d, conics, colors, opac)]
+            rc, ra = rasterize_to_pixels(p[0], p[1], p[2], p[3], W, H, ts, offs.to(DEV), flat.to(DEV),
+                                         backgrounds=backgrounds.to(DEV) if bg else None, masks=masks.to(DEV))
+            grads = torch.autograd.grad((rc * w_c).sum() + (ra * w_a).sum(), p)
+            outs[variant] = (rc, ra, grads)
+    finally:
+        lib.gsb_set_option(0, 2)
+    assert torch.equal(outs[1][0], outs[2][0]) and torch.equal(outs[1][1], outs[2][1])
+    for a, b in zip(outs[1][2], outs[2][2]):  # same kernel, same inputs: only the atomics' order differs
+        torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-5 * float(b.abs().max()))
+
+
 def test_raster_masks_empty_and_last_tile():
     from gsplat.b200_impl import rasterize_to_pixels
 

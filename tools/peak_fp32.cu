@@ -27,6 +27,60 @@ __global__ void __launch_bounds__(1024, 2) ffma_kernel(float *out, float a, floa
     if (s == 123.456f) out[0] = s;
 }
 
+// packed FP32 (Blackwell FFMA2: two FMAs per issued instruction, `fma.rn.f32x2`)
+__global__ void __launch_bounds__(1024, 2) ffma2_kernel(float *out, float a, float b) {
+    unsigned long long x[kChains], pa, pb;
+    asm("mov.b64 %0, {%1, %1};" : "=l"(pa) : "f"(a));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(pb) : "f"(b));
+#pragma unroll
+    for (int k = 0; k < kChains; ++k) {
+        const float v = (float)(threadIdx.x + k);
+        asm("mov.b64 %0, {%1, %1};" : "=l"(x[k]) : "f"(v));
+    }
+    for (int i = 0; i < kIters; ++i) {
+#pragma unroll
+        for (int k = 0; k < kChains; ++k) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(x[k]) : "l"(pa), "l"(pb));
+    }
+    unsigned long long s = 0;
+#pragma unroll
+    for (int k = 0; k < kChains; ++k) s ^= x[k];
+    if (s == 123456ull) out[0] = 1.f;
+}
+
+// issue-slot economy: the same FMA work as `ffma` / `ffma2` with one integer ALU instruction per FMA pair riding along
+template <bool PACKED>
+__global__ void __launch_bounds__(1024, 2) fma_alu_kernel(float *out, float a, float b, int c) {
+    unsigned long long x[kChains], pa, pb;
+    int y[kChains];
+    asm("mov.b64 %0, {%1, %1};" : "=l"(pa) : "f"(a));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(pb) : "f"(b));
+#pragma unroll
+    for (int k = 0; k < kChains; ++k) {
+        const float v = (float)(threadIdx.x + k);
+        asm("mov.b64 %0, {%1, %1};" : "=l"(x[k]) : "f"(v));
+        y[k] = threadIdx.x + k;
+    }
+    for (int i = 0; i < kIters; ++i) {
+#pragma unroll
+        for (int k = 0; k < kChains; ++k) {
+            if (PACKED) {
+                asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(x[k]) : "l"(pa), "l"(pb));
+            } else {
+                float lo, hi;
+                asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(x[k]));
+                lo = fmaf(lo, a, b);
+                hi = fmaf(hi, a, b);
+                asm("mov.b64 %0, {%1, %2};" : "=l"(x[k]) : "f"(lo), "f"(hi));
+            }
+            asm volatile("lop3.b32 %0, %0, %1, %0, 0x96;" : "+r"(y[k]) : "r"(c));
+        }
+    }
+    unsigned long long s = 0;
+#pragma unroll
+    for (int k = 0; k < kChains; ++k) s ^= x[k] + y[k];
+    if (s == 123456ull) out[0] = 1.f;
+}
+
 __global__ void __launch_bounds__(1024, 2) ex2_kernel(float *out, float a) {
     float x[kChains];
 #pragma unroll
@@ -124,6 +178,12 @@ int main() {
            prop.multiProcessorCount * 16.0 * sm_clock_khz * 1e3 / 1e12);
     measure([&] { ffma_kernel<<<grid, 1024>>>(out, 1.0001f, 0.5f); }, threads * kIters * kChains * 2.0, "fp32_fma",
             "TFLOP/s", false);
+    measure([&] { ffma2_kernel<<<grid, 1024>>>(out, 1.0001f, 0.5f); }, threads * kIters * kChains * 4.0,
+            "fp32_fma_packed_f32x2", "TFLOP/s", false);
+    measure([&] { fma_alu_kernel<false><<<grid, 1024>>>(out, 1.0001f, 0.5f, 3); }, threads * kIters * kChains * 4.0,
+            "fp32_2ffma_plus_1alu", "TFLOP/s", false);
+    measure([&] { fma_alu_kernel<true><<<grid, 1024>>>(out, 1.0001f, 0.5f, 3); }, threads * kIters * kChains * 4.0,
+            "fp32_1ffma2_plus_1alu", "TFLOP/s", false);
     measure([&] { ex2_kernel<<<grid, 1024>>>(out, 1e-3f); }, threads * kIters * kChains, "mufu_ex2", "Tops/s", false);
     measure([&] { mix_kernel<14><<<grid, 1024>>>(out, 1.0001f, 0.5f); }, threads * (kIters / 8) * kChains * (14 + 1) * 2.0,
             "mix_14ffma_1ex2_fp32", "TFLOP/s", false);
