@@ -4,8 +4,8 @@
 // Same semantics, same staging, same exact block culling and the SAME arithmetic per (pixel, Gaussian) pair as
 // rasterize_fwd.cu (every rounding identical: the two kernels produce bit-identical images; tests assert it). What
 // changes is the issue-slot economy, the measured limiter of v1 (ncu: 79 % issue-active, FMA pipe 34 %):
-//   * a warp owns TWO 8x4 blocks of the tile (lanes 0-15: block 2w, lanes 16-31: block 2w+1); each half walks the
-//     ballot list of its own block, so one loop iteration composites two different Gaussians onto 2 x 32 pixels;
+//   * a warp owns TWO vertically adjacent 8x4 blocks of the tile (lanes 0-15 / 16-31); each half walks the ballot
+//     list of its own block, so one loop iteration composites two different Gaussians onto 2 x 32 pixels;
 //   * a lane owns two vertically adjacent pixels and evaluates them with packed instructions (one FFMA2 = two
 //     FMAs, per-Gaussian scalars enter as broadcast operands at no cost), so the list bookkeeping, the three 16-byte
 //     shared-memory loads and most of the arithmetic are issued once per two pixels;
@@ -92,9 +92,12 @@ rasterize_fwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
     const int64_t tile_id = ((int64_t)cam * th + tile_y) * tw + tile_x;
     const int range_start = offsets[tile_id];
     const int range_end = (tile_id + 1 < (int64_t)C * th * tw) ? offsets[tile_id + 1] : (int)n_isects;
-    // block (bx = half, by = warp) of the tile: the same numbering as v1's warps, bit 2*warp + half of the mask
-    const int px = tile_x * kTile + half * 8 + (l16 & 7);
-    const int py0 = tile_y * kTile + warp * 4 + (l16 >> 3) * 2, py1 = py0 + 1;
+    // The two halves of a warp own VERTICALLY adjacent 8x4 blocks (centres 4 pixels apart; horizontal neighbours are
+    // 8 apart): their Gaussian lists overlap most, so the two list lengths, whose maximum the loop runs for, differ
+    // least. Block (bx, by) = (warp & 1, 2 (warp >> 1) + half); its bit in the staged mask is by * 2 + bx as in v1.
+    const int bx = warp & 1, by = 2 * (warp >> 1) + half;
+    const int px = tile_x * kTile + bx * 8 + (l16 & 7);
+    const int py0 = tile_y * kTile + by * 4 + (l16 >> 3) * 2, py1 = py0 + 1;
     const bool in0 = (px < W) & (py0 < H), in1 = (px < W) & (py1 < H);
 
     f32x2 pix[D];
@@ -110,7 +113,7 @@ rasterize_fwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
         const float pxf = (float)px + 0.5f;
         const f32x2 npy = pack2(-((float)py0 + 0.5f), -((float)py1 + 0.5f));
         bool warp_done = __all_sync(0xffffffffu, (T0 < 0.f) & (T1 < 0.f));
-        const int bit0 = 2 * warp, bit1 = 2 * warp + 1;
+        const int bit0 = (4 * (warp >> 1)) + bx, bit1 = bit0 + 2;  // by * 2 + bx for half 0 / half 1
 
         for (int base = range_start; base < range_end; base += kThreads2) {
             if (__syncthreads_count((T0 < 0.f) & (T1 < 0.f)) == kThreads2) break;

@@ -91,6 +91,10 @@ class _Lib:
             fn.restype = restype
             fn.argtypes = [t for t, _ in argl]
         self._dll = dll
+        # kernel-variant switches for A/B runs (include/gsplat_b200.h: GSB_OPT_*); unset = the tuned defaults
+        for which, env in ((0, "GSPLAT_B200_FWD_VARIANT"), (1, "GSPLAT_B200_BWD_VARIANT")):
+            if os.environ.get(env):
+                dll.gsb_set_option(which, int(os.environ[env]))
         return dll
 
     def __getattr__(self, name):

@@ -778,11 +778,25 @@ class _RasterizeToPixels(torch.autograd.Function):
         if flatten_ids.dtype != torch.int32:
             flatten_ids = flatten_ids.int()
         m8 = masks.to(torch.uint8) if masks is not None else None
-        rec = torch.empty((2, max(P, 1), 4), dtype=torch.float32, device=dev)
-        lib.gsb_rasterize_pack(P, ptr(means2d), ptr(conics), ptr(opacities), ptr(rec[0]), ptr(rec[1]), st)
         render_colors = torch.empty((C, height, width, D), dtype=torch.float32, device=dev)
         render_alphas = torch.empty((C, height, width, 1), dtype=torch.float32, device=dev)
         last_ids = torch.empty((C, height, width), dtype=torch.int32, device=dev)
+        if tile_size != 16:
+            # the tuned compositor is built around 16x16 tiles; every other tile size takes the plain kernels
+            if pending is not None:
+                n_isects = min(n_isects, pending.wait())
+            lib.gsb_rasterize_fwd_generic(C, n_isects, D, ptr(means2d), ptr(conics), ptr(opacities), ptr(colors),
+                                          ptr(backgrounds), ptr(m8), width, height, tile_size, tile_width, tile_height,
+                                          ptr(isect_offsets), ptr(flatten_ids), ptr(render_colors), ptr(render_alphas),
+                                          ptr(last_ids), st)
+            ctx.pending = pending
+            ctx.save_for_backward(means2d, conics, colors, backgrounds, m8, isect_offsets, flatten_ids, render_alphas,
+                                  last_ids, opacities)
+            ctx.width, ctx.height, ctx.tile_size, ctx.absgrad = width, height, tile_size, absgrad
+            ctx.shapes = (conics.shape, opacities.shape)
+            return render_colors, render_alphas
+        rec = torch.empty((2, max(P, 1), 4), dtype=torch.float32, device=dev)
+        lib.gsb_rasterize_pack(P, ptr(means2d), ptr(conics), ptr(opacities), ptr(rec[0]), ptr(rec[1]), st)
         n_dev = ptr(pending.n_dev) if (pending is not None and pending.n is None) else None
         if pending is not None and pending.n is not None:
             n_isects = min(n_isects, pending.n)
@@ -803,8 +817,13 @@ class _RasterizeToPixels(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, v_render_colors, v_render_alphas):
-        (means2d, rec, colors, backgrounds, m8, isect_offsets, flatten_ids, render_alphas,
-         last_ids, block_masks) = ctx.saved_tensors
+        generic = ctx.tile_size != 16
+        if generic:
+            (means2d, conics, colors, backgrounds, m8, isect_offsets, flatten_ids, render_alphas, last_ids,
+             opacities) = ctx.saved_tensors
+        else:
+            (means2d, rec, colors, backgrounds, m8, isect_offsets, flatten_ids, render_alphas,
+             last_ids, block_masks) = ctx.saved_tensors
         C, tile_height, tile_width = isect_offsets.shape
         D = colors.shape[-1]
         dev = means2d.device
@@ -822,11 +841,19 @@ class _RasterizeToPixels(torch.autograd.Function):
         v_opacities = parts[3].view(opac_shape)
         v_abs = parts[4].view(means2d.shape) if ctx.absgrad else None
         n_isects = flatten_ids.numel() if ctx.pending is None else min(flatten_ids.numel(), ctx.pending.wait())
-        lib.gsb_rasterize_bwd(C, n_isects, D, ptr(rec[0]), ptr(rec[1]), ptr(colors), ptr(backgrounds),
-                              ptr(m8), ctx.width, ctx.height, ctx.tile_size, tile_width, tile_height,
-                              ptr(isect_offsets), ptr(flatten_ids), ptr(render_alphas), ptr(last_ids),
-                              ptr(block_masks), ptr(v_render_colors), ptr(v_render_alphas), ptr(v_abs), ptr(v_means2d),
-                              ptr(v_conics), ptr(v_colors), ptr(v_opacities), stream_of(means2d))
+        if generic:
+            lib.gsb_rasterize_bwd_generic(C, n_isects, D, ptr(means2d), ptr(conics), ptr(opacities), ptr(colors),
+                                          ptr(backgrounds), ptr(m8), ctx.width, ctx.height, ctx.tile_size, tile_width,
+                                          tile_height, ptr(isect_offsets), ptr(flatten_ids), ptr(render_alphas),
+                                          ptr(last_ids), ptr(v_render_colors), ptr(v_render_alphas), ptr(v_abs),
+                                          ptr(v_means2d), ptr(v_conics), ptr(v_colors), ptr(v_opacities),
+                                          stream_of(means2d))
+        else:
+            lib.gsb_rasterize_bwd(C, n_isects, D, ptr(rec[0]), ptr(rec[1]), ptr(colors), ptr(backgrounds),
+                                  ptr(m8), ctx.width, ctx.height, ctx.tile_size, tile_width, tile_height,
+                                  ptr(isect_offsets), ptr(flatten_ids), ptr(render_alphas), ptr(last_ids),
+                                  ptr(block_masks), ptr(v_render_colors), ptr(v_render_alphas), ptr(v_abs),
+                                  ptr(v_means2d), ptr(v_conics), ptr(v_colors), ptr(v_opacities), stream_of(means2d))
         if ctx.absgrad:
             means2d.absgrad = v_abs
         v_backgrounds = None

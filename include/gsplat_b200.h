@@ -220,6 +220,21 @@ int gsb_rasterize_count(int C, int64_t n_isects, const float *recA, const float 
                         int height, int tile_size, int tile_width, int tile_height, const int32_t *isect_offsets,
                         const int32_t *flatten_ids, float *counts, float *render_alphas, int32_t *last_ids,
                         int64_t *warp_pairs, cudaStream_t stream);
+/* Any other tile size (1 <= tile_size^2 <= 1024; the reference's tests use 4): the plain one-thread-per-pixel
+ * compositor of csrc/rasterize_generic.cu on the unpacked means2d / conics / opacities (no splat records). Same
+ * contracts as gsb_rasterize_fwd / gsb_rasterize_bwd (gradient buffers zero-filled by the caller). */
+int gsb_rasterize_fwd_generic(int C, int64_t n_isects, int D, const float *means2d, const float *conics,
+                              const float *opacities, const float *colors, const float *backgrounds,
+                              const uint8_t *masks, int width, int height, int tile_size, int tile_width,
+                              int tile_height, const int32_t *isect_offsets, const int32_t *flatten_ids,
+                              float *render_colors, float *render_alphas, int32_t *last_ids, cudaStream_t stream);
+int gsb_rasterize_bwd_generic(int C, int64_t n_isects, int D, const float *means2d, const float *conics,
+                              const float *opacities, const float *colors, const float *backgrounds,
+                              const uint8_t *masks, int width, int height, int tile_size, int tile_width,
+                              int tile_height, const int32_t *isect_offsets, const int32_t *flatten_ids,
+                              const float *render_alphas, const int32_t *last_ids, const float *v_render_colors,
+                              const float *v_render_alphas, float *v_means2d_abs, float *v_means2d, float *v_conics,
+                              float *v_colors, float *v_opacities, cudaStream_t stream);
 /* diagnostics: iterations of the v2 forward kernel's inner loop (x 64 lanes = executed evaluations), D = 1 */
 int gsb_rasterize_fwd2_count(int C, int64_t n_isects, const float *recA, const float *recB, const float *ones,
                              int width, int height, int tile_width, int tile_height, const int32_t *isect_offsets,

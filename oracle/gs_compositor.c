@@ -126,12 +126,12 @@ int gso_rasterize_bwd(int C, int64_t P, int64_t n_isects, int D, const float *me
         double *bgl = (double *)malloc(sizeof(double) * D);
 #pragma omp for schedule(dynamic, 1)
         for (int64_t t = 0; t < n_tiles; ++t) {
-            if (masks != NULL && !masks[t]) continue;
             const int cam = (int)(t / ((int64_t)th * tw));
             const int ty = (int)((t / tw) % th), tx = (int)(t % tw);
             const int lo = offsets[t];
             const int hi = (t + 1 < n_tiles) ? offsets[t + 1] : (int)n_isects;
-            const int n = hi - lo;
+            /* a masked-out tile shows the background only (alpha 0): it still feeds v_backgrounds */
+            const int n = (masks != NULL && !masks[t]) ? 0 : hi - lo;
             for (int k = 0; k < D; ++k) bgl[k] = 0.0;
             if (n > 0) {
                 if ((size_t)n * S > local_cap) {

@@ -104,6 +104,18 @@ def test_rasterization_covars_channels_and_ortho():
         rasterization(*[t.to(DEV) for t in cpu], W, H, camera_model="equirectangular")
 
 
+@pytest.mark.parametrize("tile_size,packed", [(8, False), (4, True)])
+def test_rasterization_other_tile_sizes(tile_size, packed):
+    """rasterization(tile_size != 16) end to end: intersection keys, offsets and the plain compositor."""
+    from parity import check_pair, run_pair
+
+    means, quats, scales, opac, colors, viewmats, Ks, W, H = _scene(step=60, cams=2)
+    r = run_pair((means, quats, scales, opac, colors), viewmats, Ks, W, H, dict(tile_size=tile_size), packed=packed)
+    assert r["meta"]["tile_size"] == tile_size and r["meta"]["isect_offsets"].shape[1:] == (
+        -(-H // tile_size), -(-W // tile_size))
+    check_pair(r, f"tile_size {tile_size} packed={packed}")
+
+
 def test_full_size_properties_cfg2():
     """BASELINE cfg2 (1M Gaussians, SH deg 3, 1920x1080): size-independent properties."""
     import sys, os
