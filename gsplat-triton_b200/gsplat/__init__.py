@@ -36,6 +36,16 @@ def __getattr__(name):
         from .b200_impl import accumulate
 
         return accumulate
+    if name == "quat_scale_to_covar_preci":
+        from .b200_impl._covar import quat_scale_to_covar_preci
+
+        return quat_scale_to_covar_preci
+    if name in ("DefaultStrategy", "MCMCStrategy", "Strategy"):
+        # the reference's own strategy package, unmodified, resolved through GSPLAT_REFERENCE_PATH (it is pure torch
+        # on top of rasterization()'s `meta`, gsplat.relocation and gsplat.quat_scale_to_covar_preci)
+        from . import strategy
+
+        return getattr(strategy, name)
     if name == "SelectiveAdam":
         from .optimizers import SelectiveAdam
 
