@@ -27,5 +27,16 @@ for packed in (False, True):
                                          render_mode="RGB+ED", sparse_grad=False)
             (rc.sum() + ra.sum()).backward()
             n += 1
+# the plain kernels behind tile_size != 16 and the first-generation forward kernel
+from gsplat.b200_impl._lib import lib  # noqa: E402
+
+for tile_size, variant in ((8, 2), (16, 1)):
+    lib.gsb_set_option(0, variant)
+    p = [t.clone().to(dev).requires_grad_(True) for t in (means, quats, scales * 3 + 0.002, opac, shs)]
+    rc, ra, meta = rasterization(*p, viewmats[:2].to(dev), Ks[:2].to(dev), W, H, sh_degree=2, packed=False,
+                                 tile_size=tile_size, absgrad=True)
+    (rc.sum() + ra.sum()).backward()
+    n += 1
+lib.gsb_set_option(0, 2)
 torch.cuda.synchronize()
 print("sanitize_small: %d fwd+bwd passes, last n_isects=%d" % (n, meta["flatten_ids"].numel()))
