@@ -13,10 +13,13 @@
 // no host synchronisation; the transfer overlaps the packing store by store.
 //
 // Mailbox layout (identical on every rank):
-//   [0, 128)     uint64 flags_fwd[16]   slot s = epoch of the last forward put completed by rank s
-//   [128, 256)   uint64 flags_bwd[16]
-//   [256, 264)   uint32 done[2]         CTA completion counters of the local put kernels
-//   [1024, ...)  4 regions of `cap` bytes: (direction, epoch parity) -> 1024 + (2*dir + parity) * cap
+//   [128 ch, +128)  uint64 flags[ch][16]  slot s = epoch of the last put completed by rank s on channel ch;
+//                   channels: 0 forward (geometry, or all fields), 1 backward (geometry, or all fields),
+//                   2 forward colours, 3 backward colours (the split exchange: colours travel under the receiver's
+//                   intersection pipeline)
+//   [768, 784)      uint32 done[4]        CTA completion counters of the local put kernels, per channel
+//   [1024, ...)     4 regions of `cap` bytes: (direction = ch & 1, epoch parity) -> 1024 + (2*dir + parity) * cap;
+//                   both channels of a direction write disjoint fields of the same region
 // Two regions per direction: a peer may start step t+1's put while this rank still unpacks step t,
 // but cannot reach step t+2's put before this rank has published step t+1 (stream order), see DESIGN.md 6.
 #include "common.cuh"
@@ -51,12 +54,15 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
     return t;
 }
 
-// called by every thread of the CTA after its peer stores: the last CTA of the grid publishes `epoch`
+constexpr int kChannels = 4;
+constexpr int64_t kDoneOffset = 768;
+
+// called by every thread of the CTA after its peer stores: the last CTA of the grid publishes `epoch` on channel `dir`
 __device__ __forceinline__ void publish_when_grid_done(const PeerTable &peers, int world, int rank, int dir,
                                                        unsigned long long epoch) {
     __shared__ bool s_last;
     __syncthreads();  // every thread's peer stores happen-before thread 0's fence (cumulative)
-    unsigned *done = reinterpret_cast<unsigned *>(peers.base[rank] + 256) + dir;
+    unsigned *done = reinterpret_cast<unsigned *>(peers.base[rank] + kDoneOffset) + dir;
     if (threadIdx.x == 0) {
         __threadfence_system();
         unsigned prev = atomicAdd(done, 1u);
@@ -82,7 +88,8 @@ constexpr int kPackedFields = 8;  // + camera ids, Gaussian ids (packed rows onl
 struct Fields {
     const float *src[kFields];
     int width[kFields];
-    int count;
+    int count;            // number of entries of `active`
+    int active[kFields];  // the fields this launch sends (a split exchange sends geometry and colours separately)
 };
 __host__ __device__ __forceinline__ int64_t round_up4(int64_t v) { return (v + 3) & ~(int64_t)3; }
 __host__ __device__ __forceinline__ int64_t field_offset(const int *width, int field, int64_t rows) {
@@ -121,11 +128,11 @@ __device__ __forceinline__ void copy_run(const float *__restrict__ src, float *_
 // at rows [c_local, n_base .. n_base + N_local) of its [C_local, N_total] table
 __global__ void __launch_bounds__(kThreads)
 put_fwd_kernel(PeerTable peers, Fields fields, int world, int rank, int C_local, int64_t N_local, int64_t N_total,
-               int64_t n_base, int64_t region_offset, unsigned long long epoch) {
+               int64_t n_base, int64_t region_offset, unsigned long long epoch, int channel) {
     // segment order: camera fastest and rotated by rank, so the CTAs in flight at any moment cover every
     // destination and no two senders start on the same one (an 8-to-1 incast would share one ingress port)
     const int n_cam = world * C_local;
-    const int f = blockIdx.y / n_cam;
+    const int f = fields.active[blockIdx.y / n_cam];
     const int c = (blockIdx.y % n_cam + (rank + 1) * C_local) % n_cam;
     const int dest = c / C_local, c_local = c - dest * C_local;
     const int w = fields.width[f];
@@ -133,17 +140,17 @@ put_fwd_kernel(PeerTable peers, Fields fields, int world, int rank, int C_local,
     float *dst = reinterpret_cast<float *>(peers.base[dest] + region_offset) +
                  field_offset(fields.width, f, (int64_t)C_local * N_total) + ((int64_t)c_local * N_total + n_base) * w;
     copy_run(src, dst, N_local * w);
-    publish_when_grid_done(peers, world, rank, 0, epoch);
+    publish_when_grid_done(peers, world, rank, channel, epoch);
 }
 
 // backward: segment (local camera c_local, destination rank r, field f): the N_r gradient rows of rank r's
 // Gaussians -> rank r, at rows [rank*C_local + c_local, 0 .. N_r) of its [world*C_local, N_r] table
 __global__ void __launch_bounds__(kThreads)
 put_bwd_kernel(PeerTable peers, Fields fields, RankBases bases, int world, int rank, int C_local, int64_t N_total,
-               int64_t region_offset, unsigned long long epoch) {
+               int64_t region_offset, unsigned long long epoch, int channel) {
     // destination fastest and rotated by rank (see put_fwd_kernel)
     const int n_seg = world * C_local;
-    const int f = blockIdx.y / n_seg;
+    const int f = fields.active[blockIdx.y / n_seg];
     const int q = blockIdx.y % n_seg;
     const int dest = (q + rank + 1) % world, c_local = q / world;
     const int w = fields.width[f];
@@ -153,7 +160,7 @@ put_bwd_kernel(PeerTable peers, Fields fields, RankBases bases, int world, int r
                  field_offset(fields.width, f, (int64_t)world * C_local * N_dest) +
                  ((int64_t)rank * C_local + c_local) * N_dest * w;
     copy_run(src, dst, N_dest * w);
-    publish_when_grid_done(peers, world, rank, 1, epoch);
+    publish_when_grid_done(peers, world, rank, channel, epoch);
 }
 
 // ---- packed rows (COO): variable row counts per destination --------------------------------------------
@@ -219,7 +226,8 @@ put_packed_bwd_kernel(PeerTable peers, PackedFields fields, PackedPlan plan, int
 // wait until every rank has published `epoch` in direction `dir`, then copy the local region out
 __global__ void __launch_bounds__(kThreads)
 wait_copy_kernel(const char *__restrict__ local_base, int world, int dir, unsigned long long epoch,
-                 int64_t region_offset, int64_t n_floats, float *__restrict__ out, int *timeout_flag) {
+                 int64_t region_offset, int64_t begin0, int64_t end0, int64_t begin1, int64_t end1,
+                 float *__restrict__ out, int *timeout_flag) {
     if (threadIdx.x < world) {
         const unsigned long long *flag =
             reinterpret_cast<const unsigned long long *>(local_base + 128 * dir) + threadIdx.x;
@@ -238,11 +246,14 @@ wait_copy_kernel(const char *__restrict__ local_base, int world, int dir, unsign
     __syncthreads();
     // region and `out` are 16-byte aligned (region offsets are multiples of 1 KB); peers wrote through L2,
     // so read with .cg: never served from a stale L1 line
+    // two float ranges of the region (field offsets are multiples of 4 floats): [begin0, end0) and [begin1, end1)
     const float4 *box = reinterpret_cast<const float4 *>(local_base + region_offset);
     float4 *o4 = reinterpret_cast<float4 *>(out);
-    const int64_t n4 = n_floats >> 2;
-    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n4; i += (int64_t)gridDim.x * kThreads)
-        o4[i] = __ldcg(box + i);
+    const int64_t b0 = begin0 >> 2, n0 = (end0 - begin0) >> 2, b1 = begin1 >> 2, n1 = (end1 - begin1) >> 2;
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n0 + n1; i += (int64_t)gridDim.x * kThreads) {
+        const int64_t k = i < n0 ? b0 + i : b1 + (i - n0);
+        o4[k] = __ldcg(box + k);
+    }
 }
 
 int fill_peers(PeerTable &t, const void *const *peer_bases_host, int world) {

@@ -165,8 +165,9 @@ def run_pair(cpu_leaves, viewmats, Ks, W, H, kw, packed=False, device="cuda", gp
     w_c, w_a = torch.rand(o_rc.shape, generator=g), torch.rand(o_ra.shape, generator=g)
     keep = (~flag)[..., None].float()
     w_c, w_a = w_c * keep, w_a * keep
-    grads = torch.autograd.grad((rc * w_c.to(device)).sum() + (ra * w_a.to(device)).sum(), leaves)
-    o_grads = torch.autograd.grad((o_rc * w_c).sum() + (o_ra * w_a).sum(), o_leaves)
+    # a leaf may be unused (colours in depth-only modes, quats / scales when covars are given): None on both sides
+    grads = torch.autograd.grad((rc * w_c.to(device)).sum() + (ra * w_a.to(device)).sum(), leaves, allow_unused=True)
+    o_grads = torch.autograd.grad((o_rc * w_c).sum() + (o_ra * w_a).sum(), o_leaves, allow_unused=True)
     return dict(rc=rc, ra=ra, meta=meta, grads=grads, o_rc=o_rc, o_ra=o_ra, o_meta=o_meta, o_grads=o_grads, flag=flag,
                 leaves=leaves)
 
@@ -177,4 +178,6 @@ def check_pair(r, what, atol_rel=1e-4, channels=None):
     assert_close_classified(r["rc"], r["o_rc"], r["flag"], 1e-4, 1e-4, what + " colours")
     assert_close_classified(r["ra"], r["o_ra"], r["flag"], 1e-4, 1e-4, what + " alphas")
     for name, a, b in zip(GRAD_TOL, r["grads"], r["o_grads"]):
-        assert_grads_close(a, b, GRAD_TOL[name], atol_rel, f"{what} v_{name} (masked loss)")
+        assert (a is None) == (b is None), f"{what}: v_{name} is unused on one side only"
+        if a is not None:
+            assert_grads_close(a, b, GRAD_TOL[name], atol_rel, f"{what} v_{name} (masked loss)")
