@@ -343,34 +343,57 @@ unsigned blocks_per_run(int64_t len) {
 }
 }  // namespace
 
+namespace {
+// fields selected by `mask` (bit f = field f), in field order
+void select_fields(Fields &fields, int n_fields, int mask) {
+    fields.count = 0;
+    for (int f = 0; f < n_fields; ++f)
+        if ((mask >> f) & 1) fields.active[fields.count++] = f;
+}
+}  // namespace
+
+extern "C" int gsb_a2a_put_fwd_part(int world, int rank, int C_local, int64_t N_local, int64_t N_total, int64_t n_base,
+                                    int D, const float *means2d, const float *depths, const float *conics,
+                                    const float *opacities, const float *colors, const int32_t *radii,
+                                    int fields_mask, int channel, const void *const *peer_bases_host,
+                                    int64_t region_offset, int64_t epoch, cudaStream_t stream) {
+    GSB_REQUIRE(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, "bad world/rank");
+    GSB_REQUIRE(C_local >= 1 && N_local >= 0 && N_total >= N_local && n_base >= 0 && D >= 1, "bad sizes");
+    GSB_REQUIRE((int64_t)world * C_local * kFields <= 65535, "too many cameras for one launch");
+    GSB_REQUIRE(region_offset >= kHeaderBytes && epoch > 0, "bad region/epoch");
+    GSB_REQUIRE((channel == 0 || channel == 2) && fields_mask > 0 && fields_mask < (1 << kFields), "bad channel/fields");
+    PeerTable peers;
+    GSB_REQUIRE(fill_peers(peers, peer_bases_host, world) == 0, "null peer mailbox");
+    Fields fields = {{means2d, depths, conics, opacities, colors, reinterpret_cast<const float *>(radii)},
+                     {2, 1, 3, 1, D, 1}, 0, {0, 0, 0, 0, 0, 0}};
+    select_fields(fields, kFields, fields_mask);
+    for (int i = 0; i < fields.count; ++i) GSB_REQUIRE(fields.src[fields.active[i]] != nullptr, "null field");
+    dim3 grid(blocks_per_run(N_local * (D > 3 ? D : 3)), (unsigned)(world * C_local * fields.count));
+    put_fwd_kernel<<<grid, kThreads, 0, stream>>>(peers, fields, world, rank, C_local, N_local, N_total, n_base,
+                                                 region_offset, (unsigned long long)epoch, channel);
+    return gsb_check_launch("a2a_put_fwd");
+}
+
 extern "C" int gsb_a2a_put_fwd(int world, int rank, int C_local, int64_t N_local, int64_t N_total, int64_t n_base,
                                int D, const float *means2d, const float *depths, const float *conics,
                                const float *opacities, const float *colors, const int32_t *radii,
                                const void *const *peer_bases_host, int64_t region_offset, int64_t epoch,
                                cudaStream_t stream) {
-    GSB_REQUIRE(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, "bad world/rank");
-    GSB_REQUIRE(C_local >= 1 && N_local >= 0 && N_total >= N_local && n_base >= 0 && D >= 1, "bad sizes");
-    GSB_REQUIRE((int64_t)world * C_local * kFields <= 65535, "too many cameras for one launch");
-    GSB_REQUIRE(region_offset >= kHeaderBytes && epoch > 0, "bad region/epoch");
-    PeerTable peers;
-    GSB_REQUIRE(fill_peers(peers, peer_bases_host, world) == 0, "null peer mailbox");
-    Fields fields = {{means2d, depths, conics, opacities, colors, reinterpret_cast<const float *>(radii)},
-                     {2, 1, 3, 1, D, 1}, kFields};
-    dim3 grid(blocks_per_run(N_local * (D > 3 ? D : 3)), (unsigned)(world * C_local * kFields));
-    put_fwd_kernel<<<grid, kThreads, 0, stream>>>(peers, fields, world, rank, C_local, N_local, N_total, n_base,
-                                                 region_offset, (unsigned long long)epoch);
-    return gsb_check_launch("a2a_put_fwd");
+    return gsb_a2a_put_fwd_part(world, rank, C_local, N_local, N_total, n_base, D, means2d, depths, conics, opacities,
+                                colors, radii, (1 << kFields) - 1, 0, peer_bases_host, region_offset, epoch, stream);
 }
 
-extern "C" int gsb_a2a_put_bwd(int world, int rank, int C_local, int64_t N_total, const int64_t *n_bases_host, int D,
-                               const float *v_means2d, const float *v_depths, const float *v_conics,
-                               const float *v_opacities, const float *v_colors,
-                               const void *const *peer_bases_host, int64_t region_offset, int64_t epoch,
-                               cudaStream_t stream) {
+extern "C" int gsb_a2a_put_bwd_part(int world, int rank, int C_local, int64_t N_total, const int64_t *n_bases_host,
+                                    int D, const float *v_means2d, const float *v_depths, const float *v_conics,
+                                    const float *v_opacities, const float *v_colors, int fields_mask, int channel,
+                                    const void *const *peer_bases_host, int64_t region_offset, int64_t epoch,
+                                    cudaStream_t stream) {
     GSB_REQUIRE(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, "bad world/rank");
     GSB_REQUIRE(C_local >= 1 && N_total >= 0 && D >= 1 && n_bases_host != nullptr, "bad sizes");
     GSB_REQUIRE((int64_t)world * C_local * kFields <= 65535, "too many cameras for one launch");
     GSB_REQUIRE(region_offset >= kHeaderBytes && epoch > 0, "bad region/epoch");
+    GSB_REQUIRE((channel == 1 || channel == 3) && fields_mask > 0 && fields_mask < (1 << (kFields - 1)),
+                "bad channel/fields");
     PeerTable peers;
     GSB_REQUIRE(fill_peers(peers, peer_bases_host, world) == 0, "null peer mailbox");
     RankBases bases;
@@ -381,25 +404,47 @@ extern "C" int gsb_a2a_put_bwd(int world, int rank, int C_local, int64_t N_total
         if (bases.base[i + 1] - bases.base[i] > widest) widest = bases.base[i + 1] - bases.base[i];
     }
     GSB_REQUIRE(bases.base[0] == 0 && bases.base[world] == N_total, "n_bases must run from 0 to N_total");
-    Fields fields = {{v_means2d, v_depths, v_conics, v_opacities, v_colors, nullptr}, {2, 1, 3, 1, D, 1}, kFields - 1};
-    dim3 grid(blocks_per_run(widest * (D > 3 ? D : 3)), (unsigned)(world * C_local * (kFields - 1)));
+    Fields fields = {{v_means2d, v_depths, v_conics, v_opacities, v_colors, nullptr}, {2, 1, 3, 1, D, 1}, 0,
+                     {0, 0, 0, 0, 0, 0}};
+    select_fields(fields, kFields - 1, fields_mask);
+    dim3 grid(blocks_per_run(widest * (D > 3 ? D : 3)), (unsigned)(world * C_local * fields.count));
     put_bwd_kernel<<<grid, kThreads, 0, stream>>>(peers, fields, bases, world, rank, C_local, N_total, region_offset,
-                                                 (unsigned long long)epoch);
+                                                 (unsigned long long)epoch, channel);
     return gsb_check_launch("a2a_put_bwd");
+}
+
+extern "C" int gsb_a2a_put_bwd(int world, int rank, int C_local, int64_t N_total, const int64_t *n_bases_host, int D,
+                               const float *v_means2d, const float *v_depths, const float *v_conics,
+                               const float *v_opacities, const float *v_colors,
+                               const void *const *peer_bases_host, int64_t region_offset, int64_t epoch,
+                               cudaStream_t stream) {
+    return gsb_a2a_put_bwd_part(world, rank, C_local, N_total, n_bases_host, D, v_means2d, v_depths, v_conics,
+                                v_opacities, v_colors, (1 << (kFields - 1)) - 1, 1, peer_bases_host, region_offset,
+                                epoch, stream);
+}
+
+extern "C" int gsb_a2a_wait_copy_part(int world, int channel, int64_t epoch, const void *local_base,
+                                      int64_t region_offset, int64_t begin0, int64_t end0, int64_t begin1,
+                                      int64_t end1, float *out, int *timeout_flag, cudaStream_t stream) {
+    GSB_REQUIRE(world >= 1 && world <= kMaxPeers && channel >= 0 && channel < kChannels, "bad world/channel");
+    GSB_REQUIRE(begin0 >= 0 && end0 >= begin0 && begin1 >= 0 && end1 >= begin1 && local_base != nullptr, "bad ranges");
+    GSB_REQUIRE(((begin0 | end0 | begin1 | end1) & 3) == 0, "ranges must be multiples of 4 floats");
+    GSB_REQUIRE(region_offset >= kHeaderBytes && (region_offset & 15) == 0 && epoch > 0, "bad region/epoch");
+    GSB_REQUIRE(((uintptr_t)out & 15) == 0, "output buffer must be 16-byte aligned");
+    const int64_t n_floats = (end0 - begin0) + (end1 - begin1);
+    int64_t b = (n_floats / 4 + kThreads - 1) / kThreads;
+    unsigned grid = (unsigned)(b < 1 ? 1 : (b > 148 * 8 ? 148 * 8 : b));
+    wait_copy_kernel<<<grid, kThreads, 0, stream>>>(reinterpret_cast<const char *>(local_base), world, channel,
+                                                   (unsigned long long)epoch, region_offset, begin0, end0, begin1, end1,
+                                                   out, timeout_flag);
+    return gsb_check_launch("a2a_wait_copy");
 }
 
 extern "C" int gsb_a2a_wait_copy(int world, int dir, int64_t epoch, const void *local_base, int64_t region_offset,
                                  int64_t n_floats, float *out, int *timeout_flag, cudaStream_t stream) {
-    GSB_REQUIRE(world >= 1 && world <= kMaxPeers && (dir == 0 || dir == 1), "bad world/dir");
-    GSB_REQUIRE(n_floats >= 0 && (n_floats & 3) == 0 && local_base != nullptr, "bad sizes");
-    GSB_REQUIRE(region_offset >= kHeaderBytes && (region_offset & 15) == 0 && epoch > 0, "bad region/epoch");
-    GSB_REQUIRE(((uintptr_t)out & 15) == 0, "output buffer must be 16-byte aligned");
-    int64_t b = (n_floats / 4 + kThreads - 1) / kThreads;
-    unsigned grid = (unsigned)(b < 1 ? 1 : (b > 148 * 8 ? 148 * 8 : b));
-    wait_copy_kernel<<<grid, kThreads, 0, stream>>>(reinterpret_cast<const char *>(local_base), world, dir,
-                                                   (unsigned long long)epoch, region_offset, n_floats, out,
-                                                   timeout_flag);
-    return gsb_check_launch("a2a_wait_copy");
+    GSB_REQUIRE((dir == 0 || dir == 1) && n_floats >= 0 && (n_floats & 3) == 0, "bad dir/size");
+    return gsb_a2a_wait_copy_part(world, dir, epoch, local_base, region_offset, 0, n_floats, 0, 0, out, timeout_flag,
+                                  stream);
 }
 
 namespace {

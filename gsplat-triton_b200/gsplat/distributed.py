@@ -398,7 +398,8 @@ class PeerMailbox:
         self.local = None  # own mailbox (device pointer, int)
         self.peers = [None] * self.world  # mapped peer mailboxes (own pointer at [rank])
         self.peer_array = (ctypes.c_void_p * self.world)()
-        self.epoch = [0, 0]  # forward, backward
+        self.epoch = [0, 0, 0, 0]  # per channel: forward, backward, forward colours, backward colours
+        self.side_stream = torch.cuda.Stream(device=self.device)  # the split exchange's puts run here
         flag = ctypes.c_void_p()
         _check(lib.gsb_peer_flag_alloc(ctypes.byref(flag)), "gsb_peer_flag_alloc")
         self.timeout_flag = flag.value
@@ -437,16 +438,32 @@ class PeerMailbox:
                 self.peers[r] = mapped.value
             self.peer_array[r] = self.peers[r]
         self.capacity = cap
-        self.epoch = [0, 0]  # fresh, zeroed flags on every rank
+        self.epoch = [0, 0, 0, 0]  # fresh, zeroed flags on every rank
         dist.barrier(self.group)  # nobody writes before every rank has mapped every mailbox
 
     def region(self, direction: int, epoch: int) -> int:
-        return self.header + (2 * direction + (epoch & 1)) * self.capacity
+        return self.header + (2 * (direction & 1) + (epoch & 1)) * self.capacity
 
-    def next_epoch(self, direction: int) -> int:
+    def next_epoch(self, channel: int) -> int:
         self.check()
-        self.epoch[direction] += 1
-        return self.epoch[direction]
+        self.epoch[channel] += 1
+        return self.epoch[channel]
+
+    def on_side_stream(self, launch, tensors) -> "torch.cuda.Event":
+        """Runs `launch(cuda_stream)` on the side stream, ordered after everything queued so far on the current
+        stream; `tensors` are the buffers it reads (kept alive for the side stream). Returns the completion event."""
+        main = torch.cuda.current_stream(self.device)
+        ready = torch.cuda.Event()
+        ready.record(main)
+        self.side_stream.wait_event(ready)
+        for t in tensors:
+            if t is not None:
+                t.record_stream(self.side_stream)
+        with torch.cuda.stream(self.side_stream):
+            launch(self.side_stream.cuda_stream)
+        done = torch.cuda.Event()
+        done.record(self.side_stream)
+        return done
 
     def check(self) -> None:
         """Raises if an earlier wait kernel gave up on a peer (it writes 1 + rank into host-mapped memory)."""
@@ -619,6 +636,167 @@ class _PeerExchangeRows(torch.autograd.Function):
             views[0].view(C, N_local, 2), views[1].view(C, N_local), views[2].view(C, N_local, 3),
             views[3].view(C, N_local), views[4].view(C, N_local, D))
         return g_means2d, g_depths, g_conics, g_opac, g_colors, None, None, None
+
+
+class SplitExchange:
+    """The unpacked peer exchange of one `rasterization()` call, split in two so that the transfers hide under
+    compute:
+
+      forward   start_geometry()  put of means2d / depths / conics / opacities / radii on the side stream, right after
+                                  the projection: it travels while the SH colour kernel runs;
+                start_colors()    put of the colours on the side stream, right after the colour kernel: it travels
+                                  while the receiver sorts its intersections (which need the geometry only);
+                finish_geometry() wait for every peer's geometry + copy out (main stream)  -> tile intersection
+                finish_colors()   wait for every peer's colours + copy out                 -> compositor
+      backward  (autograd order: colours first) each `finish_*` sends its gradients back on the side stream and waits
+                for its own channel; the colour gradients are usually home before the geometry put has finished.
+
+    Geometry and colours use separate epoch flags (channels 0/2 forward, 1/3 backward) and disjoint fields of the same
+    mailbox region."""
+
+    GEOMETRY_FWD = 0b101111  # means2d, depths, conics, opacities, radii
+    COLORS = 0b010000
+
+    def __init__(self, C_local: int, N_world: Sequence[int], D: int):
+        from .b200_impl._lib import lib
+
+        self.box = get_mailbox()
+        self.C_local, self.N_world, self.D = int(C_local), tuple(int(n) for n in N_world), int(D)
+        world, rank = self.box.world, self.box.rank
+        self.N_local, self.N_total = self.N_world[rank], sum(self.N_world)
+        self.bases = [0]
+        for n in self.N_world:
+            self.bases.append(self.bases[-1] + n)
+        C = world * self.C_local
+        self.rows_fwd, self.rows_bwd = self.C_local * self.N_total, C * self.N_local
+        self.box.ensure(4 * max(int(lib.gsb_a2a_field_offset(self.rows_fwd, D, 6)),
+                                int(lib.gsb_a2a_field_offset(C * max(self.N_world), D, 5))))
+        self.off_fwd = [int(lib.gsb_a2a_field_offset(self.rows_fwd, D, f)) for f in range(7)]
+        self.off_bwd = [int(lib.gsb_a2a_field_offset(self.rows_bwd, D, f)) for f in range(6)]
+        self.epochs = {0: self.box.next_epoch(0), 2: self.box.next_epoch(2)}  # this call's epoch on each channel
+        self.region = self.box.region(0, self.epochs[0])
+        self.out = None
+        self.done = {}
+        self.bwd_epoch = None
+        self.bwd_out = None
+
+    # ---- forward ------------------------------------------------------------------------------------------
+    def _put_fwd(self, mask, channel, means2d, depths, conics, opacities, colors, radii):
+        from .b200_impl._lib import lib, ptr
+
+        box = self.box
+        tensors = [None if t is None else t.contiguous() for t in (means2d, depths, conics, opacities, colors, radii)]
+        epoch = self.epochs[channel]
+
+        def launch(stream):
+            lib.gsb_a2a_put_fwd_part(box.world, box.rank, self.C_local, self.N_local, self.N_total,
+                                     self.bases[box.rank], self.D, *(ptr(t) for t in tensors), mask, channel,
+                                     box.peer_array, self.region, epoch, stream)
+
+        self.done[channel] = box.on_side_stream(launch, tensors)
+
+    def start_geometry(self, means2d, depths, conics, opacities, radii):
+        assert depths.shape == (self.box.world * self.C_local, self.N_local), depths.shape
+        with torch.no_grad():
+            self._put_fwd(self.GEOMETRY_FWD, 0, means2d, depths, conics, opacities, None, radii)
+
+    def start_colors(self, colors):
+        with torch.no_grad():
+            self._put_fwd(self.COLORS, 2, None, None, None, None, colors, None)
+
+    def _wait_fwd(self, channel, ranges):
+        from .b200_impl._lib import lib, ptr, stream_of
+
+        box = self.box
+        if self.out is None:
+            self.out = torch.empty((self.off_fwd[6],), dtype=torch.float32, device=box.device)
+        torch.cuda.current_stream(box.device).wait_event(self.done[channel])  # own put first: never spin on ourselves
+        (b0, e0), (b1, e1) = ranges
+        lib.gsb_a2a_wait_copy_part(box.world, channel, self.epochs[channel], box.local, self.region, b0, e0, b1, e1,
+                                   ptr(self.out), box.timeout_flag, stream_of(self.out))
+
+    def finish_geometry(self, means2d, depths, conics, opacities, radii):
+        return _SplitFinishGeometry.apply(means2d, depths, conics, opacities, radii, self)
+
+    def finish_colors(self, colors):
+        return _SplitFinishColors.apply(colors, self)
+
+    # ---- backward -----------------------------------------------------------------------------------------
+    def _exchange_bwd(self, mask, channel, grads, ranges):
+        """grads: 5 entries (means2d, depths, conics, opacities, colours), None where not sent."""
+        import ctypes
+
+        from .b200_impl._lib import lib, ptr, stream_of
+
+        box = self.box
+        world, rank = box.world, box.rank
+        if self.bwd_epoch is None:
+            self.bwd_epoch = box.next_epoch(1)
+            self.epochs.update({1: self.bwd_epoch, 3: box.next_epoch(3)})
+            self.bwd_region = box.region(1, self.bwd_epoch)
+            self.bwd_out = torch.empty((self.off_bwd[5],), dtype=torch.float32, device=box.device)
+        grads = [None if g is None else g.float().contiguous() for g in grads]
+        bases_arr = (ctypes.c_int64 * (world + 1))(*self.bases)
+        epoch = self.epochs[channel]
+
+        def launch(stream):
+            lib.gsb_a2a_put_bwd_part(world, rank, self.C_local, self.N_total, bases_arr, self.D,
+                                     *(ptr(g) for g in grads), mask, channel, box.peer_array, self.bwd_region, epoch,
+                                     stream)
+
+        done = box.on_side_stream(launch, grads)
+        torch.cuda.current_stream(box.device).wait_event(done)
+        (b0, e0), (b1, e1) = ranges
+        lib.gsb_a2a_wait_copy_part(world, channel, epoch, box.local, self.bwd_region, b0, e0, b1, e1,
+                                   ptr(self.bwd_out), box.timeout_flag, stream_of(self.bwd_out))
+
+    def bwd_view(self, field, width):
+        C = self.box.world * self.C_local
+        v = self.bwd_out[self.off_bwd[field]:self.off_bwd[field] + self.rows_bwd * width]
+        return v.view(C, self.N_local, width) if width > 1 else v.view(C, self.N_local)
+
+
+class _SplitFinishGeometry(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means2d, depths, conics, opacities, radii, ex):
+        o = ex.off_fwd
+        ex._wait_fwd(0, ((o[0], o[4]), (o[5], o[6])))
+        C_l, N_t, out = ex.C_local, ex.N_total, ex.out
+        rows = ex.rows_fwd
+        outs = (out[o[0]:o[0] + 2 * rows].view(C_l, N_t, 2), out[o[1]:o[1] + rows].view(C_l, N_t),
+                out[o[2]:o[2] + 3 * rows].view(C_l, N_t, 3), out[o[3]:o[3] + rows].view(C_l, N_t),
+                out[o[5]:o[5] + rows].view(torch.int32).view(C_l, N_t))
+        ctx.ex = ex
+        ctx.mark_non_differentiable(outs[4])
+        return outs
+
+    @staticmethod
+    def backward(ctx, v_means2d, v_depths, v_conics, v_opac, _v_radii):
+        ex = ctx.ex
+        o = ex.off_bwd
+        # depths carry no gradient unless a depth channel is rendered: the field is then neither sent nor copied
+        # (every rank runs the same graph, so every rank skips it)
+        mask = 0b01101 | (0b00010 if v_depths is not None else 0)
+        ranges = ((o[0], o[4]), (0, 0)) if v_depths is not None else ((o[0], o[1]), (o[2], o[4]))
+        ex._exchange_bwd(mask, 1, (v_means2d, v_depths, v_conics, v_opac, None), ranges)
+        return (ex.bwd_view(0, 2), ex.bwd_view(1, 1) if v_depths is not None else None, ex.bwd_view(2, 3),
+                ex.bwd_view(3, 1), None, None)
+
+
+class _SplitFinishColors(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, colors, ex):
+        o = ex.off_fwd
+        ex._wait_fwd(2, ((o[4], o[5]), (0, 0)))
+        ctx.ex = ex
+        return ex.out[o[4]:o[4] + ex.D * ex.rows_fwd].view(ex.C_local, ex.N_total, ex.D)
+
+    @staticmethod
+    def backward(ctx, v_colors):
+        ex = ctx.ex
+        o = ex.off_bwd
+        ex._exchange_bwd(0b10000, 3, (None, None, None, None, v_colors), ((o[4], o[5]), (0, 0)))
+        return ex.bwd_view(4, ex.D), None
 
 
 def peer_exchange_rows(means2d, depths, conics, opacities, colors, radii, C_local: int, N_world: Sequence[int]):

@@ -54,6 +54,7 @@ from .distributed import (
     host_trace,
     pack_rows,
     peer_exchange_available,
+    SplitExchange,
     peer_exchange_packed,
     peer_exchange_rows,
     unpack_rows,
@@ -182,6 +183,16 @@ def rasterization(
         "opacities": opacities,
     })
 
+    # b200, unpacked, one node: the exchange is split. The projected geometry leaves for the camera owners NOW, on a
+    # side stream, while the colours are still being computed; the colours follow under the receivers' tile
+    # intersection (which needs the geometry only).
+    split = None
+    if (distributed and not packed and BACKEND == "b200" and peer_exchange_available()
+            and os.environ.get("GSPLAT_B200_EXCHANGE_SPLIT", "1") == "1"):
+        D_out = 3 if sh_degree is not None else colors.shape[-1]
+        split = SplitExchange(C_world[world_rank], N_world, D_out)
+        split.start_geometry(means2d, depths, conics, opacities, radii)
+
     # Colours -> [C, N, D] or [nnz, D]
     if sh_degree is None:
         if packed:
@@ -245,6 +256,13 @@ def rasterization(
             ids = all_to_all_rows(ids, cnts, recv)
             camera_ids, gaussian_ids = ids[:, 0].contiguous(), ids[:, 1].contiguous()
             C = C_world[world_rank]
+        elif split is not None:
+            C = C_world[world_rank]
+            split.start_colors(colors)
+            means2d, depths, conics, opacities, radii = split.finish_geometry(means2d, depths, conics, opacities, radii)
+            if render_mode != "RGB":  # the depth channel is concatenated to the colours below: they are needed now
+                colors = split.finish_colors(colors)
+                split = None
         elif BACKEND == "b200" and peer_exchange_available():
             # fused pack + NVLink peer stores straight into the camera owner's [C_local, N_total] table
             C = C_world[world_rank]
@@ -289,6 +307,8 @@ def rasterization(
     speculate = BACKEND == "b200" and os.environ.get("GSPLAT_B200_SPECULATE", "1") == "1"
     tiles_per_gauss, isect_ids, flatten_ids, isect_offsets, pending = intersect(speculate)
     host_trace.mark("us_isect")
+    if distributed and split is not None:
+        colors = split.finish_colors(colors)  # the colours arrived while the intersections were being sorted
 
     # Composite
     def composite(colors_c, backgrounds_c):

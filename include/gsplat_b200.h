@@ -346,6 +346,25 @@ int gsb_a2a_put_bwd(int world, int rank, int C_local, int64_t N_total, const int
                     int64_t epoch, cudaStream_t stream);
 int gsb_a2a_wait_copy(int world, int dir, int64_t epoch, const void *local_base, int64_t region_offset,
                       int64_t n_floats, float *out, int *timeout_flag, cudaStream_t stream);
+/* Split exchange: the same puts restricted to a subset of the fields (fields_mask: bit f = field f in the order
+ * means2d, depths, conics, opacities, colours, radii) and published on their own flag channel (0 forward geometry /
+ * all, 1 backward geometry / all, 2 forward colours, 3 backward colours), so that the colours can travel on a side
+ * stream under the receiver's intersection pipeline, which needs the geometry only. gsb_a2a_wait_copy_part waits for
+ * `channel` and copies the float ranges [begin0, end0) and [begin1, end1) of the region (multiples of 4 floats:
+ * field offsets are) into the same positions of `out`. */
+int gsb_a2a_put_fwd_part(int world, int rank, int C_local, int64_t N_local, int64_t N_total, int64_t n_base, int D,
+                         const float *means2d, const float *depths, const float *conics, const float *opacities,
+                         const float *colors, const int32_t *radii, int fields_mask, int channel,
+                         const void *const *peer_bases_host, int64_t region_offset, int64_t epoch,
+                         cudaStream_t stream);
+int gsb_a2a_put_bwd_part(int world, int rank, int C_local, int64_t N_total, const int64_t *n_bases_host, int D,
+                         const float *v_means2d, const float *v_depths, const float *v_conics,
+                         const float *v_opacities, const float *v_colors, int fields_mask, int channel,
+                         const void *const *peer_bases_host, int64_t region_offset, int64_t epoch,
+                         cudaStream_t stream);
+int gsb_a2a_wait_copy_part(int world, int channel, int64_t epoch, const void *local_base, int64_t region_offset,
+                           int64_t begin0, int64_t end0, int64_t begin1, int64_t end1, float *out,
+                           int *timeout_flag, cudaStream_t stream);
 int64_t gsb_a2a_field_offset(int64_t rows, int D, int field);
 /* Packed (COO) rows over the same mailboxes (reference rendering.py:413-451: bincount + all_to_all of counts,
  * all_to_all of the rows, a second one for the rebased ids). The sender's packed rows are camera-major, so the rows
