@@ -285,6 +285,13 @@ def run_b200(args):
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch N>1 with torch.distributed.run"
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # one process per GPU: stage the pinned host buffers of the end-to-end leg on the GPU's own NUMA node
+    numa = None
+    if os.environ.get("GSPLAT_BENCH_NUMA", "1") == "1":
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        from numa_bind import bind_to_gpu
+
+        numa = bind_to_gpu(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -497,6 +504,8 @@ def run_b200(args):
             "gpu_launches": launches, "wall_s_timed_region": round(wall_s, 3), "clocks": clk,
             "roofline": roof, "stages": stages,
         }
+        if numa is not None:
+            line["e2e"]["numa_binding_rank0"] = numa
         if parity is not None:
             line["parity"] = parity
         if host_trace.enabled:
