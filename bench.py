@@ -286,7 +286,7 @@ def run_b200(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     # one process per GPU: stage the pinned host buffers of the end-to-end leg on the GPU's own NUMA node
-    numa = None
+    numa, all_cpus = None, os.sched_getaffinity(0)
     if os.environ.get("GSPLAT_BENCH_NUMA", "1") == "1":
         sys.path.insert(0, os.path.join(ROOT, "tools"))
         from numa_bind import bind_to_gpu
@@ -511,6 +511,7 @@ def run_b200(args):
         if host_trace.enabled:
             line["host_trace_us"] = host_resident
         if world == 1 and not args.no_cpu_baseline:
+            os.sched_setaffinity(0, all_cpus)  # the CPU leg uses every host core again
             line["cpu_baseline"] = cpu_baseline(config)
         print(json.dumps(line), flush=True)
     if world > 1:
