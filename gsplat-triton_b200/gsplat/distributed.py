@@ -639,20 +639,20 @@ class _PeerExchangeRows(torch.autograd.Function):
 
 
 class SplitExchange:
-    """The unpacked peer exchange of one `rasterization()` call, split in two so that the transfers hide under
-    compute:
+    """The unpacked peer exchange of one `rasterization()` call, its forward half split in two so that the transfers
+    hide under compute:
 
-      forward   start_geometry()  put of means2d / depths / conics / opacities / radii on the side stream, right after
-                                  the projection: it travels while the SH colour kernel runs;
-                start_colors()    put of the colours on the side stream, right after the colour kernel: it travels
-                                  while the receiver sorts its intersections (which need the geometry only);
-                finish_geometry() wait for every peer's geometry + copy out (main stream)  -> tile intersection
-                finish_colors()   wait for every peer's colours + copy out                 -> compositor
-      backward  (autograd order: colours first) each `finish_*` sends its gradients back on the side stream and waits
-                for its own channel; the colour gradients are usually home before the geometry put has finished.
-
-    Geometry and colours use separate epoch flags (channels 0/2 forward, 1/3 backward) and disjoint fields of the same
-    mailbox region."""
+      start_geometry()   put of means2d / depths / conics / opacities / radii on the side stream, right after the
+                         projection: it travels while the SH colour kernel runs;
+      start_colors()     put of the colours on the side stream, right after the colour kernel: it travels while the
+                         receiver sorts its intersections (which need the geometry only);
+      finish()           waits for every peer's geometry + copies it out (main stream) and returns ALL exchanged
+                         tensors; the colour tensor's contents are valid only after
+      complete_colors()  waits for every peer's colours + copies them out; called right before the compositor (stream
+                         order makes the data visible to everything queued after it).
+    Geometry and colours use separate epoch flags (channels 0 and 2) and disjoint fields of the same mailbox region.
+    The backward exchange is one put + one wait for all gradient fields (measured at 2 GPUs: splitting it as well
+    costs more in launches and stream hand-overs than the overlap returns)."""
 
     GEOMETRY_FWD = 0b101111  # means2d, depths, conics, opacities, radii
     COLORS = 0b010000
@@ -675,12 +675,10 @@ class SplitExchange:
         self.off_bwd = [int(lib.gsb_a2a_field_offset(self.rows_bwd, D, f)) for f in range(6)]
         self.epochs = {0: self.box.next_epoch(0), 2: self.box.next_epoch(2)}  # this call's epoch on each channel
         self.region = self.box.region(0, self.epochs[0])
-        self.out = None
+        self.out = torch.empty((self.off_fwd[6],), dtype=torch.float32, device=self.box.device)
         self.done = {}
-        self.bwd_epoch = None
-        self.bwd_out = None
+        self.colors_pending = False
 
-    # ---- forward ------------------------------------------------------------------------------------------
     def _put_fwd(self, mask, channel, means2d, depths, conics, opacities, colors, radii):
         from .b200_impl._lib import lib, ptr
 
@@ -703,100 +701,75 @@ class SplitExchange:
     def start_colors(self, colors):
         with torch.no_grad():
             self._put_fwd(self.COLORS, 2, None, None, None, None, colors, None)
+        self.colors_pending = True
 
     def _wait_fwd(self, channel, ranges):
         from .b200_impl._lib import lib, ptr, stream_of
 
         box = self.box
-        if self.out is None:
-            self.out = torch.empty((self.off_fwd[6],), dtype=torch.float32, device=box.device)
         torch.cuda.current_stream(box.device).wait_event(self.done[channel])  # own put first: never spin on ourselves
         (b0, e0), (b1, e1) = ranges
         lib.gsb_a2a_wait_copy_part(box.world, channel, self.epochs[channel], box.local, self.region, b0, e0, b1, e1,
                                    ptr(self.out), box.timeout_flag, stream_of(self.out))
 
-    def finish_geometry(self, means2d, depths, conics, opacities, radii):
-        return _SplitFinishGeometry.apply(means2d, depths, conics, opacities, radii, self)
+    def finish(self, means2d, depths, conics, opacities, colors, radii):
+        """-> (means2d, depths, conics, opacities, colors, radii) of the local cameras, [C_local, N_total, .];
+        `colors` becomes valid with complete_colors()."""
+        return _SplitFinish.apply(means2d, depths, conics, opacities, colors, radii, self)
 
-    def finish_colors(self, colors):
-        return _SplitFinishColors.apply(colors, self)
+    def complete_colors(self):
+        if self.colors_pending:
+            o = self.off_fwd
+            self._wait_fwd(2, ((o[4], o[5]), (0, 0)))
+            self.colors_pending = False
 
-    # ---- backward -----------------------------------------------------------------------------------------
-    def _exchange_bwd(self, mask, channel, grads, ranges):
-        """grads: 5 entries (means2d, depths, conics, opacities, colours), None where not sent."""
+
+class _SplitFinish(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means2d, depths, conics, opacities, colors, radii, ex):
+        o = ex.off_fwd
+        ex._wait_fwd(0, ((o[0], o[4]), (o[5], o[6])))
+        C_l, N_t, out, rows, D = ex.C_local, ex.N_total, ex.out, ex.rows_fwd, ex.D
+        outs = (out[o[0]:o[0] + 2 * rows].view(C_l, N_t, 2), out[o[1]:o[1] + rows].view(C_l, N_t),
+                out[o[2]:o[2] + 3 * rows].view(C_l, N_t, 3), out[o[3]:o[3] + rows].view(C_l, N_t),
+                out[o[4]:o[4] + D * rows].view(C_l, N_t, D),
+                out[o[5]:o[5] + rows].view(torch.int32).view(C_l, N_t))
+        ctx.ex = ex
+        ctx.mark_non_differentiable(outs[5])
+        return outs
+
+    @staticmethod
+    def backward(ctx, v_means2d, v_depths, v_conics, v_opac, v_colors, _v_radii):
         import ctypes
 
         from .b200_impl._lib import lib, ptr, stream_of
 
-        box = self.box
-        world, rank = box.world, box.rank
-        if self.bwd_epoch is None:
-            self.bwd_epoch = box.next_epoch(1)
-            self.epochs.update({1: self.bwd_epoch, 3: box.next_epoch(3)})
-            self.bwd_region = box.region(1, self.bwd_epoch)
-            self.bwd_out = torch.empty((self.off_bwd[5],), dtype=torch.float32, device=box.device)
-        grads = [None if g is None else g.float().contiguous() for g in grads]
-        bases_arr = (ctypes.c_int64 * (world + 1))(*self.bases)
-        epoch = self.epochs[channel]
-
-        def launch(stream):
-            lib.gsb_a2a_put_bwd_part(world, rank, self.C_local, self.N_total, bases_arr, self.D,
-                                     *(ptr(g) for g in grads), mask, channel, box.peer_array, self.bwd_region, epoch,
-                                     stream)
-
-        done = box.on_side_stream(launch, grads)
-        torch.cuda.current_stream(box.device).wait_event(done)
-        (b0, e0), (b1, e1) = ranges
-        lib.gsb_a2a_wait_copy_part(world, channel, epoch, box.local, self.bwd_region, b0, e0, b1, e1,
-                                   ptr(self.bwd_out), box.timeout_flag, stream_of(self.bwd_out))
-
-    def bwd_view(self, field, width):
-        C = self.box.world * self.C_local
-        v = self.bwd_out[self.off_bwd[field]:self.off_bwd[field] + self.rows_bwd * width]
-        return v.view(C, self.N_local, width) if width > 1 else v.view(C, self.N_local)
-
-
-class _SplitFinishGeometry(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, means2d, depths, conics, opacities, radii, ex):
-        o = ex.off_fwd
-        ex._wait_fwd(0, ((o[0], o[4]), (o[5], o[6])))
-        C_l, N_t, out = ex.C_local, ex.N_total, ex.out
-        rows = ex.rows_fwd
-        outs = (out[o[0]:o[0] + 2 * rows].view(C_l, N_t, 2), out[o[1]:o[1] + rows].view(C_l, N_t),
-                out[o[2]:o[2] + 3 * rows].view(C_l, N_t, 3), out[o[3]:o[3] + rows].view(C_l, N_t),
-                out[o[5]:o[5] + rows].view(torch.int32).view(C_l, N_t))
-        ctx.ex = ex
-        ctx.mark_non_differentiable(outs[4])
-        return outs
-
-    @staticmethod
-    def backward(ctx, v_means2d, v_depths, v_conics, v_opac, _v_radii):
         ex = ctx.ex
+        box = ex.box
+        world, rank = box.world, box.rank
         o = ex.off_bwd
+        epoch = box.next_epoch(1)
+        region = box.region(1, epoch)
+        out = torch.empty((o[5],), dtype=torch.float32, device=box.device)
         # depths carry no gradient unless a depth channel is rendered: the field is then neither sent nor copied
         # (every rank runs the same graph, so every rank skips it)
-        mask = 0b01101 | (0b00010 if v_depths is not None else 0)
-        ranges = ((o[0], o[4]), (0, 0)) if v_depths is not None else ((o[0], o[1]), (o[2], o[4]))
-        ex._exchange_bwd(mask, 1, (v_means2d, v_depths, v_conics, v_opac, None), ranges)
-        return (ex.bwd_view(0, 2), ex.bwd_view(1, 1) if v_depths is not None else None, ex.bwd_view(2, 3),
-                ex.bwd_view(3, 1), None, None)
+        has_depth = v_depths is not None
+        mask = 0b11101 | (0b00010 if has_depth else 0)
+        ranges = ((o[0], o[5]), (0, 0)) if has_depth else ((o[0], o[1]), (o[2], o[5]))
+        grads = [None if g is None else g.float().contiguous() for g in (v_means2d, v_depths, v_conics, v_opac, v_colors)]
+        bases_arr = (ctypes.c_int64 * (world + 1))(*ex.bases)
+        st = stream_of(out)
+        lib.gsb_a2a_put_bwd_part(world, rank, ex.C_local, ex.N_total, bases_arr, ex.D, *(ptr(g) for g in grads), mask, 1,
+                                 box.peer_array, region, epoch, st)
+        (b0, e0), (b1, e1) = ranges
+        lib.gsb_a2a_wait_copy_part(world, 1, epoch, box.local, region, b0, e0, b1, e1, ptr(out), box.timeout_flag, st)
+        C, N_l, rows, D = world * ex.C_local, ex.N_local, ex.rows_bwd, ex.D
 
+        def view(f, w):
+            v = out[o[f]:o[f] + rows * w]
+            return v.view(C, N_l, w) if w > 1 else v.view(C, N_l)
 
-class _SplitFinishColors(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, colors, ex):
-        o = ex.off_fwd
-        ex._wait_fwd(2, ((o[4], o[5]), (0, 0)))
-        ctx.ex = ex
-        return ex.out[o[4]:o[4] + ex.D * ex.rows_fwd].view(ex.C_local, ex.N_total, ex.D)
-
-    @staticmethod
-    def backward(ctx, v_colors):
-        ex = ctx.ex
-        o = ex.off_bwd
-        ex._exchange_bwd(0b10000, 3, (None, None, None, None, v_colors), ((o[4], o[5]), (0, 0)))
-        return ex.bwd_view(4, ex.D), None
+        return view(0, 2), (view(1, 1) if has_depth else None), view(2, 3), view(3, 1), view(4, D), None, None
 
 
 def peer_exchange_rows(means2d, depths, conics, opacities, colors, radii, C_local: int, N_world: Sequence[int]):

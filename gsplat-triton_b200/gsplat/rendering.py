@@ -259,10 +259,10 @@ def rasterization(
         elif split is not None:
             C = C_world[world_rank]
             split.start_colors(colors)
-            means2d, depths, conics, opacities, radii = split.finish_geometry(means2d, depths, conics, opacities, radii)
+            means2d, depths, conics, opacities, colors, radii = split.finish(means2d, depths, conics, opacities,
+                                                                             colors, radii)
             if render_mode != "RGB":  # the depth channel is concatenated to the colours below: they are needed now
-                colors = split.finish_colors(colors)
-                split = None
+                split.complete_colors()
         elif BACKEND == "b200" and peer_exchange_available():
             # fused pack + NVLink peer stores straight into the camera owner's [C_local, N_total] table
             C = C_world[world_rank]
@@ -307,8 +307,8 @@ def rasterization(
     speculate = BACKEND == "b200" and os.environ.get("GSPLAT_B200_SPECULATE", "1") == "1"
     tiles_per_gauss, isect_ids, flatten_ids, isect_offsets, pending = intersect(speculate)
     host_trace.mark("us_isect")
-    if distributed and split is not None:
-        colors = split.finish_colors(colors)  # the colours arrived while the intersections were being sorted
+    if split is not None:
+        split.complete_colors()  # the colours arrived while the intersections were being sorted
 
     # Composite
     def composite(colors_c, backgrounds_c):
