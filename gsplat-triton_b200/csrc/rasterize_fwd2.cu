@@ -51,6 +51,31 @@ __device__ __forceinline__ float4 lds128(unsigned addr) {
     return v;
 }
 
+// The four decisions of one (pixel, Gaussian) pair in predicate form (FSETP with a predicate operand, predicated
+// moves) — written out because the compiler's version of the same logic spends twice the instructions on PLOP3 / SEL:
+//   hit  = !(ex > 0) && !(minus_alpha > -1/255)        go = hit && !(next_T <= 1e-4)
+//   w    = go ? minus_w : 0 ;  if (go) { cur = index; T = next_T; }  else if (hit) T = -|T| (sign bit: stopped)
+__device__ __forceinline__ float blend_decide(float ex, float minus_alpha, float next_T, float minus_w, int index,
+                                              int &cur, float &T) {
+    float w;
+    unsigned t = __float_as_uint(T);
+    asm("{\n\t"
+        ".reg .pred h, g, s;\n\t"
+        "setp.leu.ftz.f32 h, %3, 0f00000000;\n\t"
+        "setp.leu.and.ftz.f32 h, %4, 0fBB808081, h;\n\t"
+        "setp.gtu.and.ftz.f32 g, %5, 0f38D1B717, h;\n\t"
+        "and.pred s, h, !g;\n\t"
+        "selp.f32 %0, %6, 0f00000000, g;\n\t"
+        "@g mov.b32 %1, %7;\n\t"
+        "@s or.b32 %2, %2, 0x80000000;\n\t"
+        "@g mov.b32 %2, %8;\n\t"
+        "}"
+        : "=f"(w), "+r"(cur), "+r"(t)
+        : "f"(ex), "f"(minus_alpha), "f"(next_T), "f"(minus_w), "r"(index), "r"(__float_as_uint(next_T)));
+    T = __uint_as_float(t);
+    return w;
+}
+
 constexpr int kThreads2 = 128;  // 4 warps x 2 blocks
 constexpr int kWarps2 = kThreads2 / 32;
 
@@ -100,9 +125,11 @@ rasterize_fwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
     const int py0 = tile_y * kTile + by * 4 + (l16 >> 3) * 2, py1 = py0 + 1;
     const bool in0 = (px < W) & (py0 < H), in1 = (px < W) & (py1 < H);
 
-    f32x2 pix[D];
+    // MINUS the colour sums of the two pixels. Carried as scalars and packed at the use: ptxas then keeps the FFMA2
+    // accumulation in place (loop-carried 64-bit pairs cost it two register moves per channel and iteration)
+    float pa[D], pb[D];
 #pragma unroll
-    for (int k = 0; k < D; ++k) pix[k] = pack2(0.f, 0.f);  // holds MINUS the colour sums
+    for (int k = 0; k < D; ++k) pa[k] = pb[k] = 0.f;
     // |T| is the transmittance; T < 0 marks a finished pixel (saturated, or outside the image)
     float T0 = in0 ? 1.0f : -1.0f, T1 = in1 ? 1.0f : -1.0f;
     int cur0 = 0, cur1 = 0;
@@ -185,30 +212,16 @@ rasterize_fwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
                     const f32x2 na = pack2(na0, na1), T2 = pack2(T0, T1);
                     float nT0, nT1;  // T (1 - alpha); < 0 on finished pixels
                     unpack2(fma2(T2, na, T2), nT0, nT1);
-                    const bool hit0 = !(ex0 > 0.f) & !(na0 > -kAlphaMin);
-                    const bool hit1 = !(ex1 > 0.f) & !(na1 > -kAlphaMin);
-                    const bool go0 = hit0 & !(nT0 <= kTmin), go1 = hit1 & !(nT1 <= kTmin);
                     float w0, w1;  // MINUS alpha T
                     unpack2(mul2(na, T2), w0, w1);
-                    const f32x2 wn = pack2(go0 ? w0 : 0.f, go1 ? w1 : 0.f);
-#ifdef GSB_FWD2_ACC_ASM
-                    fma2_acc(pix[0], bcast2(c4.x), wn);
-                    if (D > 1) fma2_acc(pix[1], bcast2(c4.y), wn);
-                    if (D > 2) fma2_acc(pix[2], bcast2(c4.z), wn);
-                    if (D > 3) fma2_acc(pix[3], bcast2(c4.w), wn);
-#else
-                    pix[0] = fma2(bcast2(c4.x), wn, pix[0]);
-                    if (D > 1) pix[1] = fma2(bcast2(c4.y), wn, pix[1]);
-                    if (D > 2) pix[2] = fma2(bcast2(c4.z), wn, pix[2]);
-                    if (D > 3) pix[3] = fma2(bcast2(c4.w), wn, pix[3]);
-#endif
                     const int sidx = __float_as_int(p4.z);
-                    cur0 = go0 ? sidx : cur0;
-                    cur1 = go1 ? sidx : cur1;
-                    // a hit that is not composited stops the pixel *before* this splat: set the sign bit (a no-op
-                    // on finished pixels, whose T (1 - alpha) < 0 always lands here)
-                    T0 = go0 ? nT0 : __uint_as_float(__float_as_uint(T0) | (hit0 ? 0x80000000u : 0u));
-                    T1 = go1 ? nT1 : __uint_as_float(__float_as_uint(T1) | (hit1 ? 0x80000000u : 0u));
+                    w0 = blend_decide(ex0, na0, nT0, w0, sidx, cur0, T0);
+                    w1 = blend_decide(ex1, na1, nT1, w1, sidx, cur1, T1);
+                    const f32x2 wn = pack2(w0, w1);
+                    unpack2(fma2(bcast2(c4.x), wn, pack2(pa[0], pb[0])), pa[0], pb[0]);
+                    if (D > 1) unpack2(fma2(bcast2(c4.y), wn, pack2(pa[1], pb[1])), pa[1], pb[1]);
+                    if (D > 2) unpack2(fma2(bcast2(c4.z), wn, pack2(pa[2], pb[2])), pa[2], pb[2]);
+                    if (D > 3) unpack2(fma2(bcast2(c4.w), wn, pack2(pa[3], pb[3])), pa[3], pb[3]);
                 }
                 if (__all_sync(0xffffffffu, (T0 < 0.f) & (T1 < 0.f))) {
                     warp_done = true;
@@ -225,7 +238,7 @@ rasterize_fwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
     float c0v[D], c1v[D];
 #pragma unroll
     for (int k = 0; k < D; ++k) {
-        unpack2(pix[k], c0v[k], c1v[k]);
+        c0v[k] = pa[k]; c1v[k] = pb[k];
         c0v[k] = -c0v[k];
         c1v[k] = -c1v[k];
     }
