@@ -60,15 +60,14 @@ __device__ __forceinline__ float blend_decide(float ex, float minus_alpha, float
     float w;
     unsigned t = __float_as_uint(T);
     asm("{\n\t"
-        ".reg .pred h, g, s;\n\t"
+        ".reg .pred h, g;\n\t"
         "setp.leu.ftz.f32 h, %3, 0f00000000;\n\t"
         "setp.leu.and.ftz.f32 h, %4, 0fBB808081, h;\n\t"
         "setp.gtu.and.ftz.f32 g, %5, 0f38D1B717, h;\n\t"
-        "and.pred s, h, !g;\n\t"
         "selp.f32 %0, %6, 0f00000000, g;\n\t"
         "@g mov.b32 %1, %7;\n\t"
-        "@s or.b32 %2, %2, 0x80000000;\n\t"
-        "@g mov.b32 %2, %8;\n\t"
+        "@h or.b32 %2, %2, 0x80000000;\n\t"  // every hit marks the pixel stopped ...
+        "@g mov.b32 %2, %8;\n\t"              // ... and a composited one gets its new transmittance back
         "}"
         : "=f"(w), "+r"(cur), "+r"(t)
         : "f"(ex), "f"(minus_alpha), "f"(next_T), "f"(minus_w), "r"(index), "r"(__float_as_uint(next_T)));
@@ -109,7 +108,8 @@ rasterize_fwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
         st.B[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         st.Cq[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    const unsigned sP = (unsigned)__cvta_generic_to_shared(st.P);
+    unsigned sP = (unsigned)__cvta_generic_to_shared(st.P);
+    asm volatile("mov.u32 %0, %0;" : "+r"(sP));  // opaque: kept in a register instead of being recomputed per iteration
     constexpr unsigned kOffB = sizeof(float4) * (kThreads2 + 32), kOffC = 2 * kOffB;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, half = lane >> 4, l16 = lane & 15;
@@ -141,6 +141,8 @@ rasterize_fwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
         const f32x2 npy = pack2(-((float)py0 + 0.5f), -((float)py1 + 0.5f));
         bool warp_done = __all_sync(0xffffffffu, (T0 < 0.f) & (T1 < 0.f));
         const int bit0 = (4 * (warp >> 1)) + bx, bit1 = bit0 + 2;  // by * 2 + bx for half 0 / half 1
+        unsigned half_mask = half ? 0xffffffffu : 0u;
+        asm volatile("mov.u32 %0, %0;" : "+r"(half_mask));  // opaque, so the list select stays one LOP3
 
         for (int base = range_start; base < range_end; base += kThreads2) {
             if (__syncthreads_count((T0 < 0.f) & (T1 < 0.f)) == kThreads2) break;
@@ -188,7 +190,7 @@ rasterize_fwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
                 unsigned todo0 = __ballot_sync(0xffffffffu, (m >> bit0) & 1u);
                 unsigned todo1 = __ballot_sync(0xffffffffu, (m >> bit1) & 1u);
                 while (todo0 | todo1) {
-                    const unsigned todo = half ? todo1 : todo0;
+                    const unsigned todo = todo0 ^ ((todo0 ^ todo1) & half_mask);  // this half's list (one LOP3)
                     const unsigned addr = sP + 16u * (unsigned)(c0 + __ffs(todo));  // entry c0 + ffs (pad-shifted)
                     todo0 &= todo0 - 1u;
                     todo1 &= todo1 - 1u;
