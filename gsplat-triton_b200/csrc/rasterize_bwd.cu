@@ -27,10 +27,6 @@
 
 namespace raster {
 
-struct GradTargets {
-    float *v_means2d, *v_conics, *v_opacities, *v_colors, *v_abs;
-};
-
 #ifndef GSB_BWD_MIN_BLOCKS
 #define GSB_BWD_MIN_BLOCKS 4  // resident CTAs per SM the D <= 4 instantiations are register-limited to
 #endif
@@ -337,6 +333,15 @@ int dispatch_abs(bool abs, int C, int64_t n_isects, const float *recA, const flo
 
 }  // namespace raster
 
+// rasterize_bwd2.cu
+int gsb_rasterize_bwd2_dispatch(int C, int64_t n_isects, int D, const float *recA, const float *recB,
+                                const float *colors, const float *backgrounds, const uint8_t *masks, int width,
+                                int height, int tile_width, int tile_height, const int32_t *isect_offsets,
+                                const int32_t *flatten_ids, const float *render_alphas, const int32_t *last_ids,
+                                const uint8_t *block_masks, const float *v_render_colors,
+                                const float *v_render_alphas, float *v_means2d_abs, float *v_means2d, float *v_conics,
+                                float *v_colors, float *v_opacities, cudaStream_t stream);
+
 extern "C" int gsb_rasterize_bwd(int C, int64_t n_isects, int D, const float *recA, const float *recB,
                                  const float *colors, const float *backgrounds, const uint8_t *masks, int width,
                                  int height, int tile_size, int tile_width, int tile_height,
@@ -352,6 +357,11 @@ extern "C" int gsb_rasterize_bwd(int C, int64_t n_isects, int D, const float *re
     }
     GSB_REQUIRE(tile_height <= 65535 && C <= 65535, "grid too large");
     if (C == 0 || n_isects == 0) return GSB_OK;
+    if (D <= 4 && gsb_option(GSB_OPT_BWD_VARIANT) == 2)
+        return gsb_rasterize_bwd2_dispatch(C, n_isects, D, recA, recB, colors, backgrounds, masks, width, height,
+                                           tile_width, tile_height, isect_offsets, flatten_ids, render_alphas,
+                                           last_ids, block_masks, v_render_colors, v_render_alphas, v_means2d_abs,
+                                           v_means2d, v_conics, v_colors, v_opacities, stream);
     raster::GradTargets out = {v_means2d, v_conics, v_opacities, v_colors, v_means2d_abs};
     const bool abs = v_means2d_abs != nullptr;
 #define GSB_BWD_CASE(DD)                                                                                          \

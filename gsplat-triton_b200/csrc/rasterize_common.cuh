@@ -147,6 +147,48 @@ __device__ __forceinline__ unsigned splat_block_mask(const float4 &A, const floa
     return keep;
 }
 
+// ---- Blackwell packed FP32 (PTX *.f32x2 -> SASS FFMA2 / FMUL2 / FADD2): one issued instruction, two lanes of work. A
+// scalar enters as a broadcast operand at no cost (ptxas folds `mov.b64 {a, a}` into the operand modifier R.F32).
+typedef unsigned long long f32x2;
+
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 bcast2(float a) { return pack2(a, a); }
+// acc += a * b (accumulate form: no register moves around the asm)
+__device__ __forceinline__ void fma2_acc(f32x2 &acc, f32x2 a, f32x2 b) {
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
+}
+__device__ __forceinline__ float4 lds128(unsigned addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+
+struct GradTargets {
+    float *v_means2d, *v_conics, *v_opacities, *v_colors, *v_abs;
+};
+
 struct TileGeom {
     int cam, tile_x, tile_y;
     int64_t tile_id;      // flat (camera, tile) index

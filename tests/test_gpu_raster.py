@@ -323,6 +323,43 @@ def test_raster_other_tile_sizes_against_oracle(ts, D, bg, absgrad):
         assert p[0].absgrad.shape == p[0].shape and bool(torch.isfinite(p[0].absgrad).all())
 
 
+@pytest.mark.parametrize("D,bg,absgrad", [(1, False, True), (3, True, False), (3, False, True), (4, True, True)])
+def test_backward_kernel_variants_agree_and_match_oracle(D, bg, absgrad):
+    """rasterize_bwd2.cu (half-warp per block, two pixels per lane, packed FFMA2) against rasterize_bwd.cu (same
+    per-pair values, different summation order) and, on its own, against the C oracle with the classified
+    comparison; partial tiles, masks, absgrad."""
+    from gsplat.b200_impl import rasterize_to_pixels
+    from gsplat.b200_impl._lib import lib
+    from parity import check_compositor_stage
+
+    C, N, W, H, ts = 2, 4000, 200, 117, 16
+    means2d, conics, colors, opac, radii, depths = _random_splats(C, N, W, H, D, seed=31 + D)
+    tw, th = -(-W // ts), -(-H // ts)
+    _, ids, flat = O.isect_tiles(means2d, radii, depths, ts, tw, th)
+    offs = O.isect_offset_encode(ids, C, tw, th)
+    masks = torch.ones(C, th, tw, dtype=torch.bool)
+    masks[0, 1, 2] = False
+    backgrounds = torch.rand(C, D) if bg else None
+    g = torch.Generator().manual_seed(6)
+    w_c, w_a = torch.randn(C, H, W, D, generator=g).to(DEV), torch.randn(C, H, W, 1, generator=g).to(DEV)
+    outs = {}
+    try:
+        for variant in (1, 2):
+            assert lib.gsb_set_option(1, variant) == 0
+            p = [t.clone().to(DEV).requires_grad_(True) for t in (means2d, conics, colors, opac)]
+            b = backgrounds.clone().to(DEV).requires_grad_(True) if bg else None
+            rc, ra = rasterize_to_pixels(p[0], p[1], p[2], p[3], W, H, ts, offs.to(DEV), flat.to(DEV), backgrounds=b,
+                                         masks=masks.to(DEV), absgrad=absgrad)
+            grads = torch.autograd.grad((rc * w_c).sum() + (ra * w_a).sum(), p + ([b] if bg else []))
+            outs[variant] = list(grads) + ([p[0].absgrad] if absgrad else [])
+        for a, b_ in zip(outs[1], outs[2]):
+            torch.testing.assert_close(a, b_, rtol=1e-4, atol=2e-5 * float(b_.abs().max()))
+        check_compositor_stage(rasterize_to_pixels, means2d, conics, colors, opac, W, H, ts, offs, flat,
+                               backgrounds=backgrounds, masks=masks, what=f"bwd v2 D={D}", gpu_kw={"absgrad": absgrad})
+    finally:
+        lib.gsb_set_option(1, 1)
+
+
 def test_raster_masks_empty_and_last_tile():
     from gsplat.b200_impl import rasterize_to_pixels
 
