@@ -27,12 +27,13 @@ constexpr int kB2Chunk = 16;
 #define GSB_BWD2_MIN_BLOCKS 5
 #endif
 
-struct __align__(16) Bwd2Smem {
+struct __align__(256) Bwd2Smem {
+    float4 Wt[kB2Halves][kB2Chunk][16];        // phase-1 table (swizzled columns); rows are 256-byte aligned, so
+                                               // the swizzle is an XOR on address bits 4-6
+    float4 V[kB2Halves][16][2];                // colour cotangents of the half's pixels: (v0[0],v1[0],v0[1],v1[1]), (v0[2],v1[2],v0[3],v1[3])
     float4 P[kB2Threads + 1];                  // entry 0 = zero pad; x, y, sorted index, block mask
     float4 B[kB2Threads + 1];                  // staged conic (A', B', C'), MINUS opacity
     float4 Cq[kB2Threads + 1];                 // colour
-    float4 Wt[kB2Halves][kB2Chunk][16];        // phase-1 table (swizzled columns)
-    float4 V[kB2Halves][16][2];                // colour cotangents of the half's pixels: (v0[0],v1[0],v0[1],v1[1]), (v0[2],v1[2],v0[3],v1[3])
     int wcnt[kB2Warps];
     int red[kB2Halves];
 };
@@ -331,7 +332,7 @@ rasterize_bwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
                 float s0, s1, w0, w1;
                 unpack2(vs, s0, s1);
                 unpack2(nw2, w0, w1);
-                const unsigned waddr = sW + ((unsigned)n_chunk << 8) ^ (((unsigned)n_chunk & 7u) << 4);
+                const unsigned waddr = (sW + ((unsigned)n_chunk << 8)) ^ (((unsigned)n_chunk & 7u) << 4);
                 asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(waddr), "f"(s0), "f"(s1), "f"(w0), "f"(w1)
                              : "memory");
                 if (hits & half_lanes) {  // some pixel of this half's block was hit: the row is kept
