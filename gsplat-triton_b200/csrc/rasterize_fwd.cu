@@ -227,7 +227,7 @@ extern "C" int gsb_rasterize_fwd_cap(int C, int64_t n_isects, const int64_t *n_i
     GSB_REQUIRE(tile_width * tile_size >= width && tile_height * tile_size >= height, "tile grid smaller than image");
     GSB_REQUIRE(tile_height <= 65535 && C <= 65535, "grid too large");
     if (C == 0) return GSB_OK;
-    if (D <= 4 && gsb_option(GSB_OPT_FWD_VARIANT) == 2)
+    if (D <= 4 && gsb_option(GSB_OPT_FWD_VARIANT) >= 2)
         return gsb_rasterize_fwd2_dispatch(C, n_isects, n_isects_dev, D, recA, recB, colors, backgrounds, masks, width,
                                            height, tile_width, tile_height, isect_offsets, flatten_ids,
                                            render_colors, render_alphas, last_ids, block_masks, stream);

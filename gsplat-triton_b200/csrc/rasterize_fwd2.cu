@@ -224,6 +224,233 @@ rasterize_fwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// v3 = v2 + a producer warp. ncu on v2 (cfg2): the 50-instruction compositing loop draws only 44 % of the stall
+// samples; 55 % sit in the per-batch staging code (two dependent global gathers, ~200 instructions of exact culling
+// per splat, two CTA barriers) that every warp executed in lock step BEFORE it could composite. Here a fifth warp
+// stages batch k+1 (gathers in flight four deep, culling, warp-local ballot compaction: no CTA barrier at all) into
+// the second half of a double buffer while the four consumer warps composite batch k; the hand-over is two pairs of
+// named barriers (bar.sync / bar.arrive, "full" and "empty" per buffer).
+constexpr int kThreads3 = kThreads2 + 32;
+constexpr int kBarFull = 1, kBarEmpty = 3;  // + buffer index; barrier 0 is __syncthreads
+
+__device__ __forceinline__ void named_bar_sync(int id) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(kThreads3) : "memory");
+}
+__device__ __forceinline__ void named_bar_arrive(int id) {
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(kThreads3) : "memory");
+}
+
+struct __align__(16) Stage3 {
+    float4 P[kThreads2 + 1];   // entry 0 = zero pad; x, y, sorted index, block mask
+    float4 B[kThreads2 + 1];   // staged conic (A', B', C'), MINUS opacity
+    float4 Cq[kThreads2 + 1];  // colour
+};
+
+#ifndef GSB_FWD3_MIN_BLOCKS
+#define GSB_FWD3_MIN_BLOCKS 6
+#endif
+
+template <int D>
+__global__ void __launch_bounds__(kThreads3, GSB_FWD3_MIN_BLOCKS)
+rasterize_fwd3_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, const float4 *__restrict__ recB,
+                      const float *__restrict__ colors, const float *__restrict__ backgrounds,
+                      const uint8_t *__restrict__ masks, int W, int H, int tw, int th,
+                      const int32_t *__restrict__ offsets, const int32_t *__restrict__ flatten_ids,
+                      float *__restrict__ out_colors, float *__restrict__ out_alphas,
+                      int32_t *__restrict__ last_ids, const int64_t *__restrict__ n_isects_dev,
+                      uint8_t *__restrict__ block_masks) {
+    static_assert(D >= 1 && D <= 4, "one float4 of colour per staged splat");
+    if (n_isects_dev != nullptr) n_isects = min(n_isects, (int64_t)*n_isects_dev);
+    __shared__ Stage3 st[2];
+    __shared__ int s_total[2];
+    __shared__ int s_done_warps;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int cam = blockIdx.z, tile_y = blockIdx.y, tile_x = blockIdx.x;
+    const int64_t tile_id = ((int64_t)cam * th + tile_y) * tw + tile_x;
+    const int range_start = offsets[tile_id];
+    const int range_end = (tile_id + 1 < (int64_t)C * th * tw) ? offsets[tile_id + 1] : (int)n_isects;
+    const bool render = (masks == nullptr) || masks[tile_id];
+    if (tid < 2) {
+        st[tid].P[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+        st[tid].B[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+        st[tid].Cq[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    if (tid == 0) s_done_warps = 0;
+    __syncthreads();
+
+    if (warp == kWarps2) {
+        // ---------------- producer warp ----------------
+        if (!render) return;
+        int k = 0;
+        for (int base = range_start;; base += kThreads2, ++k) {
+            const int b = k & 1;
+            if (k >= 2) named_bar_sync(kBarEmpty + b);  // the consumers are done with this buffer
+            const bool stop = *reinterpret_cast<volatile int *>(&s_done_warps) == kWarps2;  // every pixel finished
+            if (base >= range_end || stop) {
+                if (lane == 0) s_total[b] = -1;  // end marker
+                __threadfence_block();
+                named_bar_arrive(kBarFull + b);
+                return;
+            }
+            // four rounds of 32 intersections; all ids, then all record gathers, are in flight together
+            int g[4];
+            float4 A[4], Bq[4];
+            float col[4][D];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int idx = base + 32 * r + lane;
+                g[r] = idx < range_end ? flatten_ids[idx] : -1;
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                if (g[r] >= 0) {
+                    A[r] = __ldg(recA + g[r]);
+                    Bq[r] = __ldg(recB + g[r]);
+#pragma unroll
+                    for (int c = 0; c < D; ++c) col[r][c] = __ldg(colors + (size_t)g[r] * D + c);
+                }
+            }
+            int cnt = 0;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int idx = base + 32 * r + lane;
+                unsigned mask = 0u;
+                if (g[r] >= 0) {
+                    mask = splat_block_mask(A[r], Bq[r], tile_x * kTile, tile_y * kTile);
+                    if (block_masks != nullptr) block_masks[idx] = (uint8_t)mask;
+                }
+                const unsigned ballot = __ballot_sync(0xffffffffu, mask != 0u);
+                if (mask != 0u) {
+                    const int slot = 1 + cnt + __popc(ballot & ((1u << lane) - 1u));  // entry 0 is the pad
+                    st[b].P[slot] = make_float4(A[r].x, A[r].y, __int_as_float(idx), __uint_as_float(mask));
+                    float4 sb = stage_conic(Bq[r]);
+                    sb.w = -sb.w;
+                    st[b].B[slot] = sb;
+                    float4 c4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    c4.x = col[r][0];
+                    if (D > 1) c4.y = col[r][1];
+                    if (D > 2) c4.z = col[r][2];
+                    if (D > 3) c4.w = col[r][3];
+                    st[b].Cq[slot] = c4;
+                }
+                cnt += __popc(ballot);
+            }
+            if (lane == 0) s_total[b] = cnt;
+            __threadfence_block();
+            named_bar_arrive(kBarFull + b);
+        }
+    }
+
+    // ---------------- consumer warps (the v2 compositor) ----------------
+    const int half = lane >> 4, l16 = lane & 15;
+    const int bx = warp & 1, by = 2 * (warp >> 1) + half;
+    const int px = tile_x * kTile + bx * 8 + (l16 & 7);
+    const int py0 = tile_y * kTile + by * 4 + (l16 >> 3) * 2, py1 = py0 + 1;
+    const bool in0 = (px < W) & (py0 < H), in1 = (px < W) & (py1 < H);
+    float pa[D], pb[D];
+#pragma unroll
+    for (int k = 0; k < D; ++k) pa[k] = pb[k] = 0.f;
+    float T0 = in0 ? 1.0f : -1.0f, T1 = in1 ? 1.0f : -1.0f;
+    int cur0 = 0, cur1 = 0;
+    if (render) {
+        const float pxf = (float)px + 0.5f;
+        const f32x2 npy = pack2(-((float)py0 + 0.5f), -((float)py1 + 0.5f));
+        bool warp_done = __all_sync(0xffffffffu, (T0 < 0.f) & (T1 < 0.f));
+        if (warp_done && lane == 0) atomicAdd(&s_done_warps, 1);
+        const int bit0 = (4 * (warp >> 1)) + bx, bit1 = bit0 + 2;
+        unsigned half_mask = half ? 0xffffffffu : 0u;
+        asm volatile("mov.u32 %0, %0;" : "+r"(half_mask));
+        unsigned sP0 = (unsigned)__cvta_generic_to_shared(st[0].P);
+        asm volatile("mov.u32 %0, %0;" : "+r"(sP0));
+        constexpr unsigned kOffB = sizeof(float4) * (kThreads2 + 1), kOffC = 2 * kOffB;
+        for (int k = 0;; ++k) {
+            const int b = k & 1;
+            named_bar_sync(kBarFull + b);
+            const int total = *reinterpret_cast<volatile int *>(&s_total[b]);
+            if (total < 0) break;
+            if (!warp_done) {
+                const unsigned sP = sP0 + (unsigned)b * (unsigned)sizeof(Stage3);
+                for (int c0 = 0; c0 < total; c0 += 32) {
+                    const int jl = c0 + lane;
+                    const unsigned m = jl < total ? __float_as_uint(st[b].P[jl + 1].w) : 0u;
+                    unsigned todo0 = __ballot_sync(0xffffffffu, (m >> bit0) & 1u);
+                    unsigned todo1 = __ballot_sync(0xffffffffu, (m >> bit1) & 1u);
+                    while (todo0 | todo1) {
+                        const unsigned todo = todo0 ^ ((todo0 ^ todo1) & half_mask);
+                        const unsigned addr = sP + 16u * (unsigned)(c0 + __ffs(todo));
+                        todo0 &= todo0 - 1u;
+                        todo1 &= todo1 - 1u;
+                        const float4 p4 = lds128(addr);
+                        const float4 b4 = lds128(addr + kOffB);
+                        const float4 c4 = lds128(addr + kOffC);
+                        const float dx = p4.x - pxf;
+                        const f32x2 dy = add2(bcast2(p4.y), npy);
+                        const f32x2 t = fma2(bcast2(b4.y), dy, bcast2(b4.x * dx));
+                        const f32x2 ex = fma2(mul2(bcast2(b4.z), dy), dy, mul2(bcast2(dx), t));
+                        float ex0, ex1;
+                        unpack2(ex, ex0, ex1);
+                        const float nopac = todo != 0u ? b4.w : 0.f;
+                        float na0, na1;
+                        unpack2(mul2(bcast2(nopac), pack2(exp2f(ex0), exp2f(ex1))), na0, na1);
+                        na0 = fmaxf(-kAlphaMax, na0);
+                        na1 = fmaxf(-kAlphaMax, na1);
+                        const f32x2 na = pack2(na0, na1), T2 = pack2(T0, T1);
+                        float nT0, nT1;
+                        unpack2(fma2(T2, na, T2), nT0, nT1);
+                        float w0, w1;
+                        unpack2(mul2(na, T2), w0, w1);
+                        const int sidx = __float_as_int(p4.z);
+                        w0 = blend_decide(ex0, na0, nT0, w0, sidx, cur0, T0);
+                        w1 = blend_decide(ex1, na1, nT1, w1, sidx, cur1, T1);
+                        const f32x2 wn = pack2(w0, w1);
+                        unpack2(fma2(bcast2(c4.x), wn, pack2(pa[0], pb[0])), pa[0], pb[0]);
+                        if (D > 1) unpack2(fma2(bcast2(c4.y), wn, pack2(pa[1], pb[1])), pa[1], pb[1]);
+                        if (D > 2) unpack2(fma2(bcast2(c4.z), wn, pack2(pa[2], pb[2])), pa[2], pb[2]);
+                        if (D > 3) unpack2(fma2(bcast2(c4.w), wn, pack2(pa[3], pb[3])), pa[3], pb[3]);
+                    }
+                    if (__all_sync(0xffffffffu, (T0 < 0.f) & (T1 < 0.f))) {
+                        warp_done = true;
+                        if (lane == 0) atomicAdd(&s_done_warps, 1);  // the producer stops once all four are
+                        break;
+                    }
+                }
+            }
+            named_bar_arrive(kBarEmpty + b);
+        }
+    }
+    T0 = fabsf(T0);
+    T1 = fabsf(T1);
+    const float *bg = backgrounds != nullptr ? backgrounds + (size_t)cam * D : nullptr;
+    if (in0) {
+        const int64_t p = ((int64_t)cam * H + py0) * W + px;
+#pragma unroll
+        for (int k = 0; k < D; ++k) out_colors[p * D + k] = bg != nullptr ? fmaf(T0, bg[k], -pa[k]) : -pa[k];
+        out_alphas[p] = 1.0f - T0;
+        last_ids[p] = cur0;
+    }
+    if (in1) {
+        const int64_t p = ((int64_t)cam * H + py1) * W + px;
+#pragma unroll
+        for (int k = 0; k < D; ++k) out_colors[p * D + k] = bg != nullptr ? fmaf(T1, bg[k], -pb[k]) : -pb[k];
+        out_alphas[p] = 1.0f - T1;
+        last_ids[p] = cur1;
+    }
+}
+
+template <int D>
+int launch_fwd3(int C, int64_t n_isects, const float *recA, const float *recB, const float *colors,
+                const float *backgrounds, const uint8_t *masks, int W, int H, int tw, int th,
+                const int32_t *offsets, const int32_t *flatten_ids, float *out_colors, float *out_alphas,
+                int32_t *last_ids, const int64_t *n_isects_dev, uint8_t *block_masks, cudaStream_t stream) {
+    dim3 grid(tw, th, C);
+    rasterize_fwd3_kernel<D><<<grid, kThreads3, 0, stream>>>(
+        C, n_isects, reinterpret_cast<const float4 *>(recA), reinterpret_cast<const float4 *>(recB), colors,
+        backgrounds, masks, W, H, tw, th, offsets, flatten_ids, out_colors, out_alphas, last_ids, n_isects_dev,
+        block_masks);
+    return gsb_check_launch("rasterize_fwd3");
+}
+
 template <int D>
 int launch_fwd2(int C, int64_t n_isects, const float *recA, const float *recB, const float *colors,
                 const float *backgrounds, const uint8_t *masks, int W, int H, int tw, int th,
@@ -247,6 +474,10 @@ int gsb_rasterize_fwd2_dispatch(int C, int64_t n_isects, const int64_t *n_isects
                                 float *render_alphas, int32_t *last_ids, uint8_t *block_masks, cudaStream_t stream) {
 #define GSB_FWD2_CASE(DD)                                                                                         \
     case DD:                                                                                                      \
+        if (gsb_option(GSB_OPT_FWD_VARIANT) == 3)                                                                 \
+            return raster::launch_fwd3<DD>(C, n_isects, recA, recB, colors, backgrounds, masks, width, height,    \
+                                           tile_width, tile_height, isect_offsets, flatten_ids, render_colors,    \
+                                           render_alphas, last_ids, n_isects_dev, block_masks, stream);           \
         return raster::launch_fwd2<DD>(C, n_isects, recA, recB, colors, backgrounds, masks, width, height,        \
                                        tile_width, tile_height, isect_offsets, flatten_ids, render_colors,        \
                                        render_alphas, last_ids, n_isects_dev, block_masks, stream);

@@ -286,7 +286,7 @@ def test_forward_kernel_variants_are_bit_identical(D, bg):
     w_c, w_a = torch.randn(C, H, W, D, generator=g).to(DEV), torch.randn(C, H, W, 1, generator=g).to(DEV)
     outs = {}
     try:
-        for variant in (1, 2):
+        for variant in (1, 2, 3):
             assert lib.gsb_set_option(0, variant) == 0
             p = [t.clone().to(DEV).requires_grad_(True) for t in (means2d, conics, colors, opac)]
             rc, ra = rasterize_to_pixels(p[0], p[1], p[2], p[3], W, H, ts, offs.to(DEV), flat.to(DEV),
@@ -295,9 +295,10 @@ def test_forward_kernel_variants_are_bit_identical(D, bg):
             outs[variant] = (rc, ra, grads)
     finally:
         lib.gsb_set_option(0, 2)
-    assert torch.equal(outs[1][0], outs[2][0]) and torch.equal(outs[1][1], outs[2][1])
-    for a, b in zip(outs[1][2], outs[2][2]):  # same kernel, same inputs: only the atomics' order differs
-        torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-5 * float(b.abs().max()))
+    for variant in (2, 3):
+        assert torch.equal(outs[1][0], outs[variant][0]) and torch.equal(outs[1][1], outs[variant][1]), variant
+        for a, b in zip(outs[1][2], outs[variant][2]):  # same kernel, same inputs: only the atomics' order differs
+            torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-5 * float(b.abs().max()))
 
 
 @pytest.mark.parametrize("ts,D,bg,absgrad", [(4, 3, True, False), (4, 32, False, False), (8, 3, True, True),
