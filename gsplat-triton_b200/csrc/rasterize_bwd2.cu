@@ -7,13 +7,14 @@
 //   * phase 1 (lane = two vertically adjacent pixels, sequential over the half-warp's splats): list bookkeeping, the
 //     three 16-byte staged loads, the exponent, T / u recurrences and both weights are issued once per two pixels and
 //     per TWO splats (the two halves of a warp walk the lists of two vertically adjacent blocks);
-//   * phase 2 (every 16 splats of a half-warp; lane = splat): one lane sums the whole 8x4 block of its splat —
-//     16 table rows of two pixels each, packed — so the v1 cross-half shuffle stage disappears and all 32 lanes
-//     reduce 32 different splats at once;
-//   * CTA = 128 threads, 42 KB of shared memory, 5 CTAs per SM.
-// Phase-1 table: per half-warp 16 rows (splats) x 16 float4 (lane: w1 of its two pixels, w2 of its two pixels), the
-// float4 column XOR-swizzled by the row so that phase 1 (a row at a time) and phase 2 (a column walk by 16 lanes on 16
-// different rows) are both bank-conflict free without padding.
+//   * phase 2 (every 8 splats of a half-warp; lane = splat x half of the block): a lane sums 8 table entries of
+//     two pixels each with packed instructions, one shuffle stage joins the two halves of the block;
+//   * CTA = 128 threads, 27 KB of shared memory: occupancy is set by registers, not by the table. (A 16-splat
+//     chunk with one lane per splat needs no shuffle stage and ~7 fewer instructions per splat, but its 42 KB cap
+//     the SM at 5 CTAs = 20 warps: ncu showed 54 % issue-active, one eligible warp per scheduler and cycle.)
+// Phase-1 table: per half-warp 8 rows (splats) x 16 float4 (lane: v_sigma of its two pixels, -alpha T of its two
+// pixels), the float4 column XOR-swizzled by the row so that phase 1 (a row at a time) and phase 2 (a column walk by
+// 8 lanes on 8 different rows) are both bank-conflict free without padding.
 #include "rasterize_common.cuh"
 
 namespace raster {
@@ -21,10 +22,10 @@ namespace raster {
 constexpr int kB2Threads = 128;
 constexpr int kB2Warps = kB2Threads / 32;
 constexpr int kB2Halves = 2 * kB2Warps;
-constexpr int kB2Chunk = 16;
+constexpr int kB2Chunk = 8;
 
 #ifndef GSB_BWD2_MIN_BLOCKS
-#define GSB_BWD2_MIN_BLOCKS 5
+#define GSB_BWD2_MIN_BLOCKS 6
 #endif
 
 struct __align__(256) Bwd2Smem {
@@ -60,60 +61,76 @@ __device__ __forceinline__ bool bwd_decide(int index, int last_id, float ex, flo
     return hit != 0;
 }
 
-// Phase 2 for the (up to 16) splats each half-warp has parked in its table: lane l16 owns splat l16 of its half.
+// Phase 2 for the (up to 8) splats each half-warp has parked in its table: lane (s = l16 & 7, q = l16 >> 3) sums, for
+// splat s, the 8 table entries of block rows 2q and 2q+1; the two q of a splat are joined by one shuffle stage and
+// lane q = 0 issues the global reductions.
 template <int D, bool ABS>
 __device__ __forceinline__ void reduce_chunk2(Bwd2Smem &sm, int hw, int l16, int count, int entry, float bcx, float bcy,
                                               const int32_t *__restrict__ flatten_ids, const GradTargets &out) {
     __syncwarp();
-    const bool valid = l16 < count;
+    const int s_ = l16 & 7, q_ = l16 >> 3;
+    const bool valid = s_ < count;
     const int e = valid ? entry : 0;
     const float4 mu = sm.P[e];
     const float4 sb = sm.B[e];
     const float ca = sb.x * kUnscaleDiag, cb = sb.y * kUnscaleOff, cc = sb.z * kUnscaleDiag, opac = -sb.w;
     const float ux = mu.x - bcx, uy = mu.y - bcy;
-    // rows of the block in pairs: R*[0] = (row 0, row 1), R*[1] = (row 2, row 3)
-    f32x2 R0[2] = {pack2(0.f, 0.f), pack2(0.f, 0.f)}, Rx[2] = {R0[0], R0[0]}, Rxx[2] = {R0[0], R0[0]};
+    f32x2 R0 = pack2(0.f, 0.f), Rx = R0, Rxx = R0;  // (row 2q, row 2q + 1)
     f32x2 col[D];
 #pragma unroll
     for (int k = 0; k < D; ++k) col[k] = pack2(0.f, 0.f);
     float abs_x = 0.f, abs_y = 0.f;
-    const float4 *row = sm.Wt[hw][l16];
-    const int sw = l16 & 7;
+    const float4 *row = sm.Wt[hw][s_];
+    const float4 *vrow = &sm.V[hw][8 * q_][0];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-        const float4 w = row[i ^ sw];  // (v_sigma pixel 0, v_sigma pixel 1, -alpha T pixel 0, -alpha T pixel 1)
-        const float4 v0 = sm.V[hw][i][0];
+    for (int i = 0; i < 8; ++i) {
+        const float4 w = row[(8 * q_ + i) ^ s_];  // (v_sigma pixel 0, v_sigma pixel 1, -alpha T pixel 0, -alpha T pixel 1)
+        const float4 v0 = vrow[2 * i];
         const f32x2 p = pack2(w.x, w.y), q = pack2(w.z, w.w);
-        const float cx = (float)(i & 7) - 3.5f;
-        const int r = i >> 3;
-        R0[r] = add2(R0[r], p);
-        Rx[r] = fma2(p, bcast2(cx), Rx[r]);
-        Rxx[r] = fma2(p, bcast2(cx * cx), Rxx[r]);
+        const float cx = (float)i - 3.5f;
+        R0 = add2(R0, p);
+        Rx = fma2(p, bcast2(cx), Rx);
+        Rxx = fma2(p, bcast2(cx * cx), Rxx);
         col[0] = fma2(q, pack2(v0.x, v0.y), col[0]);
         if (D > 1) col[1] = fma2(q, pack2(v0.z, v0.w), col[1]);
         if (D > 2) {
-            const float4 v1 = sm.V[hw][i][1];
+            const float4 v1 = vrow[2 * i + 1];
             col[2] = fma2(q, pack2(v1.x, v1.y), col[2]);
             if (D > 3) col[3] = fma2(q, pack2(v1.z, v1.w), col[3]);
         }
         if (ABS) {
-            const float dx = ux - cx, dy0 = uy - ((float)(2 * r) - 1.5f), dy1 = dy0 - 1.0f;
+            const float dx = ux - cx, dy0 = uy - ((float)(2 * q_) - 1.5f), dy1 = dy0 - 1.0f;
             abs_x += fabsf(w.x * (ca * dx + cb * dy0)) + fabsf(w.y * (ca * dx + cb * dy1));
             abs_y += fabsf(w.x * (cb * dx + cc * dy0)) + fabsf(w.y * (cb * dx + cc * dy1));
         }
     }
-    if (valid) {
-        float a0, a1, a2, a3, x0, x1, x2, x3, q0, q1, q2, q3;
-        unpack2(R0[0], a0, a1);
-        unpack2(R0[1], a2, a3);
-        unpack2(Rx[0], x0, x1);
-        unpack2(Rx[1], x2, x3);
-        unpack2(Rxx[0], q0, q1);
-        unpack2(Rxx[1], q2, q3);
-        // moments of v_sigma about the block centre; row centres at y = -1.5, -0.5, 0.5, 1.5
-        const float M0 = (a0 + a1) + (a2 + a3), Mx = (x0 + x1) + (x2 + x3), Mxx = (q0 + q1) + (q2 + q3);
-        const float My = 1.5f * (a3 - a0) + 0.5f * (a2 - a1), Mxy = 1.5f * (x3 - x0) + 0.5f * (x2 - x1);
-        const float Myy = 2.25f * (a0 + a3) + 0.25f * (a1 + a2);
+    // moments of v_sigma about the block centre over this lane's two rows (centres at y0, y0 + 1), then over the block
+    float a0, a1, x0, x1, q0, q1;
+    unpack2(R0, a0, a1);
+    unpack2(Rx, x0, x1);
+    unpack2(Rxx, q0, q1);
+    const float y0 = (float)(2 * q_) - 1.5f, y1 = y0 + 1.0f;
+    float M0 = a0 + a1, Mx = x0 + x1, Mxx = q0 + q1;
+    float My = y0 * a0 + y1 * a1, Mxy = y0 * x0 + y1 * x1, Myy = y0 * y0 * a0 + y1 * y1 * a1;
+    M0 += __shfl_xor_sync(0xffffffffu, M0, 8);
+    Mx += __shfl_xor_sync(0xffffffffu, Mx, 8);
+    My += __shfl_xor_sync(0xffffffffu, My, 8);
+    Mxx += __shfl_xor_sync(0xffffffffu, Mxx, 8);
+    Mxy += __shfl_xor_sync(0xffffffffu, Mxy, 8);
+    Myy += __shfl_xor_sync(0xffffffffu, Myy, 8);
+    float cs[D];
+#pragma unroll
+    for (int k = 0; k < D; ++k) {
+        float lo, hi;
+        unpack2(col[k], lo, hi);
+        cs[k] = lo + hi;
+        cs[k] += __shfl_xor_sync(0xffffffffu, cs[k], 8);
+    }
+    if (ABS) {
+        abs_x += __shfl_xor_sync(0xffffffffu, abs_x, 8);
+        abs_y += __shfl_xor_sync(0xffffffffu, abs_y, 8);
+    }
+    if (valid && q_ == 0) {
         const float Sx = ux * M0 - Mx, Sy = uy * M0 - My;
         const float Sxx = fmaf(ux, fmaf(ux, M0, -2.f * Mx), Mxx);
         const float Syy = fmaf(uy, fmaf(uy, M0, -2.f * My), Myy);
@@ -133,12 +150,8 @@ __device__ __forceinline__ void reduce_chunk2(Bwd2Smem &sm, int hw, int l16, int
         if (v[4] != 0.f) atomicAdd(out.v_conics + 3 * g + 2, v[4]);
         if (v[5] != 0.f) atomicAdd(out.v_opacities + g, v[5]);
 #pragma unroll
-        for (int k = 0; k < D; ++k) {
-            float lo, hi;
-            unpack2(col[k], lo, hi);
-            const float c = -(lo + hi);  // the table holds MINUS alpha T
-            if (c != 0.f) atomicAdd(out.v_colors + (int64_t)D * g + k, c);
-        }
+        for (int k = 0; k < D; ++k)
+            if (cs[k] != 0.f) atomicAdd(out.v_colors + (int64_t)D * g + k, -cs[k]);  // the table holds MINUS alpha T
         if (ABS) {
             if (abs_x != 0.f) atomicAdd(out.v_abs + 2 * g, abs_x);
             if (abs_y != 0.f) atomicAdd(out.v_abs + 2 * g + 1, abs_y);
@@ -275,7 +288,7 @@ rasterize_bwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
         }
         __syncthreads();
 
-        int n_chunk = 0, entry = 0;  // this half's chunk fill; lane l16 keeps the staged entry of the chunk's l16-th splat
+        int n_chunk = 0, entry = 0;  // this half's chunk fill; lanes l16 & 7 == s keep the staged entry of its s-th splat
         for (int c0 = 0; c0 < total; c0 += 32) {
             const int jl = c0 + lane;
             bool mine0 = false, mine1 = false;
@@ -336,7 +349,7 @@ rasterize_bwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
                 asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(waddr), "f"(s0), "f"(s1), "f"(w0), "f"(w1)
                              : "memory");
                 if (hits & half_lanes) {  // some pixel of this half's block was hit: the row is kept
-                    entry = (l16 == n_chunk) ? e : entry;
+                    entry = ((l16 & 7) == n_chunk) ? e : entry;  // both lanes (q = 0, 1) of the chunk's splat keep it
                     ++n_chunk;
                 }
                 if (__any_sync(0xffffffffu, n_chunk == kB2Chunk)) {
