@@ -46,7 +46,7 @@ void gsb_reset_launch_count(void);
  *                        2 = rasterize_fwd2.cu (half-warp per block, 2 pixels per lane, packed FFMA2) [default, D <= 4]
  *                        3 = the same compositor fed by a producer warp (double-buffered staging, named barriers)
  *   GSB_OPT_BWD_VARIANT  1 = rasterize_bwd.cu (warp per block, two-phase moment reduction)
- *                        2 = rasterize_bwd2.cu (half-warp per block, 2 pixels per lane, packed FFMA2, D <= 4) */
+ *                        2 = rasterize_bwd2.cu (half-warp per block, 2 pixels per lane, packed FFMA2) [default, D <= 4] */
 #define GSB_OPT_FWD_VARIANT 0
 #define GSB_OPT_BWD_VARIANT 1
 #define GSB_OPT_COUNT 2

@@ -358,7 +358,7 @@ def test_backward_kernel_variants_agree_and_match_oracle(D, bg, absgrad):
         check_compositor_stage(rasterize_to_pixels, means2d, conics, colors, opac, W, H, ts, offs, flat,
                                backgrounds=backgrounds, masks=masks, what=f"bwd v2 D={D}", gpu_kw={"absgrad": absgrad})
     finally:
-        lib.gsb_set_option(1, 1)
+        lib.gsb_set_option(1, 2)
 
 
 def test_raster_masks_empty_and_last_tile():

@@ -30,13 +30,15 @@ for packed in (False, True):
 # the plain kernels behind tile_size != 16 and the first-generation forward kernel
 from gsplat.b200_impl._lib import lib  # noqa: E402
 
-for tile_size, variant in ((8, 2), (16, 1)):
+for tile_size, variant in ((8, 2), (16, 1), (16, 3)):
     lib.gsb_set_option(0, variant)
+    lib.gsb_set_option(1, 1 if variant == 1 else 2)
     p = [t.clone().to(dev).requires_grad_(True) for t in (means, quats, scales * 3 + 0.002, opac, shs)]
     rc, ra, meta = rasterization(*p, viewmats[:2].to(dev), Ks[:2].to(dev), W, H, sh_degree=2, packed=False,
                                  tile_size=tile_size, absgrad=True)
     (rc.sum() + ra.sum()).backward()
     n += 1
 lib.gsb_set_option(0, 2)
+lib.gsb_set_option(1, 2)
 torch.cuda.synchronize()
 print("sanitize_small: %d fwd+bwd passes, last n_isects=%d" % (n, meta["flatten_ids"].numel()))
