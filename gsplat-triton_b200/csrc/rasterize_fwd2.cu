@@ -58,26 +58,26 @@ rasterize_fwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
                       uint8_t *__restrict__ block_masks, unsigned long long *__restrict__ warp_iters) {
     static_assert(D >= 1 && D <= 4, "v2 keeps the colour of a staged splat in one float4");
     if (n_isects_dev != nullptr) n_isects = min(n_isects, (int64_t)*n_isects_dev);
-    // Staged batch, double-buffered, NOT compacted: thread t stages intersection base + t into entry t + 1 of buffer
-    // (batch & 1), culled ones with an empty block mask (the warps' ballots skip them). One CTA barrier per batch:
-    // it publishes batch k and, because every warp has finished compositing batch k - 1 before it arrives, it also
-    // frees the other buffer for batch k + 1 (three barriers per batch with a single compacted buffer: ncu showed the
-    // barrier as the first stall reason). Entry 0 of every array is a zeroed pad: a half-warp whose list is exhausted
-    // reads entry c0 + ffs(0) = c0, harmless finite values, discarded through a zero opacity.
+    // (Measured and dropped: a double-buffered, uncompacted batch needs one CTA barrier per batch instead of three, but
+    // the warps then scan every entry's mask instead of the survivors': 0.420 ms against 0.408 ms at cfg2. The
+    // barriers top the stall samples, yet they are not what bounds the kernel: issue slots and the ALU pipe are.)
+    // Staged batch. Entry 0 of every array is a zeroed pad: a half-warp whose list is exhausted reads it (index
+    // c0 + ffs(0) = c0, harmless finite values, discarded through a zero opacity) while the other half goes on.
     struct __align__(16) Stage {
-        float4 P[kThreads2 + 1];   // x, y, sorted index, block mask
-        float4 B[kThreads2 + 1];   // staged conic (A', B', C'), MINUS opacity
-        float4 Cq[kThreads2 + 1];  // colour
+        float4 P[kThreads2 + 32];   // x, y, sorted index, block mask
+        float4 B[kThreads2 + 32];   // staged conic (A', B', C'), MINUS opacity
+        float4 Cq[kThreads2 + 32];  // colour
+        int wcnt[kWarps2];
     };
-    __shared__ Stage st[2];
-    if (threadIdx.x < 2) {
-        st[threadIdx.x].P[0] = make_float4(0.f, 0.f, 0.f, 0.f);
-        st[threadIdx.x].B[0] = make_float4(0.f, 0.f, 0.f, 0.f);
-        st[threadIdx.x].Cq[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __shared__ Stage st;
+    for (int i = threadIdx.x; i < kThreads2 + 32; i += kThreads2) {
+        st.P[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        st.B[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        st.Cq[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    unsigned sP0 = (unsigned)__cvta_generic_to_shared(st[0].P);
-    asm volatile("mov.u32 %0, %0;" : "+r"(sP0));  // opaque: kept in a register instead of being recomputed per iteration
-    constexpr unsigned kOffB = sizeof(float4) * (kThreads2 + 1), kOffC = 2 * kOffB;
+    unsigned sP = (unsigned)__cvta_generic_to_shared(st.P);
+    asm volatile("mov.u32 %0, %0;" : "+r"(sP));  // opaque: kept in a register instead of being recomputed per iteration
+    constexpr unsigned kOffB = sizeof(float4) * (kThreads2 + 32), kOffC = 2 * kOffB;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, half = lane >> 4, l16 = lane & 15;
     const int cam = blockIdx.z, tile_y = blockIdx.y, tile_x = blockIdx.x;
@@ -111,38 +111,49 @@ rasterize_fwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
         unsigned half_mask = half ? 0xffffffffu : 0u;
         asm volatile("mov.u32 %0, %0;" : "+r"(half_mask));  // opaque, so the list select stays one LOP3
 
-        int buf = 0;
-        for (int base = range_start; base < range_end; base += kThreads2, buf ^= 1) {
-            const int idx = base + tid;
-            // culled / past the end: an all-zero entry (empty block mask; finite, so the exhausted-half read is harmless)
-            float4 entryP = make_float4(0.f, 0.f, 0.f, 0.f), entryB = entryP, entryC = entryP;
-            if (idx < range_end) {
-                const int g = flatten_ids[idx];
-                const float4 A = __ldg(recA + g);
-                const float4 B = __ldg(recB + g);
-                const unsigned mask = splat_block_mask(A, B, tile_x * kTile, tile_y * kTile);
-                if (block_masks != nullptr) block_masks[idx] = (uint8_t)mask;
-                if (mask != 0u) {
-                    entryP = make_float4(A.x, A.y, __int_as_float(idx), __uint_as_float(mask));
-                    entryB = stage_conic(B);
-                    entryB.w = -entryB.w;
-                    const float *cp = colors + (size_t)g * D;
-                    entryC.x = cp[0];
-                    if (D > 1) entryC.y = cp[1];
-                    if (D > 2) entryC.z = cp[2];
-                    if (D > 3) entryC.w = cp[3];
-                }
-            }
-            st[buf].P[tid + 1] = entryP;
-            st[buf].B[tid + 1] = entryB;
-            st[buf].Cq[tid + 1] = entryC;
-            // all 256 pixels saturated (or outside the image): nothing left to composite
+        for (int base = range_start; base < range_end; base += kThreads2) {
             if (__syncthreads_count((T0 < 0.f) & (T1 < 0.f)) == kThreads2) break;
+            const int idx = base + tid;
+            unsigned mask = 0u;
+            int g = 0;
+            float4 A, B;
+            if (idx < range_end) {
+                g = flatten_ids[idx];
+                A = __ldg(recA + g);
+                B = __ldg(recB + g);
+                mask = splat_block_mask(A, B, tile_x * kTile, tile_y * kTile);
+                if (block_masks != nullptr) block_masks[idx] = (uint8_t)mask;
+            }
+            // compacting append (4 warps)
+            const unsigned ballot = __ballot_sync(0xffffffffu, mask != 0u);
+            if (lane == 0) st.wcnt[warp] = __popc(ballot);
+            __syncthreads();
+            int slot = 0, total = 0;
+#pragma unroll
+            for (int w = 0; w < kWarps2; ++w) {
+                const int c = st.wcnt[w];
+                slot += (w < warp) ? c : 0;
+                total += c;
+            }
+            slot += __popc(ballot & ((1u << lane) - 1u)) + 1;  // entry 0 is the pad
+            if (mask != 0u) {
+                st.P[slot] = make_float4(A.x, A.y, __int_as_float(idx), __uint_as_float(mask));
+                float4 sb = stage_conic(B);
+                sb.w = -sb.w;
+                st.B[slot] = sb;
+                const float *cp = colors + (size_t)g * D;
+                float4 c4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                c4.x = cp[0];
+                if (D > 1) c4.y = cp[1];
+                if (D > 2) c4.z = cp[2];
+                if (D > 3) c4.w = cp[3];
+                st.Cq[slot] = c4;
+            }
+            __syncthreads();
             if (warp_done) continue;
-            const unsigned sP = sP0 + (unsigned)buf * (unsigned)sizeof(Stage);
-            const int total = min(kThreads2, range_end - base);
             for (int c0 = 0; c0 < total; c0 += 32) {
-                const unsigned m = __float_as_uint(st[buf].P[c0 + lane + 1].w);  // entries past `total` hold mask 0
+                const int jl = c0 + lane;
+                const unsigned m = jl < total ? __float_as_uint(st.P[jl + 1].w) : 0u;
                 unsigned todo0 = __ballot_sync(0xffffffffu, (m >> bit0) & 1u);
                 unsigned todo1 = __ballot_sync(0xffffffffu, (m >> bit1) & 1u);
                 while (todo0 | todo1) {
@@ -161,7 +172,7 @@ rasterize_fwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
                     const f32x2 ex = fma2(mul2(bcast2(b4.z), dy), dy, mul2(bcast2(dx), t));
                     float ex0, ex1;
                     unpack2(ex, ex0, ex1);
-                    // MINUS alpha; an exhausted half composites a stale entry with opacity 0: never a hit
+                    // MINUS alpha; an exhausted half composites the pad with opacity 0: never a hit
                     const float nopac = todo != 0u ? b4.w : 0.f;
                     float na0, na1;
                     unpack2(mul2(bcast2(nopac), pack2(exp2f(ex0), exp2f(ex1))), na0, na1);
