@@ -196,13 +196,17 @@ def _raster_work_counts(meta, device):
                             ptr(flat), ptr(cnt), ptr(ra), ptr(last), ptr(pairs), st)
     hits = int(cnt.double().sum().item())
     lane_evals = {"gsb_rasterize_bwd": 32 * int(pairs.item())}
-    if int(lib.gsb_get_option(0)) == 2:  # forward v2: one loop iteration = 2 blocks x 32 pixels
+    if int(lib.gsb_get_option(0)) >= 2:  # forward v2 / v3: one loop iteration = 2 blocks x 32 pixels
         iters = torch.zeros((1,), dtype=torch.int64, device=device)
         s1, s2 = torch.empty_like(cnt), torch.empty_like(ra)
         s3 = torch.empty_like(last)
         lib.gsb_rasterize_fwd2_count(C, flat.numel(), ptr(rec[0]), ptr(rec[1]), ptr(ones), W, H, tw, th, ptr(offs),
                                      ptr(flat), ptr(s1), ptr(s2), ptr(s3), ptr(iters), st)
         lane_evals["gsb_rasterize_fwd_cap"] = 64 * int(iters.item())
+        if int(lib.gsb_get_option(1)) == 2:
+            # backward v2 walks the same per-half lists (cut at each block's last contributor): same count, an
+            # upper bound by the few entries behind the last contributor
+            lane_evals["gsb_rasterize_bwd"] = 64 * int(iters.item())
     else:
         lane_evals["gsb_rasterize_fwd_cap"] = 32 * int(pairs.item())
     lane_evals["gsb_rasterize_fwd"] = lane_evals["gsb_rasterize_fwd_cap"]
