@@ -183,12 +183,14 @@ def rasterization(
         "opacities": opacities,
     })
 
-    # b200, unpacked, one node: the exchange is split. The projected geometry leaves for the camera owners NOW, on a
-    # side stream, while the colours are still being computed; the colours follow under the receivers' tile
-    # intersection (which needs the geometry only).
+    # b200, unpacked, one node, GSPLAT_B200_EXCHANGE_SPLIT=1: the forward exchange is split. The projected geometry
+    # leaves for the camera owners NOW, on a side stream, while the colours are still being computed; the colours
+    # follow under the receivers' tile intersection (which needs the geometry only). Off by default: on one 8xB200 box
+    # the extra launches and stream hand-overs cost more than the overlap returns (cfg2 sharded over 8 ranks: 1.958 ms
+    # against 1.921 ms per step).
     split = None
     if (distributed and not packed and BACKEND == "b200" and peer_exchange_available()
-            and os.environ.get("GSPLAT_B200_EXCHANGE_SPLIT", "1") == "1"):
+            and os.environ.get("GSPLAT_B200_EXCHANGE_SPLIT", "0") == "1"):
         D_out = 3 if sh_degree is not None else colors.shape[-1]
         split = SplitExchange(C_world[world_rank], N_world, D_out)
         split.start_geometry(means2d, depths, conics, opacities, radii)

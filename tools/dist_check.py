@@ -82,11 +82,11 @@ def main():
             truth = dict(rc=rc[my_cams].detach(), ra=ra[my_cams].detach(),
                          grads=[p.grad[lo:hi].clone() for p in full])
             del full, rc, ra
-            for transport in ("peer", "peer_unsplit", "nccl"):
-                if transport == "peer_unsplit" and packed:
+            for transport in ("peer", "peer_split", "nccl"):
+                if transport == "peer_split" and packed:
                     continue  # packed rows have a single (unsplit) peer path
                 os.environ["GSPLAT_B200_EXCHANGE"] = "nccl" if transport == "nccl" else "peer"
-                os.environ["GSPLAT_B200_EXCHANGE_SPLIT"] = "0" if transport == "peer_unsplit" else "1"
+                os.environ["GSPLAT_B200_EXCHANGE_SPLIT"] = "1" if transport == "peer_split" else "0"
                 for step in range(3):
                     shard = [p[lo:hi].to(dev).requires_grad_(True) for p in params]
                     args = (viewmats[my_cams].to(dev), Ks[my_cams].to(dev), W, H)
@@ -117,7 +117,7 @@ def main():
         print("DIST_CHECK " + json.dumps({
             "world": world, "cases_per_rank": n_cases, "ok": flag.item() == 0, "img_max_err": w[0].item(),
             "alpha_max_err": w[1].item(), "grad_max_rel": w[2].item(),
-            "covers": "packed x {RGB classic, RGB+ED antialiased} x {peer (split exchange), peer unsplit, nccl} x {even, uneven shards} x 3 steps "
+            "covers": "packed x {RGB classic, RGB+ED antialiased} x {peer, peer with split forward exchange, nccl} x {even, uneven shards} x 3 steps "
                       "(forward-only steps in between), vs a single-GPU render of the whole scene"}), flush=True)
     dist.barrier()
     close_mailboxes()
