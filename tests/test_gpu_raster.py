@@ -448,6 +448,9 @@ def test_torch_compositor_over_our_index_kernel_equals_the_fused_compositor():
 
         rc, ra, grads = run(rasterize_to_pixels)
         t_rc, t_ra, t_grads = run(rasterize_to_pixels_torch, batch_per_iter=batch_per_iter)
+        # two CUDA paths of ours (index kernel + torch accumulate vs the fused compositor): the exp of the index
+        # kernel (expf) and of the compositor (ex2.approx) differ in the last ulps, so pairs on a threshold may flip;
+        # the fraction is bounded here and classified pixel by pixel where it matters (the fused path vs the oracle)
         _close_frac(t_rc, rc, rtol=1e-4, atol=1e-5, max_bad=3e-3)
         _close_frac(t_ra, ra, rtol=1e-4, atol=1e-5, max_bad=3e-3)
         for a, b in zip(t_grads, grads):

@@ -22,8 +22,9 @@ def _close(a, b, rtol=1e-4, atol=1e-4, **kw):
     torch.testing.assert_close(a.cpu(), b.cpu(), rtol=rtol, atol=atol, **kw)
 
 
-def _close_frac(a, b, rtol, atol, max_bad=1e-3):
-    """assert_close allowing a tiny fraction of outliers (threshold flips near alpha=1/255 etc.)."""
+def _close_frac(a, b, rtol, atol, max_bad=0.0):
+    """Elementwise |a - b| <= atol + rtol |b| with ZERO outliers (round 1 allowed 1e-3 of the elements; measured on a
+    B200: none, profiles/r02a_parity_report.txt); the worst element is printed."""
     a, b = a.cpu().double(), b.cpu().double()
     err = (a - b).abs()
     bad = (err > atol + rtol * b.abs()).double().mean().item()
@@ -95,8 +96,8 @@ def test_projection_fisheye(golden):
     v = (radii.cpu() > 0) & (ref > 0)
     _close(means2d.detach().cpu()[v], g["means2d"][v], rtol=1e-4, atol=1e-3)
     _close(depths.detach().cpu()[v], g["depths"][v])
-    _close_frac(conics.detach().cpu()[v], g["conics"][v], rtol=1e-4, atol=1e-5, max_bad=1e-3)
-    _close_frac(comps.detach().cpu()[v], g["comps"][v], rtol=1e-4, atol=1e-3, max_bad=1e-3)
+    _close_frac(conics.detach().cpu()[v], g["conics"][v], rtol=1e-4, atol=1e-5)
+    _close_frac(comps.detach().cpu()[v], g["comps"][v], rtol=1e-4, atol=1e-3)
     m = (ref > 0).float().to(DEV) * (radii > 0).float()
     w2, wd, wc, wp = _cu(g, "w_means2d", "w_depths", "w_conics", "w_comps")
     loss = ((means2d * w2).sum(-1) * m + depths * wd * m + (conics * wc).sum(-1) * m + comps * wp * m).sum()
