@@ -23,6 +23,7 @@
 // Two regions per direction: a peer may start step t+1's put while this rank still unpacks step t,
 // but cannot reach step t+2's put before this rank has published step t+1 (stream order), see DESIGN.md 6.
 #include "common.cuh"
+#include "peer_layout.cuh"
 
 #include <cstring>
 
@@ -91,12 +92,8 @@ struct Fields {
     int count;            // number of entries of `active`
     int active[kFields];  // the fields this launch sends (a split exchange sends geometry and colours separately)
 };
-__host__ __device__ __forceinline__ int64_t round_up4(int64_t v) { return (v + 3) & ~(int64_t)3; }
-__host__ __device__ __forceinline__ int64_t field_offset(const int *width, int field, int64_t rows) {
-    int64_t off = 0;
-    for (int g = 0; g < field; ++g) off += round_up4(rows * width[g]);
-    return off;
-}
+using peer::field_offset;
+using peer::round_up4;
 
 // copies `len` floats src -> dst with this CTA column (blockIdx.x of gridDim.x); src == NULL stores zeros.
 // The stores are what crosses NVLink: they are always 16-byte vectors on the 16-byte aligned body of dst (a scalar
@@ -513,4 +510,53 @@ extern "C" int gsb_a2a_put_packed_bwd(int world, int rank, int D, const int64_t 
     put_packed_bwd_kernel<<<grid, kThreads, 0, stream>>>(peers, fields, plan, world, rank, region_offset,
                                                         (unsigned long long)epoch);
     return gsb_check_launch("a2a_put_packed_bwd");
+}
+
+// ---- push exchange: the projection / colour kernels store their rows into the peers' mailboxes themselves ---------
+int gsb_fill_push_rows(peer::PushRows &push, int world, int C_local, int64_t N_total, int64_t n_base, int D,
+                       const void *const *peer_bases_host, int64_t region_offset, const float *opacities) {
+    GSB_REQUIRE(world >= 1 && world <= kMaxPeers && peer_bases_host != nullptr, "bad world / peers");
+    GSB_REQUIRE(region_offset >= kHeaderBytes && (region_offset & 15) == 0, "bad region");
+    for (int i = 0; i < peer::kMaxPeers; ++i) push.region[i] = nullptr;
+    for (int i = 0; i < world; ++i) {
+        GSB_REQUIRE(peer_bases_host[i] != nullptr, "null peer mailbox");
+        push.region[i] = reinterpret_cast<float *>(reinterpret_cast<char *>(const_cast<void *>(peer_bases_host[i])) +
+                                                   region_offset);
+    }
+    const int width[kFields] = {2, 1, 3, 1, D, 1};
+    const int64_t rows = (int64_t)C_local * N_total;
+    push.world = world;
+    push.C_local = C_local;
+    push.N_total = N_total;
+    push.n_base = n_base;
+    push.off_means2d = field_offset(width, 0, rows);
+    push.off_depths = field_offset(width, 1, rows);
+    push.off_conics = field_offset(width, 2, rows);
+    push.off_opacities = field_offset(width, 3, rows);
+    push.off_colors = field_offset(width, 4, rows);
+    push.off_radii = field_offset(width, 5, rows);
+    push.opacities = opacities;
+    return GSB_OK;
+}
+
+namespace {
+// after the pushing kernels (stream order): tell every peer that this rank's rows of `epoch` have landed
+__global__ void publish_kernel(PeerTable peers, int world, int rank, int channel, unsigned long long epoch) {
+    if (threadIdx.x < world) {
+        __threadfence_system();
+        unsigned long long *flag =
+            reinterpret_cast<unsigned long long *>(peers.base[threadIdx.x] + 128 * channel) + rank;
+        st_release_sys(flag, epoch);
+    }
+}
+}  // namespace
+
+extern "C" int gsb_a2a_publish(int world, int rank, int channel, int64_t epoch, const void *const *peer_bases_host,
+                               cudaStream_t stream) {
+    GSB_REQUIRE(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, "bad world/rank");
+    GSB_REQUIRE(channel >= 0 && channel < kChannels && epoch > 0, "bad channel/epoch");
+    PeerTable peers;
+    GSB_REQUIRE(fill_peers(peers, peer_bases_host, world) == 0, "null peer mailbox");
+    publish_kernel<<<1, 32, 0, stream>>>(peers, world, rank, channel, (unsigned long long)epoch);
+    return gsb_check_launch("a2a_publish");
 }

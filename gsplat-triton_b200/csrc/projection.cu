@@ -12,6 +12,7 @@
 // All kernels are HBM-bound element-wise passes.
 #include "common.cuh"
 #include "gsplat_b200.h"
+#include "peer_layout.cuh"
 
 namespace {
 
@@ -245,13 +246,13 @@ __device__ __forceinline__ Proj2D project_one(const Camera &c, float px, float p
 }
 
 // ---------------------------------------------------------------- forward, unpacked
-template <int MODEL>
+template <int MODEL, bool PUSH>
 __global__ void __launch_bounds__(kThreads)
 projection_fwd_kernel(int C, int N, const float *__restrict__ means, const float *__restrict__ covars,
                       const float *__restrict__ quats, const float *__restrict__ scales,
                       const float *__restrict__ viewmats, const float *__restrict__ Ks, ProjParams p,
                       int32_t *__restrict__ radii, float *__restrict__ means2d, float *__restrict__ depths,
-                      float *__restrict__ conics, float *__restrict__ comps) {
+                      float *__restrict__ conics, float *__restrict__ comps, peer::PushRows push) {
     int n = blockIdx.x * kThreads + threadIdx.x;
     if (n >= N) return;
     const float *mp = means + 3 * (size_t)n;
@@ -270,7 +271,24 @@ projection_fwd_kernel(int C, int N, const float *__restrict__ means, const float
         cp[1] = v ? o.cxy : 0.f;
         cp[2] = v ? o.cyy : 0.f;
         if (comps != nullptr) comps[row] = v ? o.comp : 0.f;
+        if (PUSH) {
+            // distributed, unpacked: the same row goes straight into the mailbox of the rank that owns camera c
+            // (NVLink peer stores; consecutive lanes = consecutive rows: coalesced), no separate put kernel
+            int64_t drow;
+            float *dst = peer::push_row(push, c, n, drow);
+            reinterpret_cast<int32_t *>(dst + push.off_radii)[drow] = o.radius;
+            dst[push.off_depths + drow] = o.depth;
+            *reinterpret_cast<float2 *>(dst + push.off_means2d + 2 * drow) =
+                v ? make_float2(o.mx, o.my) : make_float2(0.f, 0.f);
+            float *dc = dst + push.off_conics + 3 * drow;
+            dc[0] = v ? o.cxx : 0.f;
+            dc[1] = v ? o.cxy : 0.f;
+            dc[2] = v ? o.cyy : 0.f;
+            const float opac = push.opacities[n];
+            dst[push.off_opacities + drow] = comps != nullptr ? opac * (v ? o.comp : 0.f) : opac;
+        }
     }
+    if (PUSH) __threadfence_system();  // this thread's peer stores are performed before the grid can be seen complete
 }
 
 // ---------------------------------------------------------------- backward pieces
@@ -733,11 +751,12 @@ int check_model(int camera_model) {
         __VA_ARGS__;                                       \
     }
 
-extern "C" int gsb_projection_fwd(int C, int N, const float *means, const float *covars, const float *quats,
-                                  const float *scales, const float *viewmats, const float *Ks, int width, int height,
-                                  float eps2d, float near_plane, float far_plane, float radius_clip,
-                                  int camera_model, int32_t *radii, float *means2d, float *depths, float *conics,
-                                  float *compensations, cudaStream_t stream) {
+namespace {
+int projection_fwd_launch(int C, int N, const float *means, const float *covars, const float *quats,
+                          const float *scales, const float *viewmats, const float *Ks, int width, int height,
+                          float eps2d, float near_plane, float far_plane, float radius_clip, int camera_model,
+                          int32_t *radii, float *means2d, float *depths, float *conics, float *compensations,
+                          const peer::PushRows *push, cudaStream_t stream) {
     GSB_REQUIRE(C >= 0 && N >= 0, "negative size");
     GSB_REQUIRE(covars != nullptr || (quats != nullptr && scales != nullptr), "covars or (quats, scales) required");
     if (int e = check_model(camera_model)) return e;
@@ -748,10 +767,49 @@ extern "C" int gsb_projection_fwd(int C, int N, const float *means, const float 
     unsigned gy = 1;
     if (nblk < 148u * 4u) gy = (unsigned)min((long long)C, (long long)gsb_cdiv(148 * 4, nblk));
     dim3 grid(nblk, gy);
-    DISPATCH_MODEL(camera_model, (projection_fwd_kernel<M><<<grid, kThreads, 0, stream>>>(
-                                     C, N, means, covars, quats, scales, viewmats, Ks, p, radii, means2d, depths,
-                                     conics, compensations)));
+    if (push != nullptr) {
+        DISPATCH_MODEL(camera_model, (projection_fwd_kernel<M, true><<<grid, kThreads, 0, stream>>>(
+                                         C, N, means, covars, quats, scales, viewmats, Ks, p, radii, means2d, depths,
+                                         conics, compensations, *push)));
+    } else {
+        peer::PushRows none = {};
+        DISPATCH_MODEL(camera_model, (projection_fwd_kernel<M, false><<<grid, kThreads, 0, stream>>>(
+                                         C, N, means, covars, quats, scales, viewmats, Ks, p, radii, means2d, depths,
+                                         conics, compensations, none)));
+    }
     return gsb_check_launch("projection_fwd");
+}
+}  // namespace
+
+extern "C" int gsb_projection_fwd(int C, int N, const float *means, const float *covars, const float *quats,
+                                  const float *scales, const float *viewmats, const float *Ks, int width, int height,
+                                  float eps2d, float near_plane, float far_plane, float radius_clip,
+                                  int camera_model, int32_t *radii, float *means2d, float *depths, float *conics,
+                                  float *compensations, cudaStream_t stream) {
+    return projection_fwd_launch(C, N, means, covars, quats, scales, viewmats, Ks, width, height, eps2d, near_plane,
+                                 far_plane, radius_clip, camera_model, radii, means2d, depths, conics, compensations,
+                                 nullptr, stream);
+}
+
+// peer.cu
+int gsb_fill_push_rows(peer::PushRows &push, int world, int C_local, int64_t N_total, int64_t n_base, int D,
+                       const void *const *peer_bases_host, int64_t region_offset, const float *opacities);
+
+extern "C" int gsb_projection_fwd_push(int C, int N, const float *means, const float *covars, const float *quats,
+                                       const float *scales, const float *viewmats, const float *Ks, int width,
+                                       int height, float eps2d, float near_plane, float far_plane, float radius_clip,
+                                       int camera_model, int32_t *radii, float *means2d, float *depths, float *conics,
+                                       float *compensations, const float *opacities, int world, int C_local,
+                                       int64_t N_total, int64_t n_base, int D, const void *const *peer_bases_host,
+                                       int64_t region_offset, cudaStream_t stream) {
+    GSB_REQUIRE(opacities != nullptr && world >= 1 && C_local >= 1 && C == world * C_local, "bad push geometry");
+    GSB_REQUIRE(n_base >= 0 && n_base + N <= N_total, "rows do not fit the destination table");
+    peer::PushRows push;
+    if (int e = gsb_fill_push_rows(push, world, C_local, N_total, n_base, D, peer_bases_host, region_offset, opacities))
+        return e;
+    return projection_fwd_launch(C, N, means, covars, quats, scales, viewmats, Ks, width, height, eps2d, near_plane,
+                                 far_plane, radius_clip, camera_model, radii, means2d, depths, conics, compensations,
+                                 &push, stream);
 }
 
 extern "C" int gsb_projection_bwd(int C, int N, const float *means, const float *covars, const float *quats,

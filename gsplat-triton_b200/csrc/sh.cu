@@ -10,6 +10,7 @@
 // [C,N,K,3] is never materialised and, in the backward pass, v_coeffs accumulates in registers
 // over cameras and is written once with plain stores (no zero-fill, no atomics).
 #include "common.cuh"
+#include "peer_layout.cuh"
 #include "gsplat_b200.h"
 
 namespace {
@@ -258,11 +259,11 @@ sh_bwd_kernel(int64_t n_rows, int n_batch, int K, const float *__restrict__ dirs
 // (masked rows evaluate to SH = 0, exactly as `spherical_harmonics(..., masks=radii > 0)` followed by the clamp).
 // Backward: v_coeffs[n] and v_means[n] summed over cameras in registers (dirs is linear in means), the clamp's
 // pass-through mask recomputed from the forward value.
-template <int DEG>
+template <int DEG, bool PUSH>
 __global__ void __launch_bounds__(kThreads)
 sh_colors_fwd_kernel(int64_t N, int C, int K, const float *__restrict__ means, const float *__restrict__ campos,
                      const float *__restrict__ coeffs, const int32_t *__restrict__ radii,
-                     float *__restrict__ colors) {
+                     float *__restrict__ colors, peer::PushRows push) {
     constexpr int NB = (DEG + 1) * (DEG + 1);
     constexpr int S = (NB * 3) | 1;
     __shared__ float s_cf[kThreads * S];
@@ -293,7 +294,15 @@ sh_colors_fwd_kernel(int64_t N, int C, int K, const float *__restrict__ means, c
         op[0] = fmaxf(cr + 0.5f, 0.f);
         op[1] = fmaxf(cg + 0.5f, 0.f);
         op[2] = fmaxf(cb + 0.5f, 0.f);
+        if (PUSH) {  // and straight into the mailbox of the rank that owns camera c (see projection_fwd_kernel)
+            int64_t drow;
+            float *dst = peer::push_row(push, c, r, drow) + push.off_colors + 3 * drow;
+            dst[0] = op[0];
+            dst[1] = op[1];
+            dst[2] = op[2];
+        }
     }
+    if (PUSH) __threadfence_system();
 }
 
 template <int DEG, bool NEED_MEANS>
@@ -409,7 +418,29 @@ extern "C" int gsb_sh_colors_fwd(int degree, int64_t N, int C, int K, const floa
     GSB_REQUIRE(N >= 0 && C >= 0, "negative size");
     if (N == 0 || C == 0) return GSB_OK;
     unsigned nblk = gsb_cdiv(N, kThreads);
-    DISPATCH_DEG(degree, (sh_colors_fwd_kernel<D><<<nblk, kThreads, 0, stream>>>(N, C, K, means, campos, coeffs, radii, colors)));
+    peer::PushRows none = {};
+    DISPATCH_DEG(degree, (sh_colors_fwd_kernel<D, false><<<nblk, kThreads, 0, stream>>>(N, C, K, means, campos, coeffs, radii, colors, none)));
+    return gsb_check_launch("sh_colors_fwd");
+}
+
+// peer.cu
+int gsb_fill_push_rows(peer::PushRows &push, int world, int C_local, int64_t N_total, int64_t n_base, int D,
+                       const void *const *peer_bases_host, int64_t region_offset, const float *opacities);
+
+extern "C" int gsb_sh_colors_fwd_push(int degree, int64_t N, int C, int K, const float *means, const float *campos,
+                                      const float *coeffs, const int32_t *radii, float *colors, int world, int C_local,
+                                      int64_t N_total, int64_t n_base, const void *const *peer_bases_host,
+                                      int64_t region_offset, cudaStream_t stream) {
+    GSB_REQUIRE(degree >= 0 && degree <= 4, "degree must be in [0, 4]");
+    GSB_REQUIRE((degree + 1) * (degree + 1) <= K, "K is smaller than (degree+1)^2");
+    GSB_REQUIRE(N >= 0 && C >= 0 && world >= 1 && C_local >= 1 && C == world * C_local, "bad push geometry");
+    GSB_REQUIRE(n_base >= 0 && n_base + N <= N_total, "rows do not fit the destination table");
+    if (N == 0 || C == 0) return GSB_OK;
+    peer::PushRows push;
+    if (int e = gsb_fill_push_rows(push, world, C_local, N_total, n_base, 3, peer_bases_host, region_offset, nullptr))
+        return e;
+    unsigned nblk = gsb_cdiv(N, kThreads);
+    DISPATCH_DEG(degree, (sh_colors_fwd_kernel<D, true><<<nblk, kThreads, 0, stream>>>(N, C, K, means, campos, coeffs, radii, colors, push)));
     return gsb_check_launch("sh_colors_fwd");
 }
 

@@ -101,6 +101,15 @@ def fully_fused_projection(
     )
 
 
+# distributed "push" exchange (gsplat.distributed.PushExchange): while set, the unpacked projection and the fused SH
+# colour kernel also store their rows into the camera owners' mailboxes
+_PUSH_CONTEXT = [None]
+
+
+def set_push_context(ex) -> None:
+    _PUSH_CONTEXT[0] = ex
+
+
 def _f32(t: Optional[Tensor]) -> Optional[Tensor]:
     if t is None:
         return None
@@ -121,11 +130,23 @@ class _FullyFusedProjection(torch.autograd.Function):
         depths = torch.empty((C, N), dtype=torch.float32, device=dev)
         conics = torch.empty((C, N, 3), dtype=torch.float32, device=dev)
         compensations = torch.empty((C, N), dtype=torch.float32, device=dev) if calc_compensations else None
-        lib.gsb_projection_fwd(
-            C, N, ptr(means), ptr(covars), ptr(quats), ptr(scales), ptr(viewmats), ptr(Ks), width, height,
-            eps2d, near_plane, far_plane, radius_clip, model, ptr(radii), ptr(means2d), ptr(depths),
-            ptr(conics), ptr(compensations), stream_of(means),
-        )
+        ex = _PUSH_CONTEXT[0]
+        if ex is not None:
+            world, C_local, N_total, n_base, peers, region = ex.push_args()
+            assert C == world * C_local and N == ex.N_local, (C, N, world, C_local, ex.N_local)
+            lib.gsb_projection_fwd_push(
+                C, N, ptr(means), ptr(covars), ptr(quats), ptr(scales), ptr(viewmats), ptr(Ks), width, height,
+                eps2d, near_plane, far_plane, radius_clip, model, ptr(radii), ptr(means2d), ptr(depths),
+                ptr(conics), ptr(compensations), ptr(ex.opacities), world, C_local, N_total, n_base, ex.D, peers,
+                region, stream_of(means),
+            )
+            ex.pushed.add("geometry")
+        else:
+            lib.gsb_projection_fwd(
+                C, N, ptr(means), ptr(covars), ptr(quats), ptr(scales), ptr(viewmats), ptr(Ks), width, height,
+                eps2d, near_plane, far_plane, radius_clip, model, ptr(radii), ptr(means2d), ptr(depths),
+                ptr(conics), ptr(compensations), stream_of(means),
+            )
         ctx.save_for_backward(means, covars, quats, scales, viewmats, Ks, radii, conics, compensations)
         ctx.width, ctx.height, ctx.eps2d, ctx.model = width, height, eps2d, model
         ctx.mark_non_differentiable(radii)
@@ -354,7 +375,15 @@ class _ViewColors(torch.autograd.Function):
         campos = torch.empty((C, 3), dtype=torch.float32, device=means.device)
         lib.gsb_camera_centers(C, ptr(viewmats), ptr(campos), st)
         colors = torch.empty((C, N, 3), dtype=torch.float32, device=means.device)
-        lib.gsb_sh_colors_fwd(sh_degree, N, C, K, ptr(means), ptr(campos), ptr(coeffs), ptr(radii), ptr(colors), st)
+        ex = _PUSH_CONTEXT[0]
+        if ex is not None:
+            world, C_local, N_total, n_base, peers, region = ex.push_args()
+            assert C == world * C_local and N == ex.N_local and ex.D == 3
+            lib.gsb_sh_colors_fwd_push(sh_degree, N, C, K, ptr(means), ptr(campos), ptr(coeffs), ptr(radii),
+                                       ptr(colors), world, C_local, N_total, n_base, peers, region, st)
+            ex.pushed.add("colors")
+        else:
+            lib.gsb_sh_colors_fwd(sh_degree, N, C, K, ptr(means), ptr(campos), ptr(coeffs), ptr(radii), ptr(colors), st)
         ctx.save_for_backward(means, campos, coeffs, radii)
         ctx.sh_degree = sh_degree
         return colors

@@ -772,6 +772,52 @@ class _SplitFinish(torch.autograd.Function):
         return view(0, 2), (view(1, 1) if has_depth else None), view(2, 3), view(3, 1), view(4, D), None, None
 
 
+class PushExchange(SplitExchange):
+    """The unpacked peer exchange without a put kernel in the forward direction: `fully_fused_projection` and the SH
+    colour kernel store every row they produce ALSO into the mailbox of the rank that owns its camera
+    (`gsb_projection_fwd_push`, `gsb_sh_colors_fwd_push`: NVLink peer stores from the producing kernels), a one-warp
+    kernel raises the epoch flags, and `finish()` waits + copies out as before. The backward exchange is the usual
+    put + wait. `rasterization()` installs the object as the wrappers' push context around the two producer calls."""
+
+    def __init__(self, C_local: int, N_world: Sequence[int], D: int, opacities: Tensor):
+        super().__init__(C_local, N_world, D)
+        self.opacities = opacities.detach().float().contiguous()
+        self.pushed = set()
+
+    def push_args(self):
+        """(world, C_local, N_total, n_base, peer table, region offset) for the *_push entry points."""
+        box = self.box
+        return box.world, self.C_local, self.N_total, self.bases[box.rank], box.peer_array, self.region
+
+    def finish(self, means2d, depths, conics, opacities, colors, radii):
+        from .b200_impl._lib import lib, stream_of
+
+        assert self.pushed == {"geometry", "colors"}, f"push exchange: producers did not push ({self.pushed})"
+        box = self.box
+        lib.gsb_a2a_publish(box.world, box.rank, 0, self.epochs[0], box.peer_array, stream_of(means2d))
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(box.device))
+        self.done[0] = ev
+        return _PushFinish.apply(means2d, depths, conics, opacities, colors, radii, self)
+
+
+class _PushFinish(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means2d, depths, conics, opacities, colors, radii, ex):
+        o = ex.off_fwd
+        ex._wait_fwd(0, ((o[0], o[6]), (0, 0)))
+        C_l, N_t, out, rows, D = ex.C_local, ex.N_total, ex.out, ex.rows_fwd, ex.D
+        outs = (out[o[0]:o[0] + 2 * rows].view(C_l, N_t, 2), out[o[1]:o[1] + rows].view(C_l, N_t),
+                out[o[2]:o[2] + 3 * rows].view(C_l, N_t, 3), out[o[3]:o[3] + rows].view(C_l, N_t),
+                out[o[4]:o[4] + D * rows].view(C_l, N_t, D),
+                out[o[5]:o[5] + rows].view(torch.int32).view(C_l, N_t))
+        ctx.ex = ex
+        ctx.mark_non_differentiable(outs[5])
+        return outs
+
+    backward = _SplitFinish.backward
+
+
 def peer_exchange_rows(means2d, depths, conics, opacities, colors, radii, C_local: int, N_world: Sequence[int]):
     """Fused exchange of the projected rows (unpacked mode): see `_PeerExchangeRows`."""
     return _PeerExchangeRows.apply(means2d, depths, conics, opacities, colors, radii, int(C_local),

@@ -54,6 +54,7 @@ from .distributed import (
     host_trace,
     pack_rows,
     peer_exchange_available,
+    PushExchange,
     SplitExchange,
     peer_exchange_packed,
     peer_exchange_rows,
@@ -157,12 +158,28 @@ def rasterization(
         C = len(viewmats)  # global camera count from here on
         host_trace.mark("us_cameras")
 
-    proj_results = fully_fused_projection(
-        means, covars, quats, scales, viewmats, Ks, width, height,
-        eps2d=eps2d, packed=packed, near_plane=near_plane, far_plane=far_plane, radius_clip=radius_clip,
-        sparse_grad=sparse_grad, calc_compensations=(rasterize_mode == "antialiased"),
-        camera_model=camera_model,
-    )
+    # b200, one node, unpacked rows, fused SH colours, GSPLAT_B200_EXCHANGE_PUSH=1: no put kernel, the projection and
+    # the colour kernel store their rows straight into the camera owners' mailboxes. Off by default: measured no
+    # faster than the put kernel (the producers then wait for the same NVLink stores).
+    push = None
+    if (distributed and not packed and BACKEND == "b200" and sh_degree is not None and colors.dim() == 3
+            and not viewmats.requires_grad and peer_exchange_available()
+            and os.environ.get("GSPLAT_B200_EXCHANGE_PUSH", "0") == "1"):
+        from .b200_impl._wrapper import set_push_context
+
+        push = PushExchange(C_world[world_rank], N_world, 3, opacities)
+        set_push_context(push)
+    try:
+        proj_results = fully_fused_projection(
+            means, covars, quats, scales, viewmats, Ks, width, height,
+            eps2d=eps2d, packed=packed, near_plane=near_plane, far_plane=far_plane, radius_clip=radius_clip,
+            sparse_grad=sparse_grad, calc_compensations=(rasterize_mode == "antialiased"),
+            camera_model=camera_model,
+        )
+    except Exception:
+        if push is not None:
+            set_push_context(None)
+        raise
     if packed:
         camera_ids, gaussian_ids, radii, means2d, depths, conics, compensations = proj_results
         opacities = _rows_of(opacities, gaussian_ids)  # [nnz]
@@ -189,7 +206,7 @@ def rasterization(
     # the extra launches and stream hand-overs cost more than the overlap returns (cfg2 sharded over 8 ranks: 1.958 ms
     # against 1.921 ms per step).
     split = None
-    if (distributed and not packed and BACKEND == "b200" and peer_exchange_available()
+    if (push is None and distributed and not packed and BACKEND == "b200" and peer_exchange_available()
             and os.environ.get("GSPLAT_B200_EXCHANGE_SPLIT", "0") == "1"):
         D_out = 3 if sh_degree is not None else colors.shape[-1]
         split = SplitExchange(C_world[world_rank], N_world, D_out)
@@ -206,7 +223,11 @@ def rasterization(
             # dirs, the radii > 0 mask, + 0.5 and the clamp folded into the SH kernels (one pass over [C, N])
             from .b200_impl._wrapper import view_dependent_colors
 
-            colors = view_dependent_colors(sh_degree, means, viewmats, colors, radii)  # [C, N, 3]
+            try:
+                colors = view_dependent_colors(sh_degree, means, viewmats, colors, radii)  # [C, N, 3]
+            finally:
+                if push is not None:
+                    set_push_context(None)
         elif BACKEND == "b200" and packed and colors.dim() == 3 and not viewmats.requires_grad:
             # same kernels over the dense [C, N] grid (mask scattered from the packed ids); only colours are gathered
             from .b200_impl._wrapper import view_dependent_colors_packed
@@ -258,6 +279,10 @@ def rasterization(
             ids = all_to_all_rows(ids, cnts, recv)
             camera_ids, gaussian_ids = ids[:, 0].contiguous(), ids[:, 1].contiguous()
             C = C_world[world_rank]
+        elif push is not None:
+            C = C_world[world_rank]
+            means2d, depths, conics, opacities, colors, radii = push.finish(means2d, depths, conics, opacities, colors,
+                                                                            radii)
         elif split is not None:
             C = C_world[world_rank]
             split.start_colors(colors)

@@ -368,6 +368,23 @@ int gsb_a2a_wait_copy_part(int world, int channel, int64_t epoch, const void *lo
                            int64_t begin0, int64_t end0, int64_t begin1, int64_t end1, float *out,
                            int *timeout_flag, cudaStream_t stream);
 int64_t gsb_a2a_field_offset(int64_t rows, int D, int field);
+/* Push exchange (unpacked rows): instead of a separate put kernel, gsb_projection_fwd_push / gsb_sh_colors_fwd_push
+ * store every row ALSO into the mailbox region of the rank that owns its camera (same layout and positions as
+ * gsb_a2a_put_fwd would; opacities[N] x compensation goes into the opacity field), and gsb_a2a_publish, queued
+ * after them on the same stream, raises this rank's epoch flag at every peer. The receiver waits with
+ * gsb_a2a_wait_copy as before. */
+int gsb_projection_fwd_push(int C, int N, const float *means, const float *covars, const float *quats,
+                            const float *scales, const float *viewmats, const float *Ks, int width, int height,
+                            float eps2d, float near_plane, float far_plane, float radius_clip, int camera_model,
+                            int32_t *radii, float *means2d, float *depths, float *conics, float *compensations,
+                            const float *opacities, int world, int C_local, int64_t N_total, int64_t n_base, int D,
+                            const void *const *peer_bases_host, int64_t region_offset, cudaStream_t stream);
+int gsb_sh_colors_fwd_push(int degree, int64_t N, int C, int K, const float *means, const float *campos,
+                           const float *coeffs, const int32_t *radii, float *colors, int world, int C_local,
+                           int64_t N_total, int64_t n_base, const void *const *peer_bases_host, int64_t region_offset,
+                           cudaStream_t stream);
+int gsb_a2a_publish(int world, int rank, int channel, int64_t epoch, const void *const *peer_bases_host,
+                    cudaStream_t stream);
 /* Packed (COO) rows over the same mailboxes (reference rendering.py:413-451: bincount + all_to_all of counts,
  * all_to_all of the rows, a second one for the rebased ids). The sender's packed rows are camera-major, so the rows
  * for destination d are the run after those for d-1: send_counts_host[d] rows go to rows

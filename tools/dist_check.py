@@ -82,11 +82,12 @@ def main():
             truth = dict(rc=rc[my_cams].detach(), ra=ra[my_cams].detach(),
                          grads=[p.grad[lo:hi].clone() for p in full])
             del full, rc, ra
-            for transport in ("peer", "peer_split", "nccl"):
-                if transport == "peer_split" and packed:
-                    continue  # packed rows have a single (unsplit) peer path
+            for transport in ("peer", "peer_push", "peer_split", "nccl"):
+                if transport in ("peer_split", "peer_push") and packed:
+                    continue  # packed rows have a single peer path (one fused put per direction)
                 os.environ["GSPLAT_B200_EXCHANGE"] = "nccl" if transport == "nccl" else "peer"
                 os.environ["GSPLAT_B200_EXCHANGE_SPLIT"] = "1" if transport == "peer_split" else "0"
+                os.environ["GSPLAT_B200_EXCHANGE_PUSH"] = "1" if transport == "peer_push" else "0"
                 for step in range(3):
                     shard = [p[lo:hi].to(dev).requires_grad_(True) for p in params]
                     args = (viewmats[my_cams].to(dev), Ks[my_cams].to(dev), W, H)
@@ -117,7 +118,7 @@ def main():
         print("DIST_CHECK " + json.dumps({
             "world": world, "cases_per_rank": n_cases, "ok": flag.item() == 0, "img_max_err": w[0].item(),
             "alpha_max_err": w[1].item(), "grad_max_rel": w[2].item(),
-            "covers": "packed x {RGB classic, RGB+ED antialiased} x {peer, peer with split forward exchange, nccl} x {even, uneven shards} x 3 steps "
+            "covers": "packed x {RGB classic, RGB+ED antialiased} x {peer put, peer push from the producer kernels, peer with split forward exchange, nccl} x {even, uneven shards} x 3 steps "
                       "(forward-only steps in between), vs a single-GPU render of the whole scene"}), flush=True)
     dist.barrier()
     close_mailboxes()
