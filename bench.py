@@ -225,6 +225,7 @@ def _stage_table(summary, steps, meta, n_local, C, D, K, work, peaks, sm_mhz):
     I = meta["flatten_ids"].numel()
     n_tiles = meta["tile_width"] * meta["tile_height"]
     bits = 32 + (n_tiles - 1).bit_length() + max(C - 1, 0).bit_length()
+    binned = "gsb_isect_bin" in summary  # tile binning instead of the two radix passes over the intersections
     hbm = {
         "gsb_projection_fwd": 40 * n_local + 28 * P,
         "gsb_projection_bwd": 80 * n_local + 40 * P,
@@ -238,7 +239,12 @@ def _stage_table(summary, steps, meta, n_local, C, D, K, work, peaks, sm_mhz):
         "gsb_isect_count_perm": 4 * P + 4 * P,
         "gsb_isect_emit_perm": 20 * P + 8 * I,
         "gsb_isect_emit_perm_cap": 20 * P + 8 * I,  # perm 4 + one 16-byte record per row, 8 per intersection out
-        "gsb_radix_sort_pairs_u32": 4 * 16 * P + 4 * P + math.ceil((bits - 32) / 8) * 16 * I + 4 * I,
+        "gsb_radix_sort_pairs_u32": 4 * 16 * P + 4 * P + (0 if binned else math.ceil((bits - 32) / 8) * 16 * I + 4 * I),
+        "gsb_isect_row_tiles_keys": 16 * P + 28 * P,
+        "gsb_isect_count_perm_records": 20 * P + 16 * P,
+        # the rows' records twice (count, scatter) + perm / depth bits once, 12 bytes per intersection out, offsets;
+        # the chunks x bins count matrix the kernels pass between them is overhead, not counted
+        "gsb_isect_bin": 2 * 16 * P + 8 * P + 12 * I + 4 * C * n_tiles,
         "gsb_isect_finalize_cap": 8 * I + 4 * I + 8 * I + 4 * C * n_tiles,
         "gsb_a2a_put_fwd": 2 * (8 + D) * 4 * P,
         "gsb_a2a_put_bwd": 2 * (7 + D) * 4 * P,

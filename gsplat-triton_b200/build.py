@@ -14,7 +14,7 @@ OUT_DIR = os.path.join(HERE, "lib")
 OBJ_DIR = os.path.join(HERE, "build")
 LIB = os.path.join(OUT_DIR, "libgsplat_b200.so")
 
-SOURCES = ["error.cu", "projection.cu", "sh.cu", "isect.cu", "rasterize_fwd.cu", "rasterize_fwd2.cu", "rasterize_bwd.cu", "rasterize_bwd2.cu", "rasterize_generic.cu", "exchange.cu", "peer.cu", "radix_sort.cu", "indices.cu", "adam.cu"]
+SOURCES = ["error.cu", "projection.cu", "sh.cu", "isect.cu", "isect_bin.cu", "rasterize_fwd.cu", "rasterize_fwd2.cu", "rasterize_bwd.cu", "rasterize_bwd2.cu", "rasterize_generic.cu", "exchange.cu", "peer.cu", "radix_sort.cu", "indices.cu", "adam.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

@@ -196,7 +196,8 @@ template <bool PACKED>
 __global__ void __launch_bounds__(kThreads)
 row_tiles_kernel(int64_t P, int N, const float *__restrict__ means2d, const int32_t *__restrict__ radii,
                  const int64_t *__restrict__ camera_ids, int tile_size, int tw, int th, int tile_n_bits,
-                 int32_t *__restrict__ rows, int32_t *__restrict__ tiles_per_gauss, int4 *__restrict__ records) {
+                 int32_t *__restrict__ rows, int32_t *__restrict__ tiles_per_gauss, int4 *__restrict__ records,
+                 const float *__restrict__ depths, uint32_t *__restrict__ row_keys) {
     int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
     if (i >= P) return;
     int cnt = 0;
@@ -212,6 +213,35 @@ row_tiles_kernel(int64_t P, int N, const float *__restrict__ means2d, const int3
     rows[i] = (int32_t)i;
     tiles_per_gauss[i] = cnt;
     if (records != nullptr) records[i] = rec;
+    // the depth-sort key of the row: its depth bits, or all ones for a row without tiles, so that the rows that emit
+    // intersections form one contiguous run of the sorted order (the binning kernels of isect_bin.cu rely on it)
+    if (row_keys != nullptr) row_keys[i] = cnt > 0 ? (uint32_t)__float_as_int(depths[i]) : 0xffffffffu;
+}
+
+// k-th thread handles row perm[k]: gathers its 16-byte record into depth order (the binning kernels then read the
+// records coalesced) + block sums of the tile counts in that order
+__global__ void __launch_bounds__(kThreads)
+count_perm_records_kernel(int64_t P, const int32_t *__restrict__ perm, const int4 *__restrict__ records,
+                          int4 *__restrict__ sorted_records, int32_t *__restrict__ block_sums) {
+    __shared__ int s_warp[kThreads / 32];
+    int64_t k = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    int cnt = 0;
+    if (k < P) {
+        const int4 rec = __ldg(records + perm[k]);
+        sorted_records[k] = rec;
+        cnt = rec.w;
+    }
+    int sum = cnt;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; ++w) t += s_warp[w];
+        block_sums[blockIdx.x] = t;
+    }
 }
 
 // k-th thread handles row perm[k]: tile count (also stored in natural order) + block sums in permuted order
@@ -464,6 +494,15 @@ extern "C" int gsb_isect_row_tiles(int64_t P, int N, int packed, const float *me
                                    const int64_t *camera_ids, int tile_size, int tile_width, int tile_height,
                                    int tile_n_bits, int32_t *rows, int32_t *tiles_per_gauss, int32_t *row_records,
                                    cudaStream_t stream) {
+    return gsb_isect_row_tiles_keys(P, N, packed, means2d, radii, nullptr, camera_ids, tile_size, tile_width,
+                                    tile_height, tile_n_bits, rows, tiles_per_gauss, row_records, nullptr, stream);
+}
+
+extern "C" int gsb_isect_row_tiles_keys(int64_t P, int N, int packed, const float *means2d, const int32_t *radii,
+                                        const float *depths, const int64_t *camera_ids, int tile_size, int tile_width,
+                                        int tile_height, int tile_n_bits, int32_t *rows, int32_t *tiles_per_gauss,
+                                        int32_t *row_records, int32_t *row_keys, cudaStream_t stream) {
+    GSB_REQUIRE(row_keys == nullptr || depths != nullptr, "depths required for row_keys");
     GSB_REQUIRE(P >= 0 && tile_size > 0 && tile_width >= 0 && tile_height >= 0, "bad sizes");
     GSB_REQUIRE(P < ((int64_t)1 << 31), "more than 2^31-1 rows");
     GSB_REQUIRE(!packed || camera_ids != nullptr || P == 0 || row_records == nullptr, "camera_ids required when packed");
@@ -474,11 +513,27 @@ extern "C" int gsb_isect_row_tiles(int64_t P, int N, int packed, const float *me
     auto recs = reinterpret_cast<int4 *>(row_records);
     if (packed)
         row_tiles_kernel<true><<<nblk, kThreads, 0, stream>>>(P, N, means2d, radii, camera_ids, tile_size, tile_width,
-                                                              tile_height, tile_n_bits, rows, tiles_per_gauss, recs);
+                                                              tile_height, tile_n_bits, rows, tiles_per_gauss, recs,
+                                                              depths, reinterpret_cast<uint32_t *>(row_keys));
     else
         row_tiles_kernel<false><<<nblk, kThreads, 0, stream>>>(P, N, means2d, radii, camera_ids, tile_size, tile_width,
-                                                               tile_height, tile_n_bits, rows, tiles_per_gauss, recs);
+                                                               tile_height, tile_n_bits, rows, tiles_per_gauss, recs,
+                                                               depths, reinterpret_cast<uint32_t *>(row_keys));
     return gsb_check_launch("isect_row_tiles");
+}
+
+extern "C" int gsb_isect_count_perm_records(int64_t P, const int32_t *perm, const int32_t *row_records,
+                                            int32_t *sorted_records, int32_t *block_sums, int64_t *block_offsets,
+                                            int64_t *n_isects_out, cudaStream_t stream) {
+    GSB_REQUIRE(P >= 0, "negative size");
+    int64_t nblk = gsb_isect_num_blocks(P);
+    if (P > 0) {
+        count_perm_records_kernel<<<(unsigned)nblk, kThreads, 0, stream>>>(
+            P, perm, reinterpret_cast<const int4 *>(row_records), reinterpret_cast<int4 *>(sorted_records), block_sums);
+        if (int e = gsb_check_launch("isect_count_perm_records")) return e;
+    }
+    scan_block_sums_kernel<<<1, 1024, 0, stream>>>(nblk, block_sums, block_offsets, n_isects_out);
+    return gsb_check_launch("scan_block_sums");
 }
 
 extern "C" int gsb_isect_count_perm(int64_t P, const int32_t *perm, const float *means2d, const int32_t *radii,

@@ -1,0 +1,406 @@
+// Tile binning of depth-ordered rows: the second half of isect_tiles + isect_offset_encode without a global sort.
+//
+// Replaces (behaviour, not code): the key emit + radix sort + offset encode of gsplat/triton_impl/isect_tiles.py:14-133,
+// isect_offset.py:9-63 and gsplat/cuda/csrc/IntersectTile.cu:24-344 — same isect_ids / flatten_ids / offsets, bit for bit.
+//
+// Input: the rows (projected Gaussians) already sorted by depth (radix_sort.cu over P rows), their 16-byte tile
+// rectangles gathered into that order, and the exclusive scan of their tile counts per 256 rows. The intersections in
+// "emission order" (row after row in depth order, a row's tiles in row-major order) then only need a STABLE partition
+// by (camera | tile): what the reference's 64-bit sort produces. Instead of two more radix passes over all
+// intersections (emit 8 B + 2 x (read 8 B + write 8 B) + finalize) this file does a counting sort with one bin per tile:
+//
+//   bin_count_kernel    chunk c = intersections [c*8192, (c+1)*8192) of the emission order: per-bin counts -> M[c][bin]
+//   bin_scan_*          exclusive scan of M down the chunks (two levels) and of the bin totals: `offsets` falls out
+//   bin_scatter_kernel  the chunk again: expand into shared memory, stable 2-pass radix sort by bin INSIDE shared memory,
+//                       then every intersection goes to offsets[bin] + (intersections of that bin in earlier chunks) +
+//                       (its rank inside the chunk): written once, at its final place, as the 64-bit key + the row id.
+//
+// No kernel waits on another (no look-back chain), nothing is written twice. The price is the dense chunks x bins count
+// matrix, so the path is taken for C * tiles <= 8192 bins (cfg1, cfg2, cfg4); larger grids keep the radix path.
+#include "common.cuh"
+
+#include <cstdint>
+
+namespace {
+
+constexpr int kT = 8192;        // intersections per chunk
+constexpr int kThreads = 512;   // CTA of the chunk kernels
+constexpr int kWarps = kThreads / 32;
+constexpr int kItems = kT / kThreads;
+constexpr int kRowBlock = 256;  // rows per block_offsets entry (isect.cu)
+constexpr int kMaxBins = kT;    // the per-bin table of the scatter kernel aliases a sort buffer
+constexpr int kGroups = 32;     // second level of the scan down the chunks
+
+__device__ __forceinline__ int64_t clamp_count(int64_t capacity, const int64_t *n_dev) {
+    if (n_dev == nullptr) return capacity;
+    const int64_t n = *n_dev;
+    return n < capacity ? (n < 0 ? 0 : n) : capacity;
+}
+
+struct ExpandSmem {
+    int start[kThreads + 1];  // first slot of each row of the current 512-row batch, relative to the batch
+    int xy[kThreads];         // x0 | y0 << 16
+    int w[kThreads];          // rectangle width
+    int bin0[kThreads];       // camera * n_tiles
+    int warp[kWarps];
+    int b0;                   // first 256-row block overlapping the chunk
+};
+
+// Walks the chunk's slots [a, b_end) of the emission order and calls f(slot - a, bin, row index relative to row 256*b0).
+// Block-cooperative: 512 rows describe their rectangles in shared memory, then the threads take the slots one by one
+// (binary search for the owning row), so the cost does not depend on how the tiles spread over the rows.
+template <typename F>
+__device__ __forceinline__ void expand_chunk(int64_t a, int64_t b_end, int64_t P, const int4 *__restrict__ srec,
+                                             const int64_t *__restrict__ block_offsets, int64_t nblk, int tw,
+                                             int n_tiles, int tile_n_bits, ExpandSmem &s, F f) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) {
+        int64_t lo = 0, hi = nblk;  // last block with block_offsets[lo] <= a (block_offsets[0] = 0 <= a)
+        while (hi - lo > 1) {
+            const int64_t mid = (lo + hi) >> 1;
+            if (block_offsets[mid] <= a) lo = mid; else hi = mid;
+        }
+        s.b0 = (int)lo;
+    }
+    __syncthreads();
+    const int64_t b0 = s.b0;
+    for (int it = 0;; ++it) {
+        const int64_t blk = b0 + 2 * (int64_t)it;
+        if (blk >= nblk) break;
+        const int64_t base = block_offsets[blk];
+        if (base >= b_end) break;
+        const int64_t k = blk * kRowBlock + tid;
+        int4 rec = make_int4(0, 0, 0, 0);
+        if (k < P) rec = srec[k];
+        int inc = rec.w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s.warp[warp] = inc;
+        s.xy[tid] = rec.x;
+        s.w[tid] = rec.y;
+        s.bin0[tid] = (int)((uint32_t)rec.z >> tile_n_bits) * n_tiles;
+        __syncthreads();
+        int wbase = 0, total = 0;
+#pragma unroll
+        for (int wi = 0; wi < kWarps; ++wi) {
+            const int v = s.warp[wi];
+            wbase += (wi < warp) ? v : 0;
+            total += v;
+        }
+        s.start[tid] = wbase + inc - rec.w;
+        if (tid == 0) s.start[kThreads] = total;
+        __syncthreads();
+        const int64_t lo_j = a > base ? a : base;
+        const int64_t hi_j = b_end < base + total ? b_end : base + total;
+        for (int64_t j = lo_j + tid; j < hi_j; j += kThreads) {
+            const int local = (int)(j - base);
+            int lo = 0, hi = kThreads;  // invariant: start[lo] <= local < start[hi]
+#pragma unroll
+            for (int step = 0; step < 9; ++step) {
+                const int mid = (lo + hi) >> 1;
+                if (s.start[mid] <= local) lo = mid; else hi = mid;
+            }
+            const int t = local - s.start[lo];
+            const int w = s.w[lo], xy = s.xy[lo];
+            const int dy = t / w, dx = t - dy * w;
+            const int tile = ((xy >> 16) + dy) * tw + (xy & 0xffff) + dx;
+            f((int)(j - a), s.bin0[lo] + tile, (int)(blk - b0) * kRowBlock + lo);
+        }
+        __syncthreads();  // the batch tables are rewritten by the next round
+    }
+}
+
+// ---------------------------------------------------------------- counts per (chunk, bin)
+__global__ void __launch_bounds__(kThreads)
+bin_count_kernel(int64_t capacity, const int64_t *__restrict__ n_dev, int64_t P, const int4 *__restrict__ srec,
+                 const int64_t *__restrict__ block_offsets, int64_t nblk, int tw, int n_tiles, int tile_n_bits,
+                 int bins, uint32_t *__restrict__ M) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t *hist = reinterpret_cast<uint32_t *>(smem_raw);
+    __shared__ ExpandSmem s;
+    const int64_t n = clamp_count(capacity, n_dev);
+    const int64_t a = (int64_t)blockIdx.x * kT;
+    for (int i = threadIdx.x; i < bins; i += kThreads) hist[i] = 0u;
+    __syncthreads();
+    if (a < n) {
+        const int64_t b_end = a + kT < n ? a + kT : n;
+        expand_chunk(a, b_end, P, srec, block_offsets, nblk, tw, n_tiles, tile_n_bits, s,
+                     [&](int, int bin, int) { atomicAdd(&hist[bin], 1u); });
+    }
+    __syncthreads();
+    uint32_t *row = M + (int64_t)blockIdx.x * bins;
+    for (int i = threadIdx.x; i < bins; i += kThreads) row[i] = hist[i];
+}
+
+// exclusive scan of M down the chunks of one group (in place) + the group's total per bin
+__global__ void __launch_bounds__(256)
+bin_scan_chunks_kernel(int chunks, int per_group, int bins, uint32_t *__restrict__ M, uint32_t *__restrict__ G) {
+    const int bin = blockIdx.x * 256 + threadIdx.x;
+    if (bin >= bins) return;
+    const int g = blockIdx.y;
+    const int c0 = g * per_group, c1 = min(chunks, c0 + per_group);
+    uint32_t run = 0u;
+    int c = c0;
+    for (; c + 4 <= c1; c += 4) {
+        uint32_t v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = M[(int64_t)(c + u) * bins + bin];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            M[(int64_t)(c + u) * bins + bin] = run;
+            run += v[u];
+        }
+    }
+    for (; c < c1; ++c) {
+        const uint32_t v = M[(int64_t)c * bins + bin];
+        M[(int64_t)c * bins + bin] = run;
+        run += v;
+    }
+    G[(int64_t)g * bins + bin] = run;
+}
+
+// exclusive scan over the groups (in place) + the bin's total
+__global__ void __launch_bounds__(256)
+bin_scan_groups_kernel(int bins, uint32_t *__restrict__ G, uint32_t *__restrict__ totals) {
+    const int bin = blockIdx.x * 256 + threadIdx.x;
+    if (bin >= bins) return;
+    uint32_t v[kGroups];
+#pragma unroll
+    for (int g = 0; g < kGroups; ++g) v[g] = G[(int64_t)g * bins + bin];
+    uint32_t run = 0u;
+#pragma unroll
+    for (int g = 0; g < kGroups; ++g) {
+        G[(int64_t)g * bins + bin] = run;
+        run += v[g];
+    }
+    totals[bin] = run;
+}
+
+// exclusive scan of the bin totals = isect_offsets (one CTA; bins <= 8192)
+__global__ void __launch_bounds__(1024)
+bin_offsets_kernel(int bins, const uint32_t *__restrict__ totals, int32_t *__restrict__ offsets) {
+    __shared__ uint32_t s_warp[32];
+    constexpr int kPer = kMaxBins / 1024;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint32_t v[kPer], sum = 0u;
+#pragma unroll
+    for (int u = 0; u < kPer; ++u) {
+        const int i = tid * kPer + u;
+        v[u] = i < bins ? totals[i] : 0u;
+        sum += v[u];
+    }
+    uint32_t inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t run = inc - sum;
+    for (int wi = 0; wi < warp; ++wi) run += s_warp[wi];
+#pragma unroll
+    for (int u = 0; u < kPer; ++u) {
+        const int i = tid * kPer + u;
+        if (i < bins) offsets[i] = (int32_t)run;
+        run += v[u];
+    }
+}
+
+// ---------------------------------------------------------------- chunk sort + scatter to the final place
+// One stable radix pass over the chunk inside shared memory (structure of radix_sort.cu's tile: warp w ranks its
+// 512 consecutive items with one ballot per digit bit, per-warp digit counters, digit threads turn the counters into
+// first slots).
+__device__ __forceinline__ void smem_radix_pass(const uint32_t *__restrict__ src, uint32_t *__restrict__ dst, int count,
+                                                int shift, int bits, uint32_t (*s_cnt)[256], uint32_t *s_scan) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nd = 1 << bits, mask = nd - 1;
+    for (int i = tid; i < kWarps * 256; i += kThreads) (&s_cnt[0][0])[i] = 0u;
+    __syncthreads();
+    uint32_t rank[kItems];  // the only per-item state kept across the barriers (keys are re-read from src)
+    const int chunk = warp * 32 * kItems;
+    const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int i = 0; i < kItems; ++i) {
+        const int pos = chunk + i * 32 + lane;
+        const bool live = pos < count;
+        const int digit = live ? (int)(src[pos] >> shift) & mask : 0;
+        uint32_t p = __ballot_sync(0xffffffffu, live);
+        if (!live) p = ~p;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+            if (b < bits) {  // warp-uniform
+                const bool one = (digit >> b) & 1;
+                const uint32_t with_one = __ballot_sync(0xffffffffu, one);
+                p &= one ? with_one : ~with_one;
+            }
+        }
+        // one warp's shared-memory atomics execute in program order: round i's counter already holds rounds < i
+        const int leader = __ffs(p) - 1;
+        uint32_t r = 0u;
+        if (live && lane == leader) r = atomicAdd(&s_cnt[warp][digit], (uint32_t)__popc(p));
+        rank[i] = __shfl_sync(0xffffffffu, r, leader) + __popc(p & lt);
+    }
+    __syncthreads();
+    // digit threads: total of digit d, exclusive scan over the digits, first slot of every (warp, digit)
+    uint32_t total = 0u, inc = 0u;
+    if (tid < 256) {
+        if (tid < nd) {
+#pragma unroll
+            for (int wi = 0; wi < kWarps; ++wi) total += s_cnt[wi][tid];
+        }
+        inc = total;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += up;
+        }
+        if (lane == 31) s_scan[warp] = inc;
+    }
+    __syncthreads();
+    if (tid < nd) {
+        uint32_t run = inc - total;
+        for (int wi = 0; wi < warp; ++wi) run += s_scan[wi];
+#pragma unroll
+        for (int wi = 0; wi < kWarps; ++wi) {
+            const uint32_t c = s_cnt[wi][tid];
+            s_cnt[wi][tid] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < kItems; ++i) {
+        const int pos = chunk + i * 32 + lane;
+        if (pos < count) {
+            const uint32_t key = src[pos];
+            dst[s_cnt[warp][(int)(key >> shift) & mask] + rank[i]] = key;
+        }
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(kThreads, 2)
+bin_scatter_kernel(int64_t capacity, const int64_t *__restrict__ n_dev, int64_t P, const int4 *__restrict__ srec,
+                   const int64_t *__restrict__ block_offsets, int64_t nblk, const int32_t *__restrict__ perm,
+                   const uint32_t *__restrict__ sorted_keys, int tw, int n_tiles, int tile_n_bits, int bins,
+                   int bin_bits, int per_group, const uint32_t *__restrict__ M, const uint32_t *__restrict__ G,
+                   const int32_t *__restrict__ offsets, int64_t *__restrict__ isect_ids,
+                   int32_t *__restrict__ flatten_ids) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t *buf0 = reinterpret_cast<uint32_t *>(smem_raw);  // item = bin << 16 | row index relative to row 256*b0
+    uint32_t *buf1 = buf0 + kT;
+    uint32_t(*s_cnt)[256] = reinterpret_cast<uint32_t(*)[256]>(buf1 + kT);
+    __shared__ ExpandSmem s;
+    __shared__ uint32_t s_scan[kWarps];
+    const int64_t n = clamp_count(capacity, n_dev);
+    const int64_t a = (int64_t)blockIdx.x * kT;
+    if (a >= n) return;
+    const int64_t b_end = a + kT < n ? a + kT : n;
+    const int count = (int)(b_end - a);
+    expand_chunk(a, b_end, P, srec, block_offsets, nblk, tw, n_tiles, tile_n_bits, s, [&](int slot, int bin, int krel) {
+        if (krel > 0xffff) __trap();  // rows without tiles inside the run of emitting rows: the caller broke the contract
+        buf0[slot] = ((uint32_t)bin << 16) | (uint32_t)krel;
+    });
+    __syncthreads();
+    const int lo_bits = (bin_bits + 1) >> 1, hi_bits = bin_bits - lo_bits;
+    uint32_t *sorted = buf0, *spare = buf1;
+    if (lo_bits > 0) {
+        smem_radix_pass(buf0, buf1, count, 16, lo_bits, s_cnt, s_scan);
+        sorted = buf1;
+        spare = buf0;
+    }
+    if (hi_bits > 0) {
+        smem_radix_pass(sorted, spare, count, 16 + lo_bits, hi_bits, s_cnt, s_scan);
+        uint32_t *t = sorted; sorted = spare; spare = t;
+    }
+    // first slot of every bin present in the chunk -> (final position - slot) of the bin
+    int32_t *delta = reinterpret_cast<int32_t *>(spare);
+    const int chunk = blockIdx.x, g = chunk / per_group;
+    for (int i = threadIdx.x; i < count; i += kThreads) {
+        const int bin = (int)(sorted[i] >> 16);
+        if (i == 0 || (int)(sorted[i - 1] >> 16) != bin)
+            delta[bin] = offsets[bin] + (int32_t)(G[(int64_t)g * bins + bin] + M[(int64_t)chunk * bins + bin]) - i;
+    }
+    __syncthreads();
+    const int64_t row0 = (int64_t)s.b0 * kRowBlock;
+    for (int i = threadIdx.x; i < count; i += kThreads) {
+        const uint32_t item = sorted[i];
+        const int bin = (int)(item >> 16);
+        const int64_t k = row0 + (item & 0xffffu);
+        const int64_t pos = (int64_t)delta[bin] + i;
+        if (pos < capacity) {
+            const int cam = bin / n_tiles;
+            const uint32_t hi = ((uint32_t)cam << tile_n_bits) | (uint32_t)(bin - cam * n_tiles);
+            isect_ids[pos] = ((int64_t)hi << 32) | (int64_t)sorted_keys[k];
+            flatten_ids[pos] = perm[k];
+        }
+    }
+}
+
+constexpr size_t kScatterSmem = sizeof(uint32_t) * (2 * kT + kWarps * 256);
+
+}  // namespace
+
+extern "C" int gsb_isect_bin_max_bins(void) { return kMaxBins; }
+
+// M [chunks][bins] | G [kGroups][bins] | totals [bins], uint32
+extern "C" int64_t gsb_isect_bin_temp_bytes(int64_t capacity, int bins) {
+    const int64_t chunks = (capacity + kT - 1) / kT;
+    return 4 * ((chunks > 0 ? chunks : 1) + kGroups + 1) * (int64_t)bins;
+}
+
+extern "C" int gsb_isect_bin(int64_t P, int64_t capacity, const int64_t *n_isects_dev, const int32_t *sorted_records,
+                             const int32_t *perm, const int32_t *sorted_keys, const int64_t *block_offsets, int C,
+                             int tile_width, int tile_height, int tile_n_bits, void *temp, int64_t temp_bytes,
+                             int64_t *isect_ids, int32_t *flatten_ids, int32_t *offsets, cudaStream_t stream) {
+    GSB_REQUIRE(P >= 0 && capacity >= 0 && C >= 0, "bad sizes");
+    GSB_REQUIRE(P < ((int64_t)1 << 31) && capacity < ((int64_t)1 << 31), "more than 2^31-1 rows or intersections");
+    const int64_t n_tiles = (int64_t)tile_width * tile_height;
+    const int64_t bins64 = n_tiles * C;
+    GSB_REQUIRE(bins64 <= kMaxBins, "too many (camera, tile) bins for the binning path: use the radix path");
+    if (bins64 == 0) return GSB_OK;
+    const int bins = (int)bins64;
+    if (capacity == 0 || P == 0) {
+        cudaError_t e = cudaMemsetAsync(offsets, 0, sizeof(int32_t) * bins, stream);
+        if (e != cudaSuccess) { gsb_set_error("memset offsets: %s", cudaGetErrorString(e)); return GSB_ERR_CUDA; }
+        return GSB_OK;
+    }
+    GSB_REQUIRE(temp != nullptr && temp_bytes >= gsb_isect_bin_temp_bytes(capacity, bins), "temp buffer too small");
+    const int chunks = (int)((capacity + kT - 1) / kT);
+    const int per_group = (chunks + kGroups - 1) / kGroups;
+    const int64_t nblk = (P + kRowBlock - 1) / kRowBlock;
+    int bin_bits = 0;
+    while ((1 << bin_bits) < bins) ++bin_bits;
+    uint32_t *M = reinterpret_cast<uint32_t *>(temp);
+    uint32_t *G = M + (int64_t)chunks * bins;
+    uint32_t *totals = G + (int64_t)kGroups * bins;
+    auto srec = reinterpret_cast<const int4 *>(sorted_records);
+
+    static unsigned long long configured = 0ull;  // per device, like radix_sort.cu
+    int device = 0;
+    cudaGetDevice(&device);
+    if (!((configured >> (device & 63)) & 1ull)) {
+        cudaError_t e = cudaFuncSetAttribute(bin_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)kScatterSmem);
+        if (e != cudaSuccess) { gsb_set_error("isect_bin: shared memory: %s", cudaGetErrorString(e)); return GSB_ERR_CUDA; }
+        configured |= 1ull << (device & 63);
+    }
+    bin_count_kernel<<<chunks, kThreads, sizeof(uint32_t) * bins, stream>>>(
+        capacity, n_isects_dev, P, srec, block_offsets, nblk, tile_width, (int)n_tiles, tile_n_bits, bins, M);
+    if (int rc = gsb_check_launch("isect_bin_count")) return rc;
+    const unsigned bgrid = gsb_cdiv(bins, 256);
+    bin_scan_chunks_kernel<<<dim3(bgrid, kGroups), 256, 0, stream>>>(chunks, per_group, bins, M, G);
+    if (int rc = gsb_check_launch("isect_bin_scan_chunks")) return rc;
+    bin_scan_groups_kernel<<<bgrid, 256, 0, stream>>>(bins, G, totals);
+    if (int rc = gsb_check_launch("isect_bin_scan_groups")) return rc;
+    bin_offsets_kernel<<<1, 1024, 0, stream>>>(bins, totals, offsets);
+    if (int rc = gsb_check_launch("isect_bin_offsets")) return rc;
+    bin_scatter_kernel<<<chunks, kThreads, kScatterSmem, stream>>>(
+        capacity, n_isects_dev, P, srec, block_offsets, nblk, perm, reinterpret_cast<const uint32_t *>(sorted_keys),
+        tile_width, (int)n_tiles, tile_n_bits, bins, bin_bits, per_group, M, G, offsets, isect_ids, flatten_ids);
+    return gsb_check_launch("isect_bin_scatter");
+}

@@ -596,14 +596,26 @@ def _isect_presorted(means2d, radii, depths, camera_ids, C, N, P, packed, tile_s
     # (camera, tile) bucket the intersections stay depth-ordered, ties by ascending row like the reference's sort.
     # tile counts are taken in natural order (coalesced); the depth-ordered passes only gather them
     records = torch.empty((P, 4), dtype=torch.int32, device=dev)
-    lib.gsb_isect_row_tiles(P, N, int(packed), ptr(means2d), ptr(radii), ptr(camera_ids), tile_size, tile_width,
-                            tile_height, tb, ptr(rows), ptr(tiles_per_gauss), ptr(records), st)
-    _, perm = _sort_pairs_u32(depths.reshape(-1).view(torch.int32).clone(), rows, 32)
+    # rows without tiles get an all-ones key: the emitting rows are one contiguous run of the sorted order
+    row_keys = torch.empty((P,), dtype=torch.int32, device=dev)
+    lib.gsb_isect_row_tiles_keys(P, N, int(packed), ptr(means2d), ptr(radii), ptr(depths), ptr(camera_ids), tile_size,
+                                 tile_width, tile_height, tb, ptr(rows), ptr(tiles_per_gauss), ptr(records),
+                                 ptr(row_keys), st)
+    sorted_keys, perm = _sort_pairs_u32(row_keys, rows, 32)
     block_sums = torch.empty((max(nblk, 1),), dtype=torch.int32, device=dev)
     block_offsets = torch.empty((nblk + 1,), dtype=torch.int64, device=dev)
-    lib.gsb_isect_count_perm(P, ptr(perm), None, None, tile_size, tile_width, tile_height,
-                             ptr(tiles_per_gauss), ptr(block_sums), ptr(block_offsets),
-                             block_offsets.data_ptr() + 8 * nblk, st)
+    # GSPLAT_B200_ISECT=bin: tile binning (csrc/isect_bin.cu) when the (camera, tile) bins fit its count matrix;
+    # default: two radix passes over the intersections (measured faster so far: DESIGN.md 4)
+    binned = (C * tile_width * tile_height <= int(lib.gsb_isect_bin_max_bins())
+              and os.environ.get("GSPLAT_B200_ISECT", "radix") == "bin")
+    if binned:
+        sorted_records = torch.empty((P, 4), dtype=torch.int32, device=dev)
+        lib.gsb_isect_count_perm_records(P, ptr(perm), ptr(records), ptr(sorted_records), ptr(block_sums),
+                                         ptr(block_offsets), block_offsets.data_ptr() + 8 * nblk, st)
+    else:
+        lib.gsb_isect_count_perm(P, ptr(perm), None, None, tile_size, tile_width, tile_height,
+                                 ptr(tiles_per_gauss), ptr(block_sums), ptr(block_offsets),
+                                 block_offsets.data_ptr() + 8 * nblk, st)
     key = (dev.index, C, tile_width, tile_height, tile_size, bool(packed))
     estimate = _ISECT_ESTIMATE.get(key) if speculate else None
     pending = None
@@ -617,18 +629,27 @@ def _isect_presorted(means2d, radii, depths, camera_ids, C, N, P, packed, tile_s
         n_dev = block_offsets.data_ptr() + 8 * nblk
     isect_ids = torch.empty((n_isects,), dtype=torch.int64, device=dev)
     offsets = torch.empty((C, tile_height, tile_width), dtype=torch.int32, device=dev)
-    tile_keys = torch.empty((n_isects,), dtype=torch.int32, device=dev)
     flatten_ids = torch.empty((n_isects,), dtype=torch.int32, device=dev)
-    if n_isects > 0:
-        # the hand-written sort takes the device-side count itself; the library sort needs the tail padded with
-        # keys that sort last
-        pad = n_dev if not _own_sort() else None
-        lib.gsb_isect_emit_perm_cap(P, N, int(packed), ptr(perm), ptr(means2d), ptr(radii), ptr(camera_ids),
-                                    tile_size, tile_width, tile_height, tb, ptr(tiles_per_gauss), ptr(block_offsets),
-                                    ptr(tile_keys), ptr(flatten_ids), n_isects, pad, ptr(records), st)
-        tile_keys, flatten_ids = _sort_pairs_u32(tile_keys, flatten_ids, tb + cb, n_dev)
-    lib.gsb_isect_finalize_cap(n_isects, n_dev if n_isects > 0 else None, ptr(tile_keys), ptr(flatten_ids),
-                               ptr(depths), C, tile_width, tile_height, tb, ptr(isect_ids), ptr(offsets), st)
+    if binned:
+        bins = C * tile_width * tile_height
+        temp_bytes = int(lib.gsb_isect_bin_temp_bytes(n_isects, bins))
+        temp = torch.empty((max(temp_bytes, 1),), dtype=torch.uint8, device=dev)
+        lib.gsb_isect_bin(P, n_isects, n_dev if n_isects > 0 else None, ptr(sorted_records), ptr(perm),
+                          ptr(sorted_keys), ptr(block_offsets), C, tile_width, tile_height, tb, ptr(temp), temp_bytes,
+                          ptr(isect_ids), ptr(flatten_ids), ptr(offsets), st)
+    else:
+        tile_keys = torch.empty((n_isects,), dtype=torch.int32, device=dev)
+        if n_isects > 0:
+            # the hand-written sort takes the device-side count itself; the library sort needs the tail padded with
+            # keys that sort last
+            pad = n_dev if not _own_sort() else None
+            lib.gsb_isect_emit_perm_cap(P, N, int(packed), ptr(perm), ptr(means2d), ptr(radii), ptr(camera_ids),
+                                        tile_size, tile_width, tile_height, tb, ptr(tiles_per_gauss),
+                                        ptr(block_offsets), ptr(tile_keys), ptr(flatten_ids), n_isects, pad,
+                                        ptr(records), st)
+            tile_keys, flatten_ids = _sort_pairs_u32(tile_keys, flatten_ids, tb + cb, n_dev)
+        lib.gsb_isect_finalize_cap(n_isects, n_dev if n_isects > 0 else None, ptr(tile_keys), ptr(flatten_ids),
+                                   ptr(depths), C, tile_width, tile_height, tb, ptr(isect_ids), ptr(offsets), st)
     if pending is None:
         # the finalize pass already produced isect_offset_encode's answer for these ids: hand it over with them
         isect_ids._b200_offsets = (C, tile_width, tile_height, tb, offsets)

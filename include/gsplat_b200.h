@@ -191,6 +191,31 @@ int gsb_isect_finalize_cap(int64_t n_isects, const int64_t *n_isects_dev, const 
                            const int32_t *flatten_ids, const float *depths, int C, int tile_width, int tile_height,
                            int tile_n_bits, int64_t *isect_ids, int32_t *offsets, cudaStream_t stream);
 
+/* Tile binning (csrc/isect_bin.cu): steps 2-4 above without a sort over the intersections, for C * tiles <=
+ * gsb_isect_bin_max_bins() (8192) bins; same isect_ids / flatten_ids / offsets, bit for bit
+ * (isect_tiles.py:14-133 + isect_offset.py:9-63; IntersectTile.cu:24-344).
+ *   gsb_isect_row_tiles_keys      = gsb_isect_row_tiles + row_keys[i] = depth bits of row i, or 0xffffffff for a row
+ *                                   without tiles: sorting (row_keys, rows) over 32 bits puts the emitting rows first;
+ *   gsb_isect_count_perm_records  gathers the row records into that order (sorted_records int32[P,4]) and scans the
+ *                                   tile counts per 256 rows (block_offsets int64[blocks+1], total -> n_isects_out);
+ *   gsb_isect_bin                 counting sort with one bin per (camera, tile): per-chunk counts, scan, then every
+ *                                   intersection is written once at its final place. `capacity` = slots of isect_ids /
+ *                                   flatten_ids; the real count may stay on the device (n_isects_dev, or NULL when
+ *                                   capacity is the count). temp: gsb_isect_bin_temp_bytes(capacity, C * tiles). */
+int gsb_isect_row_tiles_keys(int64_t P, int N, int packed, const float *means2d, const int32_t *radii,
+                             const float *depths, const int64_t *camera_ids, int tile_size, int tile_width,
+                             int tile_height, int tile_n_bits, int32_t *rows, int32_t *tiles_per_gauss,
+                             int32_t *row_records, int32_t *row_keys, cudaStream_t stream);
+int gsb_isect_count_perm_records(int64_t P, const int32_t *perm, const int32_t *row_records, int32_t *sorted_records,
+                                 int32_t *block_sums, int64_t *block_offsets, int64_t *n_isects_out,
+                                 cudaStream_t stream);
+int gsb_isect_bin_max_bins(void);
+int64_t gsb_isect_bin_temp_bytes(int64_t capacity, int bins);
+int gsb_isect_bin(int64_t P, int64_t capacity, const int64_t *n_isects_dev, const int32_t *sorted_records,
+                  const int32_t *perm, const int32_t *sorted_keys, const int64_t *block_offsets, int C, int tile_width,
+                  int tile_height, int tile_n_bits, void *temp, int64_t temp_bytes, int64_t *isect_ids,
+                  int32_t *flatten_ids, int32_t *offsets, cudaStream_t stream);
+
 /* ---- rasterize_to_pixels ----------------------------------------------------------------------
  * replaces triton_impl/rasterize_to_pixels_fwd.py:200-275 / :21-196, rasterize_to_pixels_bwd.py:341-430
  * / :21-337 and cuda/csrc/RasterizeToPixels3DGSFwd.cu:18-188, RasterizeToPixels3DGSBwd.cu:16-278.

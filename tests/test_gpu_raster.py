@@ -156,13 +156,43 @@ def test_isect_presorted_path_equals_global_radix_sort(N, packed, monkeypatch):
         cam = torch.sort(torch.randint(0, C, shape)).values.to(DEV)
         kw = dict(packed=True, n_cameras=C, camera_ids=cam, gaussian_ids=torch.arange(C * N, device=DEV))
     out = {}
-    for mode in ("presort", "global"):
+    for mode, binning in (("presort", "bin"), ("presort", "radix"), ("global", "radix")):
         monkeypatch.setenv("GSPLAT_B200_SORT", mode)
+        monkeypatch.setenv("GSPLAT_B200_ISECT", binning)
         tpg, ids, flat = isect_tiles(means2d, radii, depths, ts, tw, th, **kw)
-        out[mode] = (tpg, ids, flat, isect_offset_encode(ids, C, tw, th))
-    for a, b in zip(out["presort"], out["global"]):
+        out[mode, binning] = (tpg, ids, flat, isect_offset_encode(ids, C, tw, th))
+    for other in (("presort", "radix"), ("presort", "bin")):
+        for a, b in zip(out[other], out["global", "radix"]):
+            assert torch.equal(a, b)
+    assert out["presort", "bin"][1].numel() > N
+
+
+@pytest.mark.parametrize("C,N,W,H,rmax", [(1, 60000, 1920, 1080, 300), (2, 20000, 1000, 1000, 900), (1, 300, 1920, 1080, 2500),
+                                          (1, 200000, 648, 420, 30)])
+def test_isect_tile_binning_equals_radix_path(C, N, W, H, rmax, monkeypatch):
+    """csrc/isect_bin.cu (counting sort, one bin per tile) against the two-pass radix path: rows covering thousands of
+    tiles (a single row larger than a chunk of 8192 intersections), ties, rows without tiles, two cameras; and through
+    isect_offset_encode recomputed from the ids."""
+    from gsplat.b200_impl import isect_offset_encode, isect_tiles
+
+    torch.manual_seed(N + rmax)
+    ts = 16
+    tw, th = -(-W // ts), -(-H // ts)
+    means2d = (torch.rand(C, N, 2) * torch.tensor([W + 200.0, H + 200.0]) - 100.0).to(DEV)
+    radii = (torch.rand(C, N) ** 4 * rmax).int().to(DEV)  # mostly small, a few huge; zeros included
+    depths = (torch.rand(C, N) * 20 + 0.05).to(DEV)
+    depths[:, ::7] = 3.0
+    out = {}
+    for binning in ("bin", "radix"):
+        monkeypatch.setenv("GSPLAT_B200_ISECT", binning)
+        tpg, ids, flat = isect_tiles(means2d, radii, depths, ts, tw, th)
+        cached = isect_offset_encode(ids, C, tw, th)
+        fresh = isect_offset_encode(ids.clone(), C, tw, th)  # a clone carries no cached offsets: recomputed from ids
+        assert torch.equal(cached, fresh)
+        out[binning] = (tpg, ids, flat, cached)
+    for a, b in zip(out["bin"], out["radix"]):
         assert torch.equal(a, b)
-    assert out["presort"][1].numel() > N
+    assert out["bin"][1].numel() > 8192
 
 
 def test_isect_packed_empty_and_docstring():
