@@ -11,12 +11,21 @@
 //
 //   bin_count_kernel    chunk c = intersections [c*8192, (c+1)*8192) of the emission order: per-bin counts -> M[c][bin]
 //   bin_scan_*          exclusive scan of M down the chunks (two levels) and of the bin totals: `offsets` falls out
-//   bin_scatter_kernel  the chunk again: expand into shared memory, stable 2-pass radix sort by bin INSIDE shared memory,
-//                       then every intersection goes to offsets[bin] + (intersections of that bin in earlier chunks) +
-//                       (its rank inside the chunk): written once, at its final place, as the 64-bit key + the row id.
+//   bin_scatter_kernel  the chunk again: every intersection goes to offsets[bin] + (intersections of that bin in
+//                       earlier chunks) + (its rank among the chunk's intersections of that bin, in emission order):
+//                       written once, at its final place, as the 64-bit key + the row id.
+//
+// The rank inside the chunk: shared-memory atomics drop the chunk's slot numbers into per-bin lists (any order), then
+// every intersection counts the smaller slot numbers of its list: with ~1 intersection per (chunk, bin) that is a
+// handful of instructions. A chunk that piles more than kFastMax intersections on one bin (a far-away object inside
+// one tile) takes a stable 2-pass radix sort inside shared memory instead.
 //
 // No kernel waits on another (no look-back chain), nothing is written twice. The price is the dense chunks x bins count
-// matrix, so the path is taken for C * tiles <= 8192 bins (cfg1, cfg2, cfg4); larger grids keep the radix path.
+// matrix (so: C * tiles <= 8192 bins) and, decisively, the final stores: a chunk holds ~1.6 intersections per bin, so
+// every 8-byte key and 4-byte id is its own 32-byte sector write (12.7 M sectors per launch at cfg2, 8 x what a radix
+// pass writes). Measured at cfg2 (6.35 M intersections, B200): count 46 us + scans 52 us + scatter 178 us under ncu,
+// 0.245 ms by CUDA events against 0.238 ms for emit + two radix passes + finalize; with the stores redirected to
+// consecutive addresses (experiment) 0.188 ms. Correct and selectable (GSPLAT_B200_ISECT=bin), NOT the default.
 #include "common.cuh"
 
 #include <cstdint>
@@ -28,8 +37,9 @@ constexpr int kThreads = 512;   // CTA of the chunk kernels
 constexpr int kWarps = kThreads / 32;
 constexpr int kItems = kT / kThreads;
 constexpr int kRowBlock = 256;  // rows per block_offsets entry (isect.cu)
-constexpr int kMaxBins = kT;    // the per-bin table of the scatter kernel aliases a sort buffer
+constexpr int kMaxBins = kT;    // per-bin tables of the scatter kernel are sized like a chunk
 constexpr int kGroups = 32;     // second level of the scan down the chunks
+constexpr int kFastMax = 128;   // longest per-bin list the counting rank handles; beyond: radix passes
 
 __device__ __forceinline__ int64_t clamp_count(int64_t capacity, const int64_t *n_dev) {
     if (n_dev == nullptr) return capacity;
@@ -37,23 +47,24 @@ __device__ __forceinline__ int64_t clamp_count(int64_t capacity, const int64_t *
     return n < capacity ? (n < 0 ? 0 : n) : capacity;
 }
 
-struct ExpandSmem {
-    int start[kThreads + 1];  // first slot of each row of the current 512-row batch, relative to the batch
-    int xy[kThreads];         // x0 | y0 << 16
-    int w[kThreads];          // rectangle width
-    int bin0[kThreads];       // camera * n_tiles
+struct ChunkSmem {
     int warp[kWarps];
-    int b0;                   // first 256-row block overlapping the chunk
+    uint32_t wmax[kWarps];
+    int b0;         // first 256-row block overlapping the chunk
+    int first_off;  // tiles of the chunk's first row that belong to the previous chunk
+    int maxcnt;
 };
 
-// Walks the chunk's slots [a, b_end) of the emission order and calls f(slot - a, bin, row index relative to row 256*b0).
-// Block-cooperative: 512 rows describe their rectangles in shared memory, then the threads take the slots one by one
-// (binary search for the owning row), so the cost does not depend on how the tiles spread over the rows.
-template <typename F>
-__device__ __forceinline__ void expand_chunk(int64_t a, int64_t b_end, int64_t P, const int4 *__restrict__ srec,
-                                             const int64_t *__restrict__ block_offsets, int64_t nblk, int tw,
-                                             int n_tiles, int tile_n_bits, ExpandSmem &s, F f) {
+// Slot -> owning row for the chunk's slots [a, b_end) of the emission order. Every row starting inside the chunk drops
+// (slot << 16 | row) at its first slot (rows are numbered from row 256*b0; the row straddling `a` owns slot 0); an
+// inclusive max-scan then carries each marker over the row's slots. Cost per slot: a few shared-memory words, no
+// search. On return mark[j] = (first slot of the owner << 16 | owner) for every slot.
+__device__ __forceinline__ void build_marks(int64_t a, int64_t b_end, int64_t P, const int4 *__restrict__ srec,
+                                            const int64_t *__restrict__ block_offsets, int64_t nblk,
+                                            uint32_t *__restrict__ mark, ChunkSmem &s) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint4 *mark4 = reinterpret_cast<uint4 *>(mark);
+    for (int i = tid; i < kT / 4; i += kThreads) mark4[i] = make_uint4(0u, 0u, 0u, 0u);
     if (tid == 0) {
         int64_t lo = 0, hi = nblk;  // last block with block_offsets[lo] <= a (block_offsets[0] = 0 <= a)
         while (hi - lo > 1) {
@@ -61,56 +72,90 @@ __device__ __forceinline__ void expand_chunk(int64_t a, int64_t b_end, int64_t P
             if (block_offsets[mid] <= a) lo = mid; else hi = mid;
         }
         s.b0 = (int)lo;
+        s.first_off = 0;
     }
     __syncthreads();
     const int64_t b0 = s.b0;
+    const int *counts = reinterpret_cast<const int *>(srec) + 3;  // .w of every record
     for (int it = 0;; ++it) {
         const int64_t blk = b0 + 2 * (int64_t)it;
         if (blk >= nblk) break;
         const int64_t base = block_offsets[blk];
         if (base >= b_end) break;
         const int64_t k = blk * kRowBlock + tid;
-        int4 rec = make_int4(0, 0, 0, 0);
-        if (k < P) rec = srec[k];
-        int inc = rec.w;
+        const int cnt = k < P ? counts[4 * k] : 0;
+        int inc = cnt;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const int t = __shfl_up_sync(0xffffffffu, inc, o);
             if (lane >= o) inc += t;
         }
         if (lane == 31) s.warp[warp] = inc;
-        s.xy[tid] = rec.x;
-        s.w[tid] = rec.y;
-        s.bin0[tid] = (int)((uint32_t)rec.z >> tile_n_bits) * n_tiles;
         __syncthreads();
-        int wbase = 0, total = 0;
+        int wbase = 0;
 #pragma unroll
-        for (int wi = 0; wi < kWarps; ++wi) {
-            const int v = s.warp[wi];
-            wbase += (wi < warp) ? v : 0;
-            total += v;
-        }
-        s.start[tid] = wbase + inc - rec.w;
-        if (tid == 0) s.start[kThreads] = total;
-        __syncthreads();
-        const int64_t lo_j = a > base ? a : base;
-        const int64_t hi_j = b_end < base + total ? b_end : base + total;
-        for (int64_t j = lo_j + tid; j < hi_j; j += kThreads) {
-            const int local = (int)(j - base);
-            int lo = 0, hi = kThreads;  // invariant: start[lo] <= local < start[hi]
-#pragma unroll
-            for (int step = 0; step < 9; ++step) {
-                const int mid = (lo + hi) >> 1;
-                if (s.start[mid] <= local) lo = mid; else hi = mid;
+        for (int wi = 0; wi < kWarps; ++wi) wbase += (wi < warp) ? s.warp[wi] : 0;
+        const int64_t start = base + wbase + inc - cnt;
+        if (cnt > 0 && start < b_end && start + cnt > a) {
+            const int krel = (int)(blk - b0) * kRowBlock + tid;
+            if (krel > 0xffff) __trap();  // rows without tiles inside the run of emitting rows: contract broken
+            if (start < a) {
+                s.first_off = (int)(a - start);
+                mark[0] = (uint32_t)krel;
+            } else {
+                const int pos = (int)(start - a);
+                mark[pos] = ((uint32_t)pos << 16) | (uint32_t)krel;
             }
-            const int t = local - s.start[lo];
-            const int w = s.w[lo], xy = s.xy[lo];
-            const int dy = t / w, dx = t - dy * w;
-            const int tile = ((xy >> 16) + dy) * tw + (xy & 0xffff) + dx;
-            f((int)(j - a), s.bin0[lo] + tile, (int)(blk - b0) * kRowBlock + lo);
         }
-        __syncthreads();  // the batch tables are rewritten by the next round
+        __syncthreads();  // s.warp is rewritten by the next round; also publishes the markers
     }
+    // inclusive max-scan, 16 consecutive slots per thread
+    uint4 q[kItems / 4];
+#pragma unroll
+    for (int u = 0; u < kItems / 4; ++u) q[u] = mark4[tid * (kItems / 4) + u];
+    uint32_t run = 0u;
+#pragma unroll
+    for (int u = 0; u < kItems / 4; ++u) {
+        run = max(run, q[u].x); q[u].x = run;
+        run = max(run, q[u].y); q[u].y = run;
+        run = max(run, q[u].z); q[u].z = run;
+        run = max(run, q[u].w); q[u].w = run;
+    }
+    uint32_t inc = run;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc = max(inc, t);
+    }
+    if (lane == 31) s.wmax[warp] = inc;
+    uint32_t carry = __shfl_up_sync(0xffffffffu, inc, 1);
+    if (lane == 0) carry = 0u;
+    __syncthreads();
+#pragma unroll
+    for (int wi = 0; wi < kWarps; ++wi) carry = max(carry, (wi < warp) ? s.wmax[wi] : 0u);
+#pragma unroll
+    for (int u = 0; u < kItems / 4; ++u) {
+        q[u].x = max(q[u].x, carry); q[u].y = max(q[u].y, carry);
+        q[u].z = max(q[u].z, carry); q[u].w = max(q[u].w, carry);
+        mark4[tid * (kItems / 4) + u] = q[u];
+    }
+    __syncthreads();
+}
+
+// (camera, tile) bin and owning row of slot j (relative to the chunk) from its scanned marker
+__device__ __forceinline__ int bin_of_slot(uint32_t m, int j, int first_off, const int4 *__restrict__ rows0, int tw,
+                                           int n_tiles, int tile_n_bits, int &krel) {
+    krel = (int)(m & 0xffffu);
+    const int p = (int)(m >> 16);
+    const int t = j - p + (p == 0 ? first_off : 0);
+    const int4 rec = __ldg(rows0 + krel);
+    const int w = rec.y;
+    int dy = (int)__fdividef((float)t + 0.5f, (float)w);  // t / w, fixed up below: no integer division
+    int dx = t - dy * w;
+    if (dx < 0) { dy -= 1; dx += w; }
+    if (dx >= w) { dy += 1; dx -= w; }
+    const int tile = ((rec.x >> 16) + dy) * tw + (rec.x & 0xffff) + dx;
+    return (int)((uint32_t)rec.z >> tile_n_bits) * n_tiles + tile;
 }
 
 // ---------------------------------------------------------------- counts per (chunk, bin)
@@ -119,16 +164,26 @@ bin_count_kernel(int64_t capacity, const int64_t *__restrict__ n_dev, int64_t P,
                  const int64_t *__restrict__ block_offsets, int64_t nblk, int tw, int n_tiles, int tile_n_bits,
                  int bins, uint32_t *__restrict__ M) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint32_t *hist = reinterpret_cast<uint32_t *>(smem_raw);
-    __shared__ ExpandSmem s;
+    uint32_t *mark = reinterpret_cast<uint32_t *>(smem_raw);
+    uint32_t *hist = mark + kT;
+    __shared__ ChunkSmem s;
     const int64_t n = clamp_count(capacity, n_dev);
     const int64_t a = (int64_t)blockIdx.x * kT;
     for (int i = threadIdx.x; i < bins; i += kThreads) hist[i] = 0u;
-    __syncthreads();
     if (a < n) {
         const int64_t b_end = a + kT < n ? a + kT : n;
-        expand_chunk(a, b_end, P, srec, block_offsets, nblk, tw, n_tiles, tile_n_bits, s,
-                     [&](int, int bin, int) { atomicAdd(&hist[bin], 1u); });
+        const int count = (int)(b_end - a);
+        build_marks(a, b_end, P, srec, block_offsets, nblk, mark, s);
+        const int4 *rows0 = srec + (int64_t)s.b0 * kRowBlock;
+        const int first_off = s.first_off;
+#pragma unroll 4
+        for (int i = 0; i < kItems; ++i) {
+            const int j = i * kThreads + threadIdx.x;
+            if (j < count) {
+                int krel;
+                atomicAdd(&hist[bin_of_slot(mark[j], j, first_off, rows0, tw, n_tiles, tile_n_bits, krel)], 1u);
+            }
+        }
     }
     __syncthreads();
     uint32_t *row = M + (int64_t)blockIdx.x * bins;
@@ -283,28 +338,137 @@ __device__ __forceinline__ void smem_radix_pass(const uint32_t *__restrict__ src
     __syncthreads();
 }
 
+// shared memory of the scatter kernel: three chunk-sized tables
+//   mark  [kT]            slot markers, later the per-bin slot lists (uint16)     | radix fallback: buf0
+//   cnt   [kMaxBins + 16] per-bin counts -> list starts -> list ends               | radix fallback: buf1
+//   base  [kMaxBins]      final position of the bin's first intersection of this chunk | radix fallback: warp counters
+constexpr size_t kScatterSmem = sizeof(uint32_t) * (kT + (kMaxBins + 16) + kMaxBins);
+static_assert(kMaxBins + 16 >= kT && kMaxBins >= kWarps * 256, "fallback buffers alias the tables");
+
 __global__ void __launch_bounds__(kThreads, 2)
 bin_scatter_kernel(int64_t capacity, const int64_t *__restrict__ n_dev, int64_t P, const int4 *__restrict__ srec,
                    const int64_t *__restrict__ block_offsets, int64_t nblk, const int32_t *__restrict__ perm,
-                   const uint32_t *__restrict__ sorted_keys, int tw, int n_tiles, int tile_n_bits, int bins,
+                   const uint32_t *__restrict__ sorted_keys, int C, int tw, int n_tiles, int tile_n_bits, int bins,
                    int bin_bits, int per_group, const uint32_t *__restrict__ M, const uint32_t *__restrict__ G,
                    const int32_t *__restrict__ offsets, int64_t *__restrict__ isect_ids,
-                   int32_t *__restrict__ flatten_ids) {
+                   int32_t *__restrict__ flatten_ids, int force_radix) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint32_t *buf0 = reinterpret_cast<uint32_t *>(smem_raw);  // item = bin << 16 | row index relative to row 256*b0
-    uint32_t *buf1 = buf0 + kT;
-    uint32_t(*s_cnt)[256] = reinterpret_cast<uint32_t(*)[256]>(buf1 + kT);
-    __shared__ ExpandSmem s;
+    uint32_t *mark = reinterpret_cast<uint32_t *>(smem_raw);
+    uint32_t *cnt = mark + kT;
+    int32_t *base = reinterpret_cast<int32_t *>(cnt + kMaxBins + 16);
+    __shared__ ChunkSmem s;
     __shared__ uint32_t s_scan[kWarps];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t n = clamp_count(capacity, n_dev);
     const int64_t a = (int64_t)blockIdx.x * kT;
     if (a >= n) return;
     const int64_t b_end = a + kT < n ? a + kT : n;
     const int count = (int)(b_end - a);
-    expand_chunk(a, b_end, P, srec, block_offsets, nblk, tw, n_tiles, tile_n_bits, s, [&](int slot, int bin, int krel) {
-        if (krel > 0xffff) __trap();  // rows without tiles inside the run of emitting rows: the caller broke the contract
-        buf0[slot] = ((uint32_t)bin << 16) | (uint32_t)krel;
-    });
+    const int chunk = blockIdx.x, g = chunk / per_group;
+    for (int i = tid; i < kMaxBins + 16; i += kThreads) cnt[i] = 0u;
+    if (tid == 0) s.maxcnt = 0;
+    build_marks(a, b_end, P, srec, block_offsets, nblk, mark, s);
+    const int64_t row0 = (int64_t)s.b0 * kRowBlock;
+    const int4 *rows0 = srec + row0;
+    const int first_off = s.first_off;
+
+    // ---- the chunk's intersections: (bin << 16 | row) in registers, counted per bin
+    uint32_t item[kItems];
+#pragma unroll
+    for (int i = 0; i < kItems; ++i) {
+        const int j = i * kThreads + tid;
+        item[i] = 0xffffffffu;
+        if (j < count) {
+            int krel;
+            const int bin = bin_of_slot(mark[j], j, first_off, rows0, tw, n_tiles, tile_n_bits, krel);
+            item[i] = ((uint32_t)bin << 16) | (uint32_t)krel;
+            atomicAdd(&cnt[bin], 1u);
+        }
+    }
+    // final position of every bin's first intersection of this chunk (dense, coalesced; in flight during the scan)
+    for (int b = tid; b < bins; b += kThreads)
+        base[b] = offsets[b] + (int32_t)(G[(int64_t)g * bins + b] + M[(int64_t)chunk * bins + b]);
+    __syncthreads();
+
+    // ---- exclusive scan of the counts (16 consecutive bins per thread) -> list starts; longest list
+    {
+        uint4 *cnt4 = reinterpret_cast<uint4 *>(cnt);
+        uint4 q[kItems / 4];
+        uint32_t sum = 0u, longest = 0u;
+#pragma unroll
+        for (int u = 0; u < kItems / 4; ++u) {
+            q[u] = cnt4[tid * (kItems / 4) + u];
+            longest = max(max(longest, q[u].x), max(q[u].y, max(q[u].z, q[u].w)));
+            sum += q[u].x + q[u].y + q[u].z + q[u].w;
+        }
+        uint32_t inc = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_scan[warp] = inc;
+        longest = (uint32_t)warp_max_i((int)longest);
+        if (lane == 0 && longest > 0u) atomicMax(&s.maxcnt, (int)longest);
+        __syncthreads();
+        uint32_t run = inc - sum;
+#pragma unroll
+        for (int wi = 0; wi < kWarps; ++wi) run += (wi < warp) ? s_scan[wi] : 0u;
+#pragma unroll
+        for (int u = 0; u < kItems / 4; ++u) {
+            uint4 o4;
+            o4.x = run; run += q[u].x;
+            o4.y = run; run += q[u].y;
+            o4.z = run; run += q[u].z;
+            o4.w = run; run += q[u].w;
+            cnt4[tid * (kItems / 4) + u] = o4;
+        }
+        __syncthreads();
+    }
+
+    if (s.maxcnt <= kFastMax && !force_radix) {
+        // ---- drop the slot numbers into the per-bin lists (any order inside a list)
+        uint16_t *list = reinterpret_cast<uint16_t *>(mark);
+#pragma unroll
+        for (int i = 0; i < kItems; ++i) {
+            const int j = i * kThreads + tid;
+            if (j < count) list[atomicAdd(&cnt[item[i] >> 16], 1u)] = (uint16_t)j;
+        }
+        __syncthreads();
+        // ---- rank inside the list = smaller slot numbers in it (emission order); write at the final place
+#pragma unroll
+        for (int i = 0; i < kItems; ++i) {
+            const int j = i * kThreads + tid;
+            if (j < count) {
+                const int bin = (int)(item[i] >> 16);
+                const int lo = bin ? (int)cnt[bin - 1] : 0, hi = (int)cnt[bin];  // list ends = next list's start
+                int rank = 0;
+                for (int qi = lo; qi < hi; ++qi) rank += (int)list[qi] < j;
+                const int64_t pos = (int64_t)base[bin] + rank;
+                if (pos < capacity) {
+                    const int64_t k = row0 + (item[i] & 0xffffu);
+                    uint32_t hi_word = (uint32_t)bin;
+                    if (C > 1) {
+                        const int cam = bin / n_tiles;
+                        hi_word = ((uint32_t)cam << tile_n_bits) | (uint32_t)(bin - cam * n_tiles);
+                    }
+                    isect_ids[pos] = ((int64_t)hi_word << 32) | (int64_t)sorted_keys[k];
+                    flatten_ids[pos] = perm[k];
+                }
+            }
+        }
+        return;
+    }
+
+    // ---- a bin with a long list: stable 2-pass radix sort of the chunk by bin inside shared memory
+    __syncthreads();  // every thread has read s.maxcnt and the tables are dead
+    uint32_t *buf0 = mark, *buf1 = cnt;
+    uint32_t(*s_cnt)[256] = reinterpret_cast<uint32_t(*)[256]>(base);
+#pragma unroll
+    for (int i = 0; i < kItems; ++i) {
+        const int j = i * kThreads + tid;
+        if (j < count) buf0[j] = item[i];
+    }
     __syncthreads();
     const int lo_bits = (bin_bits + 1) >> 1, hi_bits = bin_bits - lo_bits;
     uint32_t *sorted = buf0, *spare = buf1;
@@ -319,29 +483,25 @@ bin_scatter_kernel(int64_t capacity, const int64_t *__restrict__ n_dev, int64_t 
     }
     // first slot of every bin present in the chunk -> (final position - slot) of the bin
     int32_t *delta = reinterpret_cast<int32_t *>(spare);
-    const int chunk = blockIdx.x, g = chunk / per_group;
-    for (int i = threadIdx.x; i < count; i += kThreads) {
+    for (int i = tid; i < count; i += kThreads) {
         const int bin = (int)(sorted[i] >> 16);
         if (i == 0 || (int)(sorted[i - 1] >> 16) != bin)
             delta[bin] = offsets[bin] + (int32_t)(G[(int64_t)g * bins + bin] + M[(int64_t)chunk * bins + bin]) - i;
     }
     __syncthreads();
-    const int64_t row0 = (int64_t)s.b0 * kRowBlock;
-    for (int i = threadIdx.x; i < count; i += kThreads) {
-        const uint32_t item = sorted[i];
-        const int bin = (int)(item >> 16);
-        const int64_t k = row0 + (item & 0xffffu);
+    for (int i = tid; i < count; i += kThreads) {
+        const uint32_t it = sorted[i];
+        const int bin = (int)(it >> 16);
+        const int64_t k = row0 + (it & 0xffffu);
         const int64_t pos = (int64_t)delta[bin] + i;
         if (pos < capacity) {
             const int cam = bin / n_tiles;
-            const uint32_t hi = ((uint32_t)cam << tile_n_bits) | (uint32_t)(bin - cam * n_tiles);
-            isect_ids[pos] = ((int64_t)hi << 32) | (int64_t)sorted_keys[k];
+            const uint32_t hi_word = ((uint32_t)cam << tile_n_bits) | (uint32_t)(bin - cam * n_tiles);
+            isect_ids[pos] = ((int64_t)hi_word << 32) | (int64_t)sorted_keys[k];
             flatten_ids[pos] = perm[k];
         }
     }
 }
-
-constexpr size_t kScatterSmem = sizeof(uint32_t) * (2 * kT + kWarps * 256);
 
 }  // namespace
 
@@ -386,10 +546,13 @@ extern "C" int gsb_isect_bin(int64_t P, int64_t capacity, const int64_t *n_isect
     if (!((configured >> (device & 63)) & 1ull)) {
         cudaError_t e = cudaFuncSetAttribute(bin_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)kScatterSmem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(bin_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)(sizeof(uint32_t) * (kT + kMaxBins)));
         if (e != cudaSuccess) { gsb_set_error("isect_bin: shared memory: %s", cudaGetErrorString(e)); return GSB_ERR_CUDA; }
         configured |= 1ull << (device & 63);
     }
-    bin_count_kernel<<<chunks, kThreads, sizeof(uint32_t) * bins, stream>>>(
+    bin_count_kernel<<<chunks, kThreads, sizeof(uint32_t) * (kT + bins), stream>>>(
         capacity, n_isects_dev, P, srec, block_offsets, nblk, tile_width, (int)n_tiles, tile_n_bits, bins, M);
     if (int rc = gsb_check_launch("isect_bin_count")) return rc;
     const unsigned bgrid = gsb_cdiv(bins, 256);
@@ -400,7 +563,8 @@ extern "C" int gsb_isect_bin(int64_t P, int64_t capacity, const int64_t *n_isect
     bin_offsets_kernel<<<1, 1024, 0, stream>>>(bins, totals, offsets);
     if (int rc = gsb_check_launch("isect_bin_offsets")) return rc;
     bin_scatter_kernel<<<chunks, kThreads, kScatterSmem, stream>>>(
-        capacity, n_isects_dev, P, srec, block_offsets, nblk, perm, reinterpret_cast<const uint32_t *>(sorted_keys),
-        tile_width, (int)n_tiles, tile_n_bits, bins, bin_bits, per_group, M, G, offsets, isect_ids, flatten_ids);
+        capacity, n_isects_dev, P, srec, block_offsets, nblk, perm, reinterpret_cast<const uint32_t *>(sorted_keys), C,
+        tile_width, (int)n_tiles, tile_n_bits, bins, bin_bits, per_group, M, G, offsets, isect_ids, flatten_ids,
+        gsb_option(GSB_OPT_ISECT_BIN_RADIX));
     return gsb_check_launch("isect_bin_scatter");
 }

@@ -46,10 +46,12 @@ void gsb_reset_launch_count(void);
  *                        2 = rasterize_fwd2.cu (half-warp per block, 2 pixels per lane, packed FFMA2) [default, D <= 4]
  *                        3 = the same compositor fed by a producer warp (double-buffered staging, named barriers)
  *   GSB_OPT_BWD_VARIANT  1 = rasterize_bwd.cu (warp per block, two-phase moment reduction)
- *                        2 = rasterize_bwd2.cu (half-warp per block, 2 pixels per lane, packed FFMA2) [default, D <= 4] */
+ *                        2 = rasterize_bwd2.cu (half-warp per block, 2 pixels per lane, packed FFMA2) [default, D <= 4]
+ *   GSB_OPT_ISECT_BIN_RADIX  1 = gsb_isect_bin ranks every chunk with its radix fallback (tests; default 0) */
 #define GSB_OPT_FWD_VARIANT 0
 #define GSB_OPT_BWD_VARIANT 1
-#define GSB_OPT_COUNT 2
+#define GSB_OPT_ISECT_BIN_RADIX 2
+#define GSB_OPT_COUNT 3
 int gsb_set_option(int which, int value);
 int gsb_get_option(int which);
 

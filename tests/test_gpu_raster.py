@@ -167,31 +167,39 @@ def test_isect_presorted_path_equals_global_radix_sort(N, packed, monkeypatch):
     assert out["presort", "bin"][1].numel() > N
 
 
-@pytest.mark.parametrize("C,N,W,H,rmax", [(1, 60000, 1920, 1080, 300), (2, 20000, 1000, 1000, 900), (1, 300, 1920, 1080, 2500),
-                                          (1, 200000, 648, 420, 30)])
-def test_isect_tile_binning_equals_radix_path(C, N, W, H, rmax, monkeypatch):
+@pytest.mark.parametrize("C,N,W,H,rmax,spread", [(1, 60000, 1920, 1080, 300, 1.0), (2, 20000, 1000, 1000, 900, 1.0),
+                                                 (1, 300, 1920, 1080, 2500, 1.0), (1, 200000, 648, 420, 30, 1.0),
+                                                 (1, 100000, 1920, 1080, 12, 0.03)])
+def test_isect_tile_binning_equals_radix_path(C, N, W, H, rmax, spread, monkeypatch):
     """csrc/isect_bin.cu (counting sort, one bin per tile) against the two-pass radix path: rows covering thousands of
-    tiles (a single row larger than a chunk of 8192 intersections), ties, rows without tiles, two cameras; and through
-    isect_offset_encode recomputed from the ids."""
+    tiles (a single row larger than a chunk of 8192 intersections), ties, rows without tiles, two cameras, everything
+    piled on a few tiles (spread 0.03: per-bin lists beyond the counting rank -> the kernel's radix fallback), the
+    fallback forced for every chunk; and through isect_offset_encode recomputed from the ids."""
     from gsplat.b200_impl import isect_offset_encode, isect_tiles
+    from gsplat.b200_impl._lib import lib
 
     torch.manual_seed(N + rmax)
     ts = 16
     tw, th = -(-W // ts), -(-H // ts)
-    means2d = (torch.rand(C, N, 2) * torch.tensor([W + 200.0, H + 200.0]) - 100.0).to(DEV)
+    means2d = ((torch.rand(C, N, 2) * spread + (1 - spread) / 2) * torch.tensor([W + 200.0, H + 200.0]) - 100.0).to(DEV)
     radii = (torch.rand(C, N) ** 4 * rmax).int().to(DEV)  # mostly small, a few huge; zeros included
     depths = (torch.rand(C, N) * 20 + 0.05).to(DEV)
     depths[:, ::7] = 3.0
     out = {}
-    for binning in ("bin", "radix"):
-        monkeypatch.setenv("GSPLAT_B200_ISECT", binning)
-        tpg, ids, flat = isect_tiles(means2d, radii, depths, ts, tw, th)
+    for binning in ("bin", "bin_all_radix", "radix"):
+        monkeypatch.setenv("GSPLAT_B200_ISECT", binning.split("_")[0])
+        lib.gsb_set_option(2, int(binning == "bin_all_radix"))  # GSB_OPT_ISECT_BIN_RADIX
+        try:
+            tpg, ids, flat = isect_tiles(means2d, radii, depths, ts, tw, th)
+        finally:
+            lib.gsb_set_option(2, 0)
         cached = isect_offset_encode(ids, C, tw, th)
         fresh = isect_offset_encode(ids.clone(), C, tw, th)  # a clone carries no cached offsets: recomputed from ids
         assert torch.equal(cached, fresh)
         out[binning] = (tpg, ids, flat, cached)
-    for a, b in zip(out["bin"], out["radix"]):
-        assert torch.equal(a, b)
+    for other in ("bin", "bin_all_radix"):
+        for a, b in zip(out[other], out["radix"]):
+            assert torch.equal(a, b)
     assert out["bin"][1].numel() > 8192
 
 
