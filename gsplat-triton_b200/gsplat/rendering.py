@@ -169,13 +169,41 @@ def rasterization(
 
         push = PushExchange(C_world[world_rank], N_world, 3, opacities)
         set_push_context(push)
-    try:
-        proj_results = fully_fused_projection(
+    # b200, one GPU, SH colours: the projection and the intersection pipeline (a dozen latency-bound kernels that leave
+    # the memory system idle) run on a high-priority second stream, the HBM-bound colour kernels on the caller's; both
+    # are joined before the compositor. Autograd replays the split backward: the projection's backward kernel then
+    # shares the memory system with the colour backward instead of queueing behind it.
+    overlap, use_side = None, False
+    if BACKEND == "b200" and not distributed and sh_degree is not None:
+        from .b200_impl._wrapper import overlap_enabled, side_stream
+
+        use_side = overlap_enabled()
+    if use_side:
+        main, side = torch.cuda.current_stream(device), side_stream(device)
+        start = torch.cuda.Event()
+        start.record(main)
+
+    def project():
+        return fully_fused_projection(
             means, covars, quats, scales, viewmats, Ks, width, height,
             eps2d=eps2d, packed=packed, near_plane=near_plane, far_plane=far_plane, radius_clip=radius_clip,
             sparse_grad=sparse_grad, calc_compensations=(rasterize_mode == "antialiased"),
             camera_model=camera_model,
         )
+
+    try:
+        if use_side:
+            with torch.cuda.stream(side):
+                side.wait_event(start)
+                proj_results = project()
+                overlap = torch.cuda.Event()
+                overlap.record(side)
+            main.wait_event(overlap)
+            for t in proj_results:
+                if isinstance(t, Tensor):
+                    t.record_stream(main)  # allocated under the side stream, read on both
+        else:
+            proj_results = project()
     except Exception:
         if push is not None:
             set_push_context(None)
@@ -332,7 +360,22 @@ def rasterization(
     # b200: intersection buffers sized from the previous call's count, the real count is read back only after
     # the compositor has been queued (no GPU bubble at the reference's `.item()`, isect_tiles.py:102)
     speculate = BACKEND == "b200" and os.environ.get("GSPLAT_B200_SPECULATE", "1") == "1"
-    tiles_per_gauss, isect_ids, flatten_ids, isect_offsets, pending = intersect(speculate)
+    if overlap is not None:
+        if tile_size == 16 and colors.shape[-1] <= channel_chunk:
+            from .b200_impl._wrapper import prepack_splats
+
+            prepack_splats(means2d, conics, opacities)  # the compositor's splat records, also beside the side stream
+        main, side = torch.cuda.current_stream(device), side_stream(device)
+        with torch.cuda.stream(side):
+            side.wait_event(overlap)
+            tiles_per_gauss, isect_ids, flatten_ids, isect_offsets, pending = intersect(speculate)
+            isect_done = torch.cuda.Event()
+            isect_done.record(side)
+        main.wait_event(isect_done)
+        for t in (tiles_per_gauss, isect_ids, flatten_ids, isect_offsets):
+            t.record_stream(main)  # allocated under the side stream, read by the compositor and its backward
+    else:
+        tiles_per_gauss, isect_ids, flatten_ids, isect_offsets, pending = intersect(speculate)
     host_trace.mark("us_isect")
     if split is not None:
         split.complete_colors()  # the colours arrived while the intersections were being sorted

@@ -180,7 +180,8 @@ int gsb_isect_finalize(int64_t n_isects, const int32_t *tile_keys, const int32_t
 /* Speculatively sized variants (no host read-back of n_isects before the compositor is launched): buffers hold
  * `capacity` slots, the real count stays on the device (`n_isects_dev`, the total written by gsb_isect_count_perm).
  * emit writes only slots < capacity and pads [n_isects, capacity) with 0xffffffff keys (they sort last); finalize
- * treats min(*n_isects_dev, capacity) as the count. The caller reads the count back later and, if it exceeded
+ * treats min(*n_isects_dev, capacity) as the count (isect_ids or offsets may be NULL: only the other output is
+ * written, so the ids, which the compositor does not read, can be produced on a second stream). The caller reads the count back later and, if it exceeded
  * the capacity, redoes the step with exact sizes. row_records (or NULL): the per-row records of
  * gsb_isect_row_tiles; with them emit gathers one 16-byte record per row instead of means2d/radii/camera_ids. */
 int gsb_isect_emit_perm_cap(int64_t P, int N, int packed, const int32_t *perm, const float *means2d,
