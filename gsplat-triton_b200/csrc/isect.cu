@@ -191,30 +191,61 @@ row_keys_kernel(int64_t P, int N, const float *__restrict__ depths, const int64_
 // natural order (coalesced): rows[i] = i, the tile count of row i and, for the depth-ordered emission, ONE 16-byte
 // record per row (x0 | y0 << 16, width, camera << tile_bits, count): the emit pass then gathers a single sector per
 // row instead of four (means2d, radius, count, camera id)
+// shared-memory digit histograms of 32-bit keys for the onesweep sort that follows (gsb_radix_prepare): the producer
+// of the keys counts the digits itself, the sort then needs no histogram pass. `passes` x 256 counters.
+__device__ __forceinline__ void hist_clear(uint32_t *s_hist, int passes) {
+    for (int i = threadIdx.x; i < passes * 256; i += blockDim.x) s_hist[i] = 0u;
+}
+__device__ __forceinline__ void hist_add(uint32_t *s_hist, uint32_t key, int passes, int end_bit) {
+    for (int p = 0; p < passes; ++p) {
+        const int bits = min(8, end_bit - 8 * p);
+        atomicAdd(&s_hist[p * 256 + ((key >> (8 * p)) & ((1u << bits) - 1u))], 1u);
+    }
+}
+__device__ __forceinline__ void hist_flush(const uint32_t *s_hist, uint32_t *hist, int passes) {
+    for (int i = threadIdx.x; i < passes * 256; i += blockDim.x) {
+        const uint32_t c = s_hist[i];
+        if (c) atomicAdd(&hist[i], c);
+    }
+}
+
 template <bool PACKED>
 __global__ void __launch_bounds__(kThreads)
 row_tiles_kernel(int64_t P, int N, const float *__restrict__ means2d, const int32_t *__restrict__ radii,
                  const int64_t *__restrict__ camera_ids, int tile_size, int tw, int th, int tile_n_bits,
                  int32_t *__restrict__ rows, int32_t *__restrict__ tiles_per_gauss, int4 *__restrict__ records,
-                 const float *__restrict__ depths, uint32_t *__restrict__ row_keys) {
-    int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    if (i >= P) return;
-    int cnt = 0;
-    int4 rec = make_int4(0, 0, 0, 0);
-    const int r = radii[i];
-    if (r > 0) {
-        float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * i);
-        TileBox b = tile_box(m.x, m.y, r, tile_size, tw, th);
-        cnt = (b.x1 - b.x0) * (b.y1 - b.y0);
-        const uint32_t cam = (uint32_t)(PACKED ? camera_ids[i] : (i / N));
-        rec = make_int4(b.x0 | (b.y0 << 16), b.x1 - b.x0, (int)(cam << tile_n_bits), cnt);
+                 const float *__restrict__ depths, uint32_t *__restrict__ row_keys, uint32_t *__restrict__ key_hist) {
+    __shared__ uint32_t s_hist[4 * 256];
+    if (key_hist != nullptr) {
+        hist_clear(s_hist, 4);
+        __syncthreads();
     }
-    rows[i] = (int32_t)i;
-    tiles_per_gauss[i] = cnt;
-    if (records != nullptr) records[i] = rec;
-    // the depth-sort key of the row: its depth bits, or all ones for a row without tiles, so that the rows that emit
-    // intersections form one contiguous run of the sorted order (the binning kernels of isect_bin.cu rely on it)
-    if (row_keys != nullptr) row_keys[i] = cnt > 0 ? (uint32_t)__float_as_int(depths[i]) : 0xffffffffu;
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < P; i += (int64_t)gridDim.x * kThreads) {
+        int cnt = 0;
+        int4 rec = make_int4(0, 0, 0, 0);
+        const int r = radii[i];
+        if (r > 0) {
+            float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * i);
+            TileBox b = tile_box(m.x, m.y, r, tile_size, tw, th);
+            cnt = (b.x1 - b.x0) * (b.y1 - b.y0);
+            const uint32_t cam = (uint32_t)(PACKED ? camera_ids[i] : (i / N));
+            rec = make_int4(b.x0 | (b.y0 << 16), b.x1 - b.x0, (int)(cam << tile_n_bits), cnt);
+        }
+        rows[i] = (int32_t)i;
+        tiles_per_gauss[i] = cnt;
+        if (records != nullptr) records[i] = rec;
+        // the depth-sort key of the row: its depth bits, or all ones for a row without tiles, so that the rows that
+        // emit intersections form one contiguous run of the sorted order (the binning kernels of isect_bin.cu rely on it)
+        if (row_keys != nullptr) {
+            const uint32_t key = cnt > 0 ? (uint32_t)__float_as_int(depths[i]) : 0xffffffffu;
+            row_keys[i] = key;
+            if (key_hist != nullptr) hist_add(s_hist, key, 4, 32);
+        }
+    }
+    if (key_hist != nullptr) {
+        __syncthreads();
+        hist_flush(s_hist, key_hist, 4);
+    }
 }
 
 // k-th thread handles row perm[k]: gathers its 16-byte record into depth order (the binning kernels then read the
@@ -287,55 +318,69 @@ emit_perm_kernel(int64_t P, int N, const int32_t *__restrict__ perm, const float
                  const int32_t *__restrict__ radii, const int64_t *__restrict__ camera_ids, int tile_size, int tw,
                  int th, int tile_n_bits, const int32_t *__restrict__ tiles_per_gauss,
                  const int64_t *__restrict__ block_offsets, uint32_t *__restrict__ tile_keys,
-                 int32_t *__restrict__ flatten_ids, int64_t capacity, const int4 *__restrict__ records) {
+                 int32_t *__restrict__ flatten_ids, int64_t capacity, const int4 *__restrict__ records, int64_t nblk,
+                 uint32_t *__restrict__ key_hist, int key_bits) {
     __shared__ int s_warp[kThreads / 32];
     __shared__ int s_start[kThreads];  // first output slot of each row inside the CTA's range
     __shared__ int s_xy[kThreads];     // x0 | y0 << 16
     __shared__ int s_w[kThreads];
     __shared__ int s_row[kThreads];
     __shared__ uint32_t s_hi[kThreads];
+    __shared__ uint32_t s_hist[4 * 256];  // digit histograms of the emitted words for the tile sort (key_hist)
     const int tid = threadIdx.x;
-    int64_t k = (int64_t)blockIdx.x * kThreads + tid;
-    int64_t i = k < P ? perm[k] : 0;
-    int cnt = 0;
-    if (records != nullptr) {
-        int4 rec = make_int4(0, 0, 0, 0);
-        if (k < P) rec = __ldg(records + i);
-        cnt = rec.w;
-        s_xy[tid] = rec.x;
-        s_w[tid] = rec.y;
-        s_hi[tid] = (uint32_t)rec.z;
-    } else {
-        cnt = k < P ? tiles_per_gauss[i] : 0;
-        if (cnt > 0) {
-            float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * i);
-            TileBox b = tile_box(m.x, m.y, radii[i], tile_size, tw, th);
-            s_xy[tid] = b.x0 | (b.y0 << 16);
-            s_w[tid] = b.x1 - b.x0;
-            s_hi[tid] = (uint32_t)(PACKED ? camera_ids[i] : (i / N)) << tile_n_bits;
+    const int passes = (key_bits + 7) / 8;
+    if (key_hist != nullptr) hist_clear(s_hist, passes);
+    // a CTA takes every gridDim.x-th block of 256 rows (in permuted = depth order)
+    for (int64_t blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
+        int64_t k = blk * kThreads + tid;
+        int64_t i = k < P ? perm[k] : 0;
+        int cnt = 0;
+        if (records != nullptr) {
+            int4 rec = make_int4(0, 0, 0, 0);
+            if (k < P) rec = __ldg(records + i);
+            cnt = rec.w;
+            s_xy[tid] = rec.x;
+            s_w[tid] = rec.y;
+            s_hi[tid] = (uint32_t)rec.z;
+        } else {
+            cnt = k < P ? tiles_per_gauss[i] : 0;
+            if (cnt > 0) {
+                float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * i);
+                TileBox b = tile_box(m.x, m.y, radii[i], tile_size, tw, th);
+                s_xy[tid] = b.x0 | (b.y0 << 16);
+                s_w[tid] = b.x1 - b.x0;
+                s_hi[tid] = (uint32_t)(PACKED ? camera_ids[i] : (i / N)) << tile_n_bits;
+            }
         }
-    }
-    s_row[tid] = (int)i;
-    int block_total;
-    s_start[tid] = block_exclusive_scan(cnt, s_warp, block_total);
-    __syncthreads();
-    const int64_t base = block_offsets[blockIdx.x];
-    for (int j = tid; j < block_total; j += kThreads) {
-        // last row r with s_start[r] <= j (rows without tiles share their successor's start and are skipped)
-        int lo = 0, hi_ = kThreads;  // invariant: s_start[lo] <= j < s_start[hi_] (s_start[kThreads] = block_total)
+        s_row[tid] = (int)i;
+        int block_total;
+        s_start[tid] = block_exclusive_scan(cnt, s_warp, block_total);
+        __syncthreads();
+        const int64_t base = block_offsets[blk];
+        for (int j = tid; j < block_total; j += kThreads) {
+            // last row r with s_start[r] <= j (rows without tiles share their successor's start and are skipped)
+            int lo = 0, hi_ = kThreads;  // invariant: s_start[lo] <= j < s_start[hi_] (s_start[kThreads] = block_total)
 #pragma unroll
-        for (int step = 0; step < 8; ++step) {
-            const int mid = (lo + hi_) >> 1;
-            if (s_start[mid] <= j) lo = mid; else hi_ = mid;
+            for (int step = 0; step < 8; ++step) {
+                const int mid = (lo + hi_) >> 1;
+                if (s_start[mid] <= j) lo = mid; else hi_ = mid;
+            }
+            const int t = j - s_start[lo];
+            const int w = s_w[lo], xy = s_xy[lo];
+            const int dy = t / w, dx = t - dy * w;
+            const int64_t out = base + j;
+            if (out < capacity) {  // speculative capacity (gsb_isect_emit_perm_cap): never write past the buffers
+                const uint32_t key = s_hi[lo] | (uint32_t)(((xy >> 16) + dy) * tw + (xy & 0xffff) + dx);
+                tile_keys[out] = key;
+                flatten_ids[out] = s_row[lo];
+                if (key_hist != nullptr) hist_add(s_hist, key, passes, key_bits);
+            }
         }
-        const int t = j - s_start[lo];
-        const int w = s_w[lo], xy = s_xy[lo];
-        const int dy = t / w, dx = t - dy * w;
-        const int64_t out = base + j;
-        if (out < capacity) {  // speculative capacity (gsb_isect_emit_perm_cap): never write past the buffers
-            tile_keys[out] = s_hi[lo] | (uint32_t)(((xy >> 16) + dy) * tw + (xy & 0xffff) + dx);
-            flatten_ids[out] = s_row[lo];
-        }
+        __syncthreads();  // the row tables are rewritten by the next block
+    }
+    if (key_hist != nullptr) {
+        __syncthreads();
+        hist_flush(s_hist, key_hist, passes);
     }
 }
 
@@ -498,30 +543,36 @@ extern "C" int gsb_isect_row_tiles(int64_t P, int N, int packed, const float *me
                                    int tile_n_bits, int32_t *rows, int32_t *tiles_per_gauss, int32_t *row_records,
                                    cudaStream_t stream) {
     return gsb_isect_row_tiles_keys(P, N, packed, means2d, radii, nullptr, camera_ids, tile_size, tile_width,
-                                    tile_height, tile_n_bits, rows, tiles_per_gauss, row_records, nullptr, stream);
+                                    tile_height, tile_n_bits, rows, tiles_per_gauss, row_records, nullptr, nullptr,
+                                    stream);
 }
 
 extern "C" int gsb_isect_row_tiles_keys(int64_t P, int N, int packed, const float *means2d, const int32_t *radii,
                                         const float *depths, const int64_t *camera_ids, int tile_size, int tile_width,
                                         int tile_height, int tile_n_bits, int32_t *rows, int32_t *tiles_per_gauss,
-                                        int32_t *row_records, int32_t *row_keys, cudaStream_t stream) {
+                                        int32_t *row_records, int32_t *row_keys, void *key_hist, cudaStream_t stream) {
     GSB_REQUIRE(row_keys == nullptr || depths != nullptr, "depths required for row_keys");
+    GSB_REQUIRE(key_hist == nullptr || row_keys != nullptr, "key_hist counts the digits of row_keys");
     GSB_REQUIRE(P >= 0 && tile_size > 0 && tile_width >= 0 && tile_height >= 0, "bad sizes");
     GSB_REQUIRE(P < ((int64_t)1 << 31), "more than 2^31-1 rows");
     GSB_REQUIRE(!packed || camera_ids != nullptr || P == 0 || row_records == nullptr, "camera_ids required when packed");
     GSB_REQUIRE(packed || N > 0 || P == 0, "N required when not packed");
     GSB_REQUIRE(tile_width < 65536 && tile_height < 32768, "tile grid too large");
     if (P == 0) return GSB_OK;
-    const unsigned nblk = (unsigned)gsb_isect_num_blocks(P);
+    // with a histogram to feed, few CTAs walk the rows (one flush of 1024 counters per CTA); else one CTA per 256 rows
+    unsigned nblk = (unsigned)gsb_isect_num_blocks(P);
+    if (key_hist != nullptr && nblk > 148 * 6) nblk = 148 * 6;
     auto recs = reinterpret_cast<int4 *>(row_records);
+    auto keys = reinterpret_cast<uint32_t *>(row_keys);
+    auto hist = reinterpret_cast<uint32_t *>(key_hist);
     if (packed)
         row_tiles_kernel<true><<<nblk, kThreads, 0, stream>>>(P, N, means2d, radii, camera_ids, tile_size, tile_width,
                                                               tile_height, tile_n_bits, rows, tiles_per_gauss, recs,
-                                                              depths, reinterpret_cast<uint32_t *>(row_keys));
+                                                              depths, keys, hist);
     else
         row_tiles_kernel<false><<<nblk, kThreads, 0, stream>>>(P, N, means2d, radii, camera_ids, tile_size, tile_width,
                                                                tile_height, tile_n_bits, rows, tiles_per_gauss, recs,
-                                                               depths, reinterpret_cast<uint32_t *>(row_keys));
+                                                               depths, keys, hist);
     return gsb_check_launch("isect_row_tiles");
 }
 
@@ -559,9 +610,9 @@ extern "C" int gsb_isect_emit_perm(int64_t P, int N, int packed, const int32_t *
                                    int tile_height, int tile_n_bits, const int32_t *tiles_per_gauss,
                                    const int64_t *block_offsets, int32_t *tile_keys, int32_t *flatten_ids,
                                    cudaStream_t stream) {
-    return gsb_isect_emit_perm_cap(P, N, packed, perm, means2d, radii, camera_ids, tile_size, tile_width, tile_height,
-                                   tile_n_bits, tiles_per_gauss, block_offsets, tile_keys, flatten_ids,
-                                   INT64_MAX, nullptr, nullptr, stream);
+    return gsb_isect_emit_perm_hist(P, N, packed, perm, means2d, radii, camera_ids, tile_size, tile_width, tile_height,
+                                    tile_n_bits, tiles_per_gauss, block_offsets, tile_keys, flatten_ids,
+                                    INT64_MAX, nullptr, nullptr, nullptr, 0, stream);
 }
 
 extern "C" int gsb_isect_emit_perm_cap(int64_t P, int N, int packed, const int32_t *perm, const float *means2d,
@@ -570,23 +621,39 @@ extern "C" int gsb_isect_emit_perm_cap(int64_t P, int N, int packed, const int32
                                        const int64_t *block_offsets, int32_t *tile_keys, int32_t *flatten_ids,
                                        int64_t capacity, const int64_t *n_isects_dev, const int32_t *row_records,
                                        cudaStream_t stream) {
+    return gsb_isect_emit_perm_hist(P, N, packed, perm, means2d, radii, camera_ids, tile_size, tile_width, tile_height,
+                                    tile_n_bits, tiles_per_gauss, block_offsets, tile_keys, flatten_ids, capacity,
+                                    n_isects_dev, row_records, nullptr, 0, stream);
+}
+
+extern "C" int gsb_isect_emit_perm_hist(int64_t P, int N, int packed, const int32_t *perm, const float *means2d,
+                                        const int32_t *radii, const int64_t *camera_ids, int tile_size, int tile_width,
+                                        int tile_height, int tile_n_bits, const int32_t *tiles_per_gauss,
+                                        const int64_t *block_offsets, int32_t *tile_keys, int32_t *flatten_ids,
+                                        int64_t capacity, const int64_t *n_isects_dev, const int32_t *row_records,
+                                        void *key_hist, int key_bits, cudaStream_t stream) {
     GSB_REQUIRE(P >= 0 && tile_size > 0 && capacity >= 0, "bad sizes");
     GSB_REQUIRE(!packed || camera_ids != nullptr || P == 0, "camera_ids required when packed");
+    GSB_REQUIRE(key_hist == nullptr || (key_bits > 0 && key_bits <= 32), "key_bits: 1..32 with a histogram");
     auto tk = reinterpret_cast<uint32_t *>(tile_keys);
     auto recs = reinterpret_cast<const int4 *>(row_records);
+    auto hist = reinterpret_cast<uint32_t *>(key_hist);
     GSB_REQUIRE(tile_width < 65536 && tile_height < 32768, "tile grid too large");
     if (P > 0) {
-        unsigned nblk = (unsigned)gsb_isect_num_blocks(P);
+        const int64_t nblk = gsb_isect_num_blocks(P);
+        // with a histogram to feed, few CTAs walk the row blocks (one flush of the counters per CTA)
+        unsigned grid = (unsigned)nblk;
+        if (hist != nullptr && grid > 148 * 6) grid = 148 * 6;
         if (packed)
-            emit_perm_kernel<true><<<nblk, kThreads, 0, stream>>>(P, N, perm, means2d, radii, camera_ids, tile_size,
+            emit_perm_kernel<true><<<grid, kThreads, 0, stream>>>(P, N, perm, means2d, radii, camera_ids, tile_size,
                                                                   tile_width, tile_height, tile_n_bits,
                                                                   tiles_per_gauss, block_offsets, tk, flatten_ids,
-                                                                  capacity, recs);
+                                                                  capacity, recs, nblk, hist, key_bits);
         else
-            emit_perm_kernel<false><<<nblk, kThreads, 0, stream>>>(P, N, perm, means2d, radii, camera_ids, tile_size,
+            emit_perm_kernel<false><<<grid, kThreads, 0, stream>>>(P, N, perm, means2d, radii, camera_ids, tile_size,
                                                                    tile_width, tile_height, tile_n_bits,
                                                                    tiles_per_gauss, block_offsets, tk, flatten_ids,
-                                                                   capacity, recs);
+                                                                   capacity, recs, nblk, hist, key_bits);
         if (int e = gsb_check_launch("isect_emit_perm")) return e;
     }
     if (n_isects_dev != nullptr && capacity > 0) {

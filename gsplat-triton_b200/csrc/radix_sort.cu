@@ -281,7 +281,8 @@ onesweep_kernel(int64_t n, const int64_t *__restrict__ n_dev, const KeyT *__rest
 
 template <typename KeyT>
 int sort_pairs(int64_t n, const int64_t *n_dev, int end_bit, KeyT *keys, KeyT *keys_alt, int32_t *vals,
-               int32_t *vals_alt, void *temp, int64_t temp_bytes, int *result_in_alt, cudaStream_t stream) {
+               int32_t *vals_alt, void *temp, int64_t temp_bytes, int *result_in_alt, cudaStream_t stream,
+               bool prepared = false) {
     *result_in_alt = 0;
     if (n == 0 || end_bit == 0) return GSB_OK;
     constexpr int kTile = TileOf<KeyT>::kTile;
@@ -293,7 +294,8 @@ int sort_pairs(int64_t n, const int64_t *n_dev, int end_bit, KeyT *keys, KeyT *k
                       (long long)(words * 4));
         return GSB_ERR_INVALID;
     }
-    cudaError_t e = cudaMemsetAsync(temp, 0, (size_t)words * 4, stream);
+    cudaError_t e = cudaSuccess;
+    if (!prepared) e = cudaMemsetAsync(temp, 0, (size_t)words * 4, stream);
     if (e != cudaSuccess) {
         gsb_set_error("radix sort: memset: %s", cudaGetErrorString(e));
         return GSB_ERR_CUDA;
@@ -314,9 +316,11 @@ int sort_pairs(int64_t n, const int64_t *n_dev, int end_bit, KeyT *keys, KeyT *k
     uint32_t *hist = reinterpret_cast<uint32_t *>(temp);
     uint32_t *tickets = hist + (int64_t)passes * kBins;
     uint32_t *states = tickets + 64;
-    const unsigned hgrid = (unsigned)(tiles < 148 * 8 ? tiles : 148 * 8);
-    histogram_kernel<KeyT><<<hgrid, kThreads, 0, stream>>>(n, n_dev, keys, passes, end_bit, hist);
-    if (int rc = gsb_check_launch("radix_histogram")) return rc;
+    if (!prepared) {  // else: the caller cleared `temp` (gsb_radix_prepare) and its own kernels filled the histograms
+        const unsigned hgrid = (unsigned)(tiles < 148 * 8 ? tiles : 148 * 8);
+        histogram_kernel<KeyT><<<hgrid, kThreads, 0, stream>>>(n, n_dev, keys, passes, end_bit, hist);
+        if (int rc = gsb_check_launch("radix_histogram")) return rc;
+    }
     KeyT *kin = keys, *kout = keys_alt;
     int32_t *vin = vals, *vout = vals_alt;
     for (int p = 0; p < passes; ++p) {
@@ -347,6 +351,32 @@ extern "C" int gsb_radix_sort_pairs_u32(int64_t n, const int64_t *n_dev, int end
     return sort_pairs<uint32_t>(n, n_dev, end_bit, reinterpret_cast<uint32_t *>(keys),
                                 reinterpret_cast<uint32_t *>(keys_alt), vals, vals_alt, temp, temp_bytes,
                                 result_in_alt_host, stream);
+}
+
+// The producer of the keys can count the digits itself (it holds every key in a register anyway) and spare the sort
+// its histogram pass: gsb_radix_prepare clears `temp` (gsb_radix_temp_bytes(n, end_bit) bytes); the producer adds, for
+// every key and every pass p < ceil(end_bit / 8), one count to ((uint32_t *)temp)[p * 256 + ((key >> 8 p) & mask_p)]
+// (mask_p = 255, or the remaining bits in the last pass); gsb_radix_sort_pairs_u32_prepared then runs the passes only.
+extern "C" int gsb_radix_prepare(int64_t n, int end_bit, void *temp, int64_t temp_bytes, cudaStream_t stream) {
+    GSB_REQUIRE(n >= 0 && end_bit >= 0 && end_bit <= 64, "bad sizes");
+    const int64_t need = gsb_radix_temp_bytes(n, end_bit);
+    GSB_REQUIRE(temp != nullptr && temp_bytes >= need, "temp buffer too small");
+    cudaError_t e = cudaMemsetAsync(temp, 0, (size_t)need, stream);
+    if (e != cudaSuccess) {
+        gsb_set_error("radix prepare: memset: %s", cudaGetErrorString(e));
+        return GSB_ERR_CUDA;
+    }
+    return GSB_OK;
+}
+
+extern "C" int gsb_radix_sort_pairs_u32_prepared(int64_t n, const int64_t *n_dev, int end_bit, int32_t *keys,
+                                                 int32_t *keys_alt, int32_t *vals, int32_t *vals_alt, void *temp,
+                                                 int64_t temp_bytes, int *result_in_alt_host, cudaStream_t stream) {
+    GSB_REQUIRE(n >= 0 && n < ((int64_t)1 << 30) && end_bit >= 0 && end_bit <= 32, "bad sizes (n < 2^30)");
+    GSB_REQUIRE(result_in_alt_host != nullptr, "result_in_alt_host is required");
+    return sort_pairs<uint32_t>(n, n_dev, end_bit, reinterpret_cast<uint32_t *>(keys),
+                                reinterpret_cast<uint32_t *>(keys_alt), vals, vals_alt, temp, temp_bytes,
+                                result_in_alt_host, stream, true);
 }
 
 extern "C" int gsb_radix_sort_pairs_u64(int64_t n, const int64_t *n_dev, int end_bit, int64_t *keys,

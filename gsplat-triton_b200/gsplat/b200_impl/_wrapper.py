@@ -618,10 +618,12 @@ def _isect_presorted(means2d, radii, depths, camera_ids, C, N, P, packed, tile_s
     records = torch.empty((P, 4), dtype=torch.int32, device=dev)
     # rows without tiles get an all-ones key: the emitting rows are one contiguous run of the sorted order
     row_keys = torch.empty((P,), dtype=torch.int32, device=dev)
+    # the kernels that write sort keys also count their digits: the sorts then start with their first pass
+    row_temp = _radix_temp(P, 32, dev, True) if (_own_sort() and P > 0) else None
     lib.gsb_isect_row_tiles_keys(P, N, int(packed), ptr(means2d), ptr(radii), ptr(depths), ptr(camera_ids), tile_size,
                                  tile_width, tile_height, tb, ptr(rows), ptr(tiles_per_gauss), ptr(records),
-                                 ptr(row_keys), st)
-    sorted_keys, perm = _sort_pairs_u32(row_keys, rows, 32)
+                                 ptr(row_keys), ptr(row_temp), st)
+    sorted_keys, perm = _sort_pairs_u32(row_keys, rows, 32, None, row_temp)
     block_sums = torch.empty((max(nblk, 1),), dtype=torch.int32, device=dev)
     block_offsets = torch.empty((nblk + 1,), dtype=torch.int64, device=dev)
     # GSPLAT_B200_ISECT=bin: tile binning (csrc/isect_bin.cu) when the (camera, tile) bins fit its count matrix;
@@ -663,11 +665,12 @@ def _isect_presorted(means2d, radii, depths, camera_ids, C, N, P, packed, tile_s
             # the hand-written sort takes the device-side count itself; the library sort needs the tail padded with
             # keys that sort last
             pad = n_dev if not _own_sort() else None
-            lib.gsb_isect_emit_perm_cap(P, N, int(packed), ptr(perm), ptr(means2d), ptr(radii), ptr(camera_ids),
-                                        tile_size, tile_width, tile_height, tb, ptr(tiles_per_gauss),
-                                        ptr(block_offsets), ptr(tile_keys), ptr(flatten_ids), n_isects, pad,
-                                        ptr(records), st)
-            tile_keys, flatten_ids = _sort_pairs_u32(tile_keys, flatten_ids, tb + cb, n_dev)
+            tile_temp = _radix_temp(n_isects, tb + cb, dev, True) if (_own_sort() and tb + cb > 0) else None
+            lib.gsb_isect_emit_perm_hist(P, N, int(packed), ptr(perm), ptr(means2d), ptr(radii), ptr(camera_ids),
+                                         tile_size, tile_width, tile_height, tb, ptr(tiles_per_gauss),
+                                         ptr(block_offsets), ptr(tile_keys), ptr(flatten_ids), n_isects, pad,
+                                         ptr(records), ptr(tile_temp), tb + cb, st)
+            tile_keys, flatten_ids = _sort_pairs_u32(tile_keys, flatten_ids, tb + cb, n_dev, tile_temp)
         lib.gsb_isect_finalize_cap(n_isects, n_dev if n_isects > 0 else None, ptr(tile_keys), ptr(flatten_ids),
                                    ptr(depths), C, tile_width, tile_height, tb, ptr(isect_ids), ptr(offsets), st)
     if pending is None:
@@ -683,19 +686,33 @@ def _own_sort() -> bool:
     return os.environ.get("GSPLAT_B200_SORT_IMPL", "onesweep") != "cub"
 
 
-def _radix_sort(keys: Tensor, vals: Tensor, end_bit: int, n_dev: Optional[int] = None) -> Tuple[Tensor, Tensor]:
+def _radix_temp(n: int, end_bit: int, device, prepare: bool) -> Tensor:
+    """Scratch of one onesweep sort; `prepare`: cleared now, so that the kernel that produces the keys can add its
+    digit counts and the sort skips its histogram pass (gsb_radix_prepare)."""
+    temp_bytes = int(lib.gsb_radix_temp_bytes(n, end_bit))
+    temp = torch.empty((max(temp_bytes, 1),), dtype=torch.uint8, device=device)
+    if prepare:
+        lib.gsb_radix_prepare(n, end_bit, ptr(temp), temp.numel(), stream_of(temp))
+    return temp
+
+
+def _radix_sort(keys: Tensor, vals: Tensor, end_bit: int, n_dev: Optional[int] = None,
+                prepared: Optional[Tensor] = None) -> Tuple[Tensor, Tensor]:
     """Stable LSD radix sort of (uint32|int64 bit pattern, int32) pairs over bits [0, end_bit) with the hand-written
-    onesweep kernels (csrc/radix_sort.cu). `n_dev`: device address of an int64 item count (<= keys.numel())."""
+    onesweep kernels (csrc/radix_sort.cu). `n_dev`: device address of an int64 item count (<= keys.numel());
+    `prepared`: a `_radix_temp(..., prepare=True)` buffer whose histograms the producer of the keys has filled."""
     import ctypes
 
     n = keys.numel()
     keys_alt = torch.empty_like(keys)
     vals_alt = torch.empty_like(vals)
-    temp_bytes = int(lib.gsb_radix_temp_bytes(n, end_bit))
-    temp = torch.empty((max(temp_bytes, 1),), dtype=torch.uint8, device=keys.device)
+    temp = prepared if prepared is not None else _radix_temp(n, end_bit, keys.device, False)
     in_alt = ctypes.c_int(0)
-    fn = lib.gsb_radix_sort_pairs_u32 if keys.dtype == torch.int32 else lib.gsb_radix_sort_pairs_u64
-    fn(n, n_dev, end_bit, ptr(keys), ptr(keys_alt), ptr(vals), ptr(vals_alt), ptr(temp), temp_bytes,
+    if prepared is not None:
+        fn = lib.gsb_radix_sort_pairs_u32_prepared
+    else:
+        fn = lib.gsb_radix_sort_pairs_u32 if keys.dtype == torch.int32 else lib.gsb_radix_sort_pairs_u64
+    fn(n, n_dev, end_bit, ptr(keys), ptr(keys_alt), ptr(vals), ptr(vals_alt), ptr(temp), temp.numel(),
        ctypes.addressof(in_alt), stream_of(keys))
     return (keys_alt, vals_alt) if in_alt.value else (keys, vals)
 
@@ -717,12 +734,13 @@ def _sort_pairs(keys: Tensor, vals: Tensor, end_bit: int) -> Tuple[Tensor, Tenso
     return (keys_alt, vals_alt) if in_alt.value else (keys, vals)
 
 
-def _sort_pairs_u32(keys: Tensor, vals: Tensor, end_bit: int, n_dev: Optional[int] = None) -> Tuple[Tensor, Tensor]:
+def _sort_pairs_u32(keys: Tensor, vals: Tensor, end_bit: int, n_dev: Optional[int] = None,
+                    prepared: Optional[Tensor] = None) -> Tuple[Tensor, Tensor]:
     """Stable LSD radix sort of (uint32 bit pattern, int32) pairs over bits [0, end_bit)."""
     import ctypes
 
     if _own_sort():
-        return _radix_sort(keys, vals, end_bit, n_dev)
+        return _radix_sort(keys, vals, end_bit, n_dev, prepared)
     n = keys.numel()
     keys_alt = torch.empty_like(keys)
     vals_alt = torch.empty_like(vals)

@@ -185,6 +185,13 @@ def rasterization(
         start = torch.cuda.Event()
         start.record(main)
 
+        # leaves enter the graph on the caller's stream (a free view), not on the side stream: autograd ties a leaf's
+        # gradient accumulation to the stream current at its first use
+        def enter(t):
+            return t.view_as(t) if (t is not None and t.requires_grad and t.is_leaf) else t
+
+        means, covars, quats, scales, viewmats, Ks = (enter(t) for t in (means, covars, quats, scales, viewmats, Ks))
+
     def project():
         return fully_fused_projection(
             means, covars, quats, scales, viewmats, Ks, width, height,

@@ -208,7 +208,17 @@ int gsb_isect_finalize_cap(int64_t n_isects, const int64_t *n_isects_dev, const 
 int gsb_isect_row_tiles_keys(int64_t P, int N, int packed, const float *means2d, const int32_t *radii,
                              const float *depths, const int64_t *camera_ids, int tile_size, int tile_width,
                              int tile_height, int tile_n_bits, int32_t *rows, int32_t *tiles_per_gauss,
-                             int32_t *row_records, int32_t *row_keys, cudaStream_t stream);
+                             int32_t *row_records, int32_t *row_keys, void *key_hist, cudaStream_t stream);
+/* Producers that count the digits of the keys they write, so that the sort that follows skips its histogram pass
+ * (gsb_radix_prepare + gsb_radix_sort_pairs_u32_prepared): key_hist = the sort's temp buffer (or NULL). row_tiles_keys
+ * counts the 4 x 8-bit digits of row_keys; emit_perm_hist those of the key_bits-bit (camera | tile) words it emits
+ * (otherwise = gsb_isect_emit_perm_cap). */
+int gsb_isect_emit_perm_hist(int64_t P, int N, int packed, const int32_t *perm, const float *means2d,
+                             const int32_t *radii, const int64_t *camera_ids, int tile_size, int tile_width,
+                             int tile_height, int tile_n_bits, const int32_t *tiles_per_gauss,
+                             const int64_t *block_offsets, int32_t *tile_keys, int32_t *flatten_ids,
+                             int64_t capacity, const int64_t *n_isects_dev, const int32_t *row_records,
+                             void *key_hist, int key_bits, cudaStream_t stream);
 int gsb_isect_count_perm_records(int64_t P, const int32_t *perm, const int32_t *row_records, int32_t *sorted_records,
                                  int32_t *block_sums, int64_t *block_offsets, int64_t *n_isects_out,
                                  cudaStream_t stream);
@@ -323,6 +333,14 @@ int gsb_radix_sort_pairs_u32(int64_t n, const int64_t *n_dev, int end_bit, int32
 int gsb_radix_sort_pairs_u64(int64_t n, const int64_t *n_dev, int end_bit, int64_t *keys, int64_t *keys_alt,
                              int32_t *vals, int32_t *vals_alt, void *temp, int64_t temp_bytes,
                              int *result_in_alt_host, cudaStream_t stream);
+/* The producer of the keys may count the digits itself and spare the sort its histogram pass: gsb_radix_prepare clears
+ * `temp`; the producer adds, for every key and every pass p < ceil(end_bit / 8), one count to
+ * ((uint32_t *)temp)[p * 256 + ((key >> 8 p) & mask_p)] (mask_p = 255, or the remaining bits in the last pass);
+ * gsb_radix_sort_pairs_u32_prepared then runs the passes only (no memset, no histogram kernel). */
+int gsb_radix_prepare(int64_t n, int end_bit, void *temp, int64_t temp_bytes, cudaStream_t stream);
+int gsb_radix_sort_pairs_u32_prepared(int64_t n, const int64_t *n_dev, int end_bit, int32_t *keys, int32_t *keys_alt,
+                                      int32_t *vals, int32_t *vals_alt, void *temp, int64_t temp_bytes,
+                                      int *result_in_alt_host, cudaStream_t stream);
 
 /* ---- distributed exchange rows (rendering.py:413-494, distributed.py:170-257) -----------------
  * One fused row per projected Gaussian: means2d(2) depths(1) conics(3) opacities(1) colors(D)
