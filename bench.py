@@ -249,6 +249,7 @@ def _stage_table(summary, steps, meta, n_local, C, D, K, work, peaks, sm_mhz):
         # the producers of the keys count the digits: the sorts run their passes only
         "gsb_radix_sort_pairs_u32_prepared": 4 * 16 * P + (0 if binned else math.ceil((bits - 32) / 8) * 16 * I),
         "gsb_isect_emit_perm_hist": 20 * P + 8 * I,
+        "gsb_isect_emit_chunks": 20 * P + 8 * I,
         "gsb_isect_count_perm_records": 20 * P + 16 * P,
         # the rows' records twice (count, scatter) + perm / depth bits once, 12 bytes per intersection out, offsets;
         # the chunks x bins count matrix the kernels pass between them is overhead, not counted

@@ -196,12 +196,6 @@ row_keys_kernel(int64_t P, int N, const float *__restrict__ depths, const int64_
 __device__ __forceinline__ void hist_clear(uint32_t *s_hist, int passes) {
     for (int i = threadIdx.x; i < passes * 256; i += blockDim.x) s_hist[i] = 0u;
 }
-__device__ __forceinline__ void hist_add(uint32_t *s_hist, uint32_t key, int passes, int end_bit) {
-    for (int p = 0; p < passes; ++p) {
-        const int bits = min(8, end_bit - 8 * p);
-        atomicAdd(&s_hist[p * 256 + ((key >> (8 * p)) & ((1u << bits) - 1u))], 1u);
-    }
-}
 __device__ __forceinline__ void hist_flush(const uint32_t *s_hist, uint32_t *hist, int passes) {
     for (int i = threadIdx.x; i < passes * 256; i += blockDim.x) {
         const uint32_t c = s_hist[i];
@@ -220,10 +214,12 @@ row_tiles_kernel(int64_t P, int N, const float *__restrict__ means2d, const int3
         hist_clear(s_hist, 4);
         __syncthreads();
     }
-    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < P; i += (int64_t)gridDim.x * kThreads) {
+    for (int64_t i0 = (int64_t)blockIdx.x * kThreads; i0 < P; i0 += (int64_t)gridDim.x * kThreads) {
+        const int64_t i = i0 + threadIdx.x;
+        const bool live = i < P;
         int cnt = 0;
         int4 rec = make_int4(0, 0, 0, 0);
-        const int r = radii[i];
+        const int r = live ? radii[i] : 0;
         if (r > 0) {
             float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * i);
             TileBox b = tile_box(m.x, m.y, r, tile_size, tw, th);
@@ -231,15 +227,20 @@ row_tiles_kernel(int64_t P, int N, const float *__restrict__ means2d, const int3
             const uint32_t cam = (uint32_t)(PACKED ? camera_ids[i] : (i / N));
             rec = make_int4(b.x0 | (b.y0 << 16), b.x1 - b.x0, (int)(cam << tile_n_bits), cnt);
         }
-        rows[i] = (int32_t)i;
-        tiles_per_gauss[i] = cnt;
-        if (records != nullptr) records[i] = rec;
+        if (live) {
+            rows[i] = (int32_t)i;
+            tiles_per_gauss[i] = cnt;
+            if (records != nullptr) records[i] = rec;
+        }
         // the depth-sort key of the row: its depth bits, or all ones for a row without tiles, so that the rows that
         // emit intersections form one contiguous run of the sorted order (the binning kernels of isect_bin.cu rely on it)
         if (row_keys != nullptr) {
-            const uint32_t key = cnt > 0 ? (uint32_t)__float_as_int(depths[i]) : 0xffffffffu;
-            row_keys[i] = key;
-            if (key_hist != nullptr) hist_add(s_hist, key, 4, 32);
+            uint32_t key = 0xffffffffu;
+            if (live) {
+                if (cnt > 0) key = (uint32_t)__float_as_int(depths[i]);
+                row_keys[i] = key;
+            }
+            if (key_hist != nullptr) gsb_hist_add(s_hist, key, live, 4, 32);
         }
     }
     if (key_hist != nullptr) {
@@ -357,24 +358,30 @@ emit_perm_kernel(int64_t P, int N, const int32_t *__restrict__ perm, const float
         s_start[tid] = block_exclusive_scan(cnt, s_warp, block_total);
         __syncthreads();
         const int64_t base = block_offsets[blk];
-        for (int j = tid; j < block_total; j += kThreads) {
-            // last row r with s_start[r] <= j (rows without tiles share their successor's start and are skipped)
-            int lo = 0, hi_ = kThreads;  // invariant: s_start[lo] <= j < s_start[hi_] (s_start[kThreads] = block_total)
+        for (int j0 = 0; j0 < block_total; j0 += kThreads) {
+            const int j = j0 + tid;
+            bool live = j < block_total;
+            uint32_t key = 0u;
+            if (live) {
+                // last row r with s_start[r] <= j (rows without tiles share their successor's start and are skipped)
+                int lo = 0, hi_ = kThreads;  // invariant: s_start[lo] <= j < s_start[hi_] (s_start[kThreads] = block_total)
 #pragma unroll
-            for (int step = 0; step < 8; ++step) {
-                const int mid = (lo + hi_) >> 1;
-                if (s_start[mid] <= j) lo = mid; else hi_ = mid;
+                for (int step = 0; step < 8; ++step) {
+                    const int mid = (lo + hi_) >> 1;
+                    if (s_start[mid] <= j) lo = mid; else hi_ = mid;
+                }
+                const int t = j - s_start[lo];
+                const int w = s_w[lo], xy = s_xy[lo];
+                const int dy = t / w, dx = t - dy * w;
+                const int64_t out = base + j;
+                live = out < capacity;  // speculative capacity (gsb_isect_emit_perm_cap): never write past the buffers
+                if (live) {
+                    key = s_hi[lo] | (uint32_t)(((xy >> 16) + dy) * tw + (xy & 0xffff) + dx);
+                    tile_keys[out] = key;
+                    flatten_ids[out] = s_row[lo];
+                }
             }
-            const int t = j - s_start[lo];
-            const int w = s_w[lo], xy = s_xy[lo];
-            const int dy = t / w, dx = t - dy * w;
-            const int64_t out = base + j;
-            if (out < capacity) {  // speculative capacity (gsb_isect_emit_perm_cap): never write past the buffers
-                const uint32_t key = s_hi[lo] | (uint32_t)(((xy >> 16) + dy) * tw + (xy & 0xffff) + dx);
-                tile_keys[out] = key;
-                flatten_ids[out] = s_row[lo];
-                if (key_hist != nullptr) hist_add(s_hist, key, passes, key_bits);
-            }
+            if (key_hist != nullptr) gsb_hist_add(s_hist, key, live, passes, key_bits);
         }
         __syncthreads();  // the row tables are rewritten by the next block
     }

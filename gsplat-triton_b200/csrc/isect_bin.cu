@@ -142,9 +142,10 @@ __device__ __forceinline__ void build_marks(int64_t a, int64_t b_end, int64_t P,
     __syncthreads();
 }
 
-// (camera, tile) bin and owning row of slot j (relative to the chunk) from its scanned marker
-__device__ __forceinline__ int bin_of_slot(uint32_t m, int j, int first_off, const int4 *__restrict__ rows0, int tw,
-                                           int n_tiles, int tile_n_bits, int &krel) {
+// tile (inside its camera), camera word (camera << tile_n_bits) and owning row of slot j (relative to the chunk) from
+// its scanned marker
+__device__ __forceinline__ int tile_of_slot(uint32_t m, int j, int first_off, const int4 *__restrict__ rows0, int tw,
+                                            uint32_t &cam_word, int &krel) {
     krel = (int)(m & 0xffffu);
     const int p = (int)(m >> 16);
     const int t = j - p + (p == 0 ? first_off : 0);
@@ -154,8 +155,65 @@ __device__ __forceinline__ int bin_of_slot(uint32_t m, int j, int first_off, con
     int dx = t - dy * w;
     if (dx < 0) { dy -= 1; dx += w; }
     if (dx >= w) { dy += 1; dx -= w; }
-    const int tile = ((rec.x >> 16) + dy) * tw + (rec.x & 0xffff) + dx;
-    return (int)((uint32_t)rec.z >> tile_n_bits) * n_tiles + tile;
+    cam_word = (uint32_t)rec.z;
+    return ((rec.x >> 16) + dy) * tw + (rec.x & 0xffff) + dx;
+}
+
+// (camera, tile) bin of slot j
+__device__ __forceinline__ int bin_of_slot(uint32_t m, int j, int first_off, const int4 *__restrict__ rows0, int tw,
+                                           int n_tiles, int tile_n_bits, int &krel) {
+    uint32_t cam_word;
+    const int tile = tile_of_slot(m, j, first_off, rows0, tw, cam_word, krel);
+    return (int)(cam_word >> tile_n_bits) * n_tiles + tile;
+}
+
+// ---------------------------------------------------------------- emission for the radix path
+// The (camera | tile) words + row ids of the chunk's slots in emission order, stored coalesced, and (optionally) the
+// digit histograms of the words for the tile sort that follows. Same output as emit_perm_kernel (isect.cu), whose
+// per-slot binary search made it issue-bound (ncu: 71 % issue-active, 37 M warp instructions at cfg2).
+__global__ void __launch_bounds__(kThreads)
+emit_chunks_kernel(int64_t capacity, const int64_t *__restrict__ n_dev, int64_t P, const int4 *__restrict__ srec,
+                   const int64_t *__restrict__ block_offsets, int64_t nblk, const int32_t *__restrict__ perm, int tw,
+                   uint32_t *__restrict__ tile_keys, int32_t *__restrict__ flatten_ids,
+                   uint32_t *__restrict__ key_hist, int key_bits) {
+    __shared__ __align__(16) uint32_t mark[kT];
+    __shared__ uint32_t s_hist[4 * 256];
+    __shared__ ChunkSmem s;
+    const int tid = threadIdx.x;
+    const int64_t n = clamp_count(capacity, n_dev);
+    const int64_t a = (int64_t)blockIdx.x * kT;
+    if (a >= n) return;
+    const int64_t b_end = a + kT < n ? a + kT : n;
+    const int count = (int)(b_end - a);
+    const int passes = (key_bits + 7) / 8;
+    if (key_hist != nullptr)
+        for (int i = tid; i < passes * 256; i += kThreads) s_hist[i] = 0u;
+    build_marks(a, b_end, P, srec, block_offsets, nblk, mark, s);
+    const int64_t row0 = (int64_t)s.b0 * kRowBlock;
+    const int4 *rows0 = srec + row0;
+    const int first_off = s.first_off;
+#pragma unroll 4
+    for (int i = 0; i < kItems; ++i) {
+        const int j = i * kThreads + tid;
+        const bool live = j < count;
+        uint32_t key = 0u;
+        if (live) {
+            int krel;
+            uint32_t cam_word;
+            const int tile = tile_of_slot(mark[j], j, first_off, rows0, tw, cam_word, krel);
+            key = cam_word | (uint32_t)tile;
+            tile_keys[a + j] = key;
+            flatten_ids[a + j] = perm[row0 + krel];
+        }
+        if (key_hist != nullptr) gsb_hist_add(s_hist, key, live, passes, key_bits);
+    }
+    if (key_hist != nullptr) {
+        __syncthreads();
+        for (int i = tid; i < passes * 256; i += kThreads) {
+            const uint32_t c = s_hist[i];
+            if (c) atomicAdd(&key_hist[i], c);
+        }
+    }
 }
 
 // ---------------------------------------------------------------- counts per (chunk, bin)
@@ -504,6 +562,23 @@ bin_scatter_kernel(int64_t capacity, const int64_t *__restrict__ n_dev, int64_t 
 }
 
 }  // namespace
+
+extern "C" int gsb_isect_emit_chunks(int64_t P, int64_t capacity, const int64_t *n_isects_dev,
+                                     const int32_t *sorted_records, const int32_t *perm, const int64_t *block_offsets,
+                                     int tile_width, int32_t *tile_keys, int32_t *flatten_ids, void *key_hist,
+                                     int key_bits, cudaStream_t stream) {
+    GSB_REQUIRE(P >= 0 && capacity >= 0, "bad sizes");
+    GSB_REQUIRE(P < ((int64_t)1 << 31) && capacity < ((int64_t)1 << 31), "more than 2^31-1 rows or intersections");
+    GSB_REQUIRE(key_hist == nullptr || (key_bits > 0 && key_bits <= 32), "key_bits: 1..32 with a histogram");
+    if (P == 0 || capacity == 0) return GSB_OK;
+    const int chunks = (int)((capacity + kT - 1) / kT);
+    const int64_t nblk = (P + kRowBlock - 1) / kRowBlock;
+    emit_chunks_kernel<<<chunks, kThreads, 0, stream>>>(
+        capacity, n_isects_dev, P, reinterpret_cast<const int4 *>(sorted_records), block_offsets, nblk, perm,
+        tile_width, reinterpret_cast<uint32_t *>(tile_keys), flatten_ids, reinterpret_cast<uint32_t *>(key_hist),
+        key_bits);
+    return gsb_check_launch("isect_emit_chunks");
+}
 
 extern "C" int gsb_isect_bin_max_bins(void) { return kMaxBins; }
 

@@ -630,7 +630,12 @@ def _isect_presorted(means2d, radii, depths, camera_ids, C, N, P, packed, tile_s
     # default: two radix passes over the intersections (measured faster so far: DESIGN.md 4)
     binned = (C * tile_width * tile_height <= int(lib.gsb_isect_bin_max_bins())
               and os.environ.get("GSPLAT_B200_ISECT", "radix") == "bin")
-    if binned:
+    # GSPLAT_B200_EMIT=chunks: emission over chunks of 8192 slots with the owner rows from a marker max-scan
+    # (csrc/isect_bin.cu) instead of a binary search per slot over 256-row blocks; needs the records gathered into
+    # depth order. Same output, measured equal (54 vs 56 us per launch, 1.674 vs 1.672 ms per step at cfg2): both
+    # kernels are bound by their stores and histogram counts, not by the search. Default: the search.
+    chunked = binned or (_own_sort() and os.environ.get("GSPLAT_B200_EMIT", "search") == "chunks")
+    if chunked:
         sorted_records = torch.empty((P, 4), dtype=torch.int32, device=dev)
         lib.gsb_isect_count_perm_records(P, ptr(perm), ptr(records), ptr(sorted_records), ptr(block_sums),
                                          ptr(block_offsets), block_offsets.data_ptr() + 8 * nblk, st)
@@ -666,10 +671,14 @@ def _isect_presorted(means2d, radii, depths, camera_ids, C, N, P, packed, tile_s
             # keys that sort last
             pad = n_dev if not _own_sort() else None
             tile_temp = _radix_temp(n_isects, tb + cb, dev, True) if (_own_sort() and tb + cb > 0) else None
-            lib.gsb_isect_emit_perm_hist(P, N, int(packed), ptr(perm), ptr(means2d), ptr(radii), ptr(camera_ids),
-                                         tile_size, tile_width, tile_height, tb, ptr(tiles_per_gauss),
-                                         ptr(block_offsets), ptr(tile_keys), ptr(flatten_ids), n_isects, pad,
-                                         ptr(records), ptr(tile_temp), tb + cb, st)
+            if chunked:
+                lib.gsb_isect_emit_chunks(P, n_isects, n_dev, ptr(sorted_records), ptr(perm), ptr(block_offsets),
+                                          tile_width, ptr(tile_keys), ptr(flatten_ids), ptr(tile_temp), tb + cb, st)
+            else:
+                lib.gsb_isect_emit_perm_hist(P, N, int(packed), ptr(perm), ptr(means2d), ptr(radii), ptr(camera_ids),
+                                             tile_size, tile_width, tile_height, tb, ptr(tiles_per_gauss),
+                                             ptr(block_offsets), ptr(tile_keys), ptr(flatten_ids), n_isects, pad,
+                                             ptr(records), ptr(tile_temp), tb + cb, st)
             tile_keys, flatten_ids = _sort_pairs_u32(tile_keys, flatten_ids, tb + cb, n_dev, tile_temp)
         lib.gsb_isect_finalize_cap(n_isects, n_dev if n_isects > 0 else None, ptr(tile_keys), ptr(flatten_ids),
                                    ptr(depths), C, tile_width, tile_height, tb, ptr(isect_ids), ptr(offsets), st)

@@ -222,6 +222,13 @@ int gsb_isect_emit_perm_hist(int64_t P, int N, int packed, const int32_t *perm, 
 int gsb_isect_count_perm_records(int64_t P, const int32_t *perm, const int32_t *row_records, int32_t *sorted_records,
                                  int32_t *block_sums, int64_t *block_offsets, int64_t *n_isects_out,
                                  cudaStream_t stream);
+/* The emission step of the default pipeline on the sorted records of gsb_isect_count_perm_records: chunks of 8192
+ * slots of the emission order, owner rows from a marker max-scan instead of a search per slot; writes the same
+ * tile_keys / flatten_ids as gsb_isect_emit_perm_cap and (key_hist = the tile sort's prepared temp buffer, or NULL)
+ * counts the digits of the key_bits-bit words. */
+int gsb_isect_emit_chunks(int64_t P, int64_t capacity, const int64_t *n_isects_dev, const int32_t *sorted_records,
+                          const int32_t *perm, const int64_t *block_offsets, int tile_width, int32_t *tile_keys,
+                          int32_t *flatten_ids, void *key_hist, int key_bits, cudaStream_t stream);
 int gsb_isect_bin_max_bins(void);
 int64_t gsb_isect_bin_temp_bytes(int64_t capacity, int bins);
 int gsb_isect_bin(int64_t P, int64_t capacity, const int64_t *n_isects_dev, const int32_t *sorted_records,

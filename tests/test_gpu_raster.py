@@ -186,8 +186,10 @@ def test_isect_tile_binning_equals_radix_path(C, N, W, H, rmax, spread, monkeypa
     depths = (torch.rand(C, N) * 20 + 0.05).to(DEV)
     depths[:, ::7] = 3.0
     out = {}
-    for binning in ("bin", "bin_all_radix", "radix"):
+    for binning in ("bin", "bin_all_radix", "radix", "radix_search"):
         monkeypatch.setenv("GSPLAT_B200_ISECT", binning.split("_")[0])
+        # the radix path's emission: chunked (marker max-scan) or the default search per slot
+        monkeypatch.setenv("GSPLAT_B200_EMIT", "search" if binning == "radix_search" else "chunks")
         lib.gsb_set_option(2, int(binning == "bin_all_radix"))  # GSB_OPT_ISECT_BIN_RADIX
         try:
             tpg, ids, flat = isect_tiles(means2d, radii, depths, ts, tw, th)
@@ -197,8 +199,8 @@ def test_isect_tile_binning_equals_radix_path(C, N, W, H, rmax, spread, monkeypa
         fresh = isect_offset_encode(ids.clone(), C, tw, th)  # a clone carries no cached offsets: recomputed from ids
         assert torch.equal(cached, fresh)
         out[binning] = (tpg, ids, flat, cached)
-    for other in ("bin", "bin_all_radix"):
-        for a, b in zip(out[other], out["radix"]):
+    for other in ("bin", "bin_all_radix", "radix"):
+        for a, b in zip(out[other], out["radix_search"]):
             assert torch.equal(a, b)
     assert out["bin"][1].numel() > 8192
 
