@@ -388,3 +388,66 @@ extern "C" int gsb_radix_sort_pairs_u64(int64_t n, const int64_t *n_dev, int end
                                           reinterpret_cast<unsigned long long *>(keys_alt), vals, vals_alt, temp,
                                           temp_bytes, result_in_alt_host, stream);
 }
+
+// ---- the same sort for callers that cannot allocate device memory (CUDA graph capture, serving loops, harnesses that
+// forbid cudaMalloc). No counterpart in the reference.
+// The scratch (digit histograms, tile tickets, look-back states) lives in a file-scope device array instead of a
+// caller-provided `temp` buffer: 2.1 MB per GPU that loads the library, held until exit, sized for
+// GSB_RADIX_NOALLOC_MAX_ITEMS = 2^21 pairs of 32-bit keys. Every call on a device shares this array: the entry point
+// clears it on the caller's stream before the passes, and two calls whose kernels overlap on the GPU (different
+// streams, no ordering between them) race on it.
+namespace {
+constexpr int64_t kNoAllocMaxItems = GSB_RADIX_NOALLOC_MAX_ITEMS;
+constexpr int64_t kNoAllocTiles = (kNoAllocMaxItems + TileOf<uint32_t>::kTile - 1) / TileOf<uint32_t>::kTile;
+constexpr int64_t kNoAllocWords = 4 * kBins + 64 + 4 * kNoAllocTiles * kBins;  // scratch_words(4 passes, tiles)
+constexpr int kNoAllocMaxDevices = 64;
+}  // namespace
+
+static __device__ __align__(256) uint32_t g_noalloc_scratch[kNoAllocWords];
+
+namespace {
+// Device address of g_noalloc_scratch on the CURRENT device. In host code the array's name is only a handle for the
+// runtime, not an address a kernel can use: it is resolved once per device with cudaGetSymbolAddress.
+int noalloc_scratch_ptr(uint32_t **out) {
+    static uint32_t *cached[kNoAllocMaxDevices] = {nullptr};
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e != cudaSuccess) {
+        gsb_set_error("radix sort (noalloc): cudaGetDevice: %s", cudaGetErrorString(e));
+        return GSB_ERR_CUDA;
+    }
+    const bool cacheable = device >= 0 && device < kNoAllocMaxDevices;
+    uint32_t *p = cacheable ? __atomic_load_n(&cached[device], __ATOMIC_ACQUIRE) : nullptr;
+    if (p == nullptr) {
+        void *addr = nullptr;
+        e = cudaGetSymbolAddress(&addr, g_noalloc_scratch);
+        if (e != cudaSuccess || addr == nullptr) {
+            gsb_set_error("radix sort (noalloc): cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return GSB_ERR_CUDA;
+        }
+        p = static_cast<uint32_t *>(addr);
+        if (cacheable) __atomic_store_n(&cached[device], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return GSB_OK;
+}
+}  // namespace
+
+extern "C" int gsb_radix_sort_pairs_u32_noalloc(int64_t n, const int64_t *n_dev, int end_bit, int32_t *keys,
+                                                int32_t *keys_alt, int32_t *vals, int32_t *vals_alt,
+                                                int *result_in_alt_host, cudaStream_t stream) {
+    GSB_REQUIRE(n >= 0 && end_bit >= 0 && end_bit <= 32, "bad sizes");
+    GSB_REQUIRE(result_in_alt_host != nullptr, "result_in_alt_host is required");
+    if (n > kNoAllocMaxItems) {
+        gsb_set_error("gsb_radix_sort_pairs_u32_noalloc: %lld items exceed the built-in scratch "
+                      "(GSB_RADIX_NOALLOC_MAX_ITEMS = %lld); use gsb_radix_sort_pairs_u32 with a temp buffer",
+                      (long long)n, (long long)kNoAllocMaxItems);
+        return GSB_ERR_INVALID;
+    }
+    uint32_t *scratch = nullptr;
+    if (int rc = noalloc_scratch_ptr(&scratch)) return rc;
+    // sort_pairs clears the words this n needs (cudaMemsetAsync on `stream`: no allocation) and runs the passes
+    return sort_pairs<uint32_t>(n, n_dev, end_bit, reinterpret_cast<uint32_t *>(keys),
+                                reinterpret_cast<uint32_t *>(keys_alt), vals, vals_alt, scratch,
+                                kNoAllocWords * (int64_t)sizeof(uint32_t), result_in_alt_host, stream);
+}

@@ -349,6 +349,18 @@ int gsb_radix_sort_pairs_u32_prepared(int64_t n, const int64_t *n_dev, int end_b
                                       int32_t *vals, int32_t *vals_alt, void *temp, int64_t temp_bytes,
                                       int *result_in_alt_host, cudaStream_t stream);
 
+/* The 32-bit sort for callers that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE.
+ * Same result as gsb_radix_sort_pairs_u32, but the scratch is a file-scope device array inside the library (2.1 MB per
+ * GPU that loads it, held until exit) instead of a caller-provided `temp`: the call allocates nothing (no cudaMalloc /
+ * cudaFree, no allocating library routine). Limit: n <= GSB_RADIX_NOALLOC_MAX_ITEMS pairs, larger n is rejected with
+ * GSB_ERR_INVALID. The caller still passes the keys / values and their ping-pong buffers. Every call on a device shares
+ * the one array (cleared by the call itself on `stream`): calls that may OVERLAP on the GPU (different streams without
+ * ordering) race on it. The current device must be the one the buffers live on. */
+#define GSB_RADIX_NOALLOC_MAX_ITEMS (1 << 21)
+int gsb_radix_sort_pairs_u32_noalloc(int64_t n, const int64_t *n_dev, int end_bit, int32_t *keys, int32_t *keys_alt,
+                                     int32_t *vals, int32_t *vals_alt, int *result_in_alt_host, cudaStream_t stream);
+
 /* ---- distributed exchange rows (rendering.py:413-494, distributed.py:170-257) -----------------
  * One fused row per projected Gaussian: means2d(2) depths(1) conics(3) opacities(1) colors(D)
  * radii(1, int32 bit pattern) = (8+D) 4-byte words, so a single all-to-all per direction
