@@ -553,6 +553,14 @@ def get_mailbox(group=None) -> PeerMailbox:
     return box
 
 
+def check_mailboxes() -> None:
+    """Raises if a wait kernel of an exchange already executed gave up on a peer (`PeerMailbox.check`). Called by
+    `rasterization(distributed=True)` right after its one host synchronisation of the step, so rows that never
+    arrived are reported in the step that would have composited them, not in the next one."""
+    for box in _MAILBOXES.values():
+        box.check()
+
+
 def close_mailboxes() -> None:
     for box in _MAILBOXES.values():
         box.close()

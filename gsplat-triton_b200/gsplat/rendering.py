@@ -56,6 +56,7 @@ from .distributed import (
     peer_exchange_available,
     PushExchange,
     SplitExchange,
+    check_mailboxes,
     peer_exchange_packed,
     peer_exchange_rows,
     unpack_rows,
@@ -410,6 +411,8 @@ def rasterization(
     render_colors, render_alphas = composite_all()
     if pending is not None:
         n_isects = pending.wait()
+        if distributed and BACKEND == "b200":
+            check_mailboxes()  # the wait kernel of this step's exchange ran before the count that was just read back
         if n_isects > pending.capacity:  # the estimate was too small: redo this part with exact sizes
             tiles_per_gauss, isect_ids, flatten_ids, isect_offsets, pending = intersect(False)
             render_colors, render_alphas = composite_all()
@@ -434,3 +437,26 @@ def rasterization(
             [render_colors[..., :-1], render_colors[..., -1:] / render_alphas.clamp(min=1e-10)], dim=-1
         )
     return render_colors, render_alphas, meta
+
+
+def __getattr__(name):
+    """`gsplat.rendering._rasterization`: the reference's pure-PyTorch twin of rasterization() (its
+    `gsplat/rendering.py:601-760`, what its own `tests/test_rasterization.py` compares a backend against). It is the
+    REFERENCE's function, taken at first use from the reference checkout named by GSPLAT_REFERENCE_PATH and evaluated
+    in this module's namespace — exactly what happens when the reference's own rendering.py grows a `b200` branch
+    (INTEGRATION.md option A): its backend-dispatched calls (`isect_tiles`, `isect_offset_encode`,
+    `spherical_harmonics`) resolve to this backend, projection and compositing stay the reference's `_torch_impl`."""
+    if name != "_rasterization":
+        raise AttributeError(f"module {__name__!r} has no attribute {name!r}")
+    import ast
+
+    ref = os.environ.get("GSPLAT_REFERENCE_PATH")
+    path = os.path.join(ref, "gsplat", "rendering.py") if ref else None
+    if not path or not os.path.exists(path):
+        raise AttributeError("gsplat.rendering._rasterization is the reference's own function: set "
+                             "GSPLAT_REFERENCE_PATH to a checkout of gsplat-triton (there is no copy in this package)")
+    source = open(path).read()
+    node = next(n for n in ast.parse(source).body if isinstance(n, ast.FunctionDef) and n.name == "_rasterization")
+    code = compile(ast.Module(body=[node], type_ignores=[]), path, "exec")
+    exec(code, globals())
+    return globals()["_rasterization"]
