@@ -10,6 +10,8 @@ that (reference) module are pointed at the b200 ones before pytest starts — th
 `rendering.py:11-29` switch imports; everything else in the file (`quat_scale_to_covar_preci`, `proj`, `world_to_cam`,
 the unfused projection) stays the reference's CUDA extension. GSPLAT_REF_TEST_OPS=reference runs the same file without
 the substitution (the reference's CUDA backend against its own torch code on this GPU: the control).
+`--suite triton`: the reference's `triton_tests/{test_isect,test_fused_proj,test_sh,test_ras2pix}.py` (its Triton ops
+against `_torch_impl`, the protocol SURVEY 4 names) with the ops of `gsplat.triton_impl._wrapper` pointed at b200's.
 `--suite rasterization` (default):
 
 The test renders 24 parameter combinations (per-view colours x SH degree x RGB / RGB+D / D x packed) with
@@ -47,7 +49,7 @@ def main():
         i = sys.argv.index("--suite")
         suite = sys.argv[i + 1]
         del sys.argv[i:i + 2]
-    assert suite in ("rasterization", "basic"), suite
+    assert suite in ("rasterization", "basic", "triton"), suite
     index_op = os.environ.get("GSPLAT_REF_TEST_INDEX_OP", "reference")
     import gsplat.cuda._wrapper as W  # the reference's module, through GSPLAT_REFERENCE_PATH
 
@@ -65,6 +67,25 @@ def main():
         for fn in ("fully_fused_projection", "isect_offset_encode", "isect_tiles", "rasterize_to_pixels",
                    "spherical_harmonics"):
             setattr(W, fn, getattr(B, fn))
+    if suite == "triton" and ops == "b200":
+        # triton_tests/*.py import the ops from gsplat.triton_impl._wrapper (the reference's module): same substitution.
+        # test_fused_proj.py calls `_FullyFusedProjection.apply` with the Triton wrapper's 13 positional arguments
+        # (triton_impl/_wrapper.py:299); ours takes the camera model as a 14th
+        import gsplat.b200_impl as B
+        import gsplat.b200_impl._wrapper as BW
+        import gsplat.triton_impl._wrapper as TW
+
+        assert os.path.realpath(TW.__file__).startswith(os.path.realpath(REF)), TW.__file__
+        for fn in ("fully_fused_projection", "isect_offset_encode", "isect_tiles", "rasterize_to_pixels",
+                   "spherical_harmonics"):
+            setattr(TW, fn, getattr(B, fn))
+
+        class _FullyFusedProjection:
+            @staticmethod
+            def apply(*args):
+                return BW._FullyFusedProjection.apply(*args, "pinhole")
+
+        TW._FullyFusedProjection = _FullyFusedProjection
     # test_basic.py:21-22 puts a skipif mark on its fixture; pytest >= 9 (this image) turns that into a collection
     # error, earlier versions ignored the mark. Keep the file unmodified: ignore marks on fixtures, as pytest 8 did.
     import _pytest.mark.structures as MS
@@ -79,11 +100,19 @@ def main():
     MS.store_mark = lenient_store_mark
     lib.gsb_reset_launch_count()
     test_file = os.path.join(REF, "tests", f"test_{suite}.py")
-    rc = pytest.main([test_file, "-q", "-p", "no:cacheprovider", "--rootdir", os.path.join(REF, "tests"),
+    if suite == "triton":
+        tests = [a for a in sys.argv[1:] if a.endswith(".py")] or ["test_isect.py", "test_fused_proj.py", "test_sh.py",
+                                                                    "test_ras2pix.py"]
+        sys.argv[1:] = [a for a in sys.argv[1:] if not a.endswith(".py")]
+        test_file = [os.path.join(REF, "triton_tests", t) for t in tests]
+    else:
+        test_file = [test_file]
+    rc = pytest.main([*test_file, "-q", "-p", "no:cacheprovider", "--rootdir", os.path.dirname(test_file[0]),
                       *sys.argv[1:]])
     print("REFERENCE_TESTS " + json.dumps({
-        "file": f"tests/test_{suite}.py (reference, unmodified, from baseline/_ref)", "backend": R.BACKEND,
-        "pytest_exit_code": int(rc), "index_op": index_op, "ops_under_test": ops if suite == "basic" else "b200", "b200_kernel_launches": int(lib.gsb_launch_count()),
+        "file": ", ".join(os.path.relpath(t, REF) for t in test_file) + " (reference, unmodified, from baseline/_ref)",
+        "backend": R.BACKEND,
+        "pytest_exit_code": int(rc), "index_op": index_op, "ops_under_test": "b200" if suite == "rasterization" else ops, "b200_kernel_launches": int(lib.gsb_launch_count()),
         "gpu": torch.cuda.get_device_name(0)}), flush=True)
     sys.exit(int(rc))
 
