@@ -31,6 +31,57 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF = os.path.join(ROOT, "baseline", "_ref")
 
 
+_LAST_RASTER = {}
+
+
+def _recording(fn):
+    """rasterize_to_pixels that remembers the geometry of its last call (for `_classify_outliers`)."""
+    def rasterize_to_pixels(means2d, conics, colors, opacities, image_width, image_height, tile_size, isect_offsets,
+                            flatten_ids, *args, **kwargs):
+        _LAST_RASTER.update(means2d=means2d.detach(), conics=conics.detach(), opacities=opacities.detach(),
+                            W=image_width, H=image_height, ts=tile_size, offsets=isect_offsets, flat=flatten_ids)
+        return fn(means2d, conics, colors, opacities, image_width, image_height, tile_size, isect_offsets, flatten_ids,
+                  *args, **kwargs)
+    return rasterize_to_pixels
+
+
+def _classify_outliers(a, b, rtol, atol):
+    """For every pixel where two compositor images differ beyond tolerance: recompute, in float64, the alphas of the
+    pixel's sorted Gaussian list and report how close the nearest pair sits to one of the compositor's two decision
+    thresholds (alpha >= 1/255; stop before T (1 - alpha) <= 1e-4). A relative margin of ~1e-6 or less means that
+    float32 rounding decides the pair: the images differ by that one contribution, not by an error."""
+    import torch
+
+    g = _LAST_RASTER
+    bad = ((a - b).abs() > atol + rtol * b.abs()).any(dim=-1)
+    pixels = bad.nonzero()
+    print(f"\nOUTLIERS {int(bad.sum())} pixel(s) beyond rtol={rtol:g} atol={atol:g} of {bad.numel()}")
+    C = g["offsets"].shape[0]
+    tw = g["offsets"].shape[2]
+    offs = torch.cat([g["offsets"].flatten().long(), torch.tensor([g["flat"].numel()], device=bad.device)])
+    m2, cn, op = g["means2d"].reshape(-1, 2).double(), g["conics"].reshape(-1, 3).double(), g["opacities"].reshape(-1).double()
+    for c, y, x in pixels[:16].tolist():
+        t = (c * g["offsets"].shape[1] + y // g["ts"]) * tw + x // g["ts"]
+        ids = g["flat"][int(offs[t]):int(offs[t + 1])].long()
+        d = torch.tensor([x + 0.5, y + 0.5], device=bad.device, dtype=torch.float64) - m2[ids]
+        q = cn[ids]
+        sigma = 0.5 * (q[:, 0] * d[:, 0] ** 2 + q[:, 2] * d[:, 1] ** 2) + q[:, 1] * d[:, 0] * d[:, 1]
+        alpha = torch.clamp_max(op[ids] * torch.exp(-sigma), 0.999)
+        alpha_margin = ((alpha * 255.0 - 1.0).abs())[sigma >= 0]
+        T, t_margin = 1.0, float("inf")
+        for al in alpha[(sigma >= 0) & (alpha >= 1.0 / 255.0)].tolist():
+            nxt = T * (1.0 - al)
+            t_margin = min(t_margin, abs(nxt / 1e-4 - 1.0))
+            if nxt <= 1e-4:
+                break
+            T = nxt
+        err = float((a[c, y, x] - b[c, y, x]).abs().max())
+        am = float(alpha_margin.min()) if alpha_margin.numel() else float("inf")
+        verdict = "threshold flip" if min(am, t_margin) < 1e-5 else "UNEXPLAINED"
+        print(f"OUTLIER camera {c} pixel ({y}, {x}): max |diff| {err:.3e}; {ids.numel()} Gaussians in its tile; nearest "
+              f"pair to alpha = 1/255: relative margin {am:.2e}; to T = 1e-4: {t_margin:.2e} -> {verdict}")
+
+
 def main():
     if not os.path.isdir(os.path.join(REF, "tests")):
         raise SystemExit("baseline/_ref/tests is missing: run tools/install_reference.sh in the build container")
@@ -86,6 +137,26 @@ def main():
                 return BW._FullyFusedProjection.apply(*args, "pinhole")
 
         TW._FullyFusedProjection = _FullyFusedProjection
+    if ops == "b200" and suite in ("basic", "triton"):
+        # image mismatches of the compositor tests are classified before the assertion is re-raised
+        target = W if suite == "basic" else TW
+        target.rasterize_to_pixels = _recording(target.rasterize_to_pixels)
+        assert_close = torch.testing.assert_close
+
+        def classifying_assert_close(actual, expected, *args, **kwargs):
+            try:
+                return assert_close(actual, expected, *args, **kwargs)
+            except AssertionError:
+                g = _LAST_RASTER
+                if g and actual.dim() == 4 and tuple(actual.shape[1:3]) == (g["H"], g["W"]):
+                    try:
+                        _classify_outliers(actual.detach(), expected.detach(), kwargs.get("rtol") or 1.3e-6,
+                                           kwargs.get("atol") or 1e-5)
+                    except Exception as e:  # the diagnosis must never hide the assertion
+                        print("OUTLIER classification failed:", repr(e))
+                raise
+
+        torch.testing.assert_close = classifying_assert_close
     # test_basic.py:21-22 puts a skipif mark on its fixture; pytest >= 9 (this image) turns that into a collection
     # error, earlier versions ignored the mark. Keep the file unmodified: ignore marks on fixtures, as pytest 8 did.
     import _pytest.mark.structures as MS
