@@ -10,6 +10,7 @@
 // [C,N,K,3] is never materialised and, in the backward pass, v_coeffs accumulates in registers
 // over cameras and is written once with plain stores (no zero-fill, no atomics).
 #include "common.cuh"
+#include "bulk_async.cuh"
 #include "peer_layout.cuh"
 #include "gsplat_b200.h"
 
@@ -371,6 +372,369 @@ sh_colors_bwd_kernel(int64_t N, int C, int K, const float *__restrict__ means, c
     smem_to_rows<NB * 3>(s_cf, v_coeffs, r0, rows, K * 3);
 }
 
+
+// ---- the fused colour kernels with asynchronous staging ----------------------------------------------------------
+// The kernels above stage a block's coefficient rows with ordinary loads: four 16-byte loads per thread in flight,
+// three rounds per block, then a CTA barrier, then the math, then (backward) another barrier and the stores. ncu on the
+// backward kernel: 4 CTAs per SM (127 registers), 4.0-4.5 TB/s: neither the memory system nor the issue slots are
+// busy, the phases of the few resident CTAs do not overlap well enough. Here the copies run behind the arithmetic:
+//   * persistent CTAs (one wave), each walking the row tiles blockIdx.x, + gridDim.x, ...; two stages of shared memory;
+//   * the NEXT tile's rows are requested before the math of the current tile starts and nobody waits on them until the
+//     next iteration; no CTA barrier after set-up: a warp synchronises only with the copies of its own 32 rows;
+//   * rows sit 13 x 16 bytes apart (odd), so the quarter-warps of an LDS.128 / STS.128 touch all 32 banks once:
+//     12 vector accesses per row where the scalar layout (stride 49 floats) needs 48;
+//   * backward: the gradient row overwrites the coefficient row in place and leaves from there.
+// Two ways to move the rows (GSB_OPT_SH_STAGING, measured against each other and against the plain kernels):
+//   MODE 1  cp.async.bulk (SASS UBLKCP, the 1-D form of TMA): every thread hands the copy engine its own 192-byte row,
+//           completion counted in bytes on its warp's mbarrier (SYNCS); backward: one bulk store per row, the stage is
+//           refilled once the thread's own store has finished reading it. The copy engine takes its operands from
+//           uniform registers, so the 32 requests of a warp issue one lane at a time (~9 issue slots each);
+//   MODE 2  cp.async (SASS LDGSTS): the lanes of a warp copy the warp's contiguous 6 KB of rows in 16-byte pieces,
+//           lane-consecutive (every request a full 512-byte run), into the padded rows; 12 instructions per thread and
+//           tile, completion per thread (cp.async.wait_group) + __syncwarp; backward: the rows leave the same way
+//           (LDS.128 + coalesced STG.128).
+// The arithmetic per row is the one of sh_colors_{fwd,bwd}_kernel, in the same order.
+constexpr int kBulkStages = 2;
+constexpr int kBulkCtasPerSm = 4;
+template <int NB3>
+struct BulkRow {
+    static_assert(NB3 % 4 == 0, "rows are copied in 16-byte units");
+    static constexpr int Q = NB3 / 4;               // 16-byte units per coefficient row
+    static constexpr int SQ = (Q & 1) ? Q : Q + 1;  // row stride in units: odd
+    static constexpr unsigned kRowBytes = NB3 * 4u, kStrideBytes = SQ * 16u, kStageBytes = kStrideBytes * kThreads;
+    static constexpr size_t kSmem = (size_t)kBulkStages * kStageBytes;
+};
+constexpr unsigned kBarStageStride = 8u * (kThreads / 32);  // bytes between the two stages' barrier rows
+
+__device__ __forceinline__ void cp_async16(unsigned dst_smem, const void *src_global) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src_global) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+// until at most the newest group of this thread is still in flight
+__device__ __forceinline__ void cp_async_wait_all_but_newest() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
+// Moves the coefficient rows of a tile into a stage and says when they are there; one object per thread.
+template <int MODE, int NB3>
+struct RowStager {
+    using R = BulkRow<NB3>;
+    unsigned row0;   // this thread's row in stage 0 (shared address)
+    unsigned bar0;   // MODE 1: this warp's barrier of stage 0
+    unsigned warp0;  // MODE 2: first row of this warp in stage 0
+    int64_t N;
+    const float *coeffs;
+
+    __device__ __forceinline__ void setup(unsigned char *s_rows, unsigned long long (*s_bar)[kThreads / 32], int64_t n,
+                                          const float *c) {
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        N = n;
+        coeffs = c;
+        row0 = bulk::smem_addr(s_rows) + threadIdx.x * R::kStrideBytes;
+        warp0 = bulk::smem_addr(s_rows) + (unsigned)(warp * 32) * R::kStrideBytes;
+        bar0 = bulk::smem_addr(&s_bar[0][warp]);
+        if (MODE == 1) {
+            if (lane == 0) {
+#pragma unroll
+                for (int s = 0; s < kBulkStages; ++s) bulk::mbar_init(bar0 + s * kBarStageStride, 32u);
+            }
+            bulk::mbar_init_fence();
+            __syncthreads();
+        }
+    }
+    __device__ __forceinline__ unsigned row(unsigned s) const { return row0 + s * R::kStageBytes; }
+
+    // request the rows of `tile` for stage s. The stage's previous contents must be dead for the whole warp (MODE 2:
+    // other lanes write this thread's row; the caller separates the tiles with __syncwarp) resp. this thread (MODE 1).
+    __device__ __forceinline__ void issue(int64_t tile, unsigned s) const {
+        if (MODE == 1) {
+            const int64_t r = tile * kThreads + threadIdx.x;
+            const unsigned bar = bar0 + s * kBarStageStride;
+            if (r < N) {
+                bulk::mbar_arrive_expect_tx(bar, R::kRowBytes);
+                bulk::load(row0 + s * R::kStageBytes, coeffs + (size_t)r * NB3, R::kRowBytes, bar);
+            } else {
+                bulk::mbar_arrive(bar);
+            }
+        } else {
+            const int lane = threadIdx.x & 31;
+            const int64_t first = tile * kThreads + (threadIdx.x & ~31);  // first row of this warp
+            const int64_t left = N - first;
+            const int units = (int)(left < 32 ? (left < 0 ? 0 : left) : 32) * R::Q;
+            const float4 *src = reinterpret_cast<const float4 *>(coeffs + (size_t)first * NB3);
+            const unsigned dst = warp0 + s * R::kStageBytes;
+#pragma unroll
+            for (int i = 0; i < R::Q; ++i) {
+                const int u = lane + 32 * i;
+                if (u < units) cp_async16(dst + (unsigned)(u / R::Q) * R::kStrideBytes + (unsigned)(u % R::Q) * 16u, src + u);
+            }
+            cp_async_commit();
+        }
+    }
+    // MODE 2 only: an empty group, so that "all but the newest" always means "everything up to the current tile"
+    __device__ __forceinline__ void issue_nothing() const {
+        if (MODE == 2) cp_async_commit();
+    }
+    // the rows of iteration i (stage i & 1) are in shared memory, visible to every lane of the warp
+    __device__ __forceinline__ void wait(unsigned i) const {
+        if (MODE == 1) {
+            bulk::mbar_wait(bar0 + (i & 1u) * kBarStageStride, (i >> 1) & 1u);
+        } else {
+            cp_async_wait_all_but_newest();
+            __syncwarp();
+        }
+    }
+};
+
+// col[ch] += sum_k bases[k] * row[3 k + ch], k ascending per channel (the order of the scalar kernels), the row
+// streamed through registers 16 bytes at a time
+template <int NB>
+__device__ __forceinline__ void bulk_row_dot_bases(unsigned row, const float *bases, float *col) {
+#pragma unroll
+    for (int j = 0; j < NB * 3 / 4; ++j) {
+        const float4 q = bulk::lds128(row + 16u * j);
+        const float v[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int m = 0; m < 4; ++m) col[(4 * j + m) % 3] = fmaf(bases[(4 * j + m) / 3], v[m], col[(4 * j + m) % 3]);
+    }
+}
+
+template <int DEG, int MODE>
+__global__ void __launch_bounds__(kThreads, kBulkCtasPerSm)
+sh_colors_fwd_bulk_kernel(int64_t N, int C, const float *__restrict__ means, const float *__restrict__ campos,
+                          const float *__restrict__ coeffs, const int32_t *__restrict__ radii,
+                          float *__restrict__ colors) {
+    constexpr int NB = (DEG + 1) * (DEG + 1), NB3 = NB * 3;
+    extern __shared__ __align__(128) unsigned char s_rows[];
+    __shared__ __align__(8) unsigned long long s_bar[kBulkStages][kThreads / 32];
+    RowStager<MODE, NB3> stager;
+    stager.setup(s_rows, s_bar, N, coeffs);
+    const int64_t n_tiles = (N + kThreads - 1) / kThreads;
+    int64_t t = blockIdx.x;
+    if (t >= n_tiles) return;
+    stager.issue(t, 0u);
+    for (unsigned i = 0;; ++i) {
+        const unsigned s = i & 1u;
+        const int64_t tn = t + gridDim.x;
+        // the other stage was last read in the previous iteration (values consumed): refill it behind this tile's math
+        if (MODE == 2) __syncwarp();
+        if (tn < n_tiles) stager.issue(tn, s ^ 1u);
+        else stager.issue_nothing();
+        const int64_t r = t * kThreads + threadIdx.x;
+        const bool live = r < N;
+        float mx = 0.f, my = 0.f, mz = 0.f;
+        if (live) {
+            mx = means[3 * r]; my = means[3 * r + 1]; mz = means[3 * r + 2];
+        }
+        stager.wait(i);
+        if (live) {
+            const unsigned row = stager.row(s);
+            for (int c = 0; c < C; ++c) {
+                const size_t e = (size_t)c * N + r;
+                float col[3] = {0.f, 0.f, 0.f};
+                if (radii[e] > 0) {
+                    float x = mx - campos[3 * c], y = my - campos[3 * c + 1], z = mz - campos[3 * c + 2];
+                    float inorm = rsqrtf(x * x + y * y + z * z);
+                    float bases[NB];
+                    sh_bases<DEG>(x * inorm, y * inorm, z * inorm, bases);
+                    bulk_row_dot_bases<NB>(row, bases, col);
+                }
+                float *op = colors + 3 * e;
+                op[0] = fmaxf(col[0] + 0.5f, 0.f);
+                op[1] = fmaxf(col[1] + 0.5f, 0.f);
+                op[2] = fmaxf(col[2] + 0.5f, 0.f);
+            }
+        }
+        if (tn >= n_tiles) break;
+        t = tn;
+    }
+}
+
+// ONE_CAM (C == 1): a row's gradient is the outer product bases x v_colour, written straight over the coefficient
+// row: no accumulators over cameras, half the registers. (Several cameras with v_means: 48 accumulators + 16 bases +
+// 16 projected gradients do not fit 128 registers without spilling in the camera loop: 3 CTAs per SM there.)
+template <int DEG, bool NEED_MEANS, bool ONE_CAM, int MODE>
+__global__ void __launch_bounds__(kThreads, (NEED_MEANS && !ONE_CAM) ? kBulkCtasPerSm - 1 : kBulkCtasPerSm)
+sh_colors_bwd_bulk_kernel(int64_t N, int C, const float *__restrict__ means, const float *__restrict__ campos,
+                          const float *__restrict__ coeffs, const int32_t *__restrict__ radii,
+                          const float *__restrict__ v_colors, float *__restrict__ v_coeffs,
+                          float *__restrict__ v_means) {
+    constexpr int NB = (DEG + 1) * (DEG + 1), NB3 = NB * 3;
+    using R = BulkRow<NB3>;
+    extern __shared__ __align__(128) unsigned char s_rows[];
+    __shared__ __align__(8) unsigned long long s_bar[kBulkStages][kThreads / 32];
+    RowStager<MODE, NB3> stager;
+    stager.setup(s_rows, s_bar, N, coeffs);
+    const int lane = threadIdx.x & 31;
+    const int64_t n_tiles = (N + kThreads - 1) / kThreads;
+    int64_t t = blockIdx.x;
+    if (t >= n_tiles) return;
+    stager.issue(t, 0u);
+    for (unsigned i = 0;; ++i) {
+        const unsigned s = i & 1u;
+        const int64_t tn = t + gridDim.x;
+        // the other stage holds the previous tile's gradient rows: they must have left it before it is refilled
+        if (MODE == 1) {
+            if (tn < n_tiles) bulk::wait_stores_read();  // this thread's own bulk store has finished reading
+        } else {
+            __syncwarp();  // every lane's LDS of the cooperative store below has returned (its STG has issued)
+        }
+        if (tn < n_tiles) stager.issue(tn, s ^ 1u);
+        else stager.issue_nothing();
+        const int64_t r = t * kThreads + threadIdx.x;
+        const bool live = r < N;
+        float mx = 0.f, my = 0.f, mz = 0.f;
+        if (live) {
+            mx = means[3 * r]; my = means[3 * r + 1]; mz = means[3 * r + 2];
+        }
+        stager.wait(i);
+        const unsigned row = stager.row(s);
+        if (live) {
+            float acc[ONE_CAM ? 1 : NB3];
+            if (!ONE_CAM) {
+#pragma unroll
+                for (int k = 0; k < NB3; ++k) acc[k] = 0.f;
+            }
+            float vmx = 0.f, vmy = 0.f, vmz = 0.f;
+            bool written = false;
+            const int n_cam = ONE_CAM ? 1 : C;
+            for (int c = 0; c < n_cam; ++c) {
+                const size_t e = (size_t)c * N + r;
+                if (radii[e] <= 0) continue;
+                float x = mx - campos[3 * c], y = my - campos[3 * c + 1], z = mz - campos[3 * c + 2];
+                float inorm = rsqrtf(x * x + y * y + z * z);
+                x *= inorm; y *= inorm; z *= inorm;
+                float bases[NB];
+                sh_bases<DEG>(x, y, z, bases);
+                float col[3] = {0.5f, 0.5f, 0.5f};
+                bulk_row_dot_bases<NB>(row, bases, col);
+                const float *vp = v_colors + 3 * e;
+                // clamp_min(x, 0) passes the gradient where x >= 0 (torch semantics)
+                const float v[3] = {col[0] >= 0.f ? vp[0] : 0.f, col[1] >= 0.f ? vp[1] : 0.f,
+                                    col[2] >= 0.f ? vp[2] : 0.f};
+                if (NEED_MEANS) {
+                    float g[NB];
+#pragma unroll
+                    for (int j = 0; j < R::Q; ++j) {
+                        const float4 q = bulk::lds128(row + 16u * j);
+                        const float w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                        for (int m = 0; m < 4; ++m) {
+                            const int el = 4 * j + m, k = el / 3, ch = el % 3;
+                            g[k] = ch == 0 ? w[m] * v[0] : fmaf(w[m], v[ch], g[k]);
+                        }
+                    }
+                    float vx, vy, vz;
+                    sh_bases_vjp<DEG>(x, y, z, g, vx, vy, vz);
+                    float dot = x * vx + y * vy + z * vz;
+                    vmx += (vx - dot * x) * inorm;
+                    vmy += (vy - dot * y) * inorm;
+                    vmz += (vz - dot * z) * inorm;
+                }
+                if (ONE_CAM) {
+#pragma unroll
+                    for (int j = 0; j < R::Q; ++j)
+                        bulk::sts128(row + 16u * j, bases[(4 * j) / 3] * v[(4 * j) % 3],
+                                     bases[(4 * j + 1) / 3] * v[(4 * j + 1) % 3],
+                                     bases[(4 * j + 2) / 3] * v[(4 * j + 2) % 3],
+                                     bases[(4 * j + 3) / 3] * v[(4 * j + 3) % 3]);
+                    written = true;
+                } else {
+#pragma unroll
+                    for (int k = 0; k < NB3; ++k) acc[k] = fmaf(bases[k / 3], v[k % 3], acc[k]);
+                }
+            }
+            if (ONE_CAM) {
+                if (!written) {
+#pragma unroll
+                    for (int j = 0; j < R::Q; ++j) bulk::sts128(row + 16u * j, 0.f, 0.f, 0.f, 0.f);
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < R::Q; ++j)
+                    bulk::sts128(row + 16u * j, acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
+            }
+            if (NEED_MEANS) {
+                v_means[3 * r] = vmx; v_means[3 * r + 1] = vmy; v_means[3 * r + 2] = vmz;
+            }
+            if (MODE == 1) {
+                bulk::fence_smem_writes();
+                bulk::store(v_coeffs + (size_t)r * NB3, row, R::kRowBytes);
+            }
+        }
+        if (MODE == 1) {
+            bulk::commit();
+        } else {
+            // the warp's gradient rows leave as one contiguous run, lane-consecutive 16-byte pieces
+            __syncwarp();
+            const int64_t first = t * kThreads + (threadIdx.x & ~31);
+            const int64_t left = N - first;
+            const int units = (int)(left < 32 ? (left < 0 ? 0 : left) : 32) * R::Q;
+            float4 *dst = reinterpret_cast<float4 *>(v_coeffs + (size_t)first * NB3);
+            const unsigned src = stager.warp0 + s * R::kStageBytes;
+#pragma unroll
+            for (int j = 0; j < R::Q; ++j) {
+                const int u = lane + 32 * j;
+                if (u < units)
+                    dst[u] = bulk::lds128(src + (unsigned)(u / R::Q) * R::kStrideBytes + (unsigned)(u % R::Q) * 16u);
+            }
+        }
+        if (tn >= n_tiles) break;
+        t = tn;
+    }
+    if (MODE == 1) bulk::wait_stores_read();  // shared memory has to outlive the copies that read it
+}
+
+// The staged kernels take rows of exactly NB3 floats (K = (deg+1)^2) at 16-byte aligned addresses; deg 3 (K = 16) is
+// the shape the path runs at. GSB_OPT_SH_STAGING: 0 = the plain-load kernels, 1 = cp.async.bulk, 2 = cp.async.
+inline int sh_staging_mode(int option, int degree, int K, const void *a, const void *b) {
+    const int mode = gsb_option(option);
+    const bool usable = degree == 3 && K == 16 && ((uintptr_t)a & 15u) == 0 && ((uintptr_t)b & 15u) == 0;
+    return usable && (mode == 1 || mode == 2) ? mode : 0;
+}
+
+template <typename Kernel>
+int sh_bulk_grid(Kernel kernel, size_t smem, int64_t N, int limit, unsigned &grid) {
+    int device = 0, sms = 0;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int resident = 0;  // CTAs of this kernel an SM holds: the persistent grid is exactly one wave
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, kernel, kThreads, smem);
+    if (e != cudaSuccess || sms <= 0 || resident <= 0) {
+        gsb_set_error("sh_colors (staged): %s", e != cudaSuccess ? cudaGetErrorString(e) : "kernel does not fit an SM");
+        return GSB_ERR_CUDA;
+    }
+    if (limit > 0 && limit < resident) resident = limit;
+    const int64_t tiles = (N + kThreads - 1) / kThreads, cap = (int64_t)sms * resident;
+    grid = (unsigned)(tiles < cap ? tiles : cap);
+    return GSB_OK;
+}
+
+template <int MODE>
+int launch_sh_colors_fwd_staged(int64_t N, int C, const float *means, const float *campos, const float *coeffs,
+                                const int32_t *radii, float *colors, cudaStream_t stream) {
+    auto kernel = sh_colors_fwd_bulk_kernel<3, MODE>;
+    constexpr size_t smem = BulkRow<48>::kSmem;
+    unsigned grid = 0;
+    if (int rc = sh_bulk_grid(kernel, smem, N, gsb_option(GSB_OPT_SH_FWD_CTAS), grid)) return rc;
+    kernel<<<grid, kThreads, smem, stream>>>(N, C, means, campos, coeffs, radii, colors);
+    return gsb_check_launch("sh_colors_fwd_staged");
+}
+
+template <int MODE>
+int launch_sh_colors_bwd_staged(int64_t N, int C, const float *means, const float *campos, const float *coeffs,
+                                const int32_t *radii, const float *v_colors, float *v_coeffs, float *v_means,
+                                cudaStream_t stream) {
+    constexpr size_t smem = BulkRow<48>::kSmem;
+    auto kernel = v_means != nullptr ? (C == 1 ? sh_colors_bwd_bulk_kernel<3, true, true, MODE>
+                                               : sh_colors_bwd_bulk_kernel<3, true, false, MODE>)
+                                     : (C == 1 ? sh_colors_bwd_bulk_kernel<3, false, true, MODE>
+                                               : sh_colors_bwd_bulk_kernel<3, false, false, MODE>);
+    unsigned grid = 0;
+    if (int rc = sh_bulk_grid(kernel, smem, N, gsb_option(GSB_OPT_SH_CTAS), grid)) return rc;
+    kernel<<<grid, kThreads, smem, stream>>>(N, C, means, campos, coeffs, radii, v_colors, v_coeffs, v_means);
+    return gsb_check_launch("sh_colors_bwd_staged");
+}
+
 }  // namespace
 
 #define DISPATCH_DEG(deg, ...)                                        \
@@ -417,6 +781,9 @@ extern "C" int gsb_sh_colors_fwd(int degree, int64_t N, int C, int K, const floa
     GSB_REQUIRE((degree + 1) * (degree + 1) <= K, "K is smaller than (degree+1)^2");
     GSB_REQUIRE(N >= 0 && C >= 0, "negative size");
     if (N == 0 || C == 0) return GSB_OK;
+    if (const int mode = sh_staging_mode(GSB_OPT_SH_FWD_STAGING, degree, K, coeffs, coeffs))
+        return mode == 1 ? launch_sh_colors_fwd_staged<1>(N, C, means, campos, coeffs, radii, colors, stream)
+                         : launch_sh_colors_fwd_staged<2>(N, C, means, campos, coeffs, radii, colors, stream);
     unsigned nblk = gsb_cdiv(N, kThreads);
     peer::PushRows none = {};
     DISPATCH_DEG(degree, (sh_colors_fwd_kernel<D, false><<<nblk, kThreads, 0, stream>>>(N, C, K, means, campos, coeffs, radii, colors, none)));
@@ -451,6 +818,11 @@ extern "C" int gsb_sh_colors_bwd(int degree, int64_t N, int C, int K, const floa
     GSB_REQUIRE((degree + 1) * (degree + 1) <= K, "K is smaller than (degree+1)^2");
     GSB_REQUIRE(N >= 0 && C >= 0, "negative size");
     if (N == 0) return GSB_OK;
+    if (const int mode = C >= 1 ? sh_staging_mode(GSB_OPT_SH_STAGING, degree, K, coeffs, v_coeffs) : 0)
+        return mode == 1 ? launch_sh_colors_bwd_staged<1>(N, C, means, campos, coeffs, radii, v_colors, v_coeffs,
+                                                          v_means, stream)
+                         : launch_sh_colors_bwd_staged<2>(N, C, means, campos, coeffs, radii, v_colors, v_coeffs,
+                                                          v_means, stream);
     unsigned nblk = gsb_cdiv(N, kThreads);
     if (v_means != nullptr) {
         DISPATCH_DEG(degree, (sh_colors_bwd_kernel<D, true><<<nblk, kThreads, 0, stream>>>(N, C, K, means, campos, coeffs, radii,

@@ -92,7 +92,10 @@ class _Lib:
             fn.argtypes = [t for t, _ in argl]
         self._dll = dll
         # kernel-variant switches for A/B runs (include/gsplat_b200.h: GSB_OPT_*); unset = the tuned defaults
-        for which, env in ((0, "GSPLAT_B200_FWD_VARIANT"), (1, "GSPLAT_B200_BWD_VARIANT")):
+        for which, env in ((0, "GSPLAT_B200_FWD_VARIANT"), (1, "GSPLAT_B200_BWD_VARIANT"),
+                           (3, "GSPLAT_B200_SH_STAGING"), (4, "GSPLAT_B200_FINALIZE_VEC"),
+                           (5, "GSPLAT_B200_SH_CTAS"), (6, "GSPLAT_B200_SH_FWD_STAGING"),
+                           (7, "GSPLAT_B200_SH_FWD_CTAS")):
             if os.environ.get(env):
                 dll.gsb_set_option(which, int(os.environ[env]))
         return dll

@@ -386,6 +386,26 @@ def view_dependent_colors(sh_degree: int, means: Tensor, viewmats: Tensor, coeff
                              radii.contiguous())
 
 
+# The staged colour kernels (csrc/sh.cu) run persistent CTAs. Alone on the GPU they take every SM slot that fits;
+# beside the intersection pipeline / the projection backward on rasterization()'s second stream they must not: a
+# persistent CTA never gives its slot back, so the other stream's (critical-path) kernels would queue behind the whole
+# colour kernel. Measured at cfg2 (ms per step): forward kernel on 1 CTA per SM + backward on 3: 1.639; both on all
+# four: 1.676 (no better than the plain kernels, 1.675); forward plain + backward on 4 / 3 / 2 / 1: 1.650 / 1.644 /
+# 1.644 / 1.684. rasterization() announces the two-stream case here; GSPLAT_B200_SH_FWD_CTAS / GSPLAT_B200_SH_CTAS pin
+# the caps for experiments.
+_COLOURS_BESIDE = [False]
+_GSB_OPT_SH_CTAS, _GSB_OPT_SH_FWD_CTAS = 5, 7
+
+
+def colour_kernels_share_the_gpu(flag: bool) -> None:
+    _COLOURS_BESIDE[0] = bool(flag)
+
+
+def _cap_colour_ctas(option: int, env: str, ctas_per_sm: int) -> None:
+    if os.environ.get(env) is None:
+        lib.gsb_set_option(option, ctas_per_sm)
+
+
 class _ViewColors(torch.autograd.Function):
     @staticmethod
     def forward(ctx, sh_degree, means, viewmats, coeffs, radii):
@@ -403,9 +423,11 @@ class _ViewColors(torch.autograd.Function):
                                        ptr(colors), world, C_local, N_total, n_base, peers, region, st)
             ex.pushed.add("colors")
         else:
+            _cap_colour_ctas(_GSB_OPT_SH_FWD_CTAS, "GSPLAT_B200_SH_FWD_CTAS", 1 if _COLOURS_BESIDE[0] else 0)
             lib.gsb_sh_colors_fwd(sh_degree, N, C, K, ptr(means), ptr(campos), ptr(coeffs), ptr(radii), ptr(colors), st)
         ctx.save_for_backward(means, campos, coeffs, radii)
         ctx.sh_degree = sh_degree
+        ctx.beside = _COLOURS_BESIDE[0]
         return colors
 
     @staticmethod
@@ -415,6 +437,7 @@ class _ViewColors(torch.autograd.Function):
         v_coeffs = torch.empty_like(coeffs)
         v_means = torch.empty_like(means) if ctx.needs_input_grad[1] else None
         v_colors = _f32(v_colors)
+        _cap_colour_ctas(_GSB_OPT_SH_CTAS, "GSPLAT_B200_SH_CTAS", 3 if ctx.beside else 0)
         lib.gsb_sh_colors_bwd(ctx.sh_degree, N, C, coeffs.shape[1], ptr(means), ptr(campos), ptr(coeffs), ptr(radii),
                               ptr(v_colors), ptr(v_coeffs), ptr(v_means), stream_of(means))
         return None, v_means, None, (v_coeffs if ctx.needs_input_grad[3] else None), None
@@ -471,9 +494,11 @@ class _ViewColorsPacked(torch.autograd.Function):
         campos = torch.empty((C, 3), dtype=torch.float32, device=dev)
         lib.gsb_camera_centers(C, ptr(viewmats), ptr(campos), st)
         dense = torch.empty((C * N, 3), dtype=torch.float32, device=dev)
+        _cap_colour_ctas(_GSB_OPT_SH_FWD_CTAS, "GSPLAT_B200_SH_FWD_CTAS", 1 if _COLOURS_BESIDE[0] else 0)
         lib.gsb_sh_colors_fwd(sh_degree, N, C, K, ptr(means), ptr(campos), ptr(coeffs), ptr(visible), ptr(dense), st)
         ctx.save_for_backward(means, campos, coeffs, visible, rows)
         ctx.sh_degree = sh_degree
+        ctx.beside = _COLOURS_BESIDE[0]
         return dense.index_select(0, rows)
 
     @staticmethod
@@ -484,6 +509,7 @@ class _ViewColorsPacked(torch.autograd.Function):
         v_dense.index_copy_(0, rows, _f32(v_colors))
         v_coeffs = torch.empty_like(coeffs)
         v_means = torch.empty_like(means) if ctx.needs_input_grad[1] else None
+        _cap_colour_ctas(_GSB_OPT_SH_CTAS, "GSPLAT_B200_SH_CTAS", 3 if ctx.beside else 0)
         lib.gsb_sh_colors_bwd(ctx.sh_degree, N, C, coeffs.shape[1], ptr(means), ptr(campos), ptr(coeffs), ptr(visible),
                               ptr(v_dense), ptr(v_coeffs), ptr(v_means), stream_of(means))
         return None, v_means, None, (v_coeffs if ctx.needs_input_grad[3] else None), None, None
@@ -861,12 +887,23 @@ def rasterize_to_pixels(
 
 
 # splat records packed ahead of the compositor call (rasterization() packs them on the caller's stream while the
-# intersection pipeline runs on the side stream): ((means2d, conics, opacities data pointers, rows), records)
+# intersection pipeline runs on the side stream): ((means2d, conics, opacities data pointers, rows), records,
+# zero-filled gradient buffer for the backward pass or None)
 _PREPACKED = [None]
 
 
-def prepack_splats(means2d: Tensor, conics: Tensor, opacities: Tensor) -> None:
-    """Runs gsb_rasterize_pack now for the next rasterize_to_pixels() call on exactly these (contiguous) tensors."""
+def _grad_widths(D: int, absgrad: bool):
+    """floats per projected row the backward compositor accumulates into: v_means2d, v_conics, v_colors, v_opacities
+    (, absgrad)"""
+    return (2, 3, D, 1) + ((2,) if absgrad else ())
+
+
+def prepack_splats(means2d: Tensor, conics: Tensor, opacities: Tensor, grad_channels: Optional[int] = None,
+                   absgrad: bool = False) -> None:
+    """Runs gsb_rasterize_pack now for the next rasterize_to_pixels() call on exactly these (contiguous) tensors.
+    With `grad_channels` (the colour channels of that call, when a gradient will be asked for) the zero-filled buffer
+    the backward compositor accumulates into is also made now: the caller's stream is idle here (the intersection
+    pipeline runs on the side stream), in the backward pass the fill would sit on the critical path."""
     if not (means2d.is_contiguous() and conics.is_contiguous() and opacities.is_contiguous()):
         return
     if means2d.dtype != torch.float32 or conics.dtype != torch.float32 or opacities.dtype != torch.float32:
@@ -874,7 +911,10 @@ def prepack_splats(means2d: Tensor, conics: Tensor, opacities: Tensor) -> None:
     P = opacities.numel()
     rec = torch.empty((2, max(P, 1), 4), dtype=torch.float32, device=means2d.device)
     lib.gsb_rasterize_pack(P, ptr(means2d), ptr(conics), ptr(opacities), ptr(rec[0]), ptr(rec[1]), stream_of(means2d))
-    _PREPACKED[0] = ((means2d.data_ptr(), conics.data_ptr(), opacities.data_ptr(), P), rec)
+    zero = None
+    if grad_channels is not None:
+        zero = torch.zeros((P * sum(_grad_widths(grad_channels, absgrad)),), dtype=torch.float32, device=means2d.device)
+    _PREPACKED[0] = ((means2d.data_ptr(), conics.data_ptr(), opacities.data_ptr(), P), rec, zero)
 
 
 class _RasterizeToPixels(torch.autograd.Function):
@@ -910,8 +950,11 @@ class _RasterizeToPixels(torch.autograd.Function):
             ctx.shapes = (conics.shape, opacities.shape)
             return render_colors, render_alphas
         hit, _PREPACKED[0] = _PREPACKED[0], None
+        ctx.zero_buf = None
         if hit is not None and hit[0] == (means2d.data_ptr(), conics.data_ptr(), opacities.data_ptr(), P):
             rec = hit[1]
+            if hit[2] is not None and hit[2].numel() == P * sum(_grad_widths(D, absgrad)):
+                ctx.zero_buf = hit[2]  # filled while this stream waited for the intersections
         else:
             rec = torch.empty((2, max(P, 1), 4), dtype=torch.float32, device=dev)
             lib.gsb_rasterize_pack(P, ptr(means2d), ptr(conics), ptr(opacities), ptr(rec[0]), ptr(rec[1]), st)
@@ -950,8 +993,10 @@ class _RasterizeToPixels(torch.autograd.Function):
         v_render_alphas = _f32(v_render_alphas)
         # one zero-filled buffer, five views: the kernel accumulates into them with reductions
         P = means2d.numel() // 2
-        widths = (2, 3, D, 1) + ((2,) if ctx.absgrad else ())
-        flat = torch.zeros((P * sum(widths),), dtype=torch.float32, device=dev)
+        widths = _grad_widths(D, ctx.absgrad)
+        flat, ctx.zero_buf = getattr(ctx, "zero_buf", None), None  # good for one backward pass only
+        if flat is None:
+            flat = torch.zeros((P * sum(widths),), dtype=torch.float32, device=dev)
         parts = flat.split([P * w for w in widths])
         v_means2d = parts[0].view(means2d.shape)
         v_conics = parts[1].view(conics_shape)

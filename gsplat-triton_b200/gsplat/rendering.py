@@ -259,18 +259,24 @@ def rasterization(
     else:
         if BACKEND == "b200" and not packed and colors.dim() == 3 and not viewmats.requires_grad:
             # dirs, the radii > 0 mask, + 0.5 and the clamp folded into the SH kernels (one pass over [C, N])
-            from .b200_impl._wrapper import view_dependent_colors
+            from .b200_impl._wrapper import colour_kernels_share_the_gpu, view_dependent_colors
 
             try:
+                colour_kernels_share_the_gpu(use_side)  # the second stream's kernels need SM slots beside them
                 colors = view_dependent_colors(sh_degree, means, viewmats, colors, radii)  # [C, N, 3]
             finally:
+                colour_kernels_share_the_gpu(False)
                 if push is not None:
                     set_push_context(None)
         elif BACKEND == "b200" and packed and colors.dim() == 3 and not viewmats.requires_grad:
             # same kernels over the dense [C, N] grid (mask scattered from the packed ids); only colours are gathered
-            from .b200_impl._wrapper import view_dependent_colors_packed
+            from .b200_impl._wrapper import colour_kernels_share_the_gpu, view_dependent_colors_packed
 
-            colors = view_dependent_colors_packed(sh_degree, means, viewmats, colors, camera_ids, gaussian_ids)
+            try:
+                colour_kernels_share_the_gpu(use_side)
+                colors = view_dependent_colors_packed(sh_degree, means, viewmats, colors, camera_ids, gaussian_ids)
+            finally:
+                colour_kernels_share_the_gpu(False)
         else:
             camtoworlds = torch.inverse(viewmats)
             if packed:
@@ -375,7 +381,12 @@ def rasterization(
         if tile_size == 16 and colors.shape[-1] <= channel_chunk:
             from .b200_impl._wrapper import prepack_splats
 
-            prepack_splats(means2d, conics, opacities)  # the compositor's splat records, also beside the side stream
+            # the compositor's splat records (and, when a gradient will be asked for, its zero-filled gradient
+            # buffer), also beside the side stream
+            wants_grad = (torch.is_grad_enabled() and os.environ.get("GSPLAT_B200_PREZERO", "1") == "1"
+                          and any(t.requires_grad for t in (means2d, conics, colors, opacities)))
+            prepack_splats(means2d, conics, opacities, grad_channels=colors.shape[-1] if wants_grad else None,
+                           absgrad=absgrad)
         with torch.cuda.stream(side):
             side.wait_event(overlap)
             tiles_per_gauss, isect_ids, flatten_ids, isect_offsets, pending = intersect(speculate)

@@ -47,11 +47,23 @@ void gsb_reset_launch_count(void);
  *                        3 = the same compositor fed by a producer warp (double-buffered staging, named barriers)
  *   GSB_OPT_BWD_VARIANT  1 = rasterize_bwd.cu (warp per block, two-phase moment reduction)
  *                        2 = rasterize_bwd2.cu (half-warp per block, 2 pixels per lane, packed FFMA2) [default, D <= 4]
- *   GSB_OPT_ISECT_BIN_RADIX  1 = gsb_isect_bin ranks every chunk with its radix fallback (tests; default 0) */
+ *   GSB_OPT_ISECT_BIN_RADIX  1 = gsb_isect_bin ranks every chunk with its radix fallback (tests; default 0)
+ *   GSB_OPT_SH_STAGING   0 = gsb_sh_colors_fwd / _bwd stage the coefficient rows with ordinary loads and a CTA barrier
+ *                        1 = cp.async.bulk + mbarrier staging, persistent CTAs (degree 3, K = 16)
+ *                        2 = cp.async (16-byte pieces, warp-cooperative) staging, persistent CTAs [default; degree 3,
+ *                            K = 16, 16-byte aligned rows; anything else takes 0]
+ *   GSB_OPT_FINALIZE_VEC 0 = gsb_isect_finalize handles one intersection per thread [default]
+ *                        1 = four per thread with 16-byte accesses (measured slower: 61 vs 47 us at cfg2)
+ *   GSB_OPT_SH_CTAS      n > 0 caps the persistent grid of the staged colour kernels at n CTAs per SM (0 = all that fit) */
 #define GSB_OPT_FWD_VARIANT 0
 #define GSB_OPT_BWD_VARIANT 1
 #define GSB_OPT_ISECT_BIN_RADIX 2
-#define GSB_OPT_COUNT 3
+#define GSB_OPT_SH_STAGING 3
+#define GSB_OPT_FINALIZE_VEC 4
+#define GSB_OPT_SH_CTAS 5
+#define GSB_OPT_SH_FWD_STAGING 6
+#define GSB_OPT_SH_FWD_CTAS 7
+#define GSB_OPT_COUNT 8
 int gsb_set_option(int which, int value);
 int gsb_get_option(int which);
 

@@ -96,6 +96,52 @@ def test_fused_view_dependent_colors_equals_the_unfused_glue():
         assert bool((fused[radii == 0] == 0.5).all())
 
 
+@pytest.mark.parametrize("mode", [1, 2])
+@pytest.mark.parametrize("C,N", [(1, 1), (1, 37), (3, 128), (1, 4099), (2, 4099), (1, 300_001), (3, 100_003)])
+def test_staged_colour_kernels_equal_the_plain_ones(mode, C, N):
+    """gsb_sh_colors_fwd / _bwd with asynchronous staging of the coefficient rows (GSB_OPT_SH_STAGING 1 = cp.async.bulk
+    + mbarrier, 2 = cp.async; persistent CTAs, two stages) against the plain-load kernels (0) on the same inputs,
+    through the C ABI: same arithmetic in the same order. Sizes: a single row, partial warps / tiles, more tiles than
+    resident CTAs (several tiles per CTA, both stages reused), one camera (outer-product path) and several."""
+    from gsplat.b200_impl._lib import lib, ptr, stream_of
+
+    OPTS = (3, 6)  # GSB_OPT_SH_STAGING (backward kernel), GSB_OPT_SH_FWD_STAGING (forward kernel)
+    g = torch.Generator().manual_seed(100 * C + N % 97)
+    means = torch.randn(N, 3, generator=g).to(DEV)
+    coeffs = (torch.randn(N, 16, 3, generator=g) * 0.4).to(DEV)
+    radii = torch.randint(0, 3, (C, N), generator=g, dtype=torch.int32).to(DEV)
+    campos = (torch.randn(C, 3, generator=g) * 3).to(DEV)
+    v_colors = torch.randn(C, N, 3, generator=g).to(DEV)
+
+    def run(option, need_means):
+        for opt in OPTS:
+            lib.gsb_set_option(opt, option)
+        colors = torch.full((C, N, 3), float("nan"), device=DEV)
+        v_coeffs = torch.full((N, 16, 3), float("nan"), device=DEV)
+        v_means = torch.full((N, 3), float("nan"), device=DEV) if need_means else None
+        st = stream_of(means)
+        lib.gsb_sh_colors_fwd(3, N, C, 16, ptr(means), ptr(campos), ptr(coeffs), ptr(radii), ptr(colors), st)
+        lib.gsb_sh_colors_bwd(3, N, C, 16, ptr(means), ptr(campos), ptr(coeffs), ptr(radii), ptr(v_colors),
+                              ptr(v_coeffs), ptr(v_means), st)
+        torch.cuda.synchronize()
+        return colors, v_coeffs, v_means
+
+    defaults = [lib.gsb_get_option(opt) for opt in OPTS]
+    try:
+        for need_means in (True, False):
+            ref = run(0, need_means)
+            out = run(mode, need_means)
+            for name, a, b in zip(("colors", "v_coeffs", "v_means"), out, ref):
+                if b is None:
+                    assert a is None
+                    continue
+                assert bool(torch.isfinite(a).all()), f"{name}: rows left unwritten"
+                torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-6, msg=lambda m: f"{name}: {m}")
+    finally:
+        for opt, value in zip(OPTS, defaults):
+            lib.gsb_set_option(opt, value)
+
+
 # ---------------------------------------------------------------------------------------------
 # isect_tiles / isect_offset_encode: bit-exact given the reference's projection outputs
 # ---------------------------------------------------------------------------------------------
@@ -135,6 +181,36 @@ def test_isect_random_against_oracle(C, N, W, H):
     _, ids_u, flat_u = isect_tiles(means2d.to(DEV), radii.to(DEV), depths.to(DEV), ts, tw, th, sort=False)
     _, o_ids_u, o_flat_u = O.isect_tiles(means2d, radii, depths, ts, tw, th, sort=False)
     assert torch.equal(ids_u.cpu(), o_ids_u) and torch.equal(flat_u.cpu(), o_flat_u)
+
+
+@pytest.mark.parametrize("N", [1, 3, 5000, 250_001])
+def test_isect_finalize_variants_are_identical(N):
+    """gsb_isect_finalize with four intersections per thread (GSB_OPT_FINALIZE_VEC 1) against one per thread
+    (0, default): ids, row ids and offsets bit-identical, also when the count is not a multiple of four."""
+    from gsplat.b200_impl import isect_offset_encode, isect_tiles
+    from gsplat.b200_impl._lib import lib
+
+    OPT = 4  # GSB_OPT_FINALIZE_VEC
+    g = torch.Generator().manual_seed(N)
+    C, W, H, ts = 2, 200, 120, 16
+    tw, th = -(-W // ts), -(-H // ts)
+    means2d = (torch.rand(C, N, 2, generator=g) * torch.tensor([W * 0.7, H * 1.0])).to(DEV)  # some tiles stay empty
+    radii = torch.randint(0, 20, (C, N), generator=g, dtype=torch.int32).to(DEV)
+    depths = (torch.rand(C, N, generator=g) * 5 + 0.1).to(DEV)
+    default = lib.gsb_get_option(OPT)
+    out = {}
+    try:
+        for opt in (0, 1):
+            lib.gsb_set_option(OPT, opt)
+            tpg, ids, flat = isect_tiles(means2d, radii, depths, ts, tw, th)
+            out[opt] = (tpg, ids, flat, isect_offset_encode(ids, C, tw, th))
+    finally:
+        lib.gsb_set_option(OPT, default)
+    for a, b in zip(out[0], out[1]):
+        assert torch.equal(a, b)
+    o_tpg, o_ids, o_flat = O.isect_tiles(means2d.cpu(), radii.cpu(), depths.cpu(), ts, tw, th)
+    assert torch.equal(out[1][1].cpu(), o_ids) and torch.equal(out[1][2].cpu(), o_flat)
+    assert torch.equal(out[1][3].cpu(), O.isect_offset_encode(o_ids, C, tw, th))
 
 
 @pytest.mark.parametrize("N,packed", [(3000, False), (30000, True), (400000, False)])
