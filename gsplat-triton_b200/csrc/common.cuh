@@ -24,6 +24,46 @@ static inline int gsb_check_launch(const char *what) {
 
 static inline unsigned gsb_cdiv(long long a, long long b) { return (unsigned)((a + b - 1) / b); }
 
+// ---- chained launches (programmatic dependent launch, sm_90+) ---------------------------------------------------
+// The intersection pipeline is a dozen short, dependent kernels on one stream; between two of them the GPU drains,
+// the next grid is launched and ramps up: a few microseconds each time in which nothing runs. A kernel launched with
+// gsb_launch_chained may become resident while its predecessor in the stream is still finishing: its CTAs take the SM
+// slots the predecessor's last CTAs free and stop at gsb_chain_enter() — `griddepcontrol.wait`: until the predecessor
+// grid has completed and its writes are visible — which therefore has to be the FIRST statement of every kernel
+// launched this way, executed by every thread, before any early return (a grid whose CTAs skipped it could complete
+// before its predecessor, and its own successor would then overtake that one too). `griddepcontrol.launch_dependents`
+// right behind it lets the successor in, in turn, once every CTA of this grid has started.
+// GSB_OPT_CHAINED_LAUNCH is a mask of kernel groups; a group whose bit is clear is launched the ordinary way (the
+// instructions are then no-ops).
+#ifdef __CUDACC__
+__device__ __forceinline__ void gsb_chain_enter() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+// kernel groups, one bit each in GSB_OPT_CHAINED_LAUNCH
+enum { GSB_CHAIN_ISECT = 1, GSB_CHAIN_PROJECTION = 2, GSB_CHAIN_COLOURS = 4, GSB_CHAIN_PACK = 8, GSB_CHAIN_FWD = 16,
+       GSB_CHAIN_BWD = 32 };
+
+template <typename... P, typename... A>
+inline void gsb_launch_chained(int group, void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                               A &&...args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr.val.programmaticStreamSerializationAllowed = 1;
+    if ((gsb_option(GSB_OPT_CHAINED_LAUNCH) & group) != 0) {
+        cfg.attrs = &attr;
+        cfg.numAttrs = 1;
+    }
+    cudaLaunchKernelEx(&cfg, kernel, static_cast<P>(args)...);  // errors surface in gsb_check_launch (cudaGetLastError)
+}
+#endif
+
 #define GSB_REQUIRE(cond, msg)                  \
     do {                                        \
         if (!(cond)) {                          \

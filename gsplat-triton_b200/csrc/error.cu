@@ -9,7 +9,7 @@ namespace {
 thread_local char g_error[512] = "";
 std::atomic<long long> g_launches{0};
 // kernel-variant switches for A/B measurements (gsb_set_option); the defaults are the tuned path
-std::atomic<int> g_options[GSB_OPT_COUNT] = {{2}, {2}, {0}, {2}, {0}, {0}, {2}, {0}};
+std::atomic<int> g_options[GSB_OPT_COUNT] = {{2}, {2}, {0}, {2}, {0}, {0}, {2}, {0}, {37}};
 }  // namespace
 
 int gsb_option(int which) { return g_options[which].load(std::memory_order_relaxed); }

@@ -90,6 +90,7 @@ isect_count_kernel(int64_t P, const float *__restrict__ means2d, const int32_t *
 __global__ void __launch_bounds__(1024)
 scan_block_sums_kernel(int64_t n, const int32_t *__restrict__ in, int64_t *__restrict__ out,
                        int64_t *__restrict__ total_out) {
+    gsb_chain_enter();
     __shared__ long long s_warp[32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t per = (n + 1023) / 1024;
@@ -209,6 +210,7 @@ row_tiles_kernel(int64_t P, int N, const float *__restrict__ means2d, const int3
                  const int64_t *__restrict__ camera_ids, int tile_size, int tw, int th, int tile_n_bits,
                  int32_t *__restrict__ rows, int32_t *__restrict__ tiles_per_gauss, int4 *__restrict__ records,
                  const float *__restrict__ depths, uint32_t *__restrict__ row_keys, uint32_t *__restrict__ key_hist) {
+    gsb_chain_enter();
     __shared__ uint32_t s_hist[4 * 256];
     if (key_hist != nullptr) {
         hist_clear(s_hist, 4);
@@ -280,6 +282,7 @@ __global__ void __launch_bounds__(kThreads)
 count_perm_kernel(int64_t P, const int32_t *__restrict__ perm, const float *__restrict__ means2d,
                   const int32_t *__restrict__ radii, int tile_size, int tw, int th,
                   int32_t *__restrict__ tiles_per_gauss, int32_t *__restrict__ block_sums) {
+    gsb_chain_enter();
     __shared__ int s_warp[kThreads / 32];
     int64_t k = (int64_t)blockIdx.x * kThreads + threadIdx.x;
     int cnt = 0;
@@ -321,6 +324,7 @@ emit_perm_kernel(int64_t P, int N, const int32_t *__restrict__ perm, const float
                  const int64_t *__restrict__ block_offsets, uint32_t *__restrict__ tile_keys,
                  int32_t *__restrict__ flatten_ids, int64_t capacity, const int4 *__restrict__ records, int64_t nblk,
                  uint32_t *__restrict__ key_hist, int key_bits) {
+    gsb_chain_enter();
     __shared__ int s_warp[kThreads / 32];
     __shared__ int s_start[kThreads];  // first output slot of each row inside the CTA's range
     __shared__ int s_xy[kThreads];     // x0 | y0 << 16
@@ -395,6 +399,7 @@ emit_perm_kernel(int64_t P, int N, const int32_t *__restrict__ perm, const float
 __global__ void __launch_bounds__(kThreads)
 pad_tail_kernel(const int64_t *__restrict__ n_isects_dev, int64_t capacity, uint32_t *__restrict__ tile_keys,
                 int32_t *__restrict__ flatten_ids) {
+    gsb_chain_enter();
     const int64_t n = *n_isects_dev;
     for (int64_t i = n + (int64_t)blockIdx.x * kThreads + threadIdx.x; i < capacity; i += (int64_t)gridDim.x * kThreads) {
         tile_keys[i] = 0xffffffffu;
@@ -407,6 +412,7 @@ __global__ void __launch_bounds__(kThreads)
 finalize_kernel(int64_t n_isects, const int64_t *__restrict__ n_isects_dev, const uint32_t *__restrict__ tile_keys,
                 const int32_t *__restrict__ flatten_ids, const float *__restrict__ depths, int n_tiles,
                 int tile_n_bits, int64_t total_tiles, int64_t *__restrict__ isect_ids, int32_t *__restrict__ offsets) {
+    gsb_chain_enter();
     int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
     if (n_isects_dev != nullptr) {  // n_isects is the buffer capacity, the real count lives on the device
         const int64_t n = *n_isects_dev;
@@ -523,14 +529,14 @@ extern "C" int gsb_isect_count(int64_t P, const float *means2d, const int32_t *r
                                                                    tile_height, tiles_per_gauss, block_sums);
         if (int e = gsb_check_launch("isect_count")) return e;
     }
-    scan_block_sums_kernel<<<1, 1024, 0, stream>>>(nblk, block_sums, block_offsets, n_isects_out);
+    gsb_launch_chained(GSB_CHAIN_ISECT, scan_block_sums_kernel, 1, 1024, 0, stream, nblk, block_sums, block_offsets, n_isects_out);
     return gsb_check_launch("scan_block_sums");
 }
 
 extern "C" int gsb_scan_i32_to_i64(int64_t n, const int32_t *in, int64_t *out, int64_t *total_out,
                                    cudaStream_t stream) {
     GSB_REQUIRE(n >= 0, "negative size");
-    scan_block_sums_kernel<<<1, 1024, 0, stream>>>(n, in, out, total_out);
+    gsb_launch_chained(GSB_CHAIN_ISECT, scan_block_sums_kernel, 1, 1024, 0, stream, n, in, out, total_out);
     return gsb_check_launch("scan_i32_to_i64");
 }
 
@@ -643,13 +649,11 @@ extern "C" int gsb_isect_row_tiles_keys(int64_t P, int N, int packed, const floa
     auto keys = reinterpret_cast<uint32_t *>(row_keys);
     auto hist = reinterpret_cast<uint32_t *>(key_hist);
     if (packed)
-        row_tiles_kernel<true><<<nblk, kThreads, 0, stream>>>(P, N, means2d, radii, camera_ids, tile_size, tile_width,
-                                                              tile_height, tile_n_bits, rows, tiles_per_gauss, recs,
-                                                              depths, keys, hist);
+        gsb_launch_chained(GSB_CHAIN_ISECT, row_tiles_kernel<true>, nblk, kThreads, 0, stream, P, N, means2d, radii, camera_ids, tile_size,
+                           tile_width, tile_height, tile_n_bits, rows, tiles_per_gauss, recs, depths, keys, hist);
     else
-        row_tiles_kernel<false><<<nblk, kThreads, 0, stream>>>(P, N, means2d, radii, camera_ids, tile_size, tile_width,
-                                                               tile_height, tile_n_bits, rows, tiles_per_gauss, recs,
-                                                               depths, keys, hist);
+        gsb_launch_chained(GSB_CHAIN_ISECT, row_tiles_kernel<false>, nblk, kThreads, 0, stream, P, N, means2d, radii, camera_ids, tile_size,
+                           tile_width, tile_height, tile_n_bits, rows, tiles_per_gauss, recs, depths, keys, hist);
     return gsb_check_launch("isect_row_tiles");
 }
 
@@ -663,7 +667,7 @@ extern "C" int gsb_isect_count_perm_records(int64_t P, const int32_t *perm, cons
             P, perm, reinterpret_cast<const int4 *>(row_records), reinterpret_cast<int4 *>(sorted_records), block_sums);
         if (int e = gsb_check_launch("isect_count_perm_records")) return e;
     }
-    scan_block_sums_kernel<<<1, 1024, 0, stream>>>(nblk, block_sums, block_offsets, n_isects_out);
+    gsb_launch_chained(GSB_CHAIN_ISECT, scan_block_sums_kernel, 1, 1024, 0, stream, nblk, block_sums, block_offsets, n_isects_out);
     return gsb_check_launch("scan_block_sums");
 }
 
@@ -674,11 +678,11 @@ extern "C" int gsb_isect_count_perm(int64_t P, const int32_t *perm, const float 
     GSB_REQUIRE(P >= 0 && tile_size > 0 && tile_width >= 0 && tile_height >= 0, "bad sizes");
     int64_t nblk = gsb_isect_num_blocks(P);
     if (P > 0) {
-        count_perm_kernel<<<(unsigned)nblk, kThreads, 0, stream>>>(P, perm, means2d, radii, tile_size, tile_width,
-                                                                  tile_height, tiles_per_gauss, block_sums);
+        gsb_launch_chained(GSB_CHAIN_ISECT, count_perm_kernel, (unsigned)nblk, kThreads, 0, stream, P, perm, means2d, radii, tile_size,
+                           tile_width, tile_height, tiles_per_gauss, block_sums);
         if (int e = gsb_check_launch("isect_count_perm")) return e;
     }
-    scan_block_sums_kernel<<<1, 1024, 0, stream>>>(nblk, block_sums, block_offsets, n_isects_out);
+    gsb_launch_chained(GSB_CHAIN_ISECT, scan_block_sums_kernel, 1, 1024, 0, stream, nblk, block_sums, block_offsets, n_isects_out);
     return gsb_check_launch("scan_block_sums");
 }
 
@@ -722,19 +726,17 @@ extern "C" int gsb_isect_emit_perm_hist(int64_t P, int N, int packed, const int3
         unsigned grid = (unsigned)nblk;
         if (hist != nullptr && grid > 148 * 6) grid = 148 * 6;
         if (packed)
-            emit_perm_kernel<true><<<grid, kThreads, 0, stream>>>(P, N, perm, means2d, radii, camera_ids, tile_size,
-                                                                  tile_width, tile_height, tile_n_bits,
-                                                                  tiles_per_gauss, block_offsets, tk, flatten_ids,
-                                                                  capacity, recs, nblk, hist, key_bits);
+            gsb_launch_chained(GSB_CHAIN_ISECT, emit_perm_kernel<true>, grid, kThreads, 0, stream, P, N, perm, means2d, radii, camera_ids,
+                               tile_size, tile_width, tile_height, tile_n_bits, tiles_per_gauss, block_offsets, tk,
+                               flatten_ids, capacity, recs, nblk, hist, key_bits);
         else
-            emit_perm_kernel<false><<<grid, kThreads, 0, stream>>>(P, N, perm, means2d, radii, camera_ids, tile_size,
-                                                                   tile_width, tile_height, tile_n_bits,
-                                                                   tiles_per_gauss, block_offsets, tk, flatten_ids,
-                                                                   capacity, recs, nblk, hist, key_bits);
+            gsb_launch_chained(GSB_CHAIN_ISECT, emit_perm_kernel<false>, grid, kThreads, 0, stream, P, N, perm, means2d, radii, camera_ids,
+                               tile_size, tile_width, tile_height, tile_n_bits, tiles_per_gauss, block_offsets, tk,
+                               flatten_ids, capacity, recs, nblk, hist, key_bits);
         if (int e = gsb_check_launch("isect_emit_perm")) return e;
     }
     if (n_isects_dev != nullptr && capacity > 0) {
-        pad_tail_kernel<<<148, kThreads, 0, stream>>>(n_isects_dev, capacity, tk, flatten_ids);
+        gsb_launch_chained(GSB_CHAIN_ISECT, pad_tail_kernel, 148, kThreads, 0, stream, n_isects_dev, capacity, tk, flatten_ids);
         return gsb_check_launch("isect_pad_tail");
     }
     return GSB_OK;
@@ -795,8 +797,8 @@ extern "C" int gsb_isect_finalize_cap(int64_t n_isects, const int64_t *n_isects_
             tile_n_bits, total, isect_ids, offsets);
         return gsb_check_launch("isect_finalize4");
     }
-    finalize_kernel<<<gsb_cdiv(n_isects, kThreads), kThreads, 0, stream>>>(
-        n_isects, n_isects_dev, reinterpret_cast<const uint32_t *>(tile_keys), flatten_ids, depths, (int)n_tiles,
-        tile_n_bits, total, isect_ids, offsets);
+    gsb_launch_chained(GSB_CHAIN_ISECT, finalize_kernel, gsb_cdiv(n_isects, kThreads), kThreads, 0, stream, n_isects, n_isects_dev,
+                       reinterpret_cast<const uint32_t *>(tile_keys), flatten_ids, depths, (int)n_tiles, tile_n_bits, total,
+                       isect_ids, offsets);
     return gsb_check_launch("isect_finalize");
 }

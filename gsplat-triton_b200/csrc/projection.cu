@@ -253,6 +253,7 @@ projection_fwd_kernel(int C, int N, const float *__restrict__ means, const float
                       const float *__restrict__ viewmats, const float *__restrict__ Ks, ProjParams p,
                       int32_t *__restrict__ radii, float *__restrict__ means2d, float *__restrict__ depths,
                       float *__restrict__ conics, float *__restrict__ comps, peer::PushRows push) {
+    gsb_chain_enter();
     int n = blockIdx.x * kThreads + threadIdx.x;
     if (n >= N) return;
     const float *mp = means + 3 * (size_t)n;
@@ -539,6 +540,7 @@ projection_bwd_kernel(int C, int N, const float *__restrict__ means, const float
                       const float *__restrict__ v_depths, const float *__restrict__ v_conics,
                       const float *__restrict__ v_comps, float *__restrict__ v_means, float *__restrict__ v_covars,
                       float *__restrict__ v_quats, float *__restrict__ v_scales, float *__restrict__ v_viewmats) {
+    gsb_chain_enter();
     __shared__ float s_vm[12];
     int n = blockIdx.x * kThreads + threadIdx.x;
     bool in_range = n < N;
@@ -768,14 +770,14 @@ int projection_fwd_launch(int C, int N, const float *means, const float *covars,
     if (nblk < 148u * 4u) gy = (unsigned)min((long long)C, (long long)gsb_cdiv(148 * 4, nblk));
     dim3 grid(nblk, gy);
     if (push != nullptr) {
-        DISPATCH_MODEL(camera_model, (projection_fwd_kernel<M, true><<<grid, kThreads, 0, stream>>>(
-                                         C, N, means, covars, quats, scales, viewmats, Ks, p, radii, means2d, depths,
-                                         conics, compensations, *push)));
+        DISPATCH_MODEL(camera_model, (gsb_launch_chained(GSB_CHAIN_PROJECTION, projection_fwd_kernel<M, true>, grid, kThreads, 0, stream, C, N,
+                                                         means, covars, quats, scales, viewmats, Ks, p, radii, means2d,
+                                                         depths, conics, compensations, *push)));
     } else {
         peer::PushRows none = {};
-        DISPATCH_MODEL(camera_model, (projection_fwd_kernel<M, false><<<grid, kThreads, 0, stream>>>(
-                                         C, N, means, covars, quats, scales, viewmats, Ks, p, radii, means2d, depths,
-                                         conics, compensations, none)));
+        DISPATCH_MODEL(camera_model, (gsb_launch_chained(GSB_CHAIN_PROJECTION, projection_fwd_kernel<M, false>, grid, kThreads, 0, stream, C, N,
+                                                         means, covars, quats, scales, viewmats, Ks, p, radii, means2d,
+                                                         depths, conics, compensations, none)));
     }
     return gsb_check_launch("projection_fwd");
 }
@@ -829,15 +831,15 @@ extern "C" int gsb_projection_bwd(int C, int N, const float *means, const float 
     ProjParams p = {width, height, eps2d, 0.f, 0.f, 0.f};
     unsigned nblk = gsb_cdiv(N, kThreads);
     if (v_viewmats != nullptr) {
-        DISPATCH_MODEL(camera_model, (projection_bwd_kernel<M, true><<<nblk, kThreads, 0, stream>>>(
-                                         C, N, means, covars, quats, scales, viewmats, Ks, p, radii, conics,
-                                         compensations, v_means2d, v_depths, v_conics, v_compensations, v_means,
-                                         v_covars, v_quats, v_scales, v_viewmats)));
+        DISPATCH_MODEL(camera_model, (gsb_launch_chained(GSB_CHAIN_PROJECTION, projection_bwd_kernel<M, true>, nblk, kThreads, 0, stream, C, N,
+                                                         means, covars, quats, scales, viewmats, Ks, p, radii, conics,
+                                                         compensations, v_means2d, v_depths, v_conics, v_compensations,
+                                                         v_means, v_covars, v_quats, v_scales, v_viewmats)));
     } else {
-        DISPATCH_MODEL(camera_model, (projection_bwd_kernel<M, false><<<nblk, kThreads, 0, stream>>>(
-                                         C, N, means, covars, quats, scales, viewmats, Ks, p, radii, conics,
-                                         compensations, v_means2d, v_depths, v_conics, v_compensations, v_means,
-                                         v_covars, v_quats, v_scales, v_viewmats)));
+        DISPATCH_MODEL(camera_model, (gsb_launch_chained(GSB_CHAIN_PROJECTION, projection_bwd_kernel<M, false>, nblk, kThreads, 0, stream, C, N,
+                                                         means, covars, quats, scales, viewmats, Ks, p, radii, conics,
+                                                         compensations, v_means2d, v_depths, v_conics, v_compensations,
+                                                         v_means, v_covars, v_quats, v_scales, v_viewmats)));
     }
     return gsb_check_launch("projection_bwd");
 }

@@ -113,6 +113,7 @@ onesweep_kernel(int64_t n, const int64_t *__restrict__ n_dev, const KeyT *__rest
                 const int32_t *__restrict__ vals_in, KeyT *__restrict__ keys_out, int32_t *__restrict__ vals_out,
                 int shift, int bits, const uint32_t *__restrict__ hist, uint32_t *__restrict__ ticket,
                 uint32_t *__restrict__ states) {
+    gsb_chain_enter();
     constexpr int kItems = TileOf<KeyT>::kItems, kTile = TileOf<KeyT>::kTile;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     int32_t *s_global = reinterpret_cast<int32_t *>(smem_raw);     // (global position - staged slot) of each digit
@@ -325,8 +326,8 @@ int sort_pairs(int64_t n, const int64_t *n_dev, int end_bit, KeyT *keys, KeyT *k
     int32_t *vin = vals, *vout = vals_alt;
     for (int p = 0; p < passes; ++p) {
         const int bits = end_bit - 8 * p < 8 ? end_bit - 8 * p : 8;
-        onesweep_kernel<KeyT><<<(unsigned)tiles, kThreads, TileOf<KeyT>::kSmem, stream>>>(
-            n, n_dev, kin, vin, kout, vout, 8 * p, bits, hist + p * kBins, tickets + p, states + (int64_t)p * tiles * kBins);
+        gsb_launch_chained(GSB_CHAIN_ISECT, onesweep_kernel<KeyT>, (unsigned)tiles, kThreads, TileOf<KeyT>::kSmem, stream, n, n_dev, kin, vin,
+                           kout, vout, 8 * p, bits, hist + p * kBins, tickets + p, states + (int64_t)p * tiles * kBins);
         if (int rc = gsb_check_launch("radix_onesweep")) return rc;
         KeyT *tk = kin; kin = kout; kout = tk;
         int32_t *tv = vin; vin = vout; vout = tv;

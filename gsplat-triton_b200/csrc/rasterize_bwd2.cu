@@ -170,6 +170,7 @@ rasterize_bwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
                       const uint8_t *__restrict__ block_masks, const float *__restrict__ v_render_colors,
                       const float *__restrict__ v_render_alphas, GradTargets out) {
     static_assert(D >= 1 && D <= 4, "v2 keeps the colour of a staged splat in one float4");
+    gsb_chain_enter();
     __shared__ Bwd2Smem sm;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, half = lane >> 4, l16 = lane & 15;
     const int hw = 2 * warp + half;
@@ -373,10 +374,10 @@ int launch_bwd2(int C, int64_t n_isects, const float *recA, const float *recB, c
                 const uint8_t *block_masks, const float *v_render_colors, const float *v_render_alphas,
                 GradTargets out, cudaStream_t stream) {
     dim3 grid(tw, th, C);
-    rasterize_bwd2_kernel<D, ABS><<<grid, kB2Threads, 0, stream>>>(
-        C, n_isects, reinterpret_cast<const float4 *>(recA), reinterpret_cast<const float4 *>(recB), colors,
-        backgrounds, masks, W, H, tw, th, offsets, flatten_ids, render_alphas, last_ids, block_masks, v_render_colors,
-        v_render_alphas, out);
+    gsb_launch_chained(GSB_CHAIN_BWD, rasterize_bwd2_kernel<D, ABS>, grid, kB2Threads, 0, stream, C, n_isects,
+                       reinterpret_cast<const float4 *>(recA), reinterpret_cast<const float4 *>(recB), colors, backgrounds,
+                       masks, W, H, tw, th, offsets, flatten_ids, render_alphas, last_ids, block_masks, v_render_colors,
+                       v_render_alphas, out);
     return gsb_check_launch("rasterize_bwd2");
 }
 

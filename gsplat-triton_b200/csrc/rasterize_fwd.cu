@@ -21,6 +21,7 @@ namespace raster {
 __global__ void __launch_bounds__(256)
 splat_pack_kernel(int64_t P, const float *__restrict__ means2d, const float *__restrict__ conics,
                   const float *__restrict__ opacities, float4 *__restrict__ recA, float4 *__restrict__ recB) {
+    gsb_chain_enter();
     int64_t g = (int64_t)blockIdx.x * 256 + threadIdx.x;
     if (g >= P) return;
     float2 m = *reinterpret_cast<const float2 *>(means2d + 2 * g);
@@ -197,8 +198,8 @@ extern "C" int gsb_rasterize_pack(int64_t P, const float *means2d, const float *
                                   float *recA, float *recB, cudaStream_t stream) {
     GSB_REQUIRE(P >= 0, "negative size");
     if (P == 0) return GSB_OK;
-    raster::splat_pack_kernel<<<gsb_cdiv(P, 256), 256, 0, stream>>>(
-        P, means2d, conics, opacities, reinterpret_cast<float4 *>(recA), reinterpret_cast<float4 *>(recB));
+    gsb_launch_chained(GSB_CHAIN_PACK, raster::splat_pack_kernel, gsb_cdiv(P, 256), 256, 0, stream, P, means2d, conics, opacities,
+                       reinterpret_cast<float4 *>(recA), reinterpret_cast<float4 *>(recB));
     return gsb_check_launch("rasterize_pack");
 }
 

@@ -57,6 +57,7 @@ rasterize_fwd2_kernel(int C, int64_t n_isects, const float4 *__restrict__ recA, 
                       int32_t *__restrict__ last_ids, const int64_t *__restrict__ n_isects_dev,
                       uint8_t *__restrict__ block_masks, unsigned long long *__restrict__ warp_iters) {
     static_assert(D >= 1 && D <= 4, "v2 keeps the colour of a staged splat in one float4");
+    gsb_chain_enter();
     if (n_isects_dev != nullptr) n_isects = min(n_isects, (int64_t)*n_isects_dev);
     // (Measured and dropped: a double-buffered, uncompacted batch needs one CTA barrier per batch instead of three, but
     // the warps then scan every entry's mask instead of the survivors': 0.420 ms against 0.408 ms at cfg2. The
@@ -460,10 +461,10 @@ int launch_fwd2(int C, int64_t n_isects, const float *recA, const float *recB, c
                 const int32_t *offsets, const int32_t *flatten_ids, float *out_colors, float *out_alphas,
                 int32_t *last_ids, const int64_t *n_isects_dev, uint8_t *block_masks, cudaStream_t stream) {
     dim3 grid(tw, th, C);
-    rasterize_fwd2_kernel<D><<<grid, kThreads2, 0, stream>>>(
-        C, n_isects, reinterpret_cast<const float4 *>(recA), reinterpret_cast<const float4 *>(recB), colors,
-        backgrounds, masks, W, H, tw, th, offsets, flatten_ids, out_colors, out_alphas, last_ids, n_isects_dev,
-        block_masks, nullptr);
+    gsb_launch_chained(GSB_CHAIN_FWD, rasterize_fwd2_kernel<D, false>, grid, kThreads2, 0, stream, C, n_isects,
+                       reinterpret_cast<const float4 *>(recA), reinterpret_cast<const float4 *>(recB), colors, backgrounds,
+                       masks, W, H, tw, th, offsets, flatten_ids, out_colors, out_alphas, last_ids, n_isects_dev,
+                       block_masks, (unsigned long long *)nullptr);
     return gsb_check_launch("rasterize_fwd2");
 }
 

@@ -505,6 +505,7 @@ sh_colors_fwd_bulk_kernel(int64_t N, int C, const float *__restrict__ means, con
     constexpr int NB = (DEG + 1) * (DEG + 1), NB3 = NB * 3;
     extern __shared__ __align__(128) unsigned char s_rows[];
     __shared__ __align__(8) unsigned long long s_bar[kBulkStages][kThreads / 32];
+    gsb_chain_enter();
     RowStager<MODE, NB3> stager;
     stager.setup(s_rows, s_bar, N, coeffs);
     const int64_t n_tiles = (N + kThreads - 1) / kThreads;
@@ -561,6 +562,7 @@ sh_colors_bwd_bulk_kernel(int64_t N, int C, const float *__restrict__ means, con
     using R = BulkRow<NB3>;
     extern __shared__ __align__(128) unsigned char s_rows[];
     __shared__ __align__(8) unsigned long long s_bar[kBulkStages][kThreads / 32];
+    gsb_chain_enter();
     RowStager<MODE, NB3> stager;
     stager.setup(s_rows, s_bar, N, coeffs);
     const int lane = threadIdx.x & 31;
@@ -716,7 +718,7 @@ int launch_sh_colors_fwd_staged(int64_t N, int C, const float *means, const floa
     constexpr size_t smem = BulkRow<48>::kSmem;
     unsigned grid = 0;
     if (int rc = sh_bulk_grid(kernel, smem, N, gsb_option(GSB_OPT_SH_FWD_CTAS), grid)) return rc;
-    kernel<<<grid, kThreads, smem, stream>>>(N, C, means, campos, coeffs, radii, colors);
+    gsb_launch_chained(GSB_CHAIN_COLOURS, kernel, grid, kThreads, smem, stream, N, C, means, campos, coeffs, radii, colors);
     return gsb_check_launch("sh_colors_fwd_staged");
 }
 
@@ -731,7 +733,8 @@ int launch_sh_colors_bwd_staged(int64_t N, int C, const float *means, const floa
                                                : sh_colors_bwd_bulk_kernel<3, false, false, MODE>);
     unsigned grid = 0;
     if (int rc = sh_bulk_grid(kernel, smem, N, gsb_option(GSB_OPT_SH_CTAS), grid)) return rc;
-    kernel<<<grid, kThreads, smem, stream>>>(N, C, means, campos, coeffs, radii, v_colors, v_coeffs, v_means);
+    gsb_launch_chained(GSB_CHAIN_COLOURS, kernel, grid, kThreads, smem, stream, N, C, means, campos, coeffs, radii, v_colors, v_coeffs,
+                       v_means);
     return gsb_check_launch("sh_colors_bwd_staged");
 }
 

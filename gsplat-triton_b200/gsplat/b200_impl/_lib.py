@@ -95,7 +95,7 @@ class _Lib:
         for which, env in ((0, "GSPLAT_B200_FWD_VARIANT"), (1, "GSPLAT_B200_BWD_VARIANT"),
                            (3, "GSPLAT_B200_SH_STAGING"), (4, "GSPLAT_B200_FINALIZE_VEC"),
                            (5, "GSPLAT_B200_SH_CTAS"), (6, "GSPLAT_B200_SH_FWD_STAGING"),
-                           (7, "GSPLAT_B200_SH_FWD_CTAS")):
+                           (7, "GSPLAT_B200_SH_FWD_CTAS"), (8, "GSPLAT_B200_CHAINED_LAUNCH")):
             if os.environ.get(env):
                 dll.gsb_set_option(which, int(os.environ[env]))
         return dll

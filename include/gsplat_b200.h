@@ -54,7 +54,16 @@ void gsb_reset_launch_count(void);
  *                            K = 16, 16-byte aligned rows; anything else takes 0]
  *   GSB_OPT_FINALIZE_VEC 0 = gsb_isect_finalize handles one intersection per thread [default]
  *                        1 = four per thread with 16-byte accesses (measured slower: 61 vs 47 us at cfg2)
- *   GSB_OPT_SH_CTAS      n > 0 caps the persistent grid of the staged colour kernels at n CTAs per SM (0 = all that fit) */
+ *   GSB_OPT_SH_CTAS      n > 0 caps the persistent grid of the staged backward colour kernel at n CTAs per SM (0 = all
+ *                        that fit); GSB_OPT_SH_FWD_STAGING / GSB_OPT_SH_FWD_CTAS: the same two switches for the forward
+ *                        kernel (a persistent CTA never gives its SM slot back: beside another stream's kernels the
+ *                        caps decide who waits)
+ *   GSB_OPT_CHAINED_LAUNCH  mask of kernel groups launched with programmatic stream serialization (a grid becomes
+ *                        resident while its predecessor in the stream drains and waits at `griddepcontrol.wait`):
+ *                        1 = intersection pipeline incl. the radix sort passes, 2 = projection, 4 = staged colour
+ *                        kernels, 8 = splat records, 16 = forward compositor v2, 32 = backward compositor v2.
+ *                        Default 37 (1 + 4 + 32), measured at cfg2: 0 -> 1.624 ms per step, 1 -> 1.619, 5 -> 1.606,
+ *                        37 -> 1.603, 13 -> 1.637, 63 -> 1.628 */
 #define GSB_OPT_FWD_VARIANT 0
 #define GSB_OPT_BWD_VARIANT 1
 #define GSB_OPT_ISECT_BIN_RADIX 2
@@ -63,7 +72,8 @@ void gsb_reset_launch_count(void);
 #define GSB_OPT_SH_CTAS 5
 #define GSB_OPT_SH_FWD_STAGING 6
 #define GSB_OPT_SH_FWD_CTAS 7
-#define GSB_OPT_COUNT 8
+#define GSB_OPT_CHAINED_LAUNCH 8
+#define GSB_OPT_COUNT 9
 int gsb_set_option(int which, int value);
 int gsb_get_option(int which);
 
