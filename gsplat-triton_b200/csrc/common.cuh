@@ -87,7 +87,8 @@ __device__ __forceinline__ int warp_max_i(int v) {
 // Shared-memory digit histograms (`passes` x 256 counters) for the onesweep sort that follows a producer of 32-bit
 // keys (gsb_radix_prepare): one count per live key and pass. (Merging the lanes of a warp that hold the same high digit
 // with match.any before the atomic was measured: +10 us per step at cfg2, the match costs more than the serialised
-// shared-memory increments it saves.)
+// shared-memory increments it saves. Aggregating only the TOP digit, which the lanes of a warp mostly share, with
+// one shuffle and two votes: 1.617-1.626 ms per step against 1.602-1.605, profiles/r04_staging/r04l_*.)
 __device__ __forceinline__ void gsb_hist_add(uint32_t *s_hist, uint32_t key, bool live, int passes, int end_bit) {
     if (!live) return;
     for (int p = 0; p < passes; ++p) {
