@@ -392,7 +392,8 @@ def view_dependent_colors(sh_degree: int, means: Tensor, viewmats: Tensor, coeff
 # colour kernel. Measured at cfg2 (ms per step): forward kernel on 1 CTA per SM + backward on 3: 1.639; both on all
 # four: 1.676 (no better than the plain kernels, 1.675); forward plain + backward on 4 / 3 / 2 / 1: 1.650 / 1.644 /
 # 1.644 / 1.684. rasterization() announces the two-stream case here; GSPLAT_B200_SH_FWD_CTAS / GSPLAT_B200_SH_CTAS pin
-# the caps for experiments.
+# the caps for experiments. The forward cap is for ONE camera, where the colour kernel has 300 us of slack; with more
+# cameras it is real work (cfg3, 8 cameras: 1.6 ms on 1 CTA per SM, 15.39 ms per step against 14.78 uncapped).
 _COLOURS_BESIDE = [False]
 _GSB_OPT_SH_CTAS, _GSB_OPT_SH_FWD_CTAS = 5, 7
 
@@ -423,7 +424,7 @@ class _ViewColors(torch.autograd.Function):
                                        ptr(colors), world, C_local, N_total, n_base, peers, region, st)
             ex.pushed.add("colors")
         else:
-            _cap_colour_ctas(_GSB_OPT_SH_FWD_CTAS, "GSPLAT_B200_SH_FWD_CTAS", 1 if _COLOURS_BESIDE[0] else 0)
+            _cap_colour_ctas(_GSB_OPT_SH_FWD_CTAS, "GSPLAT_B200_SH_FWD_CTAS", 1 if (_COLOURS_BESIDE[0] and C == 1) else 0)
             lib.gsb_sh_colors_fwd(sh_degree, N, C, K, ptr(means), ptr(campos), ptr(coeffs), ptr(radii), ptr(colors), st)
         ctx.save_for_backward(means, campos, coeffs, radii)
         ctx.sh_degree = sh_degree
@@ -494,7 +495,7 @@ class _ViewColorsPacked(torch.autograd.Function):
         campos = torch.empty((C, 3), dtype=torch.float32, device=dev)
         lib.gsb_camera_centers(C, ptr(viewmats), ptr(campos), st)
         dense = torch.empty((C * N, 3), dtype=torch.float32, device=dev)
-        _cap_colour_ctas(_GSB_OPT_SH_FWD_CTAS, "GSPLAT_B200_SH_FWD_CTAS", 1 if _COLOURS_BESIDE[0] else 0)
+        _cap_colour_ctas(_GSB_OPT_SH_FWD_CTAS, "GSPLAT_B200_SH_FWD_CTAS", 1 if (_COLOURS_BESIDE[0] and C == 1) else 0)
         lib.gsb_sh_colors_fwd(sh_degree, N, C, K, ptr(means), ptr(campos), ptr(coeffs), ptr(visible), ptr(dense), st)
         ctx.save_for_backward(means, campos, coeffs, visible, rows)
         ctx.sh_degree = sh_degree
