@@ -28,6 +28,8 @@
 // consecutive addresses (experiment) 0.188 ms. Correct and selectable (GSPLAT_B200_ISECT=bin), NOT the default.
 #include "common.cuh"
 
+#include <atomic>
+
 #include <cstdint>
 
 namespace {
@@ -615,17 +617,17 @@ extern "C" int gsb_isect_bin(int64_t P, int64_t capacity, const int64_t *n_isect
     uint32_t *totals = G + (int64_t)kGroups * bins;
     auto srec = reinterpret_cast<const int4 *>(sorted_records);
 
-    static unsigned long long configured = 0ull;  // per device, like radix_sort.cu
+    static std::atomic<unsigned long long> configured{0ull};  // per device, like radix_sort.cu
     int device = 0;
     cudaGetDevice(&device);
-    if (!((configured >> (device & 63)) & 1ull)) {
+    if (!((configured.load(std::memory_order_acquire) >> (device & 63)) & 1ull)) {
         cudaError_t e = cudaFuncSetAttribute(bin_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)kScatterSmem);
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(bin_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)(sizeof(uint32_t) * (kT + kMaxBins)));
         if (e != cudaSuccess) { gsb_set_error("isect_bin: shared memory: %s", cudaGetErrorString(e)); return GSB_ERR_CUDA; }
-        configured |= 1ull << (device & 63);
+        configured.fetch_or(1ull << (device & 63), std::memory_order_release);
     }
     bin_count_kernel<<<chunks, kThreads, sizeof(uint32_t) * (kT + bins), stream>>>(
         capacity, n_isects_dev, P, srec, block_offsets, nblk, tile_width, (int)n_tiles, tile_n_bits, bins, M);

@@ -18,6 +18,8 @@
 // in digit order and written out as coalesced runs.
 #include "common.cuh"
 
+#include <atomic>
+
 #include <cstdint>
 
 namespace {
@@ -302,17 +304,17 @@ int sort_pairs(int64_t n, const int64_t *n_dev, int end_bit, KeyT *keys, KeyT *k
         return GSB_ERR_CUDA;
     }
     // one instantiation per key type; the attribute is per DEVICE: bit d = configured on device d
-    static unsigned long long configured = 0ull;
+    static std::atomic<unsigned long long> configured{0ull};
     int device = 0;
     cudaGetDevice(&device);
-    if (!((configured >> (device & 63)) & 1ull)) {
+    if (!((configured.load(std::memory_order_acquire) >> (device & 63)) & 1ull)) {
         e = cudaFuncSetAttribute(onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)TileOf<KeyT>::kSmem);
         if (e != cudaSuccess) {
             gsb_set_error("radix sort: shared memory: %s", cudaGetErrorString(e));
             return GSB_ERR_CUDA;
         }
-        configured |= 1ull << (device & 63);
+        configured.fetch_or(1ull << (device & 63), std::memory_order_release);
     }
     uint32_t *hist = reinterpret_cast<uint32_t *>(temp);
     uint32_t *tickets = hist + (int64_t)passes * kBins;

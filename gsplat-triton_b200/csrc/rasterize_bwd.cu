@@ -25,6 +25,8 @@
 //   * one set of global reductions per (warp, splat), issued by the lane that owns the splat.
 #include "rasterize_common.cuh"
 
+#include <atomic>
+
 namespace raster {
 
 #ifndef GSB_BWD_MIN_BLOCKS
@@ -297,16 +299,16 @@ int launch_bwd(int C, int64_t n_isects, const float *recA, const float *recB, co
     constexpr size_t smem = BwdSmem<D>::bytes;
     auto kernel = rasterize_bwd_kernel<D, ABS>;
     // one instantiation per (D, ABS); the attribute is per DEVICE: bit d = configured on device d
-    static unsigned long long configured = 0ull;
+    static std::atomic<unsigned long long> configured{0ull};
     int device = 0;
     cudaGetDevice(&device);
-    if (!((configured >> (device & 63)) & 1ull)) {
+    if (!((configured.load(std::memory_order_acquire) >> (device & 63)) & 1ull)) {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) {
             gsb_set_error("rasterize_bwd: cannot reserve %zu B of shared memory: %s", smem, cudaGetErrorString(e));
             return GSB_ERR_CUDA;
         }
-        configured |= 1ull << (device & 63);
+        configured.fetch_or(1ull << (device & 63), std::memory_order_release);
     }
     dim3 grid(tw, th, C);
     kernel<<<grid, kThreads, smem, stream>>>(C, n_isects, reinterpret_cast<const float4 *>(recA),

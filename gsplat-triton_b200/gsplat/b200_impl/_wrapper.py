@@ -170,6 +170,9 @@ class _FullyFusedProjection(torch.autograd.Function):
         ctx.save_for_backward(means, covars, quats, scales, viewmats, Ks, radii, conics, compensations)
         ctx.width, ctx.height, ctx.eps2d, ctx.model = width, height, eps2d, model
         ctx.mark_non_differentiable(radii)
+        # outputs nobody differentiates (radii always, depths in the RGB modes) arrive as None in backward instead of
+        # zero tensors autograd would fill on the critical path (the kernel takes NULL for v_depths / v_compensations)
+        ctx.set_materialize_grads(False)
         return radii, means2d, depths, conics, compensations
 
     @staticmethod
@@ -184,6 +187,10 @@ class _FullyFusedProjection(torch.autograd.Function):
         v_viewmats = torch.empty_like(viewmats) if need[4] else None
         if compensations is None:
             v_compensations = None
+        if v_means2d is None:
+            v_means2d = torch.zeros((C, N, 2), dtype=torch.float32, device=means.device)
+        if v_conics is None:
+            v_conics = torch.zeros((C, N, 3), dtype=torch.float32, device=means.device)
         # converted cotangents stay bound until after the launch (a temporary freed before the launch could be
         # handed to the next conversion by the caching allocator and overwritten on the same stream)
         v_means2d, v_depths, v_conics, v_compensations = (
@@ -249,6 +256,7 @@ class _FullyFusedProjectionPacked(torch.autograd.Function):
                               compensations)
         ctx.width, ctx.height, ctx.eps2d, ctx.model, ctx.sparse_grad = width, height, eps2d, model, sparse_grad
         ctx.mark_non_differentiable(camera_ids, gaussian_ids, radii)
+        ctx.set_materialize_grads(False)  # see _FullyFusedProjection
         _PACKED_COUNTS[0] = (camera_ids.data_ptr(), nnz, [int(b - a) for a, b in zip(bounds[:-1], bounds[1:])])
         return camera_ids, gaussian_ids, radii, means2d, depths, conics, compensations
 
@@ -275,6 +283,10 @@ class _FullyFusedProjectionPacked(torch.autograd.Function):
         acc = None if sparse else torch.empty((N, 9), dtype=torch.float32, device=dev)
         if compensations is None:
             v_compensations = None
+        if v_means2d is None:
+            v_means2d = torch.zeros((nnz, 2), dtype=torch.float32, device=dev)
+        if v_conics is None:
+            v_conics = torch.zeros((nnz, 3), dtype=torch.float32, device=dev)
         v_means2d, v_depths, v_conics, v_compensations = (
             _f32(t) for t in (v_means2d, v_depths, v_conics, v_compensations))  # bound past the launch
         lib.gsb_projection_packed_bwd(

@@ -177,7 +177,8 @@ def rasterization(
     # exchange sits between the colours and the intersections, nothing is left to run beside them (measured at 2
     # ranks: 1.86-1.90 ms with the second stream against 1.85 without).
     overlap, use_side = None, False
-    if BACKEND == "b200" and not distributed and sh_degree is not None:
+    dist_overlap = int(os.environ.get("GSPLAT_B200_OVERLAP_DIST", "0")) if distributed else 0
+    if BACKEND == "b200" and (not distributed or dist_overlap) and sh_degree is not None:
         from .b200_impl._wrapper import overlap_enabled, side_stream
 
         use_side = overlap_enabled()
@@ -212,6 +213,8 @@ def rasterization(
             for t in proj_results:
                 if isinstance(t, Tensor):
                     t.record_stream(main)  # allocated under the side stream, read on both
+            if dist_overlap == 1:
+                overlap = None  # experiment: only the projection (and so its backward) on the second stream
         else:
             proj_results = project()
     except Exception:
