@@ -304,6 +304,69 @@ def test_speculative_intersection_buffers_match_exact(packed, monkeypatch):
     assert float(ra.abs().max()) == 0.0 and int(m["isect_offsets"].abs().max()) == 0
 
 
+@pytest.mark.parametrize("packed", [False, True])
+def test_launch_and_stream_variants_give_the_same_render(packed, monkeypatch):
+    """The scheduling switches of the round-2 path change WHEN kernels run, never what they compute: chained launches
+    (programmatic dependent launch) off / on for every kernel group, one stream instead of two, the gradient buffer
+    zero-filled in the backward pass, plain / cp.async.bulk / cp.async staging of the SH colour kernels. Images, ids and
+    offsets bit-identical (images within 2e-6 across the separately compiled SH kernels); gradients to the last few
+    ulps (atomics accumulate in scheduling order)."""
+    from gsplat.b200_impl._lib import lib
+    from gsplat.rendering import rasterization
+
+    torch.manual_seed(11)
+    N, W, H, C = 30_000, 320, 200, 2
+    means = torch.rand(N, 3) * torch.tensor([6.0, 4.0, 4.0]) + torch.tensor([-3.0, -2.0, 2.0])
+    quats, scales, opac = torch.randn(N, 4), torch.rand(N, 3) * 0.08 + 0.01, torch.rand(N)
+    shs = torch.randn(N, 16, 3) * 0.3
+    viewmats = torch.eye(4).repeat(C, 1, 1)
+    viewmats[1, 0, 3] = 0.3
+    Ks = torch.tensor([[200.0, 0.0, W / 2], [0.0, 200.0, H / 2], [0.0, 0.0, 1.0]]).repeat(C, 1, 1)
+    args = [t.to(DEV) for t in (means, quats, scales, opac, shs, viewmats, Ks)]
+    CHAIN, SH_BWD, SH_FWD = 8, 3, 6  # GSB_OPT_CHAINED_LAUNCH, GSB_OPT_SH_STAGING, GSB_OPT_SH_FWD_STAGING
+    defaults = {o: lib.gsb_get_option(o) for o in (CHAIN, SH_BWD, SH_FWD)}
+
+    def run(options=(), env=()):
+        for k, v in env:
+            monkeypatch.setenv(k, v)
+        for o, v in options:
+            lib.gsb_set_option(o, v)
+        try:
+            out = None
+            for _ in range(2):  # the second call runs with speculatively sized intersection buffers
+                p = [t.clone().requires_grad_(True) for t in args[:5]]
+                rc, ra, meta = rasterization(*p, args[5], args[6], W, H, sh_degree=3, packed=packed)
+                (rc * rc).sum().backward()
+                torch.cuda.synchronize()
+                out = (rc.detach(), ra.detach(), meta["isect_ids"], meta["flatten_ids"], meta["isect_offsets"],
+                       [t.grad for t in p])
+            return out
+        finally:
+            for o, v in defaults.items():
+                lib.gsb_set_option(o, v)
+            for k, _ in env:
+                monkeypatch.delenv(k, raising=False)
+
+    ref = run()
+    variants = {
+        "no chained launches": dict(options=[(CHAIN, 0)]),
+        "every group chained": dict(options=[(CHAIN, 63)]),
+        "one stream": dict(env=[("GSPLAT_B200_OVERLAP", "0")]),
+        "gradient buffer filled in the backward pass": dict(env=[("GSPLAT_B200_PREZERO", "0")]),
+        "plain SH staging": dict(options=[(SH_BWD, 0), (SH_FWD, 0)]),
+        "cp.async.bulk SH staging": dict(options=[(SH_BWD, 1), (SH_FWD, 1)]),
+    }
+    for name, kw in variants.items():
+        out = run(**kw)
+        for a, b, what in zip(out[:5], ref[:5], ("colours", "alphas", "isect_ids", "flatten_ids", "offsets")):
+            if "SH staging" in name and what == "colours":  # other kernels: same arithmetic, compiled separately
+                assert torch.allclose(a, b, rtol=0.0, atol=2e-6), (name, what)
+            else:
+                assert torch.equal(a, b), (name, what)
+        for a, b in zip(out[5], ref[5]):
+            assert torch.allclose(a, b, rtol=1e-4, atol=1e-6 + 1e-5 * b.abs().max().item()), name
+
+
 def test_rasterization_fisheye_matches_oracle():
     """camera_model="fisheye" end to end (forward image + gradients) against the oracle restatement."""
     from gsplat.rendering import rasterization
