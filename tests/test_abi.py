@@ -38,6 +38,33 @@ def test_pure_queries_work_without_a_gpu():
     assert int(_lib.lib.gsb_launch_count()) == 0
 
 
+def test_kernel_variant_switches_are_consistent():
+    """GSB_OPT_* indices in the header are 0..GSB_OPT_COUNT-1, the library holds a default for each (the tuned path),
+    set / get round-trips, out-of-range indices are refused, and every environment override `_lib.py` installs names an
+    existing switch."""
+    import re
+
+    header = open(os.path.join(ROOT, "include", "gsplat_b200.h")).read()
+    opts = {m.group(1): int(m.group(2)) for m in re.finditer(r"#define (GSB_OPT_[A-Z0-9_]+) (\d+)", header)}
+    count = opts.pop("GSB_OPT_COUNT")
+    assert sorted(opts.values()) == list(range(count)), opts
+    lib = _lib.lib
+    defaults = [int(lib.gsb_get_option(i)) for i in range(count)]
+    assert all(d >= 0 for d in defaults), defaults
+    assert defaults[opts["GSB_OPT_FWD_VARIANT"]] == 2 and defaults[opts["GSB_OPT_BWD_VARIANT"]] == 2
+    assert defaults[opts["GSB_OPT_SH_STAGING"]] == 2 and defaults[opts["GSB_OPT_SH_FWD_STAGING"]] == 2  # cp.async
+    assert defaults[opts["GSB_OPT_FINALIZE_VEC"]] == 0 and defaults[opts["GSB_OPT_CHAINED_LAUNCH"]] == 37
+    assert int(lib.gsb_get_option(count)) == -1 and int(lib.gsb_set_option(count, 1)) != 0
+    which = opts["GSB_OPT_ISECT_BIN_RADIX"]
+    try:
+        assert int(lib.gsb_set_option(which, 1)) == 0 and int(lib.gsb_get_option(which)) == 1
+    finally:
+        lib.gsb_set_option(which, defaults[which])
+    source = open(os.path.join(PKG, "gsplat", "b200_impl", "_lib.py")).read()
+    env = re.findall(r"\((\d+), \"(GSPLAT_B200_[A-Z_]+)\"\)", source)
+    assert len(env) >= 6 and all(int(i) < count for i, _ in env), env
+
+
 def test_library_is_sm100a_only():
     out = subprocess.run(["cuobjdump", "--list-elf", _lib.LIB_PATH], capture_output=True, text=True)
     if out.returncode != 0:
