@@ -143,6 +143,9 @@ __device__ __forceinline__ void reduce_chunk2(Bwd2Smem &sm, int hw, int l16, int
         v[3] = Sxy;
         v[4] = 0.5f * Syy;
         v[5] = -__fdividef(M0, opac);  // v_opacity = sum e^-sigma v_alpha = -sum v_sigma / opacity
+        // (v_means2d / absgrad as ONE 8-byte reduction, REDG.E.ADD.F32x2: -3 us per step at cfg2, but the five
+        // gradient arrays are views of one buffer and only 4-byte aligned in general, e.g. absgrad behind 9 P floats
+        // with P odd: misaligned address. Scalar reductions stay.)
         if (v[0] != 0.f) atomicAdd(out.v_means2d + 2 * g, v[0]);
         if (v[1] != 0.f) atomicAdd(out.v_means2d + 2 * g + 1, v[1]);
         if (v[2] != 0.f) atomicAdd(out.v_conics + 3 * g, v[2]);
