@@ -905,6 +905,13 @@ def rasterize_to_pixels(
 _PREPACKED = [None]
 
 
+def drop_prepacked() -> None:
+    """Forgets records packed ahead of a compositor call that never came (rasterization() calls this when it starts and
+    when its compositor call returns or raises): a stale entry is matched by data pointers, and a later call's tensors
+    may well live at the addresses a failed call's tensors were freed from."""
+    _PREPACKED[0] = None
+
+
 def _grad_widths(D: int, absgrad: bool):
     """floats per projected row the backward compositor accumulates into: v_means2d, v_conics, v_colors, v_opacities
     (, absgrad)"""

@@ -380,10 +380,11 @@ def rasterization(
     # the compositor has been queued (no GPU bubble at the reference's `.item()`, isect_tiles.py:102)
     speculate = BACKEND == "b200" and os.environ.get("GSPLAT_B200_SPECULATE", "1") == "1"
     if overlap is not None:
-        main, side = torch.cuda.current_stream(device), side_stream(device)
-        if tile_size == 16 and colors.shape[-1] <= channel_chunk:
-            from .b200_impl._wrapper import prepack_splats
+        from .b200_impl._wrapper import drop_prepacked, prepack_splats
 
+        main, side = torch.cuda.current_stream(device), side_stream(device)
+        drop_prepacked()  # leftovers of a call that failed between packing and compositing
+        if tile_size == 16 and colors.shape[-1] <= channel_chunk:
             # the compositor's splat records (and, when a gradient will be asked for, its zero-filled gradient
             # buffer), also beside the side stream
             wants_grad = (torch.is_grad_enabled() and os.environ.get("GSPLAT_B200_PREZERO", "1") == "1"
@@ -422,7 +423,11 @@ def rasterization(
             return torch.cat(chunks, dim=-1), alphas
         return composite(colors, backgrounds)
 
-    render_colors, render_alphas = composite_all()
+    try:
+        render_colors, render_alphas = composite_all()
+    finally:
+        if overlap is not None:
+            drop_prepacked()  # consumed by the compositor call above, or never to be used
     if pending is not None:
         n_isects = pending.wait()
         if distributed and BACKEND == "b200":
